@@ -1,0 +1,461 @@
+#!/usr/bin/env python
+"""bench.py -- embedding lookups/s of the sum-pool hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c4|c5]
+
+One "step" = one pass of the hot path over one batch: every local table pools its B bags.
+N=1 workload = BASELINE.json configs[1] ("c2"): 26 tables x 1M rows x dim 16, batch 65536,
+pooling U{1..20}, uniform indices, int32 fixed-point tables (the DPU representation).
+N>1 (torchrun, one rank per GPU): weak scaling -- every rank owns 26 such tables and pools
+the whole global batch for them; pooled rows go to the rank that owns each sample
+(table-parallel -> batch-parallel, extend_distributed.py:389-426) either straight from the
+pooling kernel over NVLink peer memory (--exchange fused, default) or by one NCCL
+all_to_all_single (--exchange nccl).
+
+Numbers: `value` = lookups/s with inputs resident in HBM (CUDA events, max over ranks);
+`e2e` = the same through the host-pointer C-ABI call (emb_lookup_ex: pinned host buffers,
+H2D + kernel + D2H inside the timed region); `roofline` = algorithmic bytes of one pooling
+launch / its mean CUDA-event duration against MEASURED_PEAKS.json; `cpu_baseline` = the
+oracle port (multi-threaded C) on this box's host cores, N=1 only.
+`--impl reference` times the CPU implementation alone (see DESIGN.md "Reference arm").
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "oracle")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+WORKLOADS = {
+    # BASELINE.json configs[1]
+    "c2": dict(name="embedding-bag microbench: 26 tables x 1M rows x dim 16, batch 65536, pooling U{1..20}, "
+                    "uniform indices", T=26, R=1_000_000, D=16, B=65536, pool=(1, 20), dist="uniform"),
+    # configs[4], RM2-like: dim 128, pooling 80, Zipf indices
+    "c5": dict(name="RM2-like: 32 tables x 500k rows x dim 128, batch 4096, pooling 80, zipf(1.05) indices",
+               T=32, R=500_000, D=128, B=4096, pool=(80, 80), dist="zipf"),
+    # configs[3] shape per GPU (dim 64): uniform, fixed pooling 10
+    "c4": dict(name="dim-64 tables: 26 x 1M rows x dim 64, batch 65536, pooling 10, uniform indices",
+               T=26, R=1_000_000, D=64, B=65536, pool=(10, 10), dist="uniform"),
+}
+N_BATCHES = 4  # distinct index batches rotated through the timed steps
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--unroll", type=int, default=0)
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+# synthetic inputs: seeded NumPy on the host
+# ---------------------------------------------------------------------------------------------
+
+def make_batch(w, seed, n_tables=None):
+    """One batch for n_tables tables: lists of uint32 indices [L_t] and offsets [B]."""
+    rng = np.random.default_rng(seed)
+    T = w["T"] if n_tables is None else n_tables
+    lo, hi = w["pool"]
+    idx, off = [], []
+    for _ in range(T):
+        lens = rng.integers(lo, hi + 1, size=w["B"])
+        off.append(np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.uint32))
+        n = int(lens.sum())
+        if w["dist"] == "zipf":
+            # power-law over a fixed random permutation of the row ids (duplicates kept)
+            r = rng.zipf(1.05, size=n)
+            r = (r - 1) % w["R"]
+            perm = np.random.default_rng(99).permutation(w["R"]).astype(np.uint32)
+            idx.append(perm[r])
+        else:
+            idx.append(rng.integers(0, w["R"], size=n, dtype=np.int64).astype(np.uint32))
+    return idx, off
+
+
+def algorithmic_bytes(n_lookups, n_bags, D):
+    # per lookup 4D (row) + 4 (index); per bag 4D (output row) + 4 (offset)
+    return (n_lookups + n_bags) * (4 * D + 4)
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks during the timed region (NVML, sampled every ~5 ms from a thread)
+# ---------------------------------------------------------------------------------------------
+
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self._stop, self._t = [], set(), None, False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:  # noqa: BLE001
+            self.nv, self.err = None, repr(e)
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for b, name in self.REASONS.items():
+                    if bits & b and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.005)
+
+    def __enter__(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop = True
+        if self._t:
+            self._t.join()
+
+    def summary(self):
+        if not self.nv:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "error": self.err}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU side: the oracle port (the checker, here only timed) and the reference's float CPU path
+# ---------------------------------------------------------------------------------------------
+
+def time_oracle_port(tables_i32, idx, off, budget_s=12.0, min_reps=2):
+    """Fixed-point path (quantised tables, wrapping int32 pool, /1e9) in multi-threaded C."""
+    import emb_oracle as eo
+    n = sum(len(i) for i in idx)
+    eo.lookup_rows(tables_i32, idx, off)  # warm-up (page-in)
+    reps, t_tot = 0, 0.0
+    while reps < min_reps or (t_tot < budget_s and reps < 50):
+        t0 = time.perf_counter()
+        eo.lookup_rows(tables_i32, idx, off)
+        t_tot += time.perf_counter() - t0
+        reps += 1
+    return n * reps / t_tot, eo.num_threads(), reps
+
+
+def time_torch_embeddingbag(tables_f32, idx, off, budget_s=10.0):
+    """The reference's CPU path: nn.EmbeddingBag(mode="sum") per table (dlrm_s_pytorch.py:483-488)."""
+    import torch
+    bags = [torch.nn.EmbeddingBag.from_pretrained(torch.from_numpy(w), mode="sum", freeze=True) for w in tables_f32]
+    ti = [torch.from_numpy(i.astype(np.int64)) for i in idx]
+    to = [torch.from_numpy(o.astype(np.int64)) for o in off]
+    n = sum(len(i) for i in idx)
+
+    def one():
+        with torch.no_grad():
+            for k, e in enumerate(bags):
+                e(ti[k], to[k])
+    one()
+    reps, t_tot = 0, 0.0
+    while reps < 2 or (t_tot < budget_s and reps < 50):
+        t0 = time.perf_counter()
+        one()
+        t_tot += time.perf_counter() - t0
+        reps += 1
+    return n * reps / t_tot, torch.get_num_threads(), reps
+
+
+def host_tables(w, n_tables, seed=1234):
+    """Quantised int32 tables as export_emb would make them (U(-1/sqrt(R), 1/sqrt(R)) * 1e9)."""
+    rng = np.random.default_rng(seed)
+    lim = int(1e9 / np.sqrt(w["R"]))
+    return [rng.integers(-lim, lim + 1, size=(w["R"], w["D"]), dtype=np.int32) for _ in range(n_tables)]
+
+
+def run_reference(args, w):
+    """--impl reference: the CPU implementation alone, all host threads, bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    # bounded sample of the workload: the first T_s tables of one batch (same shapes and
+    # distributions as the GPU arm); each step = one pass over the sample
+    T_s = min(w["T"], 8)
+    tabs = host_tables(w, T_s)
+    idx, off = make_batch(w, seed=123, n_tables=T_s)
+    import emb_oracle as eo
+    n = sum(len(i) for i in idx)
+    for _ in range(max(1, min(args.warmup, 3))):
+        eo.lookup_rows(tabs, idx, off)
+    steps = max(1, min(args.steps, 30))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        eo.lookup_rows(tabs, idx, off)
+    dt = time.perf_counter() - t0
+    val = n * steps / dt
+    tv, tthreads, _ = time_torch_embeddingbag([t.astype(np.float32) * np.float32(1e-9) for t in tabs], idx, off, 6.0)
+    sample = f"{T_s} of {w['T']} tables x {w['B']} bags ({n} lookups) per step, {steps} steps"
+    print(json.dumps({
+        "impl": "reference", "metric": "embedding lookups/sec", "value": val, "unit": "lookups/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": dt / steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "config": {"workload": w["name"], "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "lookups/s", "cores": eo.num_threads(), "kind": "port",
+                         "sample": sample,
+                         "why_port": "the reference's own lookup() is undefined at this shape "
+                                     "(B<=512, T*D<=256, SURVEY.md Q3/Q4/Q13); oracle/_ref covers the golden shapes"},
+        "cpu_torch_embeddingbag": {"value": tv, "unit": "lookups/s", "threads": tthreads,
+                                   "what": "nn.EmbeddingBag(mode=sum) fp32 per table, dlrm_s_pytorch.py:483-488"},
+        "e2e": {"value": val, "unit": "lookups/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+
+def pinned_u32(lib, n):
+    """n uint32 of cudaHostAlloc memory as a NumPy array (emb_host_alloc)."""
+    p = C.c_void_p()
+    rc = lib.emb_host_alloc(C.byref(p), max(4 * n, 4))
+    if rc:
+        raise RuntimeError("emb_host_alloc failed")
+    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint32)), shape=(n,))
+
+
+def run_b200(args, w):
+    import torch
+    import torch.distributed as dist
+
+    from pim_embedding_lookup_b200 import emblib, exchange
+    from pim_embedding_lookup_b200.dputypes import EMB_TABLE_FIXED
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = emblib.load()
+    T, R, D, B = w["T"], w["R"], w["D"], w["B"]
+    emblib.configure(T, D, 0, 0, device=local)
+    if args.unroll:
+        emblib.check(lib.emb_set_unroll(args.unroll))
+    stream = torch.cuda.current_stream()
+
+    # tables: int32 fixed point as export_emb makes them, generated on the device
+    gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
+    lim = int(1e9 / np.sqrt(R))
+    for t in range(T):
+        a = torch.randint(-lim, lim + 1, (R, D), dtype=torch.int32, device="cuda", generator=gen)
+        emblib.check(lib.emb_populate_table_device(t, R, a.data_ptr(), 0, EMB_TABLE_FIXED, stream.cuda_stream))
+        del a
+    torch.cuda.empty_cache()
+
+    # index batches: every rank pools the whole global batch for its own tables
+    batches = [make_batch(w, seed=123 + 1000 * rank + k) for k in range(N_BATCHES)]
+    lookups = [sum(len(i) for i in b[0]) for b in batches]
+    dev_batches = []
+    for idx, off in batches:
+        dev_batches.append(([torch.from_numpy(i.view(np.int32)).cuda() for i in idx],
+                            [torch.from_numpy(o.view(np.int32)).cuda() for o in off]))
+
+    # outputs + plans (descriptors uploaded once; a step is one kernel launch)
+    slabs = None
+    if world > 1 and args.exchange == "fused":
+        slabs = exchange.PeerSlabs(B, [T] * world, D)
+    per = B // world
+    plans, keep = [], []
+    for k, (di, do) in enumerate(dev_batches):
+        qs = []
+        if slabs is not None:
+            for t in range(T):
+                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=None, out_stride=slabs.stride,
+                               bags_per_rank=per, out_peer=slabs.out_peer(t)))
+        elif world > 1:  # nccl: send buffer [N, B/N, T_local, D] == bag-major rows of stride T*D
+            buf = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
+            keep.append(buf)
+            for t in range(T):
+                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=buf[:, t, :], out_stride=T * D))
+        else:  # the reference's layout: one [B, D] result per table (emb_host.h:207-212)
+            buf = torch.empty((T, B, D), dtype=torch.float32, device="cuda")
+            keep.append(buf)
+            for t in range(T):
+                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=buf[t]))
+        plans.append(emblib.Plan(qs))
+
+    def step(k):
+        plans[k % N_BATCHES].launch(stream)
+        if slabs is not None:
+            slabs.barrier()
+        elif world > 1:
+            exchange.nccl_all_to_all(keep[k % N_BATCHES], B, [T] * world, D)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for k in range(max(args.warmup, 3)):
+        step(k)
+    sync_all()
+    if lib.emb_check_indices():
+        raise RuntimeError("out-of-range index in the synthetic batch")
+
+    K = args.steps
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = emblib.launch_count()
+    with ClockSampler(local) as clk:
+        sync_all()
+        e0.record(stream)
+        for k in range(K):
+            ev[k][0].record(stream)
+            plans[k % N_BATCHES].launch(stream)
+            ev[k][1].record(stream)
+            if slabs is not None:
+                slabs.barrier()
+            elif world > 1:
+                exchange.nccl_all_to_all(keep[k % N_BATCHES], B, [T] * world, D)
+        e1.record(stream)
+        sync_all()
+    gpu_launches = emblib.launch_count() - launches0
+    total_ms = e0.elapsed_time(e1)
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    n_lookups = sum(lookups[k % N_BATCHES] for k in range(K))
+    t = torch.tensor([total_ms, float(n_lookups), kernel_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        total_ms, n_lookups, kernel_ms = float(tmax[0]), float(tsum[1]), float(tmax[2])
+    value = n_lookups / (total_ms * 1e-3)
+
+    # roofline of the pooling kernel on this rank (algorithmic bytes / mean launch duration)
+    peak, peak_src = load_peaks()
+    bytes_per_launch = float(np.mean([algorithmic_bytes(lookups[k % N_BATCHES], T * B, D) for k in range(K)]))
+    achieved = bytes_per_launch / (kernel_ms * 1e-3) / 1e9
+
+    # ---- e2e: the host-pointer C-ABI call, pinned host buffers, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        host = []
+        for idx, off in batches[:2]:
+            hi = [pinned_u32(lib, len(i)) for i in idx]
+            ho = [pinned_u32(lib, len(o)) for o in off]
+            for a, b in zip(hi + ho, idx + off):
+                a[:] = b
+            host.append((hi, ho))
+        res = [pinned_u32(lib, B * D).view(np.float32).reshape(B, D) for _ in range(T)]
+        for k in range(3):
+            emblib.lookup_ex(host[k % 2][0], host[k % 2][1], res)
+        Ke = max(3, min(K, 50))
+        sync_all()
+        t0 = time.perf_counter()
+        for k in range(Ke):
+            emblib.lookup_ex(host[k % 2][0], host[k % 2][1], res)  # synchronous: results are on the host
+        dt = time.perf_counter() - t0
+        tm = emblib.last_timings()
+        n_e = sum(lookups[k % 2] for k in range(Ke))
+        te = torch.tensor([dt, float(n_e)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            a = te.clone()
+            dist.all_reduce(a, op=dist.ReduceOp.MAX)
+            b = te.clone()
+            dist.all_reduce(b, op=dist.ReduceOp.SUM)
+            dt, n_e = float(a[0]), float(b[1])
+        e2e = {"value": n_e / dt, "unit": "lookups/s", "h2d_bytes_per_step": int(tm.h2d_bytes),
+               "d2h_bytes_per_step": int(tm.d2h_bytes), "ms_per_step": dt / Ke * 1e3, "steps": Ke,
+               "call": "emb_lookup_ex (host pointers, pinned), per rank",
+               "last_call_ms": {"h2d": tm.h2d_ms, "kernel": tm.kernel_ms, "d2h": tm.d2h_ms, "total": tm.total_ms}}
+
+    # ---- CPU baseline on this box's host cores (rank 0, N=1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        T_s = min(T, 8)
+        tabs = [emblib.table_read(t, 0, R) for t in range(T_s)]
+        sidx, soff = batches[0][0][:T_s], batches[0][1][:T_s]
+        v, cores, reps = time_oracle_port(tabs, sidx, soff)
+        sample = f"{T_s} of {T} tables x {B} bags ({sum(len(i) for i in sidx)} lookups) x {reps} passes"
+        cpu = {"value": v, "unit": "lookups/s", "cores": cores, "kind": "port", "sample": sample}
+        try:
+            tv, tth, treps = time_torch_embeddingbag([x.astype(np.float32) * np.float32(1e-9) for x in tabs], sidx, soff)
+            cpu["torch_embeddingbag"] = {"value": tv, "unit": "lookups/s", "threads": tth, "passes": treps}
+        except Exception as e:  # noqa: BLE001
+            cpu["torch_embeddingbag"] = {"error": repr(e)}
+
+    if rank == 0:
+        out = {
+            "metric": "embedding lookups/sec", "value": value, "unit": "lookups/s", "n_gpus": world, "steps": K,
+            "warmup": max(args.warmup, 3), "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": w["name"], "tables_per_gpu": T, "rows": R, "dim": D, "global_batch": B,
+                       "lookups_per_step_per_gpu": int(np.mean(lookups)),
+                       "l2": f"inputs larger than L2: tables {T * R * D * 4 / 1e9:.2f} GB per GPU, "
+                             f"{N_BATCHES} rotating index batches",
+                       "exchange": ("none (1 GPU)" if world == 1 else args.exchange),
+                       "parallelism": f"table-wise x{world}, pooled rows to the sample's rank"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms,
+                         "algorithmic_bytes_per_launch": bytes_per_launch,
+                         "frac_of_nominal_8000": achieved / 8000.0},
+            "clocks": clk.summary(), "gpu_launches": int(gpu_launches),
+        }
+        if e2e:
+            out["e2e"] = e2e
+        if cpu:
+            out["cpu_baseline"] = cpu
+        print(json.dumps(out))
+    sync_all()
+    for p in plans:
+        p.close()
+    if slabs is not None:
+        slabs.close()
+    emblib.shutdown()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    w = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, w)
+    else:
+        run_b200(args, w)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,257 @@
+/*
+ * emb_b200.h -- C ABI of the B200 embedding-lookup backend (shared object: emblib.so).
+ *
+ * Drop-in boundary for the ONE hot path of UBC-ECE-Sasha/PIM-Embedding-Lookup: the
+ * sum-pooled EmbeddingBag lookup behind populate_mram()/lookup().  Plain C: pointers and
+ * sizes only, no CUDA or torch types (a cudaStream_t travels as void*).
+ *
+ * Part 1 keeps the reference's two exported entry points and its ABI-visible structs, bit
+ * for bit.  Part 2 is new surface (explicit lengths, device-resident buffers, float
+ * tables, row-range shards, peer output slabs) that the reference's callers do not know
+ * about; nothing in part 1 depends on it.
+ *
+ * Reference paths are relative to the upstream repository root.
+ */
+#ifndef EMB_B200_H
+#define EMB_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ======================================================================================
+ * Part 1 -- the reference's plugin surface
+ * ==================================================================================== */
+
+/* upmem/include/emb_host.h:41-48; ctypes mirror upmem/dputypes.py:66-79.  Seconds. */
+typedef struct dpu_runtime_totals {
+    double execution_time_prepare;          /* host-side staging                    */
+    double execution_time_populate_copy_in; /* populate_mram: host -> HBM           */
+    double execution_time_copy_in;          /* lookup: indices/offsets host -> HBM   */
+    double execution_time_copy_out;         /* lookup: pooled rows HBM -> host       */
+    double execution_time_aggregate_result; /* dequantise (fused: always 0)          */
+    double execution_time_launch;           /* kernel time                           */
+} dpu_runtime_totals;
+
+/* emb_host.h:54-57; dputypes.py:18-33 (note the field order: nsec first). */
+typedef struct dpu_timespec {
+    long tv_nsec;
+    long tv_sec;
+} dpu_timespec;
+
+/* emb_host.h:63-66; dputypes.py:35-46 */
+typedef struct dpu_runtime_interval {
+    dpu_timespec start;
+    dpu_timespec stop;
+} dpu_runtime_interval;
+
+/* emb_host.h:72-75; dputypes.py:12-16 */
+typedef enum dpu_runtime_config { RT_ALL = 0, RT_LAUNCH = 1 } dpu_runtime_config;
+
+/* emb_host.h:81-85; dputypes.py:48-64 */
+typedef struct dpu_runtime_group {
+    unsigned int in_use;
+    unsigned int length;
+    dpu_runtime_interval *intervals;
+} dpu_runtime_group;
+
+/* upmem/include/emb_types.h:21-24 (packed pair pushed to every DPU before a launch). */
+struct query_len {
+    uint32_t indices_len;
+    uint32_t nr_batches;
+} __attribute__((packed));
+
+/* Opaque here: the reference hands the UPMEM SDK's set to Python as an integer and back
+ * (dlrm_dpu_pytorch.py:327,332,564).  The B200 library returns the address of its
+ * process-wide context under the same type name. */
+struct dpu_set_t;
+
+/*
+ * Replaces upmem/include/emb_host.h:136-183.
+ * Store column `col` of table `table_id` (nr_rows int32 fixed-point values, scale 1e9) in
+ * HBM.  Called once per (table, column) by PIM-dlrm-new/dlrm_dpu_pytorch.py:328-332.
+ * The first call initialises the device and reads the shape from the environment
+ * variables NR_TABLES, NR_COLS, MAX_NR_BATCHES, MAX_INDICES_PER_BATCH (compile-time
+ * macros in the reference, upmem/Makefile:69-81) unless emb_configure() ran before.
+ * `runtime` may be NULL; when given, execution_time_populate_copy_in is accumulated.
+ * table_data is caller-owned and may be freed on return.  Errors print and exit(1), as
+ * DPU_ASSERT does.  Returns the context handle to pass to lookup().
+ */
+struct dpu_set_t *populate_mram(uint32_t table_id, uint64_t nr_rows, uint32_t col,
+                                int32_t *table_data, dpu_runtime_totals *runtime);
+
+/*
+ * Replaces upmem/include/emb_host.h:234-404 (+ post_process :186-222 and the DPU program
+ * upmem/src/dpu/emb_dpu_lookup.c:35-138).
+ * For every table t < NR_TABLES: indices[t] holds MAX_NR_BATCHES*MAX_INDICES_PER_BATCH
+ * uint32 row ids, offsets[t] holds MAX_NR_BATCHES bag start positions (bag 0 starts at 0
+ * whatever offsets[t][0] says; the last bag ends at INDICES_LEN), final_results[t]
+ * receives MAX_NR_BATCHES x NR_COLS floats, row-major:
+ *     final_results[t][b*NR_COLS + j] = (float)(int32 wrap-sum of column j) / 1e9 .
+ * All pointers are HOST pointers; the call is synchronous.  dpu_set_ptr is the value
+ * populate_mram() returned (ignored beyond a sanity check).  latency_print == 1 prints the
+ * reference's six stage-latency lines (emb_host.h:395-402).  Returns NULL like the
+ * reference (`return 0`).
+ */
+int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results,
+                void *dpu_set_ptr, int64_t latency_print);
+
+/* ======================================================================================
+ * Part 2 -- extensions (new names; all return 0 on success, a negative EMB_E* otherwise)
+ * ==================================================================================== */
+
+#define EMB_OK 0
+#define EMB_EINVAL (-1)  /* bad argument / shape                    */
+#define EMB_ENOMEM (-2)  /* host or device allocation failed        */
+#define EMB_ECUDA (-3)   /* a CUDA call failed, see emb_last_error  */
+#define EMB_ESTATE (-4)  /* not configured / table not populated    */
+#define EMB_ERANGE (-5)  /* an index fell outside its table         */
+
+#define EMB_MAX_PEERS 8
+
+/* table element kinds */
+#define EMB_TABLE_FIXED 1 /* int32 fixed point, scale 1e9 (the DPU representation)        */
+#define EMB_TABLE_FLOAT 2 /* fp32 (the CPU path, nn.EmbeddingBag(mode="sum"))             */
+
+/* emb_dev_query.flags */
+#define EMB_Q_RAW_SUMS 1u /* FIXED tables: write the int32 sums, skip the /1e9 (row shards) */
+
+typedef struct emb_shape {
+    uint32_t nr_tables;             /* NR_TABLES                                      */
+    uint32_t nr_cols;               /* NR_COLS (embedding dimension)                   */
+    uint32_t max_nr_batches;        /* MAX_NR_BATCHES (bags per table per lookup())   */
+    uint32_t max_indices_per_batch; /* MAX_INDICES_PER_BATCH (pooling factor)         */
+} emb_shape;
+
+/* Runtime replacement for the reference's -D shape macros (upmem/Makefile:69-81).
+ * device < 0: use $EMB_DEVICE, else $LOCAL_RANK, else 0.  May be called again to change
+ * max_nr_batches / max_indices_per_batch; nr_cols cannot change once a table exists. */
+int emb_configure(uint32_t nr_tables, uint32_t nr_cols, uint32_t max_nr_batches,
+                  uint32_t max_indices_per_batch, int device);
+int emb_get_shape(emb_shape *out);
+int emb_device(void);
+/* Frees every table, buffer, plan-independent resource; the next call re-initialises.
+ * (The reference never frees its DPU set, emb_host.h:156-160.) */
+void emb_shutdown(void);
+const char *emb_last_error(void);
+
+/* ---- tables ------------------------------------------------------------------------ */
+
+/* Whole-table load from HOST memory, row-major [nr_rows][nr_cols].
+ * emb_populate_table_i32: already-quantised int32 (what nr_cols populate_mram calls build).
+ * emb_populate_table_f32 with kind EMB_TABLE_FIXED runs the reference's export arithmetic
+ *   (dlrm_dpu_pytorch.py:318-320: float32 product by 1e9, rint, int64, low 32 bits) on the
+ *   GPU; with EMB_TABLE_FLOAT the fp32 values are kept as they are. */
+int emb_populate_table_i32(uint32_t table_id, uint64_t nr_rows, const int32_t *row_major);
+int emb_populate_table_f32(uint32_t table_id, uint64_t nr_rows, const float *row_major, int kind);
+/* Same, source already in DEVICE memory (copied; `stream` is a cudaStream_t or NULL). */
+int emb_populate_table_device(uint32_t table_id, uint64_t nr_rows, const void *dev_row_major,
+                              int src_is_f32, int kind, void *stream);
+/* Row-range shard: the table slot holds global rows [row_base, row_base + nr_rows).
+ * Indices outside the range contribute nothing (and are not errors). */
+int emb_table_set_row_base(uint32_t table_id, uint64_t row_base);
+/* Copy rows [row0, row0+n) back to the host as stored (int32 or fp32), row-major. */
+int emb_table_read(uint32_t table_id, uint64_t row0, uint64_t n, void *dst_host);
+int emb_table_info(uint32_t table_id, uint64_t *nr_rows, int *kind, const void **dev_ptr);
+int emb_free_table(uint32_t table_id);
+/* Mark a byte range of a table as L2-persisting for subsequent launches on `stream`
+ * (cudaAccessPolicyWindow); nbytes == 0 clears the window. */
+int emb_l2_persist(uint32_t table_id, uint64_t first_row, uint64_t nr_rows, float hit_ratio,
+                   void *stream);
+
+/* ---- lookups with explicit lengths, HOST pointers ------------------------------------ */
+
+/* Like lookup() but per-table lengths are arguments (the historical signatures in
+ * upmem/c_test.py:48 and dlrm_dpu_pytorch.py:631-640 carried them too), so pooling may
+ * vary per bag and per call.  Tables 0..nr_tables-1.  Bag b of table t covers
+ * indices[t][start_b .. end_b) with start_0 = 0, start_b = offsets[t][b],
+ * end_b = offsets[t][b+1], end_last = indices_len[t]. */
+int emb_lookup_ex(uint32_t nr_tables, const uint32_t *const *indices,
+                  const uint32_t *const *offsets, const uint32_t *indices_len,
+                  const uint32_t *nr_batches, float *const *final_results);
+
+/* ---- device-resident lookups (plans) -------------------------------------------------- */
+
+typedef struct emb_dev_query {
+    uint32_t table_id;
+    uint32_t nr_batches;      /* bags                                                  */
+    uint32_t indices_len;     /* end of the last bag                                   */
+    uint32_t flags;           /* EMB_Q_*                                               */
+    const uint32_t *indices;  /* DEVICE, uint32 [indices_len]                           */
+    const uint32_t *offsets;  /* DEVICE, uint32 [nr_batches]                            */
+    void *out;                /* DEVICE, bag b -> out + b*out_stride elements (4 B each) */
+    uint32_t out_stride;      /* elements between bags; 0 means nr_cols                 */
+    /* When bags_per_rank != 0 the output of bag b goes to the slab of rank b / bags_per_rank:
+     * out_peer[b / bags_per_rank] + (b % bags_per_rank)*out_stride.  The slabs may be
+     * peer-GPU memory mapped with emb_ipc_open(): the pooled rows then cross NVLink straight
+     * from the pooling kernel (fused all-to-all). */
+    uint32_t bags_per_rank;
+    void *out_peer[EMB_MAX_PEERS];
+} emb_dev_query;
+
+typedef struct emb_plan emb_plan;
+
+/* Validate + upload the descriptors once; launches are then a single kernel with no copies. */
+int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out);
+int emb_plan_launch(emb_plan *plan, void *stream);
+void emb_plan_destroy(emb_plan *plan);
+/* Algorithmic bytes of one launch: L*(4D+4) + bags*(4D+4); needs host-known
+ * sizes only. */
+uint64_t emb_plan_bytes(const emb_plan *plan);
+uint32_t emb_plan_grid(const emb_plan *plan);
+/* One-shot convenience: create, launch, destroy. */
+int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream);
+/* Non-zero once any launch has seen an out-of-range index (cleared by the call; syncs). */
+int emb_check_indices(void);
+
+/* out[b*out_stride + j] = combine over s < n_parts of parts[s][b*part_stride + j]:
+ * raw int32 partials are wrap-added then divided by 1e9 (is_raw_i32 = 1); fp32 partials are
+ * added in order s = 0,1,...  Used at the receiving rank for row-split tables. */
+int emb_reduce_partials(const void *const *parts_dev, uint32_t n_parts, uint32_t part_stride,
+                        void *out_dev, uint32_t out_stride, uint64_t nr_bags, int is_raw_i32,
+                        void *stream);
+
+/* ---- memory helpers -------------------------------------------------------------------- */
+
+int emb_device_alloc(void **dev_ptr, size_t nbytes); /* cudaMalloc (IPC-exportable)         */
+int emb_device_free(void *dev_ptr);
+int emb_host_alloc(void **host_ptr, size_t nbytes);  /* pinned                              */
+int emb_host_free(void *host_ptr);
+int emb_memcpy_h2d(void *dst_dev, const void *src_host, size_t nbytes, void *stream);
+int emb_memcpy_d2h(void *dst_host, const void *src_dev, size_t nbytes, void *stream);
+int emb_stream_sync(void *stream);
+
+#define EMB_IPC_HANDLE_BYTES 64
+typedef struct emb_ipc_handle {
+    unsigned char bytes[EMB_IPC_HANDLE_BYTES];
+} emb_ipc_handle;
+/* Export a buffer from emb_device_alloc() / open a peer's export in this process. */
+int emb_ipc_export(void *dev_ptr, emb_ipc_handle *out);
+int emb_ipc_open(const emb_ipc_handle *h, void **peer_dev_ptr);
+int emb_ipc_close(void *peer_dev_ptr);
+
+/* ---- timings ----------------------------------------------------------------------------- */
+
+typedef struct emb_timings {
+    double h2d_ms;    /* indices + offsets host -> device   */
+    double kernel_ms; /* pooling kernel                     */
+    double d2h_ms;    /* pooled rows device -> host         */
+    double total_ms;  /* wall clock of the whole call       */
+    uint64_t h2d_bytes;
+    uint64_t d2h_bytes;
+    uint64_t launches; /* kernels launched by the call       */
+} emb_timings;
+/* Stage times of the last lookup()/emb_lookup_ex() call (CUDA events). */
+int emb_last_timings(emb_timings *out);
+/* Kernels this library has launched since load (bench.py's gpu_launches). */
+uint64_t emb_launch_count(void);
+/* Tuning knob, mostly for measurement: rows in flight per sub-warp (4 or 8); 0 = default. */
+int emb_set_unroll(int unroll);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EMB_B200_H */

@@ -1,0 +1,968 @@
+/*
+ * emb_b200.cu -- host side of emblib.so: the C ABI declared in include/emb_b200.h.
+ *
+ * Replaces the body of upmem/include/emb_host.h (populate_mram :136-183, lookup :234-404,
+ * post_process :186-222).  Where the reference allocates DPUs, pushes per-DPU buffers over
+ * the UPMEM rank transfer and launches tasklets, this file keeps tables resident in HBM,
+ * moves a call's indices/offsets with cudaMemcpyAsync and launches one pooling kernel
+ * (emb_kernels.cuh) for all tables.  There is no CPU fallback: without a CUDA device every
+ * entry point fails loudly.
+ */
+#include "emb_kernels.cuh"
+
+#include <errno.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include <algorithm>
+#include <atomic>
+#include <mutex>
+#include <vector>
+
+namespace {
+
+using emb::BagDesc;
+
+constexpr uint32_t kMaxTables = 1u << 16;
+
+struct Table {
+    void *dev = nullptr;
+    uint64_t rows = 0;
+    uint64_t row_base = 0;
+    int kind = 0;  // 0 = empty, EMB_TABLE_FIXED, EMB_TABLE_FLOAT
+    bool sharded = false;
+};
+
+struct Ctx {
+    bool configured = false;
+    bool device_ready = false;
+    int device = 0;
+    int sm_count = 148;
+    emb_shape shape = {0, 0, 0, 0};
+    std::vector<Table> tables;
+
+    cudaStream_t stream = nullptr;     // compute + H2D
+    cudaStream_t stream_out = nullptr; // D2H
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    uint32_t *d_err = nullptr;
+
+    // populate_mram() column staging
+    void *d_col = nullptr;
+    size_t col_bytes = 0;
+
+    // host-pointer lookup path: device mirrors of the caller's arrays + descriptors
+    uint32_t *d_idx = nullptr;
+    uint32_t *d_off = nullptr;
+    float *d_out = nullptr;
+    size_t idx_cap = 0, off_cap = 0, out_cap = 0;  // elements
+    BagDesc *d_descs = nullptr;
+    BagDesc *h_descs = nullptr;  // pinned
+    uint32_t desc_cap = 0;
+
+    emb_timings last = {0, 0, 0, 0, 0, 0, 0};
+    int unroll = 0;
+};
+
+Ctx g;
+std::mutex g_mu;
+std::atomic<uint64_t> g_launches{0};
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(EMB_ECUDA, "%s:%d: %s -> %s", __FILE__, __LINE__, #call,                   \
+                        cudaGetErrorString(e_));                                                   \
+    } while (0)
+
+/* The reference aborts on any SDK error (DPU_ASSERT, emb_host.h:157-173); its two entry
+ * points have no error return, so ours do the same. */
+[[noreturn]] void die(const char *where, int code)
+{
+    fprintf(stderr, "emblib(B200): %s failed (%d): %s\n", where, code, g_err);
+    exit(EXIT_FAILURE);
+}
+
+uint32_t env_u32(const char *name, uint32_t dflt)
+{
+    const char *v = getenv(name);
+    if (!v || !*v)
+        return dflt;
+    char *end = nullptr;
+    unsigned long x = strtoul(v, &end, 10);
+    return (end && *end == 0) ? (uint32_t)x : dflt;
+}
+
+double now_s()
+{
+    struct timespec t;
+    clock_gettime(CLOCK_MONOTONIC, &t);
+    return t.tv_sec + t.tv_nsec * 1e-9;
+}
+
+int ensure_device()
+{
+    if (g.device_ready)
+        return EMB_OK;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0)
+        return fail(EMB_ECUDA, "no CUDA device visible (%s): this library has no CPU path",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    if (g.device < 0 || g.device >= n)
+        return fail(EMB_EINVAL, "device %d out of range (%d visible)", g.device, n);
+    CU(cudaSetDevice(g.device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, g.device));
+    g.sm_count = prop.multiProcessorCount;
+    if (prop.major < 10)
+        fprintf(stderr, "emblib(B200): warning: device %d is sm_%d%d; kernels are built for sm_100a\n",
+                g.device, prop.major, prop.minor);
+    CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&g.stream_out, cudaStreamNonBlocking));
+    for (auto &ev : g.ev)
+        CU(cudaEventCreate(&ev));
+    CU(cudaMalloc(&g.d_err, sizeof(uint32_t)));
+    CU(cudaMemset(g.d_err, 0, sizeof(uint32_t)));
+    g.device_ready = true;
+    return EMB_OK;
+}
+
+int pick_device(int device)
+{
+    if (device >= 0)
+        return device;
+    const char *names[] = {"EMB_DEVICE", "LOCAL_RANK"};
+    for (const char *nm : names) {
+        const char *v = getenv(nm);
+        if (v && *v)
+            return atoi(v);
+    }
+    return 0;
+}
+
+int configure_locked(uint32_t T, uint32_t D, uint32_t B, uint32_t P, int device)
+{
+    if (T == 0 || T > kMaxTables || D == 0 || D > 4096)
+        return fail(EMB_EINVAL, "bad shape: NR_TABLES=%u NR_COLS=%u", T, D);
+    if ((uint64_t)B * P > 0xffffffffull)
+        return fail(EMB_EINVAL, "MAX_NR_BATCHES*MAX_INDICES_PER_BATCH overflows uint32");
+    if (g.configured && g.shape.nr_cols != D) {
+        for (const Table &t : g.tables)
+            if (t.kind)
+                return fail(EMB_ESTATE, "NR_COLS cannot change from %u to %u while tables exist",
+                            g.shape.nr_cols, D);
+    }
+    int dev = pick_device(device);
+    if (g.device_ready && dev != g.device)
+        return fail(EMB_ESTATE, "already bound to device %d", g.device);
+    g.device = dev;
+    g.shape = {T, D, B, P};
+    if (g.tables.size() < T)
+        g.tables.resize(T);
+    g.configured = true;
+    return ensure_device();
+}
+
+/* The reference bakes these four in with -D at build time (upmem/Makefile:69-81) and its
+ * Python reads NR_TABLES from the environment (dlrm_dpu_pytorch.py:128); the run scripts
+ * export all of them (upmem/run.sh:40-45,93-101).  Same names, read at first use. */
+int ensure_configured()
+{
+    if (g.configured)
+        return ensure_device();
+    uint32_t T = env_u32("NR_TABLES", 0), D = env_u32("NR_COLS", 0);
+    uint32_t B = env_u32("MAX_NR_BATCHES", 0), P = env_u32("MAX_INDICES_PER_BATCH", 0);
+    if (!T || !D)
+        return fail(EMB_ESTATE, "shape unknown: set NR_TABLES, NR_COLS, MAX_NR_BATCHES, "
+                                "MAX_INDICES_PER_BATCH in the environment or call emb_configure()");
+    return configure_locked(T, D, B, P, -1);
+}
+
+int table_slot(uint32_t table_id, Table **out)
+{
+    if (table_id >= kMaxTables)
+        return fail(EMB_EINVAL, "table_id %u too large", table_id);
+    if (table_id >= g.tables.size())
+        g.tables.resize(table_id + 1);
+    *out = &g.tables[table_id];
+    return EMB_OK;
+}
+
+int table_alloc(Table *t, uint64_t rows, int kind)
+{
+    if (rows == 0 || rows > 0xffffffffull)
+        return fail(EMB_EINVAL, "nr_rows %llu unsupported (1 .. 2^32-1)", (unsigned long long)rows);
+    if (t->dev && t->rows == rows) {
+        t->kind = kind;
+        return EMB_OK;
+    }
+    if (t->dev) {
+        cudaFree(t->dev);
+        t->dev = nullptr;
+    }
+    size_t bytes = (size_t)rows * g.shape.nr_cols * 4;
+    cudaError_t e = cudaMalloc(&t->dev, bytes);
+    if (e != cudaSuccess) {
+        t->dev = nullptr;
+        t->kind = 0;
+        return fail(EMB_ENOMEM, "cudaMalloc(%zu bytes) for a table: %s", bytes, cudaGetErrorString(e));
+    }
+    // columns arrive one populate_mram() call at a time: unwritten ones read as 0
+    e = cudaMemsetAsync(t->dev, 0, bytes, g.stream);
+    if (e != cudaSuccess)
+        return fail(EMB_ECUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+    t->rows = rows;
+    t->kind = kind;
+    return EMB_OK;
+}
+
+int grow(void **p, size_t *cap_elems, size_t want_elems, size_t elem)
+{
+    if (*cap_elems >= want_elems && *p)
+        return EMB_OK;
+    if (*p)
+        cudaFree(*p);
+    *p = nullptr;
+    size_t n = std::max(want_elems, (size_t)256);
+    cudaError_t e = cudaMalloc(p, n * elem);
+    if (e != cudaSuccess)
+        return fail(EMB_ENOMEM, "cudaMalloc(%zu bytes): %s", n * elem, cudaGetErrorString(e));
+    *cap_elems = n;
+    return EMB_OK;
+}
+
+uint32_t lanes_for_dim(uint32_t D)
+{
+    if (D % 4 != 0)
+        return 0;
+    uint32_t l = D / 4;
+    if (l > 32 || (l & (l - 1)))
+        return 0;
+    return l;
+}
+
+uint32_t bags_per_cta(uint32_t D)
+{
+    uint32_t l = lanes_for_dim(D);
+    return l ? emb::kThreads / l : emb::kThreads / 32;
+}
+
+template <int UNROLL>
+void launch_lanes(uint32_t lanes, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+{
+    switch (lanes) {
+    case 1: emb::bag_sum_kernel<1, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
+    case 2: emb::bag_sum_kernel<2, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
+    case 4: emb::bag_sum_kernel<4, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
+    case 8: emb::bag_sum_kernel<8, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
+    case 16: emb::bag_sum_kernel<16, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
+    default: emb::bag_sum_kernel<32, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
+    }
+}
+
+int launch_bag_sum(const BagDesc *d_descs, uint32_t n, uint32_t grid, cudaStream_t s)
+{
+    if (grid == 0)
+        return EMB_OK;
+    uint32_t D = g.shape.nr_cols;
+    uint32_t lanes = lanes_for_dim(D);
+    if (!lanes) {
+        emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, D, g.d_err);
+    } else {
+        int unroll = g.unroll ? g.unroll : (lanes >= 16 ? 8 : 4);
+        if (unroll == 8)
+            launch_lanes<8>(lanes, grid, s, d_descs, n);
+        else
+            launch_lanes<4>(lanes, grid, s, d_descs, n);
+    }
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+    return EMB_OK;
+}
+
+/* Fill one descriptor from a query; returns the number of CTAs it needs. */
+int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, uint32_t *chunks)
+{
+    if (q.table_id >= g.tables.size() || !g.tables[q.table_id].kind)
+        return fail(EMB_ESTATE, "table %u is not populated", q.table_id);
+    const Table &t = g.tables[q.table_id];
+    uint32_t D = g.shape.nr_cols;
+    memset(d, 0, sizeof *d);
+    d->table = t.dev;
+    d->indices = q.indices;
+    d->offsets = q.offsets;
+    d->out = q.out;
+    d->rows = (uint32_t)t.rows;
+    d->row_base = (uint32_t)t.row_base;
+    d->nr_batches = q.nr_batches;
+    d->indices_len = q.indices_len;
+    d->out_stride = q.out_stride ? q.out_stride : D;
+    d->bags_per_rank = q.bags_per_rank;
+    d->chunk_begin = chunk_begin;
+    if (d->out_stride < D)
+        return fail(EMB_EINVAL, "out_stride %u < NR_COLS %u", d->out_stride, D);
+    uint32_t flags = 0;
+    if (t.kind == EMB_TABLE_FLOAT)
+        flags |= emb::kDescFloat;
+    else if (q.flags & EMB_Q_RAW_SUMS)
+        flags |= emb::kDescRaw;
+    if (t.sharded)
+        flags |= emb::kDescSharded;
+    bool vec = d->out_stride % 4 == 0;
+    if (q.nr_batches) {
+        if (!q.offsets || (q.indices_len && !q.indices))
+            return fail(EMB_EINVAL, "query for table %u has NULL indices/offsets", q.table_id);
+        if (q.bags_per_rank) {
+            uint32_t ranks = (q.nr_batches + q.bags_per_rank - 1) / q.bags_per_rank;
+            if (ranks > EMB_MAX_PEERS)
+                return fail(EMB_EINVAL, "nr_batches/bags_per_rank = %u ranks > %d", ranks, EMB_MAX_PEERS);
+            for (uint32_t r = 0; r < ranks; r++) {
+                if (!q.out_peer[r])
+                    return fail(EMB_EINVAL, "out_peer[%u] is NULL", r);
+                d->out_peer[r] = q.out_peer[r];
+                vec = vec && ((uintptr_t)q.out_peer[r] % 16 == 0);
+            }
+        } else {
+            if (!q.out)
+                return fail(EMB_EINVAL, "query for table %u has NULL out", q.table_id);
+            vec = vec && ((uintptr_t)q.out % 16 == 0);
+        }
+    }
+    if (vec)
+        flags |= emb::kDescVecStore;
+    d->flags = flags;
+    uint32_t per = bags_per_cta(D);
+    *chunks = (q.nr_batches + per - 1) / per;
+    return EMB_OK;
+}
+
+}  // namespace
+
+struct emb_plan {
+    std::vector<BagDesc> h;
+    BagDesc *d = nullptr;
+    uint32_t grid = 0;
+    uint64_t bytes = 0;
+};
+
+extern "C" {
+
+/* ---------------------------------------------------------------- configuration ------ */
+
+int emb_configure(uint32_t nr_tables, uint32_t nr_cols, uint32_t max_nr_batches,
+                  uint32_t max_indices_per_batch, int device)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    return configure_locked(nr_tables, nr_cols, max_nr_batches, max_indices_per_batch, device);
+}
+
+int emb_get_shape(emb_shape *out)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!out)
+        return fail(EMB_EINVAL, "NULL out");
+    if (!g.configured)
+        return fail(EMB_ESTATE, "not configured");
+    *out = g.shape;
+    return EMB_OK;
+}
+
+int emb_device(void) { return g.device_ready ? g.device : -1; }
+
+const char *emb_last_error(void) { return g_err; }
+
+uint64_t emb_launch_count(void) { return g_launches.load(); }
+
+int emb_set_unroll(int unroll)
+{
+    if (unroll != 0 && unroll != 4 && unroll != 8)
+        return fail(EMB_EINVAL, "unroll must be 0, 4 or 8");
+    g.unroll = unroll;
+    return EMB_OK;
+}
+
+void emb_shutdown(void)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g.device_ready) {
+        cudaSetDevice(g.device);
+        cudaDeviceSynchronize();
+        for (Table &t : g.tables)
+            if (t.dev)
+                cudaFree(t.dev);
+        cudaFree(g.d_col);
+        cudaFree(g.d_idx);
+        cudaFree(g.d_off);
+        cudaFree(g.d_out);
+        cudaFree(g.d_descs);
+        cudaFree(g.d_err);
+        if (g.h_descs)
+            cudaFreeHost(g.h_descs);
+        for (auto &ev : g.ev)
+            if (ev)
+                cudaEventDestroy(ev);
+        if (g.stream)
+            cudaStreamDestroy(g.stream);
+        if (g.stream_out)
+            cudaStreamDestroy(g.stream_out);
+    }
+    int unroll = g.unroll;
+    g = Ctx();
+    g.unroll = unroll;
+}
+
+/* ---------------------------------------------------------------- tables -------------- */
+
+struct dpu_set_t *populate_mram(uint32_t table_id, uint64_t nr_rows, uint32_t col, int32_t *table_data,
+                                dpu_runtime_totals *runtime)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    double t0 = now_s();
+    int rc = ensure_configured();
+    if (rc)
+        die("populate_mram", rc);
+    const uint32_t D = g.shape.nr_cols;
+    if (col >= D || !table_data) {
+        fail(EMB_EINVAL, "col %u >= NR_COLS %u or NULL data", col, D);
+        die("populate_mram", EMB_EINVAL);
+    }
+    Table *t = nullptr;
+    if ((rc = table_slot(table_id, &t)) || (rc = table_alloc(t, nr_rows, EMB_TABLE_FIXED)))
+        die("populate_mram", rc);
+    size_t bytes = (size_t)nr_rows * 4;
+    size_t cap = g.col_bytes;
+    if ((rc = grow(&g.d_col, &cap, bytes, 1)))
+        die("populate_mram", rc);
+    g.col_bytes = cap;
+    cudaError_t e = cudaMemcpyAsync(g.d_col, table_data, bytes, cudaMemcpyHostToDevice, g.stream);
+    if (e == cudaSuccess) {
+        uint32_t grid = (uint32_t)std::min<uint64_t>((nr_rows + 255) / 256, (uint64_t)g.sm_count * 16);
+        emb::scatter_column_kernel<<<grid, 256, 0, g.stream>>>((uint32_t *)t->dev, (const uint32_t *)g.d_col,
+                                                               nr_rows, D, col);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(g.stream);  // table_data may be freed on return
+    if (e != cudaSuccess) {
+        fail(EMB_ECUDA, "populate_mram: %s", cudaGetErrorString(e));
+        die("populate_mram", EMB_ECUDA);
+    }
+    if (runtime)
+        runtime->execution_time_populate_copy_in += now_s() - t0;
+    return reinterpret_cast<struct dpu_set_t *>(&g);
+}
+
+static int populate_whole(uint32_t table_id, uint64_t nr_rows, const void *src, bool src_device,
+                          bool src_f32, int kind, cudaStream_t s)
+{
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (!src)
+        return fail(EMB_EINVAL, "NULL table data");
+    if (kind != EMB_TABLE_FIXED && kind != EMB_TABLE_FLOAT)
+        return fail(EMB_EINVAL, "kind must be EMB_TABLE_FIXED or EMB_TABLE_FLOAT");
+    if (kind == EMB_TABLE_FLOAT && !src_f32)
+        return fail(EMB_EINVAL, "a float table needs fp32 source data");
+    Table *t = nullptr;
+    if ((rc = table_slot(table_id, &t)) || (rc = table_alloc(t, nr_rows, kind)))
+        return rc;
+    uint64_t n = nr_rows * g.shape.nr_cols;
+    CU(cudaMemcpyAsync(t->dev, src, n * 4, src_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
+    if (kind == EMB_TABLE_FIXED && src_f32) {
+        uint32_t grid = (uint32_t)std::min<uint64_t>((n + 255) / 256, (uint64_t)g.sm_count * 32);
+        emb::quantise_kernel<<<grid, 256, 0, s>>>((int32_t *)t->dev, (const float *)t->dev, n);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        CU(cudaGetLastError());
+    }
+    CU(cudaStreamSynchronize(s));
+    return EMB_OK;
+}
+
+int emb_populate_table_i32(uint32_t table_id, uint64_t nr_rows, const int32_t *row_major)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    return populate_whole(table_id, nr_rows, row_major, false, false, EMB_TABLE_FIXED, g.stream);
+}
+
+int emb_populate_table_f32(uint32_t table_id, uint64_t nr_rows, const float *row_major, int kind)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    return populate_whole(table_id, nr_rows, row_major, false, true, kind, g.stream);
+}
+
+int emb_populate_table_device(uint32_t table_id, uint64_t nr_rows, const void *dev_row_major,
+                              int src_is_f32, int kind, void *stream)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    return populate_whole(table_id, nr_rows, dev_row_major, true, src_is_f32 != 0, kind,
+                          stream ? (cudaStream_t)stream : g.stream);
+}
+
+int emb_table_set_row_base(uint32_t table_id, uint64_t row_base)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (table_id >= g.tables.size() || !g.tables[table_id].kind)
+        return fail(EMB_ESTATE, "table %u is not populated", table_id);
+    if (row_base > 0xffffffffull)
+        return fail(EMB_EINVAL, "row_base too large");
+    g.tables[table_id].row_base = row_base;
+    g.tables[table_id].sharded = true;
+    return EMB_OK;
+}
+
+int emb_table_read(uint32_t table_id, uint64_t row0, uint64_t n, void *dst_host)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (table_id >= g.tables.size() || !g.tables[table_id].kind)
+        return fail(EMB_ESTATE, "table %u is not populated", table_id);
+    const Table &t = g.tables[table_id];
+    if (row0 + n > t.rows || !dst_host)
+        return fail(EMB_EINVAL, "rows [%llu, %llu) outside table of %llu rows", (unsigned long long)row0,
+                    (unsigned long long)(row0 + n), (unsigned long long)t.rows);
+    size_t rb = (size_t)g.shape.nr_cols * 4;
+    CU(cudaMemcpy(dst_host, (const char *)t.dev + row0 * rb, n * rb, cudaMemcpyDeviceToHost));
+    return EMB_OK;
+}
+
+int emb_table_info(uint32_t table_id, uint64_t *nr_rows, int *kind, const void **dev_ptr)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (table_id >= g.tables.size() || !g.tables[table_id].kind)
+        return fail(EMB_ESTATE, "table %u is not populated", table_id);
+    const Table &t = g.tables[table_id];
+    if (nr_rows)
+        *nr_rows = t.rows;
+    if (kind)
+        *kind = t.kind;
+    if (dev_ptr)
+        *dev_ptr = t.dev;
+    return EMB_OK;
+}
+
+int emb_free_table(uint32_t table_id)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (table_id >= g.tables.size() || !g.tables[table_id].kind)
+        return fail(EMB_ESTATE, "table %u is not populated", table_id);
+    CU(cudaDeviceSynchronize());
+    cudaFree(g.tables[table_id].dev);
+    g.tables[table_id] = Table();
+    return EMB_OK;
+}
+
+int emb_l2_persist(uint32_t table_id, uint64_t first_row, uint64_t nr_rows, float hit_ratio, void *stream)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    cudaStreamAttrValue attr;
+    memset(&attr, 0, sizeof attr);
+    if (nr_rows == 0) {
+        attr.accessPolicyWindow.num_bytes = 0;
+        CU(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr));
+        CU(cudaCtxResetPersistingL2Cache());
+        return EMB_OK;
+    }
+    if (table_id >= g.tables.size() || !g.tables[table_id].kind)
+        return fail(EMB_ESTATE, "table %u is not populated", table_id);
+    const Table &t = g.tables[table_id];
+    if (first_row + nr_rows > t.rows)
+        return fail(EMB_EINVAL, "window outside the table");
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, g.device));
+    size_t rb = (size_t)g.shape.nr_cols * 4;
+    size_t bytes = std::min((size_t)nr_rows * rb, (size_t)prop.accessPolicyMaxWindowSize);
+    CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize,
+                          std::min(bytes, (size_t)prop.persistingL2CacheMaxSize)));
+    attr.accessPolicyWindow.base_ptr = (char *)t.dev + first_row * rb;
+    attr.accessPolicyWindow.num_bytes = bytes;
+    attr.accessPolicyWindow.hitRatio = hit_ratio;
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    CU(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr));
+    return EMB_OK;
+}
+
+/* ---------------------------------------------------------------- plans ---------------- */
+
+int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (!queries || !n || !out)
+        return fail(EMB_EINVAL, "emb_plan_create: NULL/empty arguments");
+    emb_plan *p = new (std::nothrow) emb_plan();
+    if (!p)
+        return fail(EMB_ENOMEM, "out of host memory");
+    p->h.resize(n);
+    uint64_t chunk = 0;
+    const uint64_t D = g.shape.nr_cols;
+    for (uint32_t i = 0; i < n; i++) {
+        uint32_t c = 0;
+        if ((rc = fill_desc(queries[i], &p->h[i], (uint32_t)chunk, &c))) {
+            delete p;
+            return rc;
+        }
+        chunk += c;
+        p->bytes += ((uint64_t)queries[i].indices_len + queries[i].nr_batches) * (4 * D + 4);
+    }
+    if (chunk > 0x7fffffffull) {
+        delete p;
+        return fail(EMB_EINVAL, "too many bags for one launch");
+    }
+    p->grid = (uint32_t)chunk;
+    cudaError_t e = cudaMalloc(&p->d, n * sizeof(BagDesc));
+    if (e == cudaSuccess)
+        e = cudaMemcpy(p->d, p->h.data(), n * sizeof(BagDesc), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cudaFree(p->d);
+        delete p;
+        return fail(EMB_ECUDA, "plan upload: %s", cudaGetErrorString(e));
+    }
+    *out = p;
+    return EMB_OK;
+}
+
+int emb_plan_launch(emb_plan *plan, void *stream)
+{
+    if (!plan)
+        return fail(EMB_EINVAL, "NULL plan");
+    return launch_bag_sum(plan->d, (uint32_t)plan->h.size(), plan->grid,
+                          stream ? (cudaStream_t)stream : g.stream);
+}
+
+void emb_plan_destroy(emb_plan *plan)
+{
+    if (!plan)
+        return;
+    cudaFree(plan->d);
+    delete plan;
+}
+
+uint64_t emb_plan_bytes(const emb_plan *plan) { return plan ? plan->bytes : 0; }
+uint32_t emb_plan_grid(const emb_plan *plan) { return plan ? plan->grid : 0; }
+
+int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
+{
+    emb_plan *p = nullptr;
+    int rc = emb_plan_create(queries, n, &p);
+    if (rc)
+        return rc;
+    rc = emb_plan_launch(p, stream);
+    cudaError_t e = cudaStreamSynchronize(stream ? (cudaStream_t)stream : g.stream);
+    emb_plan_destroy(p);
+    if (rc)
+        return rc;
+    if (e != cudaSuccess)
+        return fail(EMB_ECUDA, "emb_lookup_device: %s", cudaGetErrorString(e));
+    return EMB_OK;
+}
+
+int emb_check_indices(void)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g.device_ready)
+        return 0;
+    uint32_t v = 0;
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(&v, g.d_err, 4, cudaMemcpyDeviceToHost));
+    if (v)
+        CU(cudaMemset(g.d_err, 0, 4));
+    return v ? 1 : 0;
+}
+
+int emb_reduce_partials(const void *const *parts_dev, uint32_t n_parts, uint32_t part_stride, void *out_dev,
+                        uint32_t out_stride, uint64_t nr_bags, int is_raw_i32, void *stream)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (!parts_dev || !n_parts || n_parts > EMB_MAX_PEERS || !out_dev)
+        return fail(EMB_EINVAL, "emb_reduce_partials: bad arguments");
+    if (!nr_bags)
+        return EMB_OK;
+    emb::PartList pl;
+    memset(&pl, 0, sizeof pl);
+    for (uint32_t s = 0; s < n_parts; s++)
+        pl.p[s] = (const uint32_t *)parts_dev[s];
+    uint32_t D = g.shape.nr_cols;
+    uint64_t n = nr_bags * D;
+    uint32_t grid = (uint32_t)std::min<uint64_t>((n + 255) / 256, (uint64_t)g.sm_count * 32);
+    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    emb::reduce_partials_kernel<<<grid, 256, 0, s>>>(pl, n_parts, part_stride ? part_stride : D,
+                                                     (uint32_t *)out_dev, out_stride ? out_stride : D, D,
+                                                     nr_bags, is_raw_i32);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+    return EMB_OK;
+}
+
+/* ---------------------------------------------------------------- host-pointer lookups -- */
+
+/* Shared body of lookup() and emb_lookup_ex(): per-table async H2D of the caller's arrays
+ * into packed device mirrors, one kernel for all tables, D2H of each table's pooled rows.
+ * emb_host.h:258-287 pushed indices/offsets/lengths to every column DPU (indices
+ * replicated NR_COLS times); here every byte crosses PCIe once. */
+static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_t *const *offsets,
+                       const uint32_t *indices_len, const uint32_t *nr_batches,
+                       float *const *final_results)
+{
+    double t_begin = now_s();
+    const uint32_t D = g.shape.nr_cols;
+    if (T > g.tables.size())
+        return fail(EMB_ESTATE, "lookup over %u tables but only %zu slots exist", T, g.tables.size());
+    uint64_t tot_idx = 0, tot_bags = 0;
+    for (uint32_t t = 0; t < T; t++) {
+        if (!g.tables[t].kind)
+            return fail(EMB_ESTATE, "table %u is not populated", t);
+        if ((indices_len[t] && !indices[t]) || (nr_batches[t] && (!offsets[t] || !final_results[t])))
+            return fail(EMB_EINVAL, "NULL array for table %u", t);
+        tot_idx += indices_len[t];
+        tot_bags += nr_batches[t];
+    }
+    int rc;
+    if ((rc = grow((void **)&g.d_idx, &g.idx_cap, tot_idx, 4)) ||
+        (rc = grow((void **)&g.d_off, &g.off_cap, tot_bags, 4)) ||
+        (rc = grow((void **)&g.d_out, &g.out_cap, tot_bags * D, 4)))
+        return rc;
+    if (g.desc_cap < T) {
+        if (g.d_descs)
+            cudaFree(g.d_descs);
+        if (g.h_descs)
+            cudaFreeHost(g.h_descs);
+        g.d_descs = nullptr;
+        g.h_descs = nullptr;
+        g.desc_cap = 0;
+        CU(cudaMalloc(&g.d_descs, T * sizeof(BagDesc)));
+        CU(cudaMallocHost(&g.h_descs, T * sizeof(BagDesc)));
+        g.desc_cap = T;
+    }
+
+    cudaStream_t s = g.stream;
+    CU(cudaEventRecord(g.ev[0], s));
+    uint64_t io = 0, oo = 0, chunk = 0, h2d = 0;
+    for (uint32_t t = 0; t < T; t++) {
+        emb_dev_query q;
+        memset(&q, 0, sizeof q);
+        q.table_id = t;
+        q.nr_batches = nr_batches[t];
+        q.indices_len = indices_len[t];
+        q.indices = g.d_idx + io;
+        q.offsets = g.d_off + oo;
+        q.out = g.d_out + oo * D;
+        q.out_stride = D;
+        uint32_t c = 0;
+        if ((rc = fill_desc(q, &g.h_descs[t], (uint32_t)chunk, &c)))
+            return rc;
+        chunk += c;
+        if (indices_len[t])
+            CU(cudaMemcpyAsync(g.d_idx + io, indices[t], (size_t)indices_len[t] * 4, cudaMemcpyHostToDevice, s));
+        if (nr_batches[t])
+            CU(cudaMemcpyAsync(g.d_off + oo, offsets[t], (size_t)nr_batches[t] * 4, cudaMemcpyHostToDevice, s));
+        h2d += ((uint64_t)indices_len[t] + nr_batches[t]) * 4;
+        io += indices_len[t];
+        oo += nr_batches[t];
+    }
+    if (chunk > 0x7fffffffull)
+        return fail(EMB_EINVAL, "too many bags for one launch");
+    CU(cudaMemcpyAsync(g.d_descs, g.h_descs, T * sizeof(BagDesc), cudaMemcpyHostToDevice, s));
+    CU(cudaEventRecord(g.ev[1], s));
+    if ((rc = launch_bag_sum(g.d_descs, T, (uint32_t)chunk, s)))
+        return rc;
+    CU(cudaEventRecord(g.ev[2], s));
+    oo = 0;
+    for (uint32_t t = 0; t < T; t++) {
+        if (nr_batches[t])
+            CU(cudaMemcpyAsync(final_results[t], g.d_out + oo * D, (size_t)nr_batches[t] * D * 4,
+                               cudaMemcpyDeviceToHost, s));
+        oo += nr_batches[t];
+    }
+    CU(cudaEventRecord(g.ev[3], s));
+    CU(cudaStreamSynchronize(s));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1]));
+    g.last.h2d_ms = ms;
+    CU(cudaEventElapsedTime(&ms, g.ev[1], g.ev[2]));
+    g.last.kernel_ms = ms;
+    CU(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3]));
+    g.last.d2h_ms = ms;
+    g.last.total_ms = (now_s() - t_begin) * 1e3;
+    g.last.h2d_bytes = h2d + T * sizeof(BagDesc);
+    g.last.d2h_bytes = tot_bags * D * 4;
+    g.last.launches = chunk ? 1 : 0;
+    return EMB_OK;
+}
+
+int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results, void *dpu_set_ptr,
+                int64_t latency_print)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        die("lookup", rc);
+    if (dpu_set_ptr && dpu_set_ptr != (void *)&g)
+        fprintf(stderr, "emblib(B200): lookup: dpu_set_ptr %p is not the handle populate_mram returned (%p); ignored\n",
+                dpu_set_ptr, (void *)&g);
+    const uint32_t T = g.shape.nr_tables, B = g.shape.max_nr_batches;
+    const uint32_t ilen = B * g.shape.max_indices_per_batch;  // INDICES_LEN, emb_host.h:30
+    if (!B || !indices || !offsets || !final_results) {
+        fail(EMB_EINVAL, "lookup: MAX_NR_BATCHES is 0 or NULL arguments");
+        die("lookup", EMB_EINVAL);
+    }
+    std::vector<uint32_t> il(T, ilen), nb(T, B);  // struct query_len, emb_host.h:280-287
+    rc = lookup_host(T, indices, offsets, il.data(), nb.data(), final_results);
+    if (rc)
+        die("lookup", rc);
+    if (latency_print == 1) {  // the reference's six lines, emb_host.h:395-402
+        printf("C: Indices and offsets copying latency: %ldμs\n", (long)(g.last.h2d_ms * 1e3));
+        printf("C: Query copying latency: %ldμs\n", 0L);
+        printf("C: Dpu launch latency: %ldμs\n", (long)(g.last.kernel_ms * 1e3));
+        printf("C: Results copy latency: %ldμs\n", (long)(g.last.d2h_ms * 1e3));
+        printf("C: Callback prep latency: %ldμs\n", 0L);
+        printf("C: DPU sync latency: %ldμs\n",
+               (long)((g.last.total_ms - g.last.h2d_ms - g.last.kernel_ms - g.last.d2h_ms) * 1e3));
+    }
+    return nullptr;
+}
+
+int emb_lookup_ex(uint32_t nr_tables, const uint32_t *const *indices, const uint32_t *const *offsets,
+                  const uint32_t *indices_len, const uint32_t *nr_batches, float *const *final_results)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (!nr_tables || !indices || !offsets || !indices_len || !nr_batches || !final_results)
+        return fail(EMB_EINVAL, "emb_lookup_ex: NULL/empty arguments");
+    return lookup_host(nr_tables, indices, offsets, indices_len, nr_batches, final_results);
+}
+
+int emb_last_timings(emb_timings *out)
+{
+    if (!out)
+        return fail(EMB_EINVAL, "NULL out");
+    *out = g.last;
+    return EMB_OK;
+}
+
+/* ---------------------------------------------------------------- memory helpers -------- */
+
+int emb_device_alloc(void **dev_ptr, size_t nbytes)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (!dev_ptr)
+        return fail(EMB_EINVAL, "NULL dev_ptr");
+    cudaError_t e = cudaMalloc(dev_ptr, nbytes ? nbytes : 1);
+    if (e != cudaSuccess)
+        return fail(EMB_ENOMEM, "cudaMalloc(%zu): %s", nbytes, cudaGetErrorString(e));
+    return EMB_OK;
+}
+
+int emb_device_free(void *dev_ptr)
+{
+    CU(cudaFree(dev_ptr));
+    return EMB_OK;
+}
+
+int emb_host_alloc(void **host_ptr, size_t nbytes)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (!host_ptr)
+        return fail(EMB_EINVAL, "NULL host_ptr");
+    cudaError_t e = cudaMallocHost(host_ptr, nbytes ? nbytes : 1);
+    if (e != cudaSuccess)
+        return fail(EMB_ENOMEM, "cudaMallocHost(%zu): %s", nbytes, cudaGetErrorString(e));
+    return EMB_OK;
+}
+
+int emb_host_free(void *host_ptr)
+{
+    CU(cudaFreeHost(host_ptr));
+    return EMB_OK;
+}
+
+int emb_memcpy_h2d(void *dst_dev, const void *src_host, size_t nbytes, void *stream)
+{
+    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    CU(cudaMemcpyAsync(dst_dev, src_host, nbytes, cudaMemcpyHostToDevice, s));
+    if (!stream)
+        CU(cudaStreamSynchronize(s));
+    return EMB_OK;
+}
+
+int emb_memcpy_d2h(void *dst_host, const void *src_dev, size_t nbytes, void *stream)
+{
+    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    CU(cudaMemcpyAsync(dst_host, src_dev, nbytes, cudaMemcpyDeviceToHost, s));
+    if (!stream)
+        CU(cudaStreamSynchronize(s));
+    return EMB_OK;
+}
+
+int emb_stream_sync(void *stream)
+{
+    if (stream)
+        CU(cudaStreamSynchronize((cudaStream_t)stream));
+    else if (g.device_ready)
+        CU(cudaDeviceSynchronize());
+    return EMB_OK;
+}
+
+int emb_ipc_export(void *dev_ptr, emb_ipc_handle *out)
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == EMB_IPC_HANDLE_BYTES, "IPC handle size");
+    if (!dev_ptr || !out)
+        return fail(EMB_EINVAL, "NULL argument");
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, dev_ptr));
+    memcpy(out->bytes, &h, sizeof h);
+    return EMB_OK;
+}
+
+int emb_ipc_open(const emb_ipc_handle *h, void **peer_dev_ptr)
+{
+    if (!h || !peer_dev_ptr)
+        return fail(EMB_EINVAL, "NULL argument");
+    cudaIpcMemHandle_t ch;
+    memcpy(&ch, h->bytes, sizeof ch);
+    CU(cudaIpcOpenMemHandle(peer_dev_ptr, ch, cudaIpcMemLazyEnablePeerAccess));
+    return EMB_OK;
+}
+
+int emb_ipc_close(void *peer_dev_ptr)
+{
+    CU(cudaIpcCloseMemHandle(peer_dev_ptr));
+    return EMB_OK;
+}
+
+}  // extern "C"

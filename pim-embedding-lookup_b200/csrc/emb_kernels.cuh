@@ -1,0 +1,339 @@
+/*
+ * emb_kernels.cuh -- sm_100a kernels of the embedding-lookup hot path.
+ *
+ * What the UPMEM build spread over NR_TABLES*NR_COLS DPUs x 14 tasklets
+ * (upmem/src/dpu/emb_dpu_lookup.c:106-128: one int32 column per DPU, one dependent 8-byte
+ * MRAM read per index) is ONE launch here: tables are row-major [rows][D] in HBM, a
+ * sub-warp of D/4 lanes owns a bag, every lane moves 16 bytes of every row of the bag
+ * (LDG.128, the row is one or more fully used 32-byte sectors), and the reference's
+ * post_process() (upmem/include/emb_host.h:207-212) is the store epilogue.
+ *
+ * HBM-bound integer work: no tensor cores, no shared-memory tiling of table data (no reuse);
+ * the CTA stages only its bags' offsets and indices in shared memory so that the row
+ * gathers of a sub-warp are independent loads that can all be in flight together.
+ */
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/emb_b200.h"
+
+namespace emb {
+
+constexpr int kThreads = 256;    // CTA size: 8 warps
+constexpr int kIdxStage = 3072;  // indices staged per CTA (12 KB)
+
+enum : uint32_t {
+    kDescFloat = 1u,    // table holds fp32
+    kDescRaw = 2u,      // write raw int32 sums (no dequantise)
+    kDescSharded = 4u,  // row-range shard: out-of-range indices are silently skipped
+    kDescVecStore = 8u, // output rows are 16-byte aligned
+};
+
+/* One per query; lives in device memory for the lifetime of a plan. */
+struct __align__(16) BagDesc {
+    const void *table;        // [rows][D] int32 or fp32
+    const uint32_t *indices;  // [indices_len]
+    const uint32_t *offsets;  // [nr_batches]
+    void *out;                // single-slab output (bags_per_rank == 0)
+    void *out_peer[EMB_MAX_PEERS];
+    uint32_t rows;       // rows held in this slot
+    uint32_t row_base;   // global id of row 0
+    uint32_t nr_batches;
+    uint32_t indices_len;
+    uint32_t out_stride;  // elements
+    uint32_t bags_per_rank;
+    uint32_t flags;
+    uint32_t chunk_begin;  // first CTA of this query
+};
+
+__device__ __forceinline__ uint4 ldg_row16(const uint4 *p)
+{
+    uint4 r;
+    // read-only, streamed: a row is touched once per bag, keep it out of L1
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t *p)
+{
+    uint32_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ void stg_stream16(void *p, uint4 v)
+{
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+
+/* emb_host.h:210  (float)s / pow(10,9): int->float RNE, divide in double, round to float.
+ * 1e9 is exact in fp32 and double has >= 2*24+2 bits, so this equals one IEEE fp32 divide. */
+__device__ __forceinline__ float dequant(uint32_t s)
+{
+    return __fdiv_rn(__int2float_rn((int)s), 1.0e9f);
+}
+
+/* dlrm_dpu_pytorch.py:318 + :329: float32 product, rint (half-to-even), int64, low 32 bits. */
+__device__ __forceinline__ int32_t quantise(float w)
+{
+    float r = rintf(__fmul_rn(w, 1.0e9f));
+    // numpy's float->int64 cast of an out-of-range / NaN value is the x86 "integer
+    // indefinite" 0x8000000000000000, whose low word is 0
+    if (!(fabsf(r) < 9.2233720e18f))
+        return 0;
+    return (int32_t)(uint32_t)(unsigned long long)__float2ll_rn(r);
+}
+
+__device__ __forceinline__ uint32_t find_desc(const BagDesc *__restrict__ descs, uint32_t n, uint32_t chunk)
+{
+    uint32_t lo = 0, hi = n;  // last desc with chunk_begin <= chunk
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(&descs[mid].chunk_begin) <= chunk)
+            lo = mid;
+        else
+            hi = mid;
+    }
+    return lo;
+}
+
+/*
+ * Sum-pool kernel, D = 4*LANES columns (LANES in 1..32, power of two).
+ * grid.x = sum over queries of ceil(nr_batches / (kThreads/LANES)); one CTA handles
+ * kThreads/LANES consecutive bags of one table.
+ */
+template <int LANES, int UNROLL>
+__global__ void __launch_bounds__(kThreads)
+bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__restrict__ err_flag)
+{
+    constexpr int BAGS = kThreads / LANES;
+    __shared__ uint32_t s_off[BAGS + 1];
+    __shared__ uint32_t s_idx[kIdxStage];
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
+    const BagDesc *__restrict__ d = descs + q;
+
+    const uint32_t B = d->nr_batches;
+    const uint32_t ilen = d->indices_len;
+    const uint32_t b0 = (blockIdx.x - d->chunk_begin) * BAGS;
+    const uint32_t nb = min((uint32_t)BAGS, B - b0);
+    const uint32_t *__restrict__ g_idx = d->indices;
+    const uint32_t *__restrict__ g_off = d->offsets;
+
+    // bag bounds, emb_dpu_lookup.c:60-63,109-110: bag 0 starts at 0 whatever offsets[0] is,
+    // bag i ends where bag i+1 starts, the last bag ends at indices_len
+    for (uint32_t i = tid; i <= nb; i += kThreads) {
+        uint32_t b = b0 + i;
+        uint32_t v = (b == 0) ? 0u : (b >= B ? ilen : ldg_stream_u32(g_off + b));
+        s_off[i] = min(v, ilen);
+    }
+    __syncthreads();
+
+    const uint32_t wlo = s_off[0], whi = s_off[nb];
+    const bool staged = whi > wlo && (whi - wlo) <= (uint32_t)kIdxStage;
+    if (staged) {
+        const uint32_t n = whi - wlo;
+        for (uint32_t i = tid; i < n; i += kThreads)
+            s_idx[i] = ldg_stream_u32(g_idx + wlo + i);
+    }
+    __syncthreads();
+
+    const uint32_t bag = tid / LANES;
+    const uint32_t lane = tid % LANES;
+    if (bag >= nb)
+        return;
+
+    const uint32_t start = s_off[bag];
+    const uint32_t end = s_off[bag + 1];
+    const uint32_t flags = d->flags;
+    const uint32_t rows = d->rows;
+    const uint32_t row_base = d->row_base;
+    const uint4 *__restrict__ table = reinterpret_cast<const uint4 *>(d->table) + lane;
+    const bool in_window = staged && start >= wlo && end <= whi;  // false only for non-monotone offsets
+
+    uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+    float4 facc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool is_float = flags & kDescFloat;
+    bool bad = false;
+
+    for (uint32_t p = start; p < end; p += UNROLL) {
+        uint32_t r[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+            uint32_t id = 0xffffffffu;
+            if (p + u < end) {
+                id = in_window ? s_idx[p + u - wlo] : __ldg(g_idx + p + u);
+                id -= row_base;  // unsigned: rows below the shard wrap to huge values
+                bad |= id >= rows;
+            } else {
+                id = 0xffffffffu;
+            }
+            r[u] = id;
+        }
+        uint4 v[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+            v[u] = make_uint4(0u, 0u, 0u, 0u);
+            if (r[u] < rows)
+                v[u] = ldg_row16(table + (size_t)r[u] * LANES);
+        }
+        if (!is_float) {
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {  // int32 wrap-around adds (emb_dpu_lookup.c:114)
+                acc.x += v[u].x;
+                acc.y += v[u].y;
+                acc.z += v[u].z;
+                acc.w += v[u].w;
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {  // fp32, strictly in index order (embedding_lookup_idx.cc:33-77)
+                facc.x = __fadd_rn(facc.x, __uint_as_float(v[u].x));
+                facc.y = __fadd_rn(facc.y, __uint_as_float(v[u].y));
+                facc.z = __fadd_rn(facc.z, __uint_as_float(v[u].z));
+                facc.w = __fadd_rn(facc.w, __uint_as_float(v[u].w));
+            }
+        }
+    }
+    if (bad && !(flags & kDescSharded))
+        atomicOr(err_flag, 1u);
+
+    uint4 o;
+    if (is_float) {
+        o = make_uint4(__float_as_uint(facc.x), __float_as_uint(facc.y), __float_as_uint(facc.z),
+                       __float_as_uint(facc.w));
+    } else if (flags & kDescRaw) {
+        o = acc;
+    } else {  // post_process, emb_host.h:210
+        o = make_uint4(__float_as_uint(dequant(acc.x)), __float_as_uint(dequant(acc.y)),
+                       __float_as_uint(dequant(acc.z)), __float_as_uint(dequant(acc.w)));
+    }
+
+    const uint32_t b = b0 + bag;
+    uint32_t *base;
+    uint32_t row;
+    const uint32_t bpr = d->bags_per_rank;
+    if (bpr) {  // pooled row goes straight to the slab of the rank that owns sample b
+        uint32_t rk = b / bpr;
+        base = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
+        row = b - rk * bpr;
+    } else {
+        base = reinterpret_cast<uint32_t *>(d->out);
+        row = b;
+    }
+    uint32_t *dst = base + (size_t)row * d->out_stride + lane * 4;
+    if (flags & kDescVecStore) {
+        stg_stream16(dst, o);
+    } else {
+        dst[0] = o.x;
+        dst[1] = o.y;
+        dst[2] = o.z;
+        dst[3] = o.w;
+    }
+}
+
+/*
+ * Any embedding dimension (D not a multiple of 4, or above 128): a warp per bag, lanes
+ * stride over the columns with 4-byte loads.  Correctness path, not a tuned one.
+ */
+__global__ void __launch_bounds__(kThreads)
+bag_sum_generic_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t dim,
+                       uint32_t *__restrict__ err_flag)
+{
+    constexpr int BAGS = kThreads / 32;
+    const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
+    const BagDesc *__restrict__ d = descs + q;
+    const uint32_t B = d->nr_batches;
+    const uint32_t b = (blockIdx.x - d->chunk_begin) * BAGS + threadIdx.x / 32;
+    const uint32_t lane = threadIdx.x % 32;
+    if (b >= B)
+        return;
+    const uint32_t ilen = d->indices_len;
+    uint32_t start = (b == 0) ? 0u : min(__ldg(d->offsets + b), ilen);
+    uint32_t end = (b == B - 1) ? ilen : min(__ldg(d->offsets + b + 1), ilen);
+    const uint32_t flags = d->flags;
+    const uint32_t *table = reinterpret_cast<const uint32_t *>(d->table);
+    const uint32_t bpr = d->bags_per_rank;
+    uint32_t *base = reinterpret_cast<uint32_t *>(bpr ? d->out_peer[b / bpr] : d->out);
+    uint32_t row = bpr ? b % bpr : b;
+    bool bad = false;
+    for (uint32_t c = lane; c < dim; c += 32) {
+        uint32_t acc = 0;
+        float facc = 0.f;
+        for (uint32_t p = start; p < end; p++) {
+            uint32_t id = __ldg(d->indices + p) - d->row_base;
+            if (id < d->rows) {
+                uint32_t v = __ldg(table + (size_t)id * dim + c);
+                acc += v;
+                facc = __fadd_rn(facc, __uint_as_float(v));
+            } else {
+                bad = true;
+            }
+        }
+        uint32_t o = (flags & kDescFloat) ? __float_as_uint(facc)
+                     : (flags & kDescRaw) ? acc
+                                          : __float_as_uint(dequant(acc));
+        base[(size_t)row * d->out_stride + c] = o;
+    }
+    if (bad && !(flags & kDescSharded))
+        atomicOr(err_flag, 1u);
+}
+
+/* populate_mram(): column `col` of a table arrives as nr_rows contiguous int32
+ * (emb_host.h:165-173 pushed it to DPU table*NR_COLS+col); here it is scattered into the
+ * row-major slab. */
+__global__ void scatter_column_kernel(uint32_t *__restrict__ slab, const uint32_t *__restrict__ column,
+                                      uint64_t nr_rows, uint32_t dim, uint32_t col)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < nr_rows; i += step)
+        slab[i * dim + col] = column[i];
+}
+
+/* export_emb (dlrm_dpu_pytorch.py:318-320) on the GPU; the slab is already row-major so
+ * the reference's transpose disappears.  dst may alias src. */
+__global__ void quantise_kernel(int32_t *dst, const float *src, uint64_t n)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += step)
+        dst[i] = quantise(src[i]);
+}
+
+/* Row-split tables: combine the per-shard partial rows at the receiving rank. */
+struct PartList {
+    const uint32_t *p[EMB_MAX_PEERS];
+};
+__global__ void reduce_partials_kernel(PartList parts, uint32_t n_parts, uint32_t part_stride,
+                                       uint32_t *__restrict__ out, uint32_t out_stride, uint32_t dim,
+                                       uint64_t nr_bags, int is_raw_i32)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t n = nr_bags * dim;
+    const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += step) {
+        uint64_t b = i / dim;
+        uint32_t c = (uint32_t)(i - b * dim);
+        if (is_raw_i32) {
+            uint32_t acc = 0;
+            for (uint32_t s = 0; s < n_parts; s++)
+                acc += parts.p[s][b * part_stride + c];
+            out[b * out_stride + c] = __float_as_uint(dequant(acc));
+        } else {
+            float acc = 0.f;
+            for (uint32_t s = 0; s < n_parts; s++)
+                acc = __fadd_rn(acc, __uint_as_float(parts.p[s][b * part_stride + c]));
+            out[b * out_stride + c] = __float_as_uint(acc);
+        }
+    }
+}
+
+}  // namespace emb

@@ -1,0 +1,284 @@
+"""ctypes bridge to emblib.so -- the Python side of the drop-in boundary.
+
+Mirrors how the reference binds its C library (PIM-dlrm-new/dlrm_dpu_pytorch.py:117-125,
+308-309; upmem/c_test.py:15-16): `CDLL("emblib.so")`, then `populate_mram` / `lookup` with
+the same argtypes.  On top of the two reference entry points it declares the extension
+entry points of include/emb_b200.h.
+
+There is no fallback: if emblib.so is missing or no CUDA device is visible every call
+raises (load()) or the C side prints and exits, as the reference's DPU_ASSERT does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from .dputypes import (EMB_MAX_PEERS, EMB_Q_RAW_SUMS, EMB_TABLE_FIXED, EMB_TABLE_FLOAT, DpuRuntimeTotals,
+                       EmbDevQuery, EmbIpcHandle, EmbShape, EmbTimings)
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "emblib.so")
+_lib = None
+
+u32p = C.POINTER(C.c_uint32)
+i32p = C.POINTER(C.c_int32)
+f32p = C.POINTER(C.c_float)
+
+
+class EmbError(RuntimeError):
+    pass
+
+
+def build(verbose: bool = False) -> str:
+    """Compile emblib.so (+ the emb_host microbenchmark) for sm_100a with nvcc."""
+    r = subprocess.run(["make", "-C", os.path.join(_PKG, "csrc"), "all"], capture_output=True, text=True)
+    if verbose or r.returncode:
+        print(r.stdout[-4000:], r.stderr[-4000:])
+    if r.returncode:
+        raise EmbError("building emblib.so failed")
+    return LIB_PATH
+
+
+def _declare(lib):
+    # --- the reference's two entry points, argtypes exactly as its callers set them ---
+    lib.populate_mram.argtypes = [C.c_uint32, C.c_uint64, C.c_uint32, i32p, C.POINTER(DpuRuntimeTotals)]
+    lib.populate_mram.restype = C.c_void_p
+    lib.lookup.argtypes = [C.POINTER(u32p), C.POINTER(u32p), C.POINTER(f32p), C.c_void_p, C.c_int64]
+    lib.lookup.restype = C.c_void_p
+    # --- extensions ---
+    sig = {
+        "emb_configure": ([C.c_uint32] * 4 + [C.c_int], C.c_int),
+        "emb_get_shape": ([C.POINTER(EmbShape)], C.c_int),
+        "emb_device": ([], C.c_int),
+        "emb_shutdown": ([], None),
+        "emb_last_error": ([], C.c_char_p),
+        "emb_populate_table_i32": ([C.c_uint32, C.c_uint64, i32p], C.c_int),
+        "emb_populate_table_f32": ([C.c_uint32, C.c_uint64, f32p, C.c_int], C.c_int),
+        "emb_populate_table_device": ([C.c_uint32, C.c_uint64, C.c_void_p, C.c_int, C.c_int, C.c_void_p], C.c_int),
+        "emb_table_set_row_base": ([C.c_uint32, C.c_uint64], C.c_int),
+        "emb_table_read": ([C.c_uint32, C.c_uint64, C.c_uint64, C.c_void_p], C.c_int),
+        "emb_table_info": ([C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_int), C.POINTER(C.c_void_p)], C.c_int),
+        "emb_free_table": ([C.c_uint32], C.c_int),
+        "emb_l2_persist": ([C.c_uint32, C.c_uint64, C.c_uint64, C.c_float, C.c_void_p], C.c_int),
+        "emb_lookup_ex": ([C.c_uint32, C.POINTER(u32p), C.POINTER(u32p), u32p, u32p, C.POINTER(f32p)], C.c_int),
+        "emb_plan_create": ([C.POINTER(EmbDevQuery), C.c_uint32, C.POINTER(C.c_void_p)], C.c_int),
+        "emb_plan_launch": ([C.c_void_p, C.c_void_p], C.c_int),
+        "emb_plan_destroy": ([C.c_void_p], None),
+        "emb_plan_bytes": ([C.c_void_p], C.c_uint64),
+        "emb_plan_grid": ([C.c_void_p], C.c_uint32),
+        "emb_lookup_device": ([C.POINTER(EmbDevQuery), C.c_uint32, C.c_void_p], C.c_int),
+        "emb_check_indices": ([], C.c_int),
+        "emb_reduce_partials": ([C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
+                                 C.c_uint64, C.c_int, C.c_void_p], C.c_int),
+        "emb_device_alloc": ([C.POINTER(C.c_void_p), C.c_size_t], C.c_int),
+        "emb_device_free": ([C.c_void_p], C.c_int),
+        "emb_host_alloc": ([C.POINTER(C.c_void_p), C.c_size_t], C.c_int),
+        "emb_host_free": ([C.c_void_p], C.c_int),
+        "emb_memcpy_h2d": ([C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p], C.c_int),
+        "emb_memcpy_d2h": ([C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p], C.c_int),
+        "emb_stream_sync": ([C.c_void_p], C.c_int),
+        "emb_ipc_export": ([C.c_void_p, C.POINTER(EmbIpcHandle)], C.c_int),
+        "emb_ipc_open": ([C.POINTER(EmbIpcHandle), C.POINTER(C.c_void_p)], C.c_int),
+        "emb_ipc_close": ([C.c_void_p], C.c_int),
+        "emb_last_timings": ([C.POINTER(EmbTimings)], C.c_int),
+        "emb_launch_count": ([], C.c_uint64),
+        "emb_set_unroll": ([C.c_int], C.c_int),
+    }
+    for name, (args, res) in sig.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = res
+    return lib
+
+
+EXPORTS = ("populate_mram", "lookup")
+
+
+def load(path: str | None = None) -> C.CDLL:
+    """CDLL the library (the reference does `CDLL("./emblib.so")` from its build directory)."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or os.environ.get("EMBLIB_SO", LIB_PATH)
+    if not os.path.exists(p):
+        raise EmbError(f"{p} not found: run __graft_entry__.build() / make -C pim-embedding-lookup_b200/csrc "
+                       "(there is no CPU fallback)")
+    lib = _declare(C.CDLL(os.path.abspath(p)))
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = "emblib") -> None:
+    if rc != 0:
+        msg = load().emb_last_error()
+        raise EmbError(f"{what} failed ({rc}): {msg.decode(errors='replace') if msg else ''}")
+
+
+def _p(a: np.ndarray, ty):
+    return a.ctypes.data_as(ty)
+
+
+def _ptr_array(arrs, ty):
+    return (ty * len(arrs))(*[_p(a, ty) for a in arrs])
+
+
+# ---------------------------------------------------------------------------------------------
+# Convenience layer (NumPy in, NumPy out).  Thin: every method is one C call.
+# ---------------------------------------------------------------------------------------------
+
+def configure(nr_tables, nr_cols, max_nr_batches=0, max_indices_per_batch=0, device=-1):
+    check(load().emb_configure(nr_tables, nr_cols, max_nr_batches, max_indices_per_batch, device), "emb_configure")
+
+
+def shutdown():
+    load().emb_shutdown()
+
+
+def shape() -> EmbShape:
+    s = EmbShape()
+    check(load().emb_get_shape(C.byref(s)), "emb_get_shape")
+    return s
+
+
+def populate_mram(table_id: int, column: np.ndarray, col: int, runtime: DpuRuntimeTotals | None = None) -> int:
+    """One (table, column) payload, as dlrm_dpu_pytorch.py:328-332 sends it."""
+    column = np.ascontiguousarray(column, dtype=np.int32)
+    rt = C.byref(runtime) if runtime is not None else None
+    return load().populate_mram(table_id, column.shape[0], col, _p(column, i32p), rt)
+
+
+def export_emb(tables_f32) -> int:
+    """The reference's export_emb (dlrm_dpu_pytorch.py:306-356) for a list of fp32 [R, D]
+    tables, minus the per-element Python: quantise + layout run on the GPU."""
+    lib = load()
+    for k, w in enumerate(tables_f32):
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        check(lib.emb_populate_table_f32(k, w.shape[0], _p(w, f32p), EMB_TABLE_FIXED), "emb_populate_table_f32")
+    return len(tables_f32)
+
+
+def populate_table_i32(table_id: int, rows_i32: np.ndarray):
+    a = np.ascontiguousarray(rows_i32, dtype=np.int32)
+    check(load().emb_populate_table_i32(table_id, a.shape[0], _p(a, i32p)), "emb_populate_table_i32")
+
+
+def populate_table_f32(table_id: int, w: np.ndarray, kind: int = EMB_TABLE_FIXED):
+    a = np.ascontiguousarray(w, dtype=np.float32)
+    check(load().emb_populate_table_f32(table_id, a.shape[0], _p(a, f32p), kind), "emb_populate_table_f32")
+
+
+def table_read(table_id: int, row0: int, n: int, dtype=np.int32) -> np.ndarray:
+    D = shape().nr_cols
+    out = np.empty((n, D), dtype=dtype)
+    check(load().emb_table_read(table_id, row0, n, out.ctypes.data), "emb_table_read")
+    return out
+
+
+def lookup(indices, offsets, handle=None, latency_print=0):
+    """The reference call: shapes come from the configured NR_TABLES/MAX_NR_BATCHES/...;
+    indices[t] uint32 [B*P], offsets[t] uint32 [B].  Returns list of fp32 [B, D]."""
+    s = shape()
+    T, B, D = s.nr_tables, s.max_nr_batches, s.nr_cols
+    idx = [np.ascontiguousarray(i, dtype=np.uint32) for i in indices]
+    off = [np.ascontiguousarray(o, dtype=np.uint32) for o in offsets]
+    assert len(idx) == T and len(off) == T
+    for t in range(T):
+        assert idx[t].size >= B * s.max_indices_per_batch and off[t].size >= B
+    res = [np.empty((B, D), dtype=np.float32) for _ in range(T)]
+    load().lookup(_ptr_array(idx, u32p), _ptr_array(off, u32p), _ptr_array(res, f32p), handle, latency_print)
+    return res
+
+
+def lookup_ex(indices, offsets, results=None):
+    """Explicit lengths, variable pooling (emb_lookup_ex).  Returns list of fp32 [B_t, D]."""
+    D = shape().nr_cols
+    idx = [np.ascontiguousarray(i, dtype=np.uint32) for i in indices]
+    off = [np.ascontiguousarray(o, dtype=np.uint32) for o in offsets]
+    T = len(idx)
+    il = np.asarray([i.size for i in idx], dtype=np.uint32)
+    nb = np.asarray([o.size for o in off], dtype=np.uint32)
+    res = results if results is not None else [np.empty((int(nb[t]), D), dtype=np.float32) for t in range(T)]
+    check(load().emb_lookup_ex(T, _ptr_array(idx, u32p), _ptr_array(off, u32p), _p(il, u32p), _p(nb, u32p),
+                               _ptr_array(res, f32p)), "emb_lookup_ex")
+    return res
+
+
+def last_timings() -> EmbTimings:
+    t = EmbTimings()
+    check(load().emb_last_timings(C.byref(t)), "emb_last_timings")
+    return t
+
+
+def launch_count() -> int:
+    return int(load().emb_launch_count())
+
+
+class Plan:
+    """Device-resident lookup: descriptors uploaded once, each launch() is one kernel.
+
+    `queries` is a list of dicts with keys table_id, indices, offsets, out (objects with
+    .data_ptr(), e.g. torch CUDA tensors, or raw ints), optional indices_len, nr_batches,
+    out_stride, flags, bags_per_rank, out_peer.  The plan keeps references to the tensors."""
+
+    def __init__(self, queries):
+        self._keep = queries
+        n = len(queries)
+        arr = (EmbDevQuery * n)()
+        for i, q in enumerate(queries):
+            e = arr[i]
+            e.table_id = q["table_id"]
+            e.indices = _addr(q["indices"])
+            e.offsets = _addr(q["offsets"])
+            e.out = _addr(q.get("out"))
+            e.nr_batches = q.get("nr_batches", _numel(q["offsets"]))
+            e.indices_len = q.get("indices_len", _numel(q["indices"]))
+            e.flags = q.get("flags", 0)
+            e.out_stride = q.get("out_stride", 0)
+            e.bags_per_rank = q.get("bags_per_rank", 0)
+            for r, p in enumerate(q.get("out_peer", ())):
+                e.out_peer[r] = _addr(p)
+        h = C.c_void_p()
+        check(load().emb_plan_create(arr, n, C.byref(h)), "emb_plan_create")
+        self._h = h
+        self.bytes = int(load().emb_plan_bytes(h))
+        self.grid = int(load().emb_plan_grid(h))
+
+    def launch(self, stream=None):
+        rc = load().emb_plan_launch(self._h, _stream(stream))
+        if rc:
+            check(rc, "emb_plan_launch")
+
+    def close(self):
+        if self._h:
+            load().emb_plan_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _addr(x):
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return x
+    return int(x.data_ptr())
+
+
+def _numel(x):
+    return int(x.numel()) if hasattr(x, "numel") else int(x.size)
+
+
+def _stream(s):
+    if s is None:
+        return None
+    if isinstance(s, int):
+        return s
+    return int(s.cuda_stream)  # torch.cuda.Stream

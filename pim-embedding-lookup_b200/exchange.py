@@ -1,0 +1,147 @@
+"""Pooled-output exchange between the GPUs of one box: table-parallel -> batch-parallel.
+
+Same meaning as the DLRM fork's `alltoall` (PIM-dlrm-new/extend_distributed.py:389-426,
+called from dlrm_dpu_pytorch.py:804): rank r pools ALL B samples for ITS tables and every
+sample's pooled rows must end up on the data-parallel rank that owns the sample
+(samples [r*B/N, (r+1)*B/N) on rank r).
+
+Two transports:
+
+* `PeerSlabs` (fused): every rank owns one output slab [B/N, T_global, D] in cudaMalloc
+  memory, exported with CUDA IPC and mapped by all peers.  The pooling kernel itself stores
+  bag b of table t at slab[b // (B/N)][b % (B/N), t, :] (emb_dev_query.bags_per_rank /
+  out_peer, include/emb_b200.h), so the rows cross NVLink as they are produced and the only
+  collective left is the completion barrier.
+* `nccl_all_to_all`: pool into a local [N, B/N, T_local, D] buffer, one
+  `all_to_all_single`, comparator and fallback.
+
+One process per GPU; `torch.distributed` (NCCL on GPUs, gloo in the CPU tests) is the
+plumbing.  Host-side layout arithmetic lives in free functions so it is testable without
+a GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from .dputypes import EmbIpcHandle
+
+
+def bags_per_rank(global_bags: int, world: int) -> int:
+    if global_bags % world:
+        raise ValueError(f"global batch {global_bags} must divide over {world} ranks")
+    return global_bags // world
+
+
+def table_ranges(tables_per_rank):
+    """tables_per_rank[r] = number of tables rank r owns -> (first_global_table[r], T_global)."""
+    first = np.concatenate([[0], np.cumsum(tables_per_rank)]).astype(np.int64)
+    return first[:-1].tolist(), int(first[-1])
+
+
+def a2a_split_sizes(global_bags, tables_per_rank, dim, rank):
+    """Element counts for all_to_all_single of a [N, B/N, T_local, D] send buffer
+    (extend_distributed.py:394-405: table_split_lengths / batch_split_lengths)."""
+    world = len(tables_per_rank)
+    per = bags_per_rank(global_bags, world)
+    send = [per * tables_per_rank[rank] * dim] * world
+    recv = [per * tables_per_rank[r] * dim for r in range(world)]
+    return send, recv
+
+
+def assemble_received(recv_flat, global_bags, tables_per_rank, dim):
+    """Received chunks (rank-major, each [B/N, T_r, D]) -> [B/N, T_global, D]."""
+    import torch
+    world = len(tables_per_rank)
+    per = bags_per_rank(global_bags, world)
+    parts, pos = [], 0
+    for r in range(world):
+        n = per * tables_per_rank[r] * dim
+        parts.append(recv_flat[pos:pos + n].view(per, tables_per_rank[r], dim))
+        pos += n
+    return torch.cat(parts, dim=1)
+
+
+def nccl_all_to_all(send, global_bags, tables_per_rank, dim, group=None):
+    """send: [N, B/N, T_local, D] contiguous (slice r goes to rank r).  Returns [B/N, T_global, D]."""
+    import torch
+    import torch.distributed as dist
+    rank = dist.get_rank(group)
+    s, r = a2a_split_sizes(global_bags, tables_per_rank, dim, rank)
+    recv = torch.empty(sum(r), dtype=send.dtype, device=send.device)
+    dist.all_to_all_single(recv, send.reshape(-1), output_split_sizes=r, input_split_sizes=s, group=group)
+    return assemble_received(recv, global_bags, tables_per_rank, dim)
+
+
+class _DevView:
+    """Raw device pointer as a __cuda_array_interface__ object (for torch.as_tensor)."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class PeerSlabs:
+    """Symmetric output slabs mapped across all ranks of `group` (one node, NVLink/NVSwitch)."""
+
+    def __init__(self, global_bags, tables_per_rank, dim, group=None, n_buffers=1):
+        import torch
+        import torch.distributed as dist
+        from . import emblib
+        self.lib = emblib.load()
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        assert len(tables_per_rank) == self.world
+        self.per = bags_per_rank(global_bags, self.world)
+        self.first_table, self.t_global = table_ranges(tables_per_rank)
+        self.dim = dim
+        self.stride = self.t_global * dim  # elements between consecutive samples in a slab
+        self.n_buffers = n_buffers
+        self.slab_bytes = self.per * self.stride * 4
+        self._mine = C.c_void_p()
+        emblib.check(self.lib.emb_device_alloc(C.byref(self._mine), self.slab_bytes * n_buffers), "emb_device_alloc")
+        h = EmbIpcHandle()
+        emblib.check(self.lib.emb_ipc_export(self._mine, C.byref(h)), "emb_ipc_export")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(h.bytes), group=group)
+        self.base = []
+        for r, hb in enumerate(handles):
+            if r == self.rank:
+                self.base.append(int(self._mine.value))
+                continue
+            ph = EmbIpcHandle()
+            C.memmove(ph.bytes, hb, len(hb))
+            p = C.c_void_p()
+            emblib.check(self.lib.emb_ipc_open(C.byref(ph), C.byref(p)), "emb_ipc_open")
+            self.base.append(int(p.value))
+        self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+
+    def out_peer(self, local_table: int, buffer: int = 0):
+        """Per-rank destination of this rank's `local_table`: pass as emb_dev_query.out_peer with
+        out_stride = self.stride and bags_per_rank = self.per."""
+        col = (self.first_table[self.rank] + local_table) * self.dim * 4
+        return [b + buffer * self.slab_bytes + col for b in self.base]
+
+    def local(self, buffer: int = 0, dtype="float32"):
+        """This rank's slab as a torch tensor [B/N, T_global, D] (no copy)."""
+        import torch
+        v = _DevView(self.base[self.rank] + buffer * self.slab_bytes, (self.per, self.t_global, self.dim),
+                     "<f4" if dtype == "float32" else "<i4")
+        return torch.as_tensor(v, device="cuda")
+
+    def barrier(self):
+        """Stream-ordered completion barrier: when it has run on this rank's current stream, every
+        rank's pooling kernel (enqueued before its own barrier call) has finished storing."""
+        import torch.distributed as dist
+        dist.all_reduce(self._flag, group=self.group)
+
+    def close(self):
+        for r, b in enumerate(self.base):
+            if r != self.rank and b:
+                self.lib.emb_ipc_close(C.c_void_p(b))
+        if self._mine:
+            self.lib.emb_device_free(self._mine)
+            self._mine = C.c_void_p()
+        self.base = []
