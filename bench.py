@@ -60,7 +60,9 @@ def parse_args():
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--variant", type=int, default=0, help="kernel variant (emb_set_tuning); 0 = default")
     ap.add_argument("--unroll", type=int, default=0)
+    ap.add_argument("--mult", type=int, default=0)
     return ap.parse_args()
 
 
@@ -269,9 +271,9 @@ def run_b200(args, w):
     lib = emblib.load()
     T, R, D, B = w["T"], w["R"], w["D"], w["B"]
     emblib.configure(T, D, 0, 0, device=local)
-    if args.unroll:
-        emblib.check(lib.emb_set_unroll(args.unroll))
-    stream = torch.cuda.current_stream()
+    emblib.check(lib.emb_set_tuning(args.variant, args.unroll, args.mult))
+    stream = torch.cuda.Stream()  # a real stream: events and launches are ordered on it
+    torch.cuda.set_stream(stream)
 
     # tables: int32 fixed point as export_emb makes them, generated on the device
     gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
@@ -426,6 +428,7 @@ def run_b200(args, w):
                        "l2": f"inputs larger than L2: tables {T * R * D * 4 / 1e9:.2f} GB per GPU, "
                              f"{N_BATCHES} rotating index batches",
                        "exchange": ("none (1 GPU)" if world == 1 else args.exchange),
+                       "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult},
                        "parallelism": f"table-wise x{world}, pooled rows to the sample's rank"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms,

@@ -250,6 +250,12 @@ int emb_last_timings(emb_timings *out);
 uint64_t emb_launch_count(void);
 /* Tuning knob, mostly for measurement: rows in flight per sub-warp (4 or 8); 0 = default. */
 int emb_set_unroll(int unroll);
+/* All tuning knobs at once (0 = default): variant 1 = one bag per sub-warp (index-ordered
+ * adds; always used when a float table is in the launch), 2 = load-balanced pieces of the
+ * index stream with shared-memory int32 accumulators; unroll as above; bags_mult = bags per
+ * CTA in units of sub-warps per CTA (1, 2 or 4; variant 2 only).  Takes effect for plans
+ * created and host-pointer lookups issued afterwards. */
+int emb_set_tuning(int variant, int unroll, int bags_mult);
 
 #ifdef __cplusplus
 }

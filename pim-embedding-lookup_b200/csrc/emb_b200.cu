@@ -63,7 +63,10 @@ struct Ctx {
     uint32_t desc_cap = 0;
 
     emb_timings last = {0, 0, 0, 0, 0, 0, 0};
-    int unroll = 0;
+    // tuning knobs (emb_set_tuning); 0 = default
+    int unroll = 0;     // rows in flight per sub-warp: 4 or 8
+    int variant = 0;    // 1 = bag-per-sub-warp kernel, 2 = load-balanced kernel
+    int bags_mult = 0;  // load-balanced kernel: bags per CTA = mult * sub-warps per CTA (1, 2, 4)
 };
 
 Ctx g;
@@ -255,39 +258,88 @@ uint32_t lanes_for_dim(uint32_t D)
     return l;
 }
 
-uint32_t bags_per_cta(uint32_t D)
-{
-    uint32_t l = lanes_for_dim(D);
-    return l ? emb::kThreads / l : emb::kThreads / 32;
-}
+/* Which kernel pools a launch, decided when the descriptors are built (the CTA -> bag
+ * mapping depends on it). */
+struct Variant {
+    int kind;      // 0 generic, 1 bag-per-sub-warp (any table kind), 2 load-balanced (int32 only)
+    int unroll;    // K
+    int mult;      // bags per CTA / sub-warps per CTA
+    uint32_t bags; // bags per CTA
+};
 
-template <int UNROLL>
-void launch_lanes(uint32_t lanes, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+Variant pick_variant(bool any_float)
 {
-    switch (lanes) {
-    case 1: emb::bag_sum_kernel<1, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
-    case 2: emb::bag_sum_kernel<2, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
-    case 4: emb::bag_sum_kernel<4, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
-    case 8: emb::bag_sum_kernel<8, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
-    case 16: emb::bag_sum_kernel<16, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
-    default: emb::bag_sum_kernel<32, UNROLL><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err); break;
+    Variant v;
+    uint32_t D = g.shape.nr_cols;
+    uint32_t lanes = lanes_for_dim(D);
+    if (!lanes) {
+        v.kind = 0;
+        v.unroll = 1;
+        v.mult = 1;
+        v.bags = emb::kThreads / 32;
+        return v;
     }
+    v.kind = g.variant ? g.variant : 2;
+    if (any_float)
+        v.kind = 1;  // fp32 sums keep index order (embedding_lookup_idx.cc:33-77)
+    v.unroll = g.unroll ? g.unroll : (v.kind == 2 ? 8 : (lanes >= 16 ? 8 : 4));
+    v.mult = (v.kind == 2) ? (g.bags_mult ? g.bags_mult : 1) : 1;
+    v.bags = emb::kThreads / lanes * v.mult;
+    return v;
 }
 
-int launch_bag_sum(const BagDesc *d_descs, uint32_t n, uint32_t grid, cudaStream_t s)
+template <int LANES>
+void launch_ordered(int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+{
+    if (unroll == 8)
+        emb::bag_sum_kernel<LANES, 8><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+    else
+        emb::bag_sum_kernel<LANES, 4><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+}
+
+template <int LANES, int K, int MINB>
+void launch_balanced_k(int mult, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+{
+    constexpr int SUB = emb::kThreads / LANES;
+    if (mult == 4)
+        emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+    else if (mult == 2)
+        emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+    else
+        emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+}
+
+template <int LANES>
+void launch_balanced(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+{
+    if (v.unroll == 8)
+        launch_balanced_k<LANES, 8, 4>(v.mult, grid, s, d, n);
+    else
+        launch_balanced_k<LANES, 4, 6>(v.mult, grid, s, d, n);
+}
+
+template <int LANES>
+void launch_for_lanes(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+{
+    if (v.kind == 2)
+        launch_balanced<LANES>(v, grid, s, d, n);
+    else
+        launch_ordered<LANES>(v.unroll, grid, s, d, n);
+}
+
+int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_t grid, cudaStream_t s)
 {
     if (grid == 0)
         return EMB_OK;
     uint32_t D = g.shape.nr_cols;
-    uint32_t lanes = lanes_for_dim(D);
-    if (!lanes) {
-        emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, D, g.d_err);
-    } else {
-        int unroll = g.unroll ? g.unroll : (lanes >= 16 ? 8 : 4);
-        if (unroll == 8)
-            launch_lanes<8>(lanes, grid, s, d_descs, n);
-        else
-            launch_lanes<4>(lanes, grid, s, d_descs, n);
+    switch (v.kind ? lanes_for_dim(D) : 0) {
+    case 0: emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, D, g.d_err); break;
+    case 1: launch_for_lanes<1>(v, grid, s, d_descs, n); break;
+    case 2: launch_for_lanes<2>(v, grid, s, d_descs, n); break;
+    case 4: launch_for_lanes<4>(v, grid, s, d_descs, n); break;
+    case 8: launch_for_lanes<8>(v, grid, s, d_descs, n); break;
+    case 16: launch_for_lanes<16>(v, grid, s, d_descs, n); break;
+    default: launch_for_lanes<32>(v, grid, s, d_descs, n); break;
     }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
@@ -295,7 +347,7 @@ int launch_bag_sum(const BagDesc *d_descs, uint32_t n, uint32_t grid, cudaStream
 }
 
 /* Fill one descriptor from a query; returns the number of CTAs it needs. */
-int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, uint32_t *chunks)
+int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, uint32_t per, uint32_t *chunks)
 {
     if (q.table_id >= g.tables.size() || !g.tables[q.table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", q.table_id);
@@ -345,7 +397,6 @@ int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, uint32_t
     if (vec)
         flags |= emb::kDescVecStore;
     d->flags = flags;
-    uint32_t per = bags_per_cta(D);
     *chunks = (q.nr_batches + per - 1) / per;
     return EMB_OK;
 }
@@ -357,6 +408,7 @@ struct emb_plan {
     BagDesc *d = nullptr;
     uint32_t grid = 0;
     uint64_t bytes = 0;
+    Variant variant = {0, 1, 1, 8};
 };
 
 extern "C" {
@@ -395,6 +447,20 @@ int emb_set_unroll(int unroll)
     return EMB_OK;
 }
 
+int emb_set_tuning(int variant, int unroll, int bags_mult)
+{
+    if (variant < 0 || variant > 2)
+        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp) or 2 (load-balanced)");
+    if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4)
+        return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2 or 4");
+    int rc = emb_set_unroll(unroll);
+    if (rc)
+        return rc;
+    g.variant = variant;
+    g.bags_mult = bags_mult;
+    return EMB_OK;
+}
+
 void emb_shutdown(void)
 {
     std::lock_guard<std::mutex> lk(g_mu);
@@ -420,9 +486,11 @@ void emb_shutdown(void)
         if (g.stream_out)
             cudaStreamDestroy(g.stream_out);
     }
-    int unroll = g.unroll;
+    int unroll = g.unroll, variant = g.variant, bags_mult = g.bags_mult;
     g = Ctx();
     g.unroll = unroll;
+    g.variant = variant;
+    g.bags_mult = bags_mult;
 }
 
 /* ---------------------------------------------------------------- tables -------------- */
@@ -620,9 +688,13 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
     p->h.resize(n);
     uint64_t chunk = 0;
     const uint64_t D = g.shape.nr_cols;
+    bool any_float = false;
+    for (uint32_t i = 0; i < n; i++)
+        any_float |= queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].kind == EMB_TABLE_FLOAT;
+    p->variant = pick_variant(any_float);
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
-        if ((rc = fill_desc(queries[i], &p->h[i], (uint32_t)chunk, &c))) {
+        if ((rc = fill_desc(queries[i], &p->h[i], (uint32_t)chunk, p->variant.bags, &c))) {
             delete p;
             return rc;
         }
@@ -650,7 +722,7 @@ int emb_plan_launch(emb_plan *plan, void *stream)
 {
     if (!plan)
         return fail(EMB_EINVAL, "NULL plan");
-    return launch_bag_sum(plan->d, (uint32_t)plan->h.size(), plan->grid,
+    return launch_bag_sum(plan->variant, plan->d, (uint32_t)plan->h.size(), plan->grid,
                           stream ? (cudaStream_t)stream : g.stream);
 }
 
@@ -762,6 +834,10 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         g.desc_cap = T;
     }
 
+    bool any_float = false;
+    for (uint32_t t = 0; t < T; t++)
+        any_float |= g.tables[t].kind == EMB_TABLE_FLOAT;
+    const Variant variant = pick_variant(any_float);
     cudaStream_t s = g.stream;
     CU(cudaEventRecord(g.ev[0], s));
     uint64_t io = 0, oo = 0, chunk = 0, h2d = 0;
@@ -776,7 +852,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         q.out = g.d_out + oo * D;
         q.out_stride = D;
         uint32_t c = 0;
-        if ((rc = fill_desc(q, &g.h_descs[t], (uint32_t)chunk, &c)))
+        if ((rc = fill_desc(q, &g.h_descs[t], (uint32_t)chunk, variant.bags, &c)))
             return rc;
         chunk += c;
         if (indices_len[t])
@@ -791,7 +867,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         return fail(EMB_EINVAL, "too many bags for one launch");
     CU(cudaMemcpyAsync(g.d_descs, g.h_descs, T * sizeof(BagDesc), cudaMemcpyHostToDevice, s));
     CU(cudaEventRecord(g.ev[1], s));
-    if ((rc = launch_bag_sum(g.d_descs, T, (uint32_t)chunk, s)))
+    if ((rc = launch_bag_sum(variant, g.d_descs, T, (uint32_t)chunk, s)))
         return rc;
     CU(cudaEventRecord(g.ev[2], s));
     oo = 0;

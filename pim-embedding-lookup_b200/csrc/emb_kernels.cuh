@@ -240,6 +240,193 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__r
 }
 
 /*
+ * Load-balanced sum-pool kernel for int32 fixed-point tables, D = 4*LANES columns.
+ *
+ * bag_sum_kernel above gives every bag to one sub-warp, so with ragged bags (pooling 1..20)
+ * a warp runs as long as its longest bag and the short bags' lanes idle -- fewer row loads in
+ * flight than the memory system needs.  Here the CTA's bags only define a window of the index
+ * stream; the window is cut into pieces of K consecutive lookups and the pieces are dealt
+ * round-robin to the sub-warps.  A sub-warp issues its K row loads back to back (every lane
+ * busy whatever the bag lengths), then walks the K rows in order, adding into registers and
+ * flushing to a per-CTA shared-memory accumulator whenever the walk crosses a bag boundary.
+ * int32 wrap-around addition (emb_dpu_lookup.c:114) is associative and commutative, so the
+ * shared-memory atomics reproduce the reference's sums bit for bit in any order.
+ *
+ * BAGS bags per CTA (a multiple of kThreads/LANES); the window is streamed through the
+ * kIdxStage-entry staging buffer in passes, so bags of any length work.
+ * Requires monotone offsets inside the CTA's chunk; a chunk that is not monotone (bags that
+ * overlap, which lookup() permits) is pooled bag by bag instead.
+ */
+template <int LANES, int K, int BAGS, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
+bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__restrict__ err_flag)
+{
+    constexpr int SUB = kThreads / LANES;  // sub-warps per CTA
+    constexpr int D = LANES * 4;
+    static_assert(BAGS % SUB == 0, "BAGS must be a multiple of the sub-warp count");
+    __shared__ uint32_t s_off[BAGS + 1];
+    __shared__ uint32_t s_idx[kIdxStage];
+    __shared__ __align__(16) uint32_t s_acc[BAGS * D];
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
+    const BagDesc *__restrict__ d = descs + q;
+
+    const uint32_t B = d->nr_batches;
+    const uint32_t ilen = d->indices_len;
+    const uint32_t b0 = (blockIdx.x - d->chunk_begin) * BAGS;
+    const uint32_t nb = min((uint32_t)BAGS, B - b0);
+    const uint32_t *__restrict__ g_idx = d->indices;
+    const uint32_t *__restrict__ g_off = d->offsets;
+
+    for (uint32_t i = tid; i <= nb; i += kThreads) {
+        uint32_t b = b0 + i;
+        uint32_t v = (b == 0) ? 0u : (b >= B ? ilen : ldg_stream_u32(g_off + b));
+        s_off[i] = min(v, ilen);
+    }
+    for (uint32_t i = tid; i < BAGS * D / 4; i += kThreads)
+        reinterpret_cast<uint4 *>(s_acc)[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    bool nonmono = false;
+    for (uint32_t i = tid; i < nb; i += kThreads)
+        nonmono |= s_off[i] > s_off[i + 1];
+    const bool ordered = __syncthreads_or(nonmono);
+
+    const uint32_t flags = d->flags;
+    const uint32_t rows = d->rows;
+    const uint32_t row_base = d->row_base;
+    const uint32_t sub = tid / LANES;
+    const uint32_t lane = tid % LANES;
+    const uint4 *__restrict__ table = reinterpret_cast<const uint4 *>(d->table) + lane;
+    bool bad = false;
+
+    if (!ordered) {
+        const uint32_t wlo = s_off[0], whi = s_off[nb];
+        for (uint32_t base = wlo; base < whi; base += kIdxStage) {
+            const uint32_t n = min((uint32_t)kIdxStage, whi - base);
+            if (base != wlo)
+                __syncthreads();  // everyone is done with the previous pass's s_idx
+            for (uint32_t i = tid; i < n; i += kThreads)
+                s_idx[i] = ldg_stream_u32(g_idx + base + i);
+            __syncthreads();
+            for (uint32_t c = sub * K; c < n; c += SUB * K) {
+                const uint32_t m = min((uint32_t)K, n - c);
+                uint32_t r[K];
+#pragma unroll
+                for (int u = 0; u < K; u++) {
+                    uint32_t id = 0xffffffffu;
+                    if ((uint32_t)u < m) {
+                        id = s_idx[c + u] - row_base;  // unsigned: rows below the shard wrap high
+                        bad |= id >= rows;
+                    }
+                    r[u] = id;
+                }
+                uint4 v[K];
+#pragma unroll
+                for (int u = 0; u < K; u++) {
+                    v[u] = make_uint4(0u, 0u, 0u, 0u);
+                    if (r[u] < rows)
+                        v[u] = ldg_row16(table + (size_t)r[u] * LANES);
+                }
+                // bag of the piece's first lookup: last i with s_off[i] <= p (skips empty bags)
+                const uint32_t p0 = base + c;
+                uint32_t lo = 0, hi = nb;
+                while (hi - lo > 1) {
+                    uint32_t mid = (lo + hi) >> 1;
+                    if (s_off[mid] <= p0)
+                        lo = mid;
+                    else
+                        hi = mid;
+                }
+                uint32_t bag = lo, bag_end = s_off[lo + 1];
+                uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+                for (int u = 0; u < K; u++) {
+                    if ((uint32_t)u < m) {
+                        if (p0 + u >= bag_end) {  // crossed into a later bag: flush the partial sum
+                            uint32_t *a = s_acc + bag * D + lane * 4;
+                            atomicAdd(a + 0, acc.x);
+                            atomicAdd(a + 1, acc.y);
+                            atomicAdd(a + 2, acc.z);
+                            atomicAdd(a + 3, acc.w);
+                            acc = make_uint4(0u, 0u, 0u, 0u);
+                            do {
+                                bag++;
+                                bag_end = s_off[bag + 1];
+                            } while (p0 + u >= bag_end);
+                        }
+                        acc.x += v[u].x;
+                        acc.y += v[u].y;
+                        acc.z += v[u].z;
+                        acc.w += v[u].w;
+                    }
+                }
+                uint32_t *a = s_acc + bag * D + lane * 4;
+                atomicAdd(a + 0, acc.x);
+                atomicAdd(a + 1, acc.y);
+                atomicAdd(a + 2, acc.z);
+                atomicAdd(a + 3, acc.w);
+            }
+        }
+    } else {
+        // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
+        for (uint32_t bag = sub; bag < nb; bag += SUB) {
+            const uint32_t start = s_off[bag], end = s_off[bag + 1];
+            uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+            for (uint32_t p = start; p < end; p++) {
+                uint32_t id = __ldg(g_idx + p) - row_base;
+                if (id < rows) {
+                    uint4 v = ldg_row16(table + (size_t)id * LANES);
+                    acc.x += v.x;
+                    acc.y += v.y;
+                    acc.z += v.z;
+                    acc.w += v.w;
+                } else {
+                    bad = true;
+                }
+            }
+            reinterpret_cast<uint4 *>(s_acc)[bag * LANES + lane] = acc;
+        }
+    }
+    if (bad && !(flags & kDescSharded))
+        atomicOr(err_flag, 1u);
+    __syncthreads();
+
+    const uint32_t bpr = d->bags_per_rank;
+    const uint32_t out_stride = d->out_stride;
+#pragma unroll
+    for (int it = 0; it < BAGS / SUB; it++) {
+        const uint32_t bag = it * SUB + sub;
+        if (bag >= nb)
+            break;
+        uint4 o = reinterpret_cast<const uint4 *>(s_acc)[bag * LANES + lane];
+        if (!(flags & kDescRaw))  // post_process, emb_host.h:210
+            o = make_uint4(__float_as_uint(dequant(o.x)), __float_as_uint(dequant(o.y)),
+                           __float_as_uint(dequant(o.z)), __float_as_uint(dequant(o.w)));
+        const uint32_t b = b0 + bag;
+        uint32_t *base;
+        uint32_t row;
+        if (bpr) {
+            uint32_t rk = b / bpr;
+            base = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
+            row = b - rk * bpr;
+        } else {
+            base = reinterpret_cast<uint32_t *>(d->out);
+            row = b;
+        }
+        uint32_t *dst = base + (size_t)row * out_stride + lane * 4;
+        if (flags & kDescVecStore) {
+            stg_stream16(dst, o);
+        } else {
+            dst[0] = o.x;
+            dst[1] = o.y;
+            dst[2] = o.z;
+            dst[3] = o.w;
+        }
+    }
+}
+
+/*
  * Any embedding dimension (D not a multiple of 4, or above 128): a warp per bag, lanes
  * stride over the columns with 4-byte loads.  Correctness path, not a tuned one.
  */

@@ -17,11 +17,68 @@
  */
 #include "emb_b200.h"
 
+#include <dlfcn.h>
+#include <libgen.h>
+#include <limits.h>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
+#include <unistd.h>
+
+/* The library is loaded by path like the reference's callers do (CDLL("./emblib.so"),
+ * dlrm_dpu_pytorch.py:123-124): next to this binary, or $EMBLIB_SO.  (Its soname is
+ * `emb_host`, upmem/Makefile:54 -- the name of this binary -- so a DT_NEEDED link would
+ * resolve to the executable itself.) */
+static struct dpu_set_t *(*p_populate_mram)(uint32_t, uint64_t, uint32_t, int32_t *, dpu_runtime_totals *);
+static int32_t *(*p_lookup)(uint32_t **, uint32_t **, float **, void *, int64_t);
+static int (*p_emb_configure)(uint32_t, uint32_t, uint32_t, uint32_t, int);
+static const char *(*p_emb_last_error)(void);
+static int (*p_emb_last_timings)(emb_timings *);
+static void (*p_emb_shutdown)(void);
+#define populate_mram p_populate_mram
+#define lookup p_lookup
+#define emb_configure p_emb_configure
+#define emb_last_error p_emb_last_error
+#define emb_last_timings p_emb_last_timings
+#define emb_shutdown p_emb_shutdown
+
+static void load_library(const char *argv0)
+{
+    char path[PATH_MAX], self[PATH_MAX];
+    const char *env = getenv("EMBLIB_SO");
+    if (env && *env) {
+        snprintf(path, sizeof path, "%s", env);
+    } else {
+        ssize_t n = readlink("/proc/self/exe", self, sizeof self - 1);
+        if (n <= 0)
+            snprintf(self, sizeof self, "%s", argv0);
+        else
+            self[n] = 0;
+        snprintf(path, sizeof path, "%s/emblib.so", dirname(self));
+    }
+    void *h = dlopen(path, RTLD_NOW | RTLD_GLOBAL);
+    if (!h) {
+        fprintf(stderr, "emb_host: %s\n", dlerror());
+        exit(1);
+    }
+#define SYM(name)                                                      \
+    do {                                                               \
+        *(void **)(&p_##name) = dlsym(h, #name);                       \
+        if (!p_##name) {                                               \
+            fprintf(stderr, "emb_host: %s lacks %s\n", path, #name);   \
+            exit(1);                                                   \
+        }                                                              \
+    } while (0)
+    SYM(populate_mram);
+    SYM(lookup);
+    SYM(emb_configure);
+    SYM(emb_last_error);
+    SYM(emb_last_timings);
+    SYM(emb_shutdown);
+#undef SYM
+}
 
 static uint64_t rng_state = 0x9E3779B97F4A7C15ull;
 
@@ -92,6 +149,7 @@ int main(int argc, char **argv)
         }
         i++;
     }
+    load_library(argv[0]);
     if (!T || !D || !B || !P || !R || iters < 1) {
         fprintf(stderr, "emb_host: tables, cols, rows, batches, pooling, iters must be > 0\n");
         return 2;

@@ -86,6 +86,7 @@ def _declare(lib):
         "emb_last_timings": ([C.POINTER(EmbTimings)], C.c_int),
         "emb_launch_count": ([], C.c_uint64),
         "emb_set_unroll": ([C.c_int], C.c_int),
+        "emb_set_tuning": ([C.c_int, C.c_int, C.c_int], C.c_int),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, name)
@@ -281,4 +282,7 @@ def _stream(s):
         return None
     if isinstance(s, int):
         return s
-    return int(s.cuda_stream)  # torch.cuda.Stream
+    h = int(s.cuda_stream)  # torch.cuda.Stream
+    # NULL means "the library's own stream" in the C ABI; torch's default stream has handle 0,
+    # so name it explicitly: cudaStreamLegacy == (cudaStream_t)0x1
+    return h if h else 1

@@ -110,19 +110,47 @@ def test_lookup_ex_matches_oracle(emblib, D):
     assert emblib.load().emb_check_indices() == 0
 
 
-@pytest.mark.parametrize("unroll", [4, 8])
-def test_unroll_variants_agree(emblib, unroll):
+TUNINGS = [(1, 4, 0), (1, 8, 0), (2, 4, 1), (2, 8, 1), (2, 4, 2), (2, 8, 4)]
+
+
+@pytest.mark.parametrize("tuning", TUNINGS, ids=[f"v{v}k{k}m{m}" for v, k, m in TUNINGS])
+@pytest.mark.parametrize("D", [4, 16, 64, 128])
+def test_kernel_variants_agree(emblib, tuning, D):
+    """Every kernel variant (bag per sub-warp / load-balanced, rows in flight, bags per CTA)."""
     rng = np.random.default_rng(5)
-    emblib.configure(1, 16)
-    emblib.load().emb_set_unroll(unroll)
+    emblib.configure(2, D)
+    assert emblib.load().emb_set_tuning(*tuning) == 0
     try:
-        q = rng.integers(-2**31, 2**31, size=(4096, 16), dtype=np.int64).astype(np.int32)
-        emblib.populate_table_i32(0, q)
-        i, o = ragged(rng, 4096, 5000, 33)
-        got = emblib.lookup_ex([i], [o])[0]
-        assert np.array_equal(bits(got), bits(eo.lookup_rows([q], [i], [o])[0]))
+        tabs, idxs, offs = [], [], []
+        for t, (R, B, L) in enumerate([(4096, 5000, 33), (100, 777, 300)]):
+            q = rng.integers(-2**31, 2**31, size=(R, D), dtype=np.int64).astype(np.int32)
+            emblib.populate_table_i32(t, q)
+            i, o = ragged(rng, R, B, L)
+            tabs.append(q), idxs.append(i), offs.append(o)
+        got = emblib.lookup_ex(idxs, offs)
+        want = eo.lookup_rows(tabs, idxs, offs)
+        for t in range(2):
+            assert np.array_equal(bits(got[t]), bits(want[t])), t
     finally:
-        emblib.load().emb_set_unroll(0)
+        emblib.load().emb_set_tuning(0, 0, 0)
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+def test_overlapping_and_backward_bags(emblib, variant):
+    """lookup() accepts any offsets: bag i covers [offsets[i], offsets[i+1]) on its own
+    (emb_dpu_lookup.c:109-116), so bags may overlap or be empty because they run backwards."""
+    rng = np.random.default_rng(11)
+    emblib.configure(1, 16)
+    assert emblib.load().emb_set_tuning(variant, 0, 0) == 0
+    try:
+        q = rng.integers(-2**31, 2**31, size=(300, 16), dtype=np.int64).astype(np.int32)
+        emblib.populate_table_i32(0, q)
+        idx = rng.integers(0, 300, size=4000).astype(np.uint32)
+        off = rng.integers(0, 4001, size=500).astype(np.uint32)  # unsorted
+        got = emblib.lookup_ex([idx], [off])[0]
+        assert np.array_equal(bits(got), bits(eo.lookup_rows([q], [idx], [off])[0]))
+    finally:
+        emblib.load().emb_set_tuning(0, 0, 0)
 
 
 def test_long_bags_beyond_the_staging_window(emblib):
