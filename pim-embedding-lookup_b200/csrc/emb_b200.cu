@@ -46,6 +46,8 @@ struct Ctx {
 
     cudaStream_t stream = nullptr;     // compute + H2D
     cudaStream_t stream_out = nullptr; // D2H
+    cudaStream_t stream_in = nullptr;  // H2D of the pipelined host-pointer path
+    std::vector<cudaEvent_t> ev_pool;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     uint32_t *d_err = nullptr;
 
@@ -136,6 +138,7 @@ int ensure_device()
                 g.device, prop.major, prop.minor);
     CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g.stream_out, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&g.stream_in, cudaStreamNonBlocking));
     for (auto &ev : g.ev)
         CU(cudaEventCreate(&ev));
     CU(cudaMalloc(&g.d_err, sizeof(uint32_t)));
@@ -233,6 +236,16 @@ int table_alloc(Table *t, uint64_t rows, int kind)
     return EMB_OK;
 }
 
+int ensure_events(size_t n)
+{
+    while (g.ev_pool.size() < n) {
+        cudaEvent_t e;
+        CU(cudaEventCreate(&e));
+        g.ev_pool.push_back(e);
+    }
+    return EMB_OK;
+}
+
 int grow(void **p, size_t *cap_elems, size_t want_elems, size_t elem)
 {
     if (*cap_elems >= want_elems && *p)
@@ -282,8 +295,10 @@ Variant pick_variant(bool any_float)
     v.kind = g.variant ? g.variant : 2;
     if (any_float)
         v.kind = 1;  // fp32 sums keep index order (embedding_lookup_idx.cc:33-77)
-    v.unroll = g.unroll ? g.unroll : (v.kind == 2 ? 8 : (lanes >= 16 ? 8 : 4));
-    v.mult = (v.kind == 2) ? (g.bags_mult ? g.bags_mult : 1) : 1;
+    // defaults from the sweeps in profiles/ (tools/sweep.py): 64-byte rows want many small CTAs,
+    // 256/512-byte rows want 8 rows in flight per sub-warp and twice the bags per CTA
+    v.unroll = g.unroll ? g.unroll : (lanes >= 16 ? 8 : 4);
+    v.mult = (v.kind == 2) ? (g.bags_mult ? g.bags_mult : (lanes >= 16 ? 2 : 1)) : 1;
     v.bags = emb::kThreads / lanes * v.mult;
     return v;
 }
@@ -485,6 +500,10 @@ void emb_shutdown(void)
             cudaStreamDestroy(g.stream);
         if (g.stream_out)
             cudaStreamDestroy(g.stream_out);
+        if (g.stream_in)
+            cudaStreamDestroy(g.stream_in);
+        for (auto &ev : g.ev_pool)
+            cudaEventDestroy(ev);
     }
     int unroll = g.unroll, variant = g.variant, bags_mult = g.bags_mult;
     g = Ctx();
@@ -795,10 +814,17 @@ int emb_reduce_partials(const void *const *parts_dev, uint32_t n_parts, uint32_t
 
 /* ---------------------------------------------------------------- host-pointer lookups -- */
 
-/* Shared body of lookup() and emb_lookup_ex(): per-table async H2D of the caller's arrays
- * into packed device mirrors, one kernel for all tables, D2H of each table's pooled rows.
- * emb_host.h:258-287 pushed indices/offsets/lengths to every column DPU (indices
- * replicated NR_COLS times); here every byte crosses PCIe once. */
+/* Shared body of lookup() and emb_lookup_ex().
+ * emb_host.h:258-287 pushed indices/offsets/lengths to every column DPU (indices replicated
+ * NR_COLS times), launched, then pulled every DPU's results (:305-321).  Here every byte
+ * crosses PCIe once and the three stages overlap: the tables are cut into groups; group g's
+ * indices/offsets go host->HBM on the copy-in stream, its pooling kernel runs on the compute
+ * stream as soon as they have landed, and its pooled rows go HBM->host on the copy-out stream
+ * while group g+1 is still arriving -- both PCIe directions busy at once.  Small calls (a few
+ * hundred KB, the reference's own shapes) take one group: one kernel, no extra events. */
+constexpr uint64_t kPipelineMinBytes = 4ull << 20;
+constexpr uint32_t kMaxGroups = 32;
+
 static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_t *const *offsets,
                        const uint32_t *indices_len, const uint32_t *nr_batches,
                        float *const *final_results)
@@ -808,6 +834,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     if (T > g.tables.size())
         return fail(EMB_ESTATE, "lookup over %u tables but only %zu slots exist", T, g.tables.size());
     uint64_t tot_idx = 0, tot_bags = 0;
+    bool any_float = false;
     for (uint32_t t = 0; t < T; t++) {
         if (!g.tables[t].kind)
             return fail(EMB_ESTATE, "table %u is not populated", t);
@@ -815,6 +842,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             return fail(EMB_EINVAL, "NULL array for table %u", t);
         tot_idx += indices_len[t];
         tot_bags += nr_batches[t];
+        any_float |= g.tables[t].kind == EMB_TABLE_FLOAT;
     }
     int rc;
     if ((rc = grow((void **)&g.d_idx, &g.idx_cap, tot_idx, 4)) ||
@@ -834,62 +862,103 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         g.desc_cap = T;
     }
 
-    bool any_float = false;
-    for (uint32_t t = 0; t < T; t++)
-        any_float |= g.tables[t].kind == EMB_TABLE_FLOAT;
-    const Variant variant = pick_variant(any_float);
-    cudaStream_t s = g.stream;
-    CU(cudaEventRecord(g.ev[0], s));
-    uint64_t io = 0, oo = 0, chunk = 0, h2d = 0;
-    for (uint32_t t = 0; t < T; t++) {
-        emb_dev_query q;
-        memset(&q, 0, sizeof q);
-        q.table_id = t;
-        q.nr_batches = nr_batches[t];
-        q.indices_len = indices_len[t];
-        q.indices = g.d_idx + io;
-        q.offsets = g.d_off + oo;
-        q.out = g.d_out + oo * D;
-        q.out_stride = D;
-        uint32_t c = 0;
-        if ((rc = fill_desc(q, &g.h_descs[t], (uint32_t)chunk, variant.bags, &c)))
-            return rc;
-        chunk += c;
-        if (indices_len[t])
-            CU(cudaMemcpyAsync(g.d_idx + io, indices[t], (size_t)indices_len[t] * 4, cudaMemcpyHostToDevice, s));
-        if (nr_batches[t])
-            CU(cudaMemcpyAsync(g.d_off + oo, offsets[t], (size_t)nr_batches[t] * 4, cudaMemcpyHostToDevice, s));
-        h2d += ((uint64_t)indices_len[t] + nr_batches[t]) * 4;
-        io += indices_len[t];
-        oo += nr_batches[t];
-    }
-    if (chunk > 0x7fffffffull)
-        return fail(EMB_EINVAL, "too many bags for one launch");
-    CU(cudaMemcpyAsync(g.d_descs, g.h_descs, T * sizeof(BagDesc), cudaMemcpyHostToDevice, s));
-    CU(cudaEventRecord(g.ev[1], s));
-    if ((rc = launch_bag_sum(variant, g.d_descs, T, (uint32_t)chunk, s)))
+    // groups of consecutive tables with about equal bytes
+    const uint64_t h2d_payload = (tot_idx + tot_bags) * 4, d2h_payload = tot_bags * D * 4;
+    uint32_t n_groups = 1;
+    if (h2d_payload + d2h_payload >= kPipelineMinBytes)
+        n_groups = std::min(std::min(T, kMaxGroups), (uint32_t)((h2d_payload + d2h_payload) / (kPipelineMinBytes / 4)) + 1);
+    if ((rc = ensure_events(3 * n_groups + 2)))
         return rc;
-    CU(cudaEventRecord(g.ev[2], s));
-    oo = 0;
-    for (uint32_t t = 0; t < T; t++) {
-        if (nr_batches[t])
-            CU(cudaMemcpyAsync(final_results[t], g.d_out + oo * D, (size_t)nr_batches[t] * D * 4,
-                               cudaMemcpyDeviceToHost, s));
-        oo += nr_batches[t];
+    const Variant variant = pick_variant(any_float);
+    std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
+    {
+        const uint64_t per_group = (h2d_payload + d2h_payload + n_groups - 1) / n_groups;
+        uint64_t acc = 0;
+        uint32_t gi = 0;
+        g_first[0] = 0;
+        for (uint32_t t = 0; t < T; t++) {
+            acc += ((uint64_t)indices_len[t] + nr_batches[t]) * 4 + (uint64_t)nr_batches[t] * D * 4;
+            if (acc >= per_group * (gi + 1) && gi + 1 < n_groups && t + 1 < T)
+                g_first[++gi] = t + 1;
+        }
+        n_groups = gi + 1;
+        g_first[n_groups] = T;
     }
-    CU(cudaEventRecord(g.ev[3], s));
-    CU(cudaStreamSynchronize(s));
-    float ms = 0;
-    CU(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1]));
+
+    // descriptors: chunk_begin is relative to the group's launch
+    uint64_t io = 0, oo = 0;
+    std::vector<uint64_t> t_io(T), t_oo(T);
+    for (uint32_t gi = 0; gi < n_groups; gi++) {
+        uint64_t chunk = 0;
+        for (uint32_t t = g_first[gi]; t < g_first[gi + 1]; t++) {
+            emb_dev_query q;
+            memset(&q, 0, sizeof q);
+            q.table_id = t;
+            q.nr_batches = nr_batches[t];
+            q.indices_len = indices_len[t];
+            q.indices = g.d_idx + io;
+            q.offsets = g.d_off + oo;
+            q.out = g.d_out + oo * D;
+            q.out_stride = D;
+            uint32_t c = 0;
+            if ((rc = fill_desc(q, &g.h_descs[t], (uint32_t)chunk, variant.bags, &c)))
+                return rc;
+            chunk += c;
+            t_io[t] = io;
+            t_oo[t] = oo;
+            io += indices_len[t];
+            oo += nr_batches[t];
+        }
+        if (chunk > 0x7fffffffull)
+            return fail(EMB_EINVAL, "too many bags for one launch");
+        g_grid[gi] = (uint32_t)chunk;
+    }
+
+    cudaStream_t s_in = g.stream_in, s_k = g.stream, s_out = g.stream_out;
+    cudaEvent_t *ev = g.ev_pool.data();
+    cudaEvent_t ev_begin = ev[3 * n_groups], ev_end = ev[3 * n_groups + 1];
+    CU(cudaEventRecord(ev_begin, s_in));
+    CU(cudaMemcpyAsync(g.d_descs, g.h_descs, T * sizeof(BagDesc), cudaMemcpyHostToDevice, s_in));
+    uint64_t launches = 0;
+    for (uint32_t gi = 0; gi < n_groups; gi++) {
+        const uint32_t t0 = g_first[gi], t1 = g_first[gi + 1];
+        for (uint32_t t = t0; t < t1; t++) {
+            if (indices_len[t])
+                CU(cudaMemcpyAsync(g.d_idx + t_io[t], indices[t], (size_t)indices_len[t] * 4,
+                                   cudaMemcpyHostToDevice, s_in));
+            if (nr_batches[t])
+                CU(cudaMemcpyAsync(g.d_off + t_oo[t], offsets[t], (size_t)nr_batches[t] * 4,
+                                   cudaMemcpyHostToDevice, s_in));
+        }
+        CU(cudaEventRecord(ev[3 * gi], s_in));
+        CU(cudaStreamWaitEvent(s_k, ev[3 * gi], 0));
+        CU(cudaEventRecord(ev[3 * gi + 1], s_k));
+        if ((rc = launch_bag_sum(variant, g.d_descs + t0, t1 - t0, g_grid[gi], s_k)))
+            return rc;
+        launches += g_grid[gi] ? 1 : 0;
+        CU(cudaEventRecord(ev[3 * gi + 2], s_k));
+        CU(cudaStreamWaitEvent(s_out, ev[3 * gi + 2], 0));
+        for (uint32_t t = t0; t < t1; t++)
+            if (nr_batches[t])
+                CU(cudaMemcpyAsync(final_results[t], g.d_out + t_oo[t] * D, (size_t)nr_batches[t] * D * 4,
+                                   cudaMemcpyDeviceToHost, s_out));
+    }
+    CU(cudaEventRecord(ev_end, s_out));
+    CU(cudaStreamSynchronize(s_out));
+    float ms = 0, k_ms = 0;
+    CU(cudaEventElapsedTime(&ms, ev_begin, ev[3 * (n_groups - 1)]));
     g.last.h2d_ms = ms;
-    CU(cudaEventElapsedTime(&ms, g.ev[1], g.ev[2]));
-    g.last.kernel_ms = ms;
-    CU(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3]));
+    for (uint32_t gi = 0; gi < n_groups; gi++) {
+        CU(cudaEventElapsedTime(&ms, ev[3 * gi + 1], ev[3 * gi + 2]));
+        k_ms += ms;
+    }
+    g.last.kernel_ms = k_ms;
+    CU(cudaEventElapsedTime(&ms, ev[2], ev_end));  // first group's rows ready -> last byte on the host
     g.last.d2h_ms = ms;
     g.last.total_ms = (now_s() - t_begin) * 1e3;
-    g.last.h2d_bytes = h2d + T * sizeof(BagDesc);
-    g.last.d2h_bytes = tot_bags * D * 4;
-    g.last.launches = chunk ? 1 : 0;
+    g.last.h2d_bytes = h2d_payload + T * sizeof(BagDesc);
+    g.last.d2h_bytes = d2h_payload;
+    g.last.launches = launches;
     return EMB_OK;
 }
 
@@ -920,7 +989,7 @@ int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results, v
         printf("C: Results copy latency: %ldμs\n", (long)(g.last.d2h_ms * 1e3));
         printf("C: Callback prep latency: %ldμs\n", 0L);
         printf("C: DPU sync latency: %ldμs\n",
-               (long)((g.last.total_ms - g.last.h2d_ms - g.last.kernel_ms - g.last.d2h_ms) * 1e3));
+               (long)(std::max(0.0, g.last.total_ms - g.last.h2d_ms - g.last.kernel_ms - g.last.d2h_ms) * 1e3));
     }
     return nullptr;
 }

@@ -1,0 +1,122 @@
+"""Two-GPU parity of the pooled-output exchange (skipped on a one-GPU box): both transports --
+peer-slab stores straight from the pooling kernel over NVLink, and NCCL all_to_all_single --
+must leave on every rank exactly the oracle's pooled rows of that rank's samples, for all
+tables, bit for bit.  Also a row-split table: raw int32 partials from two GPUs added at the
+receiver."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, tmp):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ctypes as C
+
+    import torch
+    import torch.distributed as dist
+
+    import emb_oracle as eo
+    from pim_embedding_lookup_b200 import emblib, exchange
+    from pim_embedding_lookup_b200.dputypes import EMB_Q_RAW_SUMS
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                            device_id=torch.device("cuda", rank))
+    ok = {}
+    try:
+        D, B, R = 16, 4096, 20000
+        tables_per_rank = [3, 2]
+        first, t_global = exchange.table_ranges(tables_per_rank)
+        rng = np.random.default_rng(7)  # same on both ranks: the global problem
+        tabs = [rng.integers(-2**31, 2**31, size=(R, D), dtype=np.int64).astype(np.int32) for _ in range(t_global)]
+        idx, off = [], []
+        for _ in range(t_global):
+            lens = rng.integers(0, 21, size=B)
+            off.append(np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.uint32))
+            idx.append(rng.integers(0, R, size=int(lens.sum())).astype(np.uint32))
+        want_all = np.stack(eo.lookup_rows(tabs, idx, off), axis=1)  # [B, T_global, D]
+        per = B // world
+        want = want_all[rank * per:(rank + 1) * per]
+
+        T_local = tables_per_rank[rank]
+        emblib.configure(T_local + 1, D, device=rank)
+        mine = list(range(first[rank], first[rank] + T_local))
+        dev = []
+        for lt, t in enumerate(mine):
+            emblib.populate_table_i32(lt, tabs[t])
+            dev.append((torch.from_numpy(idx[t].view(np.int32)).cuda(), torch.from_numpy(off[t].view(np.int32)).cuda()))
+        stream = torch.cuda.current_stream()
+
+        # (1) fused: the kernel stores into every rank's slab
+        slabs = exchange.PeerSlabs(B, tables_per_rank, D)
+        slabs.local().zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        plan = emblib.Plan([dict(table_id=lt, indices=dev[lt][0], offsets=dev[lt][1], out=None,
+                                 out_stride=slabs.stride, bags_per_rank=slabs.per, out_peer=slabs.out_peer(lt))
+                            for lt in range(T_local)])
+        plan.launch(stream)
+        slabs.barrier()
+        torch.cuda.synchronize()
+        got = slabs.local().cpu().numpy()
+        ok["fused"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
+        plan.close()
+
+        # (2) NCCL all_to_all_single of a [N, B/N, T_local, D] send buffer
+        send = torch.empty((B, T_local, D), dtype=torch.float32, device="cuda")
+        plan = emblib.Plan([dict(table_id=lt, indices=dev[lt][0], offsets=dev[lt][1], out=send[:, lt, :],
+                                 out_stride=T_local * D) for lt in range(T_local)])
+        plan.launch(stream)
+        got = exchange.nccl_all_to_all(send, B, tables_per_rank, D).cpu().numpy()
+        ok["nccl"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
+        plan.close()
+
+        # (3) table 0 split row-wise over the two ranks: raw int32 partials into the OWNER
+        # sample rank's scratch slabs, added there (emb_reduce_partials)
+        lo, hi = (0, R // 3) if rank == 0 else (R // 3, R)
+        emblib.populate_table_i32(T_local, tabs[0][lo:hi])
+        emblib.check(emblib.load().emb_table_set_row_base(T_local, lo))
+        parts = exchange.PeerSlabs(B, [1, 1], D)  # slab [B/N, 2, D]: column block r = partial from rank r
+        di, do = torch.from_numpy(idx[0].view(np.int32)).cuda(), torch.from_numpy(off[0].view(np.int32)).cuda()
+        plan = emblib.Plan([dict(table_id=T_local, indices=di, offsets=do, out=None, out_stride=parts.stride,
+                                 bags_per_rank=parts.per, out_peer=parts.out_peer(0), flags=EMB_Q_RAW_SUMS)])
+        plan.launch(stream)
+        parts.barrier()
+        loc = parts.local(dtype="int32")
+        res = torch.empty((per, D), dtype=torch.float32, device="cuda")
+        arr = (C.c_void_p * 2)(loc[:, 0, :].data_ptr(), loc[:, 1, :].data_ptr())
+        emblib.check(emblib.load().emb_reduce_partials(arr, 2, parts.stride, res.data_ptr(), D, per, 1,
+                                                       emblib._stream(stream)))
+        torch.cuda.synchronize()
+        ok["rowsplit"] = bool(np.array_equal(res.cpu().numpy().view(np.uint32), want[:, 0, :].view(np.uint32)))
+        ok["no_oob"] = emblib.load().emb_check_indices() == 0
+        plan.close()
+        dist.barrier()
+        parts.close()
+        slabs.close()
+        emblib.shutdown()
+    finally:
+        open(os.path.join(tmp, f"ok{rank}"), "w").write(repr(ok))
+        dist.destroy_process_group()
+
+
+def test_exchange_two_gpus(tmp_path):
+    torch = pytest.importorskip("torch")
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        got = eval(open(tmp_path / f"ok{r}").read())
+        assert got == {"fused": True, "nccl": True, "rowsplit": True, "no_oob": True}, (r, got)

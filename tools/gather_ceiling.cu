@@ -83,41 +83,39 @@ void run(const uint4 *table, uint64_t rows, const uint32_t *idx, uint64_t n_idx,
 
 int main(int argc, char **argv)
 {
-    const uint64_t table_bytes = 1664000000ull;  // as 26 x 1M x 64 B
+    // usage: gather_ceiling [n_idx] -- sweeps region size x row size; K and CTAs/SM at their best values
     const uint64_t n_idx = argc > 1 ? strtoull(argv[1], nullptr, 10) : 17891328ull;
+    const uint64_t max_bytes = 16ull << 30;
     void *table;
-    CK(cudaMalloc(&table, table_bytes));
-    CK(cudaMemset(table, 1, table_bytes));
+    CK(cudaMalloc(&table, max_bytes));
+    CK(cudaMemset(table, 1, max_bytes));
     uint32_t *out;
     CK(cudaMalloc(&out, 148 * 16 * 256 * 4));
     std::vector<uint32_t> h(n_idx);
     uint32_t *idx;
     CK(cudaMalloc(&idx, n_idx * 4));
+    const uint64_t regions[] = {64ull << 20, 128ull << 20, 256ull << 20, 512ull << 20, 1664000000ull, 4ull << 30,
+                                16ull << 30};
     const int lanes[] = {4, 16, 32};
-    for (int li = 0; li < 3; li++) {
-        uint64_t rows = table_bytes / (lanes[li] * 16);
-        uint64_t s = 88172645463325252ull;
-        for (uint64_t i = 0; i < n_idx; i++) {
-            s ^= s << 13;
-            s ^= s >> 7;
-            s ^= s << 17;
-            h[i] = (uint32_t)(s % rows);
-        }
-        CK(cudaMemcpy(idx, h.data(), n_idx * 4, cudaMemcpyHostToDevice));
-        const uint4 *t = (const uint4 *)table;
-        for (int c : {2, 4, 6, 8}) {
-            if (lanes[li] == 4) {
-                run<4, 4>(t, rows, idx, n_idx, out, c);
-                run<4, 8>(t, rows, idx, n_idx, out, c);
-                run<4, 16>(t, rows, idx, n_idx, out, c);
-            } else if (lanes[li] == 16) {
-                run<16, 4>(t, rows, idx, n_idx, out, c);
-                run<16, 8>(t, rows, idx, n_idx, out, c);
-            } else {
-                run<32, 4>(t, rows, idx, n_idx, out, c);
-                run<32, 8>(t, rows, idx, n_idx, out, c);
+    for (uint64_t region : regions)
+        for (int li = 0; li < 3; li++) {
+            uint64_t rows = region / (lanes[li] * 16);
+            uint64_t s = 88172645463325252ull;
+            for (uint64_t i = 0; i < n_idx; i++) {
+                s ^= s << 13;
+                s ^= s >> 7;
+                s ^= s << 17;
+                h[i] = (uint32_t)(s % rows);
             }
+            CK(cudaMemcpy(idx, h.data(), n_idx * 4, cudaMemcpyHostToDevice));
+            const uint4 *t = (const uint4 *)table;
+            printf("{\"region_MB\": %llu} ", (unsigned long long)(region >> 20));
+            if (lanes[li] == 4)
+                run<4, 8>(t, rows, idx, n_idx, out, 4);
+            else if (lanes[li] == 16)
+                run<16, 4>(t, rows, idx, n_idx, out, 6);
+            else
+                run<32, 4>(t, rows, idx, n_idx, out, 4);
         }
-    }
     return 0;
 }
