@@ -173,9 +173,17 @@ def time_oracle_port(tables_i32, idx, off, budget_s=12.0, min_reps=2):
     return n * reps / t_tot, eo.num_threads(), reps
 
 
+def host_cores():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def time_torch_embeddingbag(tables_f32, idx, off, budget_s=10.0):
     """The reference's CPU path: nn.EmbeddingBag(mode="sum") per table (dlrm_s_pytorch.py:483-488)."""
     import torch
+    torch.set_num_threads(host_cores())
     bags = [torch.nn.EmbeddingBag.from_pretrained(torch.from_numpy(w), mode="sum", freeze=True) for w in tables_f32]
     ti = [torch.from_numpy(i.astype(np.int64)) for i in idx]
     to = [torch.from_numpy(o.astype(np.int64)) for o in off]
@@ -213,6 +221,8 @@ def run_reference(args, w):
     tabs = host_tables(w, T_s)
     idx, off = make_batch(w, seed=123, n_tables=T_s)
     import torch
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm uses every host core it may run on
+    torch.set_num_threads(host_cores())
     n = sum(len(i) for i in idx)
     # the reference's CPU path: nn.EmbeddingBag(mode="sum", sparse=True) per table, fp32 tables,
     # int64 indices/offsets (dlrm_s_pytorch.py:295,483-488), all host threads
@@ -274,7 +284,7 @@ def run_b200(args, w):
     import torch.distributed as dist
 
     from pim_embedding_lookup_b200 import emblib, exchange
-    from pim_embedding_lookup_b200.dputypes import EMB_TABLE_FIXED
+    from pim_embedding_lookup_b200.dputypes import EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED, EMB_TABLE_FIXED
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -397,27 +407,44 @@ def run_b200(args, w):
                 a[:] = b
             host.append((hi, ho))
         res = [pinned_u32(lib, B * D).view(np.float32).reshape(B, D) for _ in range(T)]
-        for k in range(3):
-            emblib.lookup_ex(host[k % 2][0], host[k % 2][1], res)
+        # pointer arrays built once per batch, as the reference's caller does (dlrm_dpu_pytorch.py:1028-1051)
+        calls = [emblib.HostCall(hi, ho, res) for hi, ho in host]
+
+        def time_e2e(n_steps):
+            for k in range(3):
+                calls[k % 2]()
+            sync_all()
+            t0 = time.perf_counter()
+            for k in range(n_steps):
+                calls[k % 2]()  # emb_lookup_ex: synchronous, the results are in host memory on return
+            dt = time.perf_counter() - t0
+            tm = emblib.last_timings()
+            n_e = sum(lookups[k % 2] for k in range(n_steps))
+            if world > 1:
+                te = torch.tensor([dt, float(n_e)], dtype=torch.float64, device="cuda")
+                a = te.clone()
+                dist.all_reduce(a, op=dist.ReduceOp.MAX)
+                b = te.clone()
+                dist.all_reduce(b, op=dist.ReduceOp.SUM)
+                dt, n_e = float(a[0]), float(b[1])
+            return n_e / dt, dt / n_steps * 1e3, tm
+
+        PATHS = {1: "staged: cudaMemcpyAsync in, kernel, cudaMemcpyAsync out, pipelined over table groups",
+                 2: "mapped: one launch, the kernel reads indices/offsets and writes pooled rows over PCIe",
+                 3: "inputs staged by the copy engine, pooled rows written to the host arrays by the kernel's "
+                    "store epilogue over PCIe, pipelined over table groups"}
         Ke = max(3, min(K, 50))
-        sync_all()
-        t0 = time.perf_counter()
-        for k in range(Ke):
-            emblib.lookup_ex(host[k % 2][0], host[k % 2][1], res)  # synchronous: results are on the host
-        dt = time.perf_counter() - t0
-        tm = emblib.last_timings()
-        n_e = sum(lookups[k % 2] for k in range(Ke))
-        te = torch.tensor([dt, float(n_e)], dtype=torch.float64, device="cuda")
-        if world > 1:
-            a = te.clone()
-            dist.all_reduce(a, op=dist.ReduceOp.MAX)
-            b = te.clone()
-            dist.all_reduce(b, op=dist.ReduceOp.SUM)
-            dt, n_e = float(a[0]), float(b[1])
-        e2e = {"value": n_e / dt, "unit": "lookups/s", "h2d_bytes_per_step": int(tm.h2d_bytes),
-               "d2h_bytes_per_step": int(tm.d2h_bytes), "ms_per_step": dt / Ke * 1e3, "steps": Ke,
-               "call": "emb_lookup_ex (host pointers, pinned), per rank",
-               "last_call_ms": {"h2d": tm.h2d_ms, "kernel": tm.kernel_ms, "d2h": tm.d2h_ms, "total": tm.total_ms}}
+        v, ms, tm = time_e2e(Ke)  # default path (EMB_HOST_AUTO) on page-locked arrays
+        e2e = {"value": v, "unit": "lookups/s", "h2d_bytes_per_step": int(tm.h2d_bytes),
+               "d2h_bytes_per_step": int(tm.d2h_bytes), "ms_per_step": ms, "steps": Ke,
+               "call": "emb_lookup_ex (host pointers in page-locked memory), per rank", "path": PATHS[int(tm.path)],
+               "last_call_ms": {"h2d": tm.h2d_ms, "kernel": tm.kernel_ms, "d2h": tm.d2h_ms, "total": tm.total_ms},
+               "other_paths": {}}
+        for forced in (EMB_HOST_COPY, EMB_HOST_MAPPED):
+            emblib.set_host_path(forced)
+            v2, ms2, tm2 = time_e2e(max(3, Ke // 5))
+            e2e["other_paths"][PATHS[forced].split(":")[0]] = {"value": v2, "ms_per_step": ms2}
+        emblib.set_host_path(EMB_HOST_AUTO)
 
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only)
     cpu = None

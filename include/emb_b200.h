@@ -173,6 +173,27 @@ int emb_lookup_ex(uint32_t nr_tables, const uint32_t *const *indices,
                   const uint32_t *const *offsets, const uint32_t *indices_len,
                   const uint32_t *nr_batches, float *const *final_results);
 
+/* How lookup() / emb_lookup_ex() move the caller's HOST arrays across PCIe:
+ * EMB_HOST_COPY        all staged: cudaMemcpyAsync of indices/offsets into HBM, pooling kernel,
+ *                      cudaMemcpyAsync of the pooled rows back, pipelined over groups of
+ *                      tables.  Works for any host memory (pageable included).
+ * EMB_HOST_MAPPED_OUT  inputs staged as above, but the pooling kernel stores the pooled rows
+ *                      straight into final_results[t] over PCIe (no device->host copies).
+ *                      Needs page-locked final_results arrays.
+ * EMB_HOST_MAPPED      nothing staged: the kernel also reads indices/offsets in place.  One
+ *                      launch per call; the lowest latency for small calls.  Needs every array
+ *                      page-locked.
+ * EMB_HOST_AUTO        (default) MAPPED when every array is page-locked and the inputs are
+ *                      small (<= 1 MiB); else MAPPED_OUT when every final_results array is
+ *                      page-locked; else COPY.
+ * "Page-locked" = cudaHostAlloc, cudaHostRegister, emb_host_alloc or emb_host_register memory.
+ * A forced path whose requirement is not met returns EMB_EINVAL. */
+#define EMB_HOST_AUTO 0
+#define EMB_HOST_COPY 1
+#define EMB_HOST_MAPPED 2
+#define EMB_HOST_MAPPED_OUT 3
+int emb_set_host_path(int path);
+
 /* ---- device-resident lookups (plans) -------------------------------------------------- */
 
 typedef struct emb_dev_query {
@@ -220,6 +241,11 @@ int emb_device_alloc(void **dev_ptr, size_t nbytes); /* cudaMalloc (IPC-exportab
 int emb_device_free(void *dev_ptr);
 int emb_host_alloc(void **host_ptr, size_t nbytes);  /* pinned                              */
 int emb_host_free(void *host_ptr);
+/* Page-lock memory the caller already owns (cudaHostRegister, mapped + portable) so that
+ * lookup()/emb_lookup_ex() can write results into it / read inputs from it in place.  The range
+ * must stay allocated until emb_host_unregister(). */
+int emb_host_register(void *host_ptr, size_t nbytes);
+int emb_host_unregister(void *host_ptr);
 int emb_memcpy_h2d(void *dst_dev, const void *src_host, size_t nbytes, void *stream);
 int emb_memcpy_d2h(void *dst_host, const void *src_dev, size_t nbytes, void *stream);
 int emb_stream_sync(void *stream);
@@ -243,6 +269,7 @@ typedef struct emb_timings {
     uint64_t h2d_bytes;
     uint64_t d2h_bytes;
     uint64_t launches; /* kernels launched by the call       */
+    uint64_t path;     /* EMB_HOST_COPY / _MAPPED / _MAPPED_OUT: how the arrays crossed PCIe */
 } emb_timings;
 /* Stage times of the last lookup()/emb_lookup_ex() call (CUDA events). */
 int emb_last_timings(emb_timings *out);

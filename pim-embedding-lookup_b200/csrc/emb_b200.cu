@@ -64,11 +64,12 @@ struct Ctx {
     BagDesc *h_descs = nullptr;  // pinned
     uint32_t desc_cap = 0;
 
-    emb_timings last = {0, 0, 0, 0, 0, 0, 0};
+    emb_timings last = {0, 0, 0, 0, 0, 0, 0, 0};
     // tuning knobs (emb_set_tuning); 0 = default
     int unroll = 0;     // rows in flight per sub-warp: 4 or 8
     int variant = 0;    // 1 = bag-per-sub-warp kernel, 2 = load-balanced kernel
     int bags_mult = 0;  // load-balanced kernel: bags per CTA = mult * sub-warps per CTA (1, 2, 4)
+    int host_path = EMB_HOST_AUTO;  // emb_set_host_path
 };
 
 Ctx g;
@@ -476,6 +477,15 @@ int emb_set_tuning(int variant, int unroll, int bags_mult)
     return EMB_OK;
 }
 
+int emb_set_host_path(int path)
+{
+    if (path < EMB_HOST_AUTO || path > EMB_HOST_MAPPED_OUT)
+        return fail(EMB_EINVAL, "host path must be EMB_HOST_AUTO, _COPY, _MAPPED or _MAPPED_OUT");
+    std::lock_guard<std::mutex> lk(g_mu);
+    g.host_path = path;
+    return EMB_OK;
+}
+
 void emb_shutdown(void)
 {
     std::lock_guard<std::mutex> lk(g_mu);
@@ -505,11 +515,12 @@ void emb_shutdown(void)
         for (auto &ev : g.ev_pool)
             cudaEventDestroy(ev);
     }
-    int unroll = g.unroll, variant = g.variant, bags_mult = g.bags_mult;
+    int unroll = g.unroll, variant = g.variant, bags_mult = g.bags_mult, host_path = g.host_path;
     g = Ctx();
     g.unroll = unroll;
     g.variant = variant;
     g.bags_mult = bags_mult;
+    g.host_path = host_path;
 }
 
 /* ---------------------------------------------------------------- tables -------------- */
@@ -817,13 +828,36 @@ int emb_reduce_partials(const void *const *parts_dev, uint32_t n_parts, uint32_t
 /* Shared body of lookup() and emb_lookup_ex().
  * emb_host.h:258-287 pushed indices/offsets/lengths to every column DPU (indices replicated
  * NR_COLS times), launched, then pulled every DPU's results (:305-321).  Here every byte
- * crosses PCIe once and the three stages overlap: the tables are cut into groups; group g's
- * indices/offsets go host->HBM on the copy-in stream, its pooling kernel runs on the compute
- * stream as soon as they have landed, and its pooled rows go HBM->host on the copy-out stream
- * while group g+1 is still arriving -- both PCIe directions busy at once.  Small calls (a few
- * hundred KB, the reference's own shapes) take one group: one kernel, no extra events. */
+ * crosses PCIe once.  How it crosses depends on what the caller's arrays are:
+ *
+ *   inputs   staged : cudaMemcpyAsync host -> HBM arena on the copy-in stream (any host memory)
+ *            mapped : the pooling kernel reads the caller's arrays over PCIe (page-locked only)
+ *   outputs  staged : pooled rows to an HBM arena, cudaMemcpyAsync -> host on the copy-out stream
+ *            mapped : the kernel's store epilogue writes final_results[t] over PCIe (page-locked)
+ *
+ * Measured on the pool's B200 (tools/host_path_probe.py, C2 bytes): the copy engines read host
+ * memory at 55 GB/s but SM loads from mapped host memory reach only 35 GB/s (64-byte read
+ * requests, tag-limited), while SM stores to mapped host memory (posted writes) reach 52 GB/s,
+ * the same as a D2H copy, and need no extra CUDA calls.  So large calls stage the inputs and
+ * map the outputs; the tables are cut into groups so that group g's kernel is writing results
+ * to the host while group g+1's indices arrive -- both PCIe directions busy.  Small calls (the
+ * reference's own shapes, a few hundred KB) map both: one descriptor upload, one launch, one
+ * synchronise, because every CUDA call costs several microseconds of host time. */
 constexpr uint64_t kPipelineMinBytes = 4ull << 20;
+constexpr uint64_t kMapInputsMaxBytes = 1ull << 20;  // inputs are read in place below this
 constexpr uint32_t kMaxGroups = 32;
+
+/* Device-side alias of a host pointer when the GPU can address it directly (memory from
+ * cudaHostAlloc / cudaHostRegister / emb_host_alloc / emb_host_register), else NULL. */
+static void *mapped_alias(const void *p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return (a.type == cudaMemoryTypeHost) ? a.devicePointer : nullptr;
+}
 
 static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_t *const *offsets,
                        const uint32_t *indices_len, const uint32_t *nr_batches,
@@ -845,10 +879,6 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         any_float |= g.tables[t].kind == EMB_TABLE_FLOAT;
     }
     int rc;
-    if ((rc = grow((void **)&g.d_idx, &g.idx_cap, tot_idx, 4)) ||
-        (rc = grow((void **)&g.d_off, &g.off_cap, tot_bags, 4)) ||
-        (rc = grow((void **)&g.d_out, &g.out_cap, tot_bags * D, 4)))
-        return rc;
     if (g.desc_cap < T) {
         if (g.d_descs)
             cudaFree(g.d_descs);
@@ -861,18 +891,69 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         CU(cudaMallocHost(&g.h_descs, T * sizeof(BagDesc)));
         g.desc_cap = T;
     }
-
-    // groups of consecutive tables with about equal bytes
     const uint64_t h2d_payload = (tot_idx + tot_bags) * 4, d2h_payload = tot_bags * D * 4;
+
+    // which arrays can the GPU address in place?
+    std::vector<const uint32_t *> a_idx(T, nullptr), a_off(T, nullptr);
+    std::vector<float *> a_out(T, nullptr);
+    bool out_mapped = g.host_path != EMB_HOST_COPY, in_mapped = out_mapped;
+    for (uint32_t t = 0; t < T && out_mapped; t++)
+        if (nr_batches[t] && !(a_out[t] = (float *)mapped_alias(final_results[t])))
+            out_mapped = false;
+    in_mapped = out_mapped && (g.host_path == EMB_HOST_MAPPED || h2d_payload <= kMapInputsMaxBytes);
+    for (uint32_t t = 0; t < T && in_mapped; t++) {
+        if (indices_len[t] && !(a_idx[t] = (const uint32_t *)mapped_alias(indices[t])))
+            in_mapped = false;
+        if (nr_batches[t] && !(a_off[t] = (const uint32_t *)mapped_alias(offsets[t])))
+            in_mapped = false;
+    }
+    if (g.host_path == EMB_HOST_MAPPED && !(in_mapped && out_mapped))
+        return fail(EMB_EINVAL, "EMB_HOST_MAPPED: a host array is not page-locked (cudaHostAlloc / "
+                                "cudaHostRegister / emb_host_alloc / emb_host_register)");
+    if (g.host_path == EMB_HOST_MAPPED_OUT && !out_mapped)
+        return fail(EMB_EINVAL, "EMB_HOST_MAPPED_OUT: a final_results array is not page-locked");
+    if (g.host_path == EMB_HOST_MAPPED_OUT)
+        in_mapped = false;
+    // MAPPED_OUT: the offsets (4 bytes per bag) are still read in place when they are page-locked:
+    // a separate small copy per table costs more on the copy engine than it moves
+    bool off_mapped = in_mapped;
+    if (out_mapped && !in_mapped) {
+        off_mapped = true;
+        for (uint32_t t = 0; t < T && off_mapped; t++)
+            if (nr_batches[t] && !(a_off[t] = (const uint32_t *)mapped_alias(offsets[t])))
+                off_mapped = false;
+    }
+
+    if (!in_mapped && (rc = grow((void **)&g.d_idx, &g.idx_cap, tot_idx, 4)))
+        return rc;
+    if (!off_mapped && (rc = grow((void **)&g.d_off, &g.off_cap, tot_bags, 4)))
+        return rc;
+    if (!out_mapped && (rc = grow((void **)&g.d_out, &g.out_cap, tot_bags * D, 4)))
+        return rc;
+
+    // Groups of consecutive tables with about equal bytes (one group when nothing is staged).
+    // A kernel that stores to host memory only retires when its writes have drained (measured,
+    // tools/pcie_mix_probe.py: the same 109 MB take 2.08 ms in 1 launch, 2.13 in 4, 2.46 in 26) and
+    // every copy boundary idles the copy engine for a few microseconds, so groups are large:
+    // ~32 MB with mapped results, ~16 MB when the results are copied out as well (the last
+    // group's copy-out overlaps nothing).  Sweep on C2 (tools/e2e_groups_sweep.sh): 2 / 4 / 6 / 8 /
+    // 13 / 26 groups -> 3.26 / 3.05 / 3.05 / 3.09 / 3.22 / 3.60 ms per call (mapped results).
+    const uint64_t staged = (in_mapped ? 0 : h2d_payload) + d2h_payload;
     uint32_t n_groups = 1;
-    if (h2d_payload + d2h_payload >= kPipelineMinBytes)
-        n_groups = std::min(std::min(T, kMaxGroups), (uint32_t)((h2d_payload + d2h_payload) / (kPipelineMinBytes / 4)) + 1);
+    if (!(in_mapped && out_mapped) && staged >= kPipelineMinBytes) {
+        const uint64_t unit = out_mapped ? (32ull << 20) : (16ull << 20);
+        n_groups = std::min(std::min(T, kMaxGroups), std::max(2u, (uint32_t)(staged / unit)));
+    }
+    const uint32_t forced_groups = env_u32("EMB_GROUPS", 0);  // measurement knob
+    if (forced_groups && n_groups > 1)
+        n_groups = std::min(std::min(T, kMaxGroups), forced_groups);
     if ((rc = ensure_events(3 * n_groups + 2)))
         return rc;
     const Variant variant = pick_variant(any_float);
     std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
     {
-        const uint64_t per_group = (h2d_payload + d2h_payload + n_groups - 1) / n_groups;
+        const uint64_t total = h2d_payload + d2h_payload;
+        const uint64_t per_group = (total + n_groups - 1) / n_groups;
         uint64_t acc = 0;
         uint32_t gi = 0;
         g_first[0] = 0;
@@ -896,9 +977,9 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             q.table_id = t;
             q.nr_batches = nr_batches[t];
             q.indices_len = indices_len[t];
-            q.indices = g.d_idx + io;
-            q.offsets = g.d_off + oo;
-            q.out = g.d_out + oo * D;
+            q.indices = in_mapped ? a_idx[t] : g.d_idx + io;
+            q.offsets = off_mapped ? a_off[t] : g.d_off + oo;
+            q.out = out_mapped ? (void *)a_out[t] : (void *)(g.d_out + oo * D);
             q.out_stride = D;
             uint32_t c = 0;
             if ((rc = fill_desc(q, &g.h_descs[t], (uint32_t)chunk, variant.bags, &c)))
@@ -922,43 +1003,56 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     uint64_t launches = 0;
     for (uint32_t gi = 0; gi < n_groups; gi++) {
         const uint32_t t0 = g_first[gi], t1 = g_first[gi + 1];
-        for (uint32_t t = t0; t < t1; t++) {
-            if (indices_len[t])
-                CU(cudaMemcpyAsync(g.d_idx + t_io[t], indices[t], (size_t)indices_len[t] * 4,
-                                   cudaMemcpyHostToDevice, s_in));
-            if (nr_batches[t])
-                CU(cudaMemcpyAsync(g.d_off + t_oo[t], offsets[t], (size_t)nr_batches[t] * 4,
-                                   cudaMemcpyHostToDevice, s_in));
+        if (!in_mapped)
+            for (uint32_t t = t0; t < t1; t++) {
+                if (indices_len[t])
+                    CU(cudaMemcpyAsync(g.d_idx + t_io[t], indices[t], (size_t)indices_len[t] * 4,
+                                       cudaMemcpyHostToDevice, s_in));
+                if (nr_batches[t] && !off_mapped)
+                    CU(cudaMemcpyAsync(g.d_off + t_oo[t], offsets[t], (size_t)nr_batches[t] * 4,
+                                       cudaMemcpyHostToDevice, s_in));
+            }
+        if (gi == 0 || !in_mapped) {
+            CU(cudaEventRecord(ev[3 * gi], s_in));
+            CU(cudaStreamWaitEvent(s_k, ev[3 * gi], 0));
         }
-        CU(cudaEventRecord(ev[3 * gi], s_in));
-        CU(cudaStreamWaitEvent(s_k, ev[3 * gi], 0));
         CU(cudaEventRecord(ev[3 * gi + 1], s_k));
         if ((rc = launch_bag_sum(variant, g.d_descs + t0, t1 - t0, g_grid[gi], s_k)))
             return rc;
         launches += g_grid[gi] ? 1 : 0;
         CU(cudaEventRecord(ev[3 * gi + 2], s_k));
-        CU(cudaStreamWaitEvent(s_out, ev[3 * gi + 2], 0));
-        for (uint32_t t = t0; t < t1; t++)
-            if (nr_batches[t])
-                CU(cudaMemcpyAsync(final_results[t], g.d_out + t_oo[t] * D, (size_t)nr_batches[t] * D * 4,
-                                   cudaMemcpyDeviceToHost, s_out));
+        if (!out_mapped) {
+            CU(cudaStreamWaitEvent(s_out, ev[3 * gi + 2], 0));
+            for (uint32_t t = t0; t < t1; t++)
+                if (nr_batches[t])
+                    CU(cudaMemcpyAsync(final_results[t], g.d_out + t_oo[t] * D, (size_t)nr_batches[t] * D * 4,
+                                       cudaMemcpyDeviceToHost, s_out));
+        }
     }
-    CU(cudaEventRecord(ev_end, s_out));
-    CU(cudaStreamSynchronize(s_out));
+    cudaStream_t s_last = out_mapped ? s_k : s_out;
+    CU(cudaEventRecord(ev_end, s_last));
+    CU(cudaStreamSynchronize(s_last));
     float ms = 0, k_ms = 0;
-    CU(cudaEventElapsedTime(&ms, ev_begin, ev[3 * (n_groups - 1)]));
-    g.last.h2d_ms = ms;
+    g.last.h2d_ms = 0;
+    if (!in_mapped) {
+        CU(cudaEventElapsedTime(&ms, ev_begin, ev[3 * (n_groups - 1)]));
+        g.last.h2d_ms = ms;
+    }
     for (uint32_t gi = 0; gi < n_groups; gi++) {
         CU(cudaEventElapsedTime(&ms, ev[3 * gi + 1], ev[3 * gi + 2]));
         k_ms += ms;
     }
-    g.last.kernel_ms = k_ms;
-    CU(cudaEventElapsedTime(&ms, ev[2], ev_end));  // first group's rows ready -> last byte on the host
-    g.last.d2h_ms = ms;
+    g.last.kernel_ms = k_ms;  // with mapped arrays the PCIe traffic is inside the kernels
+    g.last.d2h_ms = 0;
+    if (!out_mapped) {
+        CU(cudaEventElapsedTime(&ms, ev[2], ev_end));  // first group's rows ready -> last byte on the host
+        g.last.d2h_ms = ms;
+    }
     g.last.total_ms = (now_s() - t_begin) * 1e3;
     g.last.h2d_bytes = h2d_payload + T * sizeof(BagDesc);
     g.last.d2h_bytes = d2h_payload;
     g.last.launches = launches;
+    g.last.path = (in_mapped && out_mapped) ? EMB_HOST_MAPPED : out_mapped ? EMB_HOST_MAPPED_OUT : EMB_HOST_COPY;
     return EMB_OK;
 }
 
@@ -1053,6 +1147,24 @@ int emb_host_alloc(void **host_ptr, size_t nbytes)
 int emb_host_free(void *host_ptr)
 {
     CU(cudaFreeHost(host_ptr));
+    return EMB_OK;
+}
+
+int emb_host_register(void *host_ptr, size_t nbytes)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (!host_ptr || !nbytes)
+        return fail(EMB_EINVAL, "emb_host_register: NULL/empty range");
+    CU(cudaHostRegister(host_ptr, nbytes, cudaHostRegisterMapped | cudaHostRegisterPortable));
+    return EMB_OK;
+}
+
+int emb_host_unregister(void *host_ptr)
+{
+    CU(cudaHostUnregister(host_ptr));
     return EMB_OK;
 }
 

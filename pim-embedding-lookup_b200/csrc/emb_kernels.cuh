@@ -48,28 +48,75 @@ struct __align__(16) BagDesc {
     uint32_t chunk_begin;  // first CTA of this query
 };
 
+/* EMB_LD_MODE (build-time experiment switch):
+ *   0  rows: ld.global.nc.L1::no_allocate                       (default)
+ *   1  rows: + L2 evict_last policy; indices/offsets/outputs: L2 evict_first policy
+ *   2  rows: + .L2::64B prefetch size      3  rows: + .L2::128B prefetch size */
+#ifndef EMB_LD_MODE
+#define EMB_LD_MODE 0
+#endif
+
+__device__ __forceinline__ uint64_t l2_policy_evict_last()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+
 __device__ __forceinline__ uint4 ldg_row16(const uint4 *p)
 {
     uint4 r;
     // read-only, streamed: a row is touched once per bag, keep it out of L1
+#if EMB_LD_MODE == 1
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p), "l"(l2_policy_evict_last()));
+#elif EMB_LD_MODE == 2
+    asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+#elif EMB_LD_MODE == 3
+    asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+#else
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                  : "l"(p));
+#endif
     return r;
 }
 
 __device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t *p)
 {
     uint32_t r;
+#if EMB_LD_MODE == 1
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;"
+                 : "=r"(r)
+                 : "l"(p), "l"(l2_policy_evict_first()));
+#else
     asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+#endif
     return r;
 }
 
 __device__ __forceinline__ void stg_stream16(void *p, uint4 v)
 {
+#if EMB_LD_MODE == 1
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x),
+                 "r"(v.y), "r"(v.z), "r"(v.w), "l"(l2_policy_evict_first())
+                 : "memory");
+#else
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
                  "r"(v.z), "r"(v.w)
                  : "memory");
+#endif
 }
 
 /* emb_host.h:210  (float)s / pow(10,9): int->float RNE, divide in double, round to float.

@@ -93,6 +93,7 @@ EMB_MAX_PEERS = 8
 EMB_TABLE_FIXED = 1
 EMB_TABLE_FLOAT = 2
 EMB_Q_RAW_SUMS = 1
+EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED, EMB_HOST_MAPPED_OUT = 0, 1, 2, 3
 EMB_IPC_HANDLE_BYTES = 64
 
 
@@ -114,7 +115,7 @@ class EmbDevQuery(Structure):
 
 class EmbTimings(Structure):
     _fields_ = [("h2d_ms", c_double), ("kernel_ms", c_double), ("d2h_ms", c_double), ("total_ms", c_double),
-                ("h2d_bytes", c_uint64), ("d2h_bytes", c_uint64), ("launches", c_uint64)]
+                ("h2d_bytes", c_uint64), ("d2h_bytes", c_uint64), ("launches", c_uint64), ("path", c_uint64)]
 
 
 class EmbIpcHandle(Structure):

@@ -87,6 +87,9 @@ def _declare(lib):
         "emb_launch_count": ([], C.c_uint64),
         "emb_set_unroll": ([C.c_int], C.c_int),
         "emb_set_tuning": ([C.c_int, C.c_int, C.c_int], C.c_int),
+        "emb_set_host_path": ([C.c_int], C.c_int),
+        "emb_host_register": ([C.c_void_p, C.c_size_t], C.c_int),
+        "emb_host_unregister": ([C.c_void_p], C.c_int),
     }
     for name, (args, res) in sig.items():
         fn = getattr(lib, name)
@@ -179,6 +182,24 @@ def table_read(table_id: int, row0: int, n: int, dtype=np.int32) -> np.ndarray:
     return out
 
 
+def pinned_array(shape, dtype=np.uint32) -> np.ndarray:
+    """NumPy array in page-locked host memory (emb_host_alloc): lookup()/lookup_ex() on such arrays
+    take the EMB_HOST_MAPPED path (no staging copies).  Freed with free_pinned()."""
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = C.c_void_p()
+    check(load().emb_host_alloc(C.byref(p), max(n, 16)), "emb_host_alloc")
+    buf = (C.c_ubyte * max(n, 16)).from_address(p.value)
+    return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+
+def free_pinned(a: np.ndarray) -> None:
+    check(load().emb_host_free(C.c_void_p(a.ctypes.data)), "emb_host_free")
+
+
+def set_host_path(path: int) -> None:
+    check(load().emb_set_host_path(path), "emb_set_host_path")
+
+
 def lookup(indices, offsets, handle=None, latency_print=0):
     """The reference call: shapes come from the configured NR_TABLES/MAX_NR_BATCHES/...;
     indices[t] uint32 [B*P], offsets[t] uint32 [B].  Returns list of fp32 [B, D]."""
@@ -208,6 +229,31 @@ def lookup_ex(indices, offsets, results=None):
     return res
 
 
+class HostCall:
+    """One emb_lookup_ex() call over fixed host arrays with the pointer arrays built once -- what the
+    reference's caller prepares per batch (`ind_pointers_c`, `off_pointers_c`, `final_results_ptr`,
+    dlrm_dpu_pytorch.py:484-498,1028-1051).  Calling the object is exactly one C call."""
+
+    def __init__(self, indices, offsets, results=None):
+        D = shape().nr_cols
+        self.indices = [np.ascontiguousarray(i, dtype=np.uint32) for i in indices]
+        self.offsets = [np.ascontiguousarray(o, dtype=np.uint32) for o in offsets]
+        T = len(self.indices)
+        self._il = np.asarray([i.size for i in self.indices], dtype=np.uint32)
+        self._nb = np.asarray([o.size for o in self.offsets], dtype=np.uint32)
+        self.results = results if results is not None else [np.empty((int(self._nb[t]), D), dtype=np.float32)
+                                                           for t in range(T)]
+        self._args = (T, _ptr_array(self.indices, u32p), _ptr_array(self.offsets, u32p), _p(self._il, u32p),
+                      _p(self._nb, u32p), _ptr_array(self.results, f32p))
+        self._fn = load().emb_lookup_ex
+
+    def __call__(self):
+        rc = self._fn(*self._args)
+        if rc:
+            check(rc, "emb_lookup_ex")
+        return self.results
+
+
 def last_timings() -> EmbTimings:
     t = EmbTimings()
     check(load().emb_last_timings(C.byref(t)), "emb_last_timings")
@@ -235,8 +281,8 @@ class Plan:
             e.indices = _addr(q["indices"])
             e.offsets = _addr(q["offsets"])
             e.out = _addr(q.get("out"))
-            e.nr_batches = q.get("nr_batches", _numel(q["offsets"]))
-            e.indices_len = q.get("indices_len", _numel(q["indices"]))
+            e.nr_batches = q["nr_batches"] if "nr_batches" in q else _numel(q["offsets"])
+            e.indices_len = q["indices_len"] if "indices_len" in q else _numel(q["indices"])
             e.flags = q.get("flags", 0)
             e.out_stride = q.get("out_stride", 0)
             e.bags_per_rank = q.get("bags_per_rank", 0)

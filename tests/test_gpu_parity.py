@@ -110,6 +110,99 @@ def test_lookup_ex_matches_oracle(emblib, D):
     assert emblib.load().emb_check_indices() == 0
 
 
+@pytest.mark.parametrize("D", [16, 64, 6])
+def test_page_locked_arrays_take_the_mapped_path_and_match(emblib, D):
+    """Host arrays in page-locked memory: the pooling kernel reads them and writes the results over
+    PCIe itself (EMB_HOST_MAPPED, no staging copies); pageable arrays are staged (EMB_HOST_COPY).
+    Both must give the oracle's bits."""
+    from pim_embedding_lookup_b200.dputypes import (EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED,
+                                                    EMB_HOST_MAPPED_OUT)
+    rng = np.random.default_rng(31 + D)
+    T = 4
+    emblib.configure(T, D)
+    tabs, idxs, offs, pidx, poff, pres = [], [], [], [], [], []
+    for t in range(T):
+        R = [3, 1000, 70000, 257][t]
+        q = rng.integers(-2**31, 2**31, size=(R, D), dtype=np.int64).astype(np.int32)
+        tabs.append(q)
+        emblib.populate_table_i32(t, q)
+        i, o = ragged(rng, R, [5, 4097, 1, 600][t], 30)
+        idxs.append(i)
+        offs.append(o)
+        a = emblib.pinned_array(max(i.size, 1), np.uint32)[:i.size]
+        a[:] = i
+        b = emblib.pinned_array(o.size, np.uint32)
+        b[:] = o
+        pidx.append(a)
+        poff.append(b)
+        pres.append(emblib.pinned_array((o.size, D), np.float32))
+    want = eo.lookup_rows(tabs, idxs, offs)
+
+    def run(path, i, o, r, expect):
+        emblib.set_host_path(path)
+        if r is not None:
+            for x in r:
+                x[:] = np.nan
+        got = emblib.lookup_ex(i, o, r)
+        assert emblib.last_timings().path == expect
+        for t in range(T):
+            assert np.array_equal(bits(got[t]), bits(want[t])), (path, t)
+
+    try:
+        run(EMB_HOST_AUTO, pidx, poff, pres, EMB_HOST_MAPPED)      # small + all page-locked: one launch
+        assert emblib.last_timings().launches == 1
+        run(EMB_HOST_AUTO, idxs, offs, None, EMB_HOST_COPY)        # pageable: staged both ways
+        run(EMB_HOST_AUTO, idxs, offs, pres, EMB_HOST_MAPPED_OUT)  # pageable inputs, page-locked results
+        run(EMB_HOST_MAPPED_OUT, pidx, poff, pres, EMB_HOST_MAPPED_OUT)
+        run(EMB_HOST_COPY, pidx, poff, pres, EMB_HOST_COPY)        # forced staging of page-locked arrays
+        emblib.set_host_path(EMB_HOST_MAPPED)                      # forced mapping of pageable arrays: error
+        with pytest.raises(Exception):
+            emblib.lookup_ex(idxs, offs)
+        emblib.set_host_path(EMB_HOST_MAPPED_OUT)
+        with pytest.raises(Exception):
+            emblib.lookup_ex(pidx, poff)  # results default to pageable NumPy arrays
+        # caller-owned pageable results, page-locked in place with emb_host_register
+        own = [np.full((o.size, D), np.nan, dtype=np.float32) for o in offs]
+        lib = emblib.load()
+        for r in own:
+            emblib.check(lib.emb_host_register(r.ctypes.data, r.nbytes))
+        try:
+            run(EMB_HOST_AUTO, idxs, offs, own, EMB_HOST_MAPPED_OUT)
+        finally:
+            for r in own:
+                emblib.check(lib.emb_host_unregister(r.ctypes.data))
+    finally:
+        emblib.set_host_path(EMB_HOST_AUTO)
+    assert emblib.load().emb_check_indices() == 0
+
+
+def test_large_call_pipelines_groups_with_mapped_results(emblib):
+    """Enough bytes for several pipeline groups: staged inputs, results written in place."""
+    from pim_embedding_lookup_b200.dputypes import EMB_HOST_MAPPED_OUT
+    rng = np.random.default_rng(5)
+    T, D, R, B = 6, 16, 50000, 30000
+    emblib.configure(T, D)
+    tabs, pidx, poff, pres = [], [], [], []
+    for t in range(T):
+        q = rng.integers(-2**31, 2**31, size=(R, D), dtype=np.int64).astype(np.int32)
+        tabs.append(q)
+        emblib.populate_table_i32(t, q)
+        i, o = ragged(rng, R, B, 20)
+        a = emblib.pinned_array(i.size, np.uint32)
+        a[:] = i
+        b = emblib.pinned_array(o.size, np.uint32)
+        b[:] = o
+        pidx.append(a)
+        poff.append(b)
+        pres.append(emblib.pinned_array((B, D), np.float32))
+    want = eo.lookup_rows(tabs, pidx, poff)
+    got = emblib.lookup_ex(pidx, poff, pres)
+    tm = emblib.last_timings()
+    assert tm.path == EMB_HOST_MAPPED_OUT and tm.launches > 1
+    for t in range(T):
+        assert np.array_equal(bits(got[t]), bits(want[t])), t
+
+
 TUNINGS = [(1, 4, 0), (1, 8, 0), (2, 4, 1), (2, 8, 1), (2, 4, 2), (2, 8, 4)]
 
 

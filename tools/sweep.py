@@ -23,11 +23,17 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--tunings", nargs="*", default=["1,4,0", "1,8,0", "2,4,1", "2,8,1", "2,4,2", "2,8,2", "2,4,4",
                                                      "2,8,4"])
+    ap.add_argument("--rows", type=int, default=0, help="override rows per table")
+    ap.add_argument("--tables", type=int, default=0, help="override the table count")
     args = ap.parse_args()
     import torch
 
     from pim_embedding_lookup_b200 import emblib
-    w = bench.WORKLOADS[args.workload]
+    w = dict(bench.WORKLOADS[args.workload])
+    if args.rows:
+        w["R"] = args.rows
+    if args.tables:
+        w["T"] = args.tables
     T, R, D, B = w["T"], w["R"], w["D"], w["B"]
     lib = emblib.load()
     emblib.configure(T, D, 0, 0, device=0)
@@ -67,7 +73,7 @@ def main():
         nl = np.mean([sum(len(i) for i in b[0]) for b in batches])
         by = bench.algorithmic_bytes(nl, T * B, D)
         med = ms[len(ms) // 2]
-        print(json.dumps({"workload": args.workload, "variant": v, "unroll": k, "mult": m, "grid": plans[0].grid,
+        print(json.dumps({"workload": args.workload, "rows": R, "tables": T, "variant": v, "unroll": k, "mult": m, "grid": plans[0].grid,
                           "kernel_ms_median": round(med, 4), "kernel_ms_min": round(ms[0], 4),
                           "GBps": round(by / med / 1e6, 1), "frac_of_measured_peak": round(by / med / 1e6 / peak, 4),
                           "lookups_per_s": nl / med * 1e3, "same_bits_as_first": chk == ref}), flush=True)
