@@ -396,6 +396,15 @@ def run_b200(args, w):
     bytes_per_launch = float(np.mean([algorithmic_bytes(lookups[k % N_BATCHES], T * B, D) for k in range(K)]))
     achieved = bytes_per_launch / (kernel_ms * 1e-3) / 1e9
 
+    # DRAM traffic of the same kernel from the committed ncu capture (per launch), if there is one
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if world == 1 and os.path.exists(tp):
+        rec = json.load(open(tp)).get(args.workload)
+        if rec:
+            traffic = rec["dram_bytes_read_per_launch"] + rec["dram_bytes_write_per_launch"]
+            traffic_src = rec["source"]
+
     # ---- e2e: the host-pointer C-ABI call, pinned host buffers, copies inside the timed region
     e2e = None
     if not args.no_e2e:
@@ -473,7 +482,7 @@ def run_b200(args, w):
                        "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult},
                        "parallelism": f"table-wise x{world}, pooled rows to the sample's rank"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_launch": bytes_per_launch,
                          "frac_of_nominal_8000": achieved / 8000.0},
             "clocks": clk.summary(), "gpu_launches": int(gpu_launches),

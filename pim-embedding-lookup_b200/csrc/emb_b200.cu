@@ -296,10 +296,10 @@ Variant pick_variant(bool any_float)
     v.kind = g.variant ? g.variant : 2;
     if (any_float)
         v.kind = 1;  // fp32 sums keep index order (embedding_lookup_idx.cc:33-77)
-    // defaults from the sweeps in profiles/ (tools/sweep.py): 64-byte rows want many small CTAs,
-    // 256/512-byte rows want 8 rows in flight per sub-warp and twice the bags per CTA
+    // defaults from the sweeps in profiles/r1_sweeps.md (tools/sweep.py): 64-byte rows want many
+    // small CTAs; 256-byte rows 8 rows in flight per lane and 4x the bags per CTA; 512-byte rows 2x
     v.unroll = g.unroll ? g.unroll : (lanes >= 16 ? 8 : 4);
-    v.mult = (v.kind == 2) ? (g.bags_mult ? g.bags_mult : (lanes >= 16 ? 2 : 1)) : 1;
+    v.mult = (v.kind == 2) ? (g.bags_mult ? g.bags_mult : (lanes == 16 ? 4 : lanes > 16 ? 2 : 1)) : 1;
     v.bags = emb::kThreads / lanes * v.mult;
     return v;
 }
