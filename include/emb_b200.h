@@ -183,15 +183,20 @@ int emb_lookup_ex(uint32_t nr_tables, const uint32_t *const *indices,
  * EMB_HOST_MAPPED      nothing staged: the kernel also reads indices/offsets in place.  One
  *                      launch per call; the lowest latency for small calls.  Needs every array
  *                      page-locked.
+ * EMB_HOST_BOUNCE      any host memory: the CPU copies the arrays into one page-locked arena, the
+ *                      MAPPED launch runs on the arena, the CPU copies the results out.  For
+ *                      small calls (the reference's own shapes) this is one CUDA launch instead
+ *                      of three copies per table.
  * EMB_HOST_AUTO        (default) MAPPED when every array is page-locked and the inputs are
- *                      small (<= 1 MiB); else MAPPED_OUT when every final_results array is
- *                      page-locked; else COPY.
+ *                      small (<= 1 MiB); else BOUNCE when the whole call is <= 1 MiB; else
+ *                      MAPPED_OUT when every final_results array is page-locked; else COPY.
  * "Page-locked" = cudaHostAlloc, cudaHostRegister, emb_host_alloc or emb_host_register memory.
  * A forced path whose requirement is not met returns EMB_EINVAL. */
 #define EMB_HOST_AUTO 0
 #define EMB_HOST_COPY 1
 #define EMB_HOST_MAPPED 2
 #define EMB_HOST_MAPPED_OUT 3
+#define EMB_HOST_BOUNCE 4
 int emb_set_host_path(int path);
 
 /* ---- device-resident lookups (plans) -------------------------------------------------- */
@@ -269,7 +274,7 @@ typedef struct emb_timings {
     uint64_t h2d_bytes;
     uint64_t d2h_bytes;
     uint64_t launches; /* kernels launched by the call       */
-    uint64_t path;     /* EMB_HOST_COPY / _MAPPED / _MAPPED_OUT: how the arrays crossed PCIe */
+    uint64_t path;     /* EMB_HOST_COPY / _MAPPED / _MAPPED_OUT / _BOUNCE: how the arrays crossed PCIe */
 } emb_timings;
 /* Stage times of the last lookup()/emb_lookup_ex() call (CUDA events). */
 int emb_last_timings(emb_timings *out);

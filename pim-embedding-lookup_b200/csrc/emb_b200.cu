@@ -63,6 +63,9 @@ struct Ctx {
     BagDesc *d_descs = nullptr;
     BagDesc *h_descs = nullptr;  // pinned
     uint32_t desc_cap = 0;
+    // page-locked bounce arena for small calls on pageable arrays
+    uint8_t *h_bounce = nullptr;
+    size_t bounce_cap = 0;
 
     emb_timings last = {0, 0, 0, 0, 0, 0, 0, 0};
     // tuning knobs (emb_set_tuning); 0 = default
@@ -479,8 +482,8 @@ int emb_set_tuning(int variant, int unroll, int bags_mult)
 
 int emb_set_host_path(int path)
 {
-    if (path < EMB_HOST_AUTO || path > EMB_HOST_MAPPED_OUT)
-        return fail(EMB_EINVAL, "host path must be EMB_HOST_AUTO, _COPY, _MAPPED or _MAPPED_OUT");
+    if (path < EMB_HOST_AUTO || path > EMB_HOST_BOUNCE)
+        return fail(EMB_EINVAL, "host path must be EMB_HOST_AUTO, _COPY, _MAPPED, _MAPPED_OUT or _BOUNCE");
     std::lock_guard<std::mutex> lk(g_mu);
     g.host_path = path;
     return EMB_OK;
@@ -506,6 +509,8 @@ void emb_shutdown(void)
         for (auto &ev : g.ev)
             if (ev)
                 cudaEventDestroy(ev);
+        if (g.h_bounce)
+            cudaFreeHost(g.h_bounce);
         if (g.stream)
             cudaStreamDestroy(g.stream);
         if (g.stream_out)
@@ -845,6 +850,7 @@ int emb_reduce_partials(const void *const *parts_dev, uint32_t n_parts, uint32_t
  * synchronise, because every CUDA call costs several microseconds of host time. */
 constexpr uint64_t kPipelineMinBytes = 4ull << 20;
 constexpr uint64_t kMapInputsMaxBytes = 1ull << 20;  // inputs are read in place below this
+constexpr uint64_t kBounceMaxBytes = 1ull << 20;     // pageable calls up to this size go through the bounce arena
 constexpr uint32_t kMaxGroups = 32;
 
 /* Device-side alias of a host pointer when the GPU can address it directly (memory from
@@ -906,6 +912,43 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             in_mapped = false;
         if (nr_batches[t] && !(a_off[t] = (const uint32_t *)mapped_alias(offsets[t])))
             in_mapped = false;
+    }
+    // Small call on arrays the GPU cannot address (plain malloc / NumPy memory -- what the
+    // reference's callers pass): bounce through one page-locked arena.  The CPU copies a few
+    // hundred KB faster than the 3 T cudaMemcpyAsync calls of the staged path cost to enqueue
+    // (each CUDA call is several microseconds of host time), and the launch is the mapped one.
+    bool bounce = false;
+    if ((g.host_path == EMB_HOST_AUTO && !(in_mapped && out_mapped) && h2d_payload + d2h_payload <= kBounceMaxBytes) ||
+        g.host_path == EMB_HOST_BOUNCE) {
+        const size_t need = (size_t)(h2d_payload + d2h_payload) + 64;
+        if (g.bounce_cap < need) {
+            if (g.h_bounce)
+                cudaFreeHost(g.h_bounce);
+            g.h_bounce = nullptr;
+            g.bounce_cap = 0;
+            const size_t cap = std::max(need, (size_t)kBounceMaxBytes + 64);
+            CU(cudaHostAlloc((void **)&g.h_bounce, cap, cudaHostAllocMapped | cudaHostAllocPortable));
+            g.bounce_cap = cap;
+        }
+        uint8_t *dev_base = nullptr;
+        CU(cudaHostGetDevicePointer((void **)&dev_base, g.h_bounce, 0));
+        size_t pos = 0;
+        for (uint32_t t = 0; t < T; t++) {  // indices, then offsets (4-byte items), then 16-byte aligned outputs
+            memcpy(g.h_bounce + pos, indices[t], (size_t)indices_len[t] * 4);
+            a_idx[t] = (const uint32_t *)(dev_base + pos);
+            pos += (size_t)indices_len[t] * 4;
+        }
+        for (uint32_t t = 0; t < T; t++) {
+            memcpy(g.h_bounce + pos, offsets[t], (size_t)nr_batches[t] * 4);
+            a_off[t] = (const uint32_t *)(dev_base + pos);
+            pos += (size_t)nr_batches[t] * 4;
+        }
+        pos = (pos + 15) & ~(size_t)15;
+        for (uint32_t t = 0; t < T; t++) {
+            a_out[t] = (float *)(dev_base + pos);
+            pos += (size_t)nr_batches[t] * D * 4;
+        }
+        bounce = in_mapped = out_mapped = true;
     }
     if (g.host_path == EMB_HOST_MAPPED && !(in_mapped && out_mapped))
         return fail(EMB_EINVAL, "EMB_HOST_MAPPED: a host array is not page-locked (cudaHostAlloc / "
@@ -995,7 +1038,8 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         g_grid[gi] = (uint32_t)chunk;
     }
 
-    cudaStream_t s_in = g.stream_in, s_k = g.stream, s_out = g.stream_out;
+    // nothing to stage: descriptors and launch share one stream (fewer CUDA calls per small lookup)
+    cudaStream_t s_k = g.stream, s_in = in_mapped ? s_k : g.stream_in, s_out = g.stream_out;
     cudaEvent_t *ev = g.ev_pool.data();
     cudaEvent_t ev_begin = ev[3 * n_groups], ev_end = ev[3 * n_groups + 1];
     CU(cudaEventRecord(ev_begin, s_in));
@@ -1012,7 +1056,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
                     CU(cudaMemcpyAsync(g.d_off + t_oo[t], offsets[t], (size_t)nr_batches[t] * 4,
                                        cudaMemcpyHostToDevice, s_in));
             }
-        if (gi == 0 || !in_mapped) {
+        if (s_in != s_k) {
             CU(cudaEventRecord(ev[3 * gi], s_in));
             CU(cudaStreamWaitEvent(s_k, ev[3 * gi], 0));
         }
@@ -1034,7 +1078,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     CU(cudaStreamSynchronize(s_last));
     float ms = 0, k_ms = 0;
     g.last.h2d_ms = 0;
-    if (!in_mapped) {
+    if (s_in != s_k) {
         CU(cudaEventElapsedTime(&ms, ev_begin, ev[3 * (n_groups - 1)]));
         g.last.h2d_ms = ms;
     }
@@ -1052,7 +1096,16 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     g.last.h2d_bytes = h2d_payload + T * sizeof(BagDesc);
     g.last.d2h_bytes = d2h_payload;
     g.last.launches = launches;
-    g.last.path = (in_mapped && out_mapped) ? EMB_HOST_MAPPED : out_mapped ? EMB_HOST_MAPPED_OUT : EMB_HOST_COPY;
+    if (bounce) {
+        uint8_t *dev_base = nullptr;
+        CU(cudaHostGetDevicePointer((void **)&dev_base, g.h_bounce, 0));
+        for (uint32_t t = 0; t < T; t++)
+            if (nr_batches[t])
+                memcpy(final_results[t], g.h_bounce + ((uint8_t *)a_out[t] - dev_base), (size_t)nr_batches[t] * D * 4);
+        g.last.total_ms = (now_s() - t_begin) * 1e3;
+    }
+    g.last.path = bounce ? EMB_HOST_BOUNCE
+                  : (in_mapped && out_mapped) ? EMB_HOST_MAPPED : out_mapped ? EMB_HOST_MAPPED_OUT : EMB_HOST_COPY;
     return EMB_OK;
 }
 

@@ -115,7 +115,7 @@ def test_page_locked_arrays_take_the_mapped_path_and_match(emblib, D):
     """Host arrays in page-locked memory: the pooling kernel reads them and writes the results over
     PCIe itself (EMB_HOST_MAPPED, no staging copies); pageable arrays are staged (EMB_HOST_COPY).
     Both must give the oracle's bits."""
-    from pim_embedding_lookup_b200.dputypes import (EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED,
+    from pim_embedding_lookup_b200.dputypes import (EMB_HOST_AUTO, EMB_HOST_BOUNCE, EMB_HOST_COPY, EMB_HOST_MAPPED,
                                                     EMB_HOST_MAPPED_OUT)
     rng = np.random.default_rng(31 + D)
     T = 4
@@ -151,8 +151,15 @@ def test_page_locked_arrays_take_the_mapped_path_and_match(emblib, D):
     try:
         run(EMB_HOST_AUTO, pidx, poff, pres, EMB_HOST_MAPPED)      # small + all page-locked: one launch
         assert emblib.last_timings().launches == 1
-        run(EMB_HOST_AUTO, idxs, offs, None, EMB_HOST_COPY)        # pageable: staged both ways
-        run(EMB_HOST_AUTO, idxs, offs, pres, EMB_HOST_MAPPED_OUT)  # pageable inputs, page-locked results
+        total = sum(i.nbytes + o.nbytes + o.size * D * 4 for i, o in zip(idxs, offs))
+        small = total <= (1 << 20)
+        # pageable arrays: small calls bounce through the library's page-locked arena, large ones are staged
+        run(EMB_HOST_AUTO, idxs, offs, None, EMB_HOST_BOUNCE if small else EMB_HOST_COPY)
+        run(EMB_HOST_AUTO, idxs, offs, pres, EMB_HOST_BOUNCE if small else EMB_HOST_MAPPED_OUT)
+        run(EMB_HOST_BOUNCE, idxs, offs, None, EMB_HOST_BOUNCE)
+        assert emblib.last_timings().launches == 1
+        run(EMB_HOST_COPY, idxs, offs, None, EMB_HOST_COPY)
+        run(EMB_HOST_MAPPED_OUT, idxs, offs, pres, EMB_HOST_MAPPED_OUT)  # pageable inputs, page-locked results
         run(EMB_HOST_MAPPED_OUT, pidx, poff, pres, EMB_HOST_MAPPED_OUT)
         run(EMB_HOST_COPY, pidx, poff, pres, EMB_HOST_COPY)        # forced staging of page-locked arrays
         emblib.set_host_path(EMB_HOST_MAPPED)                      # forced mapping of pageable arrays: error
@@ -167,7 +174,7 @@ def test_page_locked_arrays_take_the_mapped_path_and_match(emblib, D):
         for r in own:
             emblib.check(lib.emb_host_register(r.ctypes.data, r.nbytes))
         try:
-            run(EMB_HOST_AUTO, idxs, offs, own, EMB_HOST_MAPPED_OUT)
+            run(EMB_HOST_MAPPED_OUT, idxs, offs, own, EMB_HOST_MAPPED_OUT)
         finally:
             for r in own:
                 emblib.check(lib.emb_host_unregister(r.ctypes.data))
