@@ -228,7 +228,9 @@ void emb_plan_destroy(emb_plan *plan);
  * sizes only. */
 uint64_t emb_plan_bytes(const emb_plan *plan);
 uint32_t emb_plan_grid(const emb_plan *plan);
-/* One-shot convenience: create, launch, destroy. */
+/* One-shot: upload the descriptors and launch on `stream`, asynchronously (no synchronise, no
+ * allocation); ordered with the caller's other work on that stream.  NULL stream = the library's
+ * own stream (emb_stream_sync(NULL) waits for it). */
 int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream);
 /* Non-zero once any launch has seen an out-of-range index (cleared by the call; syncs). */
 int emb_check_indices(void);

@@ -27,6 +27,7 @@ namespace {
 using emb::BagDesc;
 
 constexpr uint32_t kMaxTables = 1u << 16;
+constexpr int kRingSlots = 4;
 
 struct Table {
     void *dev = nullptr;
@@ -63,6 +64,12 @@ struct Ctx {
     BagDesc *d_descs = nullptr;
     BagDesc *h_descs = nullptr;  // pinned
     uint32_t desc_cap = 0;
+    // descriptor ring of emb_lookup_device
+    BagDesc *ring_h[4] = {nullptr, nullptr, nullptr, nullptr};
+    BagDesc *ring_d[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ring_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t ring_cap = 0;
+    int ring_next = 0;
     // page-locked bounce arena for small calls on pageable arrays
     uint8_t *h_bounce = nullptr;
     size_t bounce_cap = 0;
@@ -511,6 +518,14 @@ void emb_shutdown(void)
                 cudaEventDestroy(ev);
         if (g.h_bounce)
             cudaFreeHost(g.h_bounce);
+        for (int i = 0; i < kRingSlots; i++) {
+            if (g.ring_h[i])
+                cudaFreeHost(g.ring_h[i]);
+            if (g.ring_d[i])
+                cudaFree(g.ring_d[i]);
+            if (g.ring_ev[i])
+                cudaEventDestroy(g.ring_ev[i]);
+        }
         if (g.stream)
             cudaStreamDestroy(g.stream);
         if (g.stream_out)
@@ -772,20 +787,58 @@ void emb_plan_destroy(emb_plan *plan)
 uint64_t emb_plan_bytes(const emb_plan *plan) { return plan ? plan->bytes : 0; }
 uint32_t emb_plan_grid(const emb_plan *plan) { return plan ? plan->grid : 0; }
 
+/* One-shot, stream-ordered and asynchronous: the descriptors go through a small ring of
+ * page-locked slots (each guarded by an event so a slot is not rewritten before its upload has
+ * run), one cudaMemcpyAsync + one launch on the caller's stream, no allocation, no synchronise. */
 int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
 {
-    emb_plan *p = nullptr;
-    int rc = emb_plan_create(queries, n, &p);
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
     if (rc)
         return rc;
-    rc = emb_plan_launch(p, stream);
-    cudaError_t e = cudaStreamSynchronize(stream ? (cudaStream_t)stream : g.stream);
-    emb_plan_destroy(p);
-    if (rc)
-        return rc;
-    if (e != cudaSuccess)
-        return fail(EMB_ECUDA, "emb_lookup_device: %s", cudaGetErrorString(e));
-    return EMB_OK;
+    if (!queries || !n)
+        return fail(EMB_EINVAL, "emb_lookup_device: NULL/empty arguments");
+    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    if (g.ring_cap < n) {
+        CU(cudaDeviceSynchronize());
+        for (int i = 0; i < kRingSlots; i++) {
+            if (g.ring_h[i])
+                cudaFreeHost(g.ring_h[i]);
+            if (g.ring_d[i])
+                cudaFree(g.ring_d[i]);
+            g.ring_h[i] = nullptr;
+            g.ring_d[i] = nullptr;
+        }
+        g.ring_cap = 0;
+        const uint32_t cap = std::max(n, 64u);
+        for (int i = 0; i < kRingSlots; i++) {
+            CU(cudaMallocHost(&g.ring_h[i], cap * sizeof(BagDesc)));
+            CU(cudaMalloc(&g.ring_d[i], cap * sizeof(BagDesc)));
+            if (!g.ring_ev[i])
+                CU(cudaEventCreateWithFlags(&g.ring_ev[i], cudaEventDisableTiming));
+        }
+        g.ring_cap = cap;
+    }
+    const int slot = g.ring_next;
+    g.ring_next = (g.ring_next + 1) % kRingSlots;
+    CU(cudaEventSynchronize(g.ring_ev[slot]));  // the slot's previous upload has executed
+    BagDesc *h = g.ring_h[slot];
+    bool any_float = false;
+    for (uint32_t i = 0; i < n; i++)
+        any_float |= queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].kind == EMB_TABLE_FLOAT;
+    const Variant variant = pick_variant(any_float);
+    uint64_t chunk = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        uint32_t c = 0;
+        if ((rc = fill_desc(queries[i], &h[i], (uint32_t)chunk, variant.bags, &c)))
+            return rc;
+        chunk += c;
+    }
+    if (chunk > 0x7fffffffull)
+        return fail(EMB_EINVAL, "too many bags for one launch");
+    CU(cudaMemcpyAsync(g.ring_d[slot], h, n * sizeof(BagDesc), cudaMemcpyHostToDevice, s));
+    CU(cudaEventRecord(g.ring_ev[slot], s));
+    return launch_bag_sum(variant, g.ring_d[slot], n, (uint32_t)chunk, s);
 }
 
 int emb_check_indices(void)

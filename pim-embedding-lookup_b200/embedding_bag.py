@@ -34,6 +34,37 @@ def dpu_lookup(final_results_ptr: int, indices_ptr: int, offsets_ptr: int, dpu_s
                          int(latency_print))
 
 
+class DeviceBags:
+    """Device-resident hand-off to the MLPs: indices/offsets are torch CUDA tensors,
+    the pooled rows come back as ONE CUDA tensor [B, T, D] -- the layout interact_features
+    concatenates into (dlrm_dpu_pytorch.py:722-755) -- written by a single launch on torch's current
+    stream.  Nothing crosses PCIe; the call is asynchronous like any torch CUDA op.
+
+    indices: int32/uint32 CUDA tensors (int64 tensors are narrowed with .to(torch.int32));
+    offsets: bag start positions as in nn.EmbeddingBag (offsets[0] == 0)."""
+
+    def __init__(self, n_tables: int, dim: int):
+        self.T, self.D = n_tables, dim
+
+    def __call__(self, lS_i, lS_o, out=None):
+        import torch
+        T, D = self.T, self.D
+        B = int(lS_o[0].numel())
+        if out is None:
+            out = torch.empty((B, T, D), dtype=torch.float32, device=lS_i[0].device)
+        qs, keep = [], []
+        for t in range(T):
+            i = lS_i[t] if lS_i[t].dtype == torch.int32 else lS_i[t].to(torch.int32)
+            o = lS_o[t] if lS_o[t].dtype == torch.int32 else lS_o[t].to(torch.int32)
+            keep.append((i, o))
+            qs.append(dict(table_id=t, indices=i, offsets=o, out=out[:, t, :], out_stride=T * D))
+        emblib.lookup_device(qs, torch.cuda.current_stream())
+        for i, o in keep:  # the caching allocator must not hand these out before the launch has run
+            i.record_stream(torch.cuda.current_stream())
+            o.record_stream(torch.cuda.current_stream())
+        return out
+
+
 def install():
     """Patch torch.nn.EmbeddingBag.forward (idempotent).  Returns the original forward."""
     global _installed

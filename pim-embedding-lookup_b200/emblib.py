@@ -273,21 +273,7 @@ class Plan:
 
     def __init__(self, queries):
         self._keep = queries
-        n = len(queries)
-        arr = (EmbDevQuery * n)()
-        for i, q in enumerate(queries):
-            e = arr[i]
-            e.table_id = q["table_id"]
-            e.indices = _addr(q["indices"])
-            e.offsets = _addr(q["offsets"])
-            e.out = _addr(q.get("out"))
-            e.nr_batches = q["nr_batches"] if "nr_batches" in q else _numel(q["offsets"])
-            e.indices_len = q["indices_len"] if "indices_len" in q else _numel(q["indices"])
-            e.flags = q.get("flags", 0)
-            e.out_stride = q.get("out_stride", 0)
-            e.bags_per_rank = q.get("bags_per_rank", 0)
-            for r, p in enumerate(q.get("out_peer", ())):
-                e.out_peer[r] = _addr(p)
+        arr, n = _query_array(queries)
         h = C.c_void_p()
         check(load().emb_plan_create(arr, n, C.byref(h)), "emb_plan_create")
         self._h = h
@@ -309,6 +295,32 @@ class Plan:
             self.close()
         except Exception:
             pass
+
+
+def _query_array(queries):
+    n = len(queries)
+    arr = (EmbDevQuery * n)()
+    for i, q in enumerate(queries):
+        e = arr[i]
+        e.table_id = q["table_id"]
+        e.indices = _addr(q["indices"])
+        e.offsets = _addr(q["offsets"])
+        e.out = _addr(q.get("out"))
+        e.nr_batches = q["nr_batches"] if "nr_batches" in q else _numel(q["offsets"])
+        e.indices_len = q["indices_len"] if "indices_len" in q else _numel(q["indices"])
+        e.flags = q.get("flags", 0)
+        e.out_stride = q.get("out_stride", 0)
+        e.bags_per_rank = q.get("bags_per_rank", 0)
+        for r, p in enumerate(q.get("out_peer", ())):
+            e.out_peer[r] = _addr(p)
+    return arr, n
+
+
+def lookup_device(queries, stream=None) -> None:
+    """One-shot device-resident lookup (emb_lookup_device): same query dicts as Plan, asynchronous on
+    `stream` (a torch.cuda.Stream, a raw handle, or None for the library's stream)."""
+    arr, n = _query_array(queries)
+    check(load().emb_lookup_device(arr, n, _stream(stream)), "emb_lookup_device")
 
 
 def _addr(x):
