@@ -44,6 +44,11 @@ WORKLOADS = {
     "c5": dict(name="RM2-like: 32 tables x 500k rows x dim 128, batch 4096, pooling 80, zipf(1.05) indices",
                T=32, R=500_000, D=128, B=4096, pool=(80, 80), dist="zipf"),
     # configs[3] shape per GPU (dim 64): uniform, fixed pooling 10
+    # configs[2] lookup shape: Kaggle cardinalities (tools/visualize.py:949), dim 16, batch 39292, one index per bag
+    "c3": dict(name="Kaggle-cardinality tables x dim 16, batch 39292, pooling 1, uniform indices", T=26, R=10131227,
+               rows=[1460, 583, 10131227, 2202608, 305, 24, 12517, 633, 3, 93145, 5683, 8351593, 3194, 27, 14992,
+                     5461306, 10, 5652, 2173, 4, 7046547, 18, 15, 286181, 105, 142572],
+               D=16, B=39292, pool=(1, 1), dist="uniform"),
     "c4": dict(name="dim-64 tables: 26 x 1M rows x dim 64, batch 65536, pooling 10, uniform indices",
                T=26, R=1_000_000, D=64, B=65536, pool=(10, 10), dist="uniform"),
 }
@@ -76,18 +81,19 @@ def make_batch(w, seed, n_tables=None):
     T = w["T"] if n_tables is None else n_tables
     lo, hi = w["pool"]
     idx, off = [], []
-    for _ in range(T):
+    for t in range(T):
+        R = w["rows"][t] if "rows" in w else w["R"]
         lens = rng.integers(lo, hi + 1, size=w["B"])
         off.append(np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.uint32))
         n = int(lens.sum())
         if w["dist"] == "zipf":
             # power-law over a fixed random permutation of the row ids (duplicates kept)
             r = rng.zipf(1.05, size=n)
-            r = (r - 1) % w["R"]
-            perm = np.random.default_rng(99).permutation(w["R"]).astype(np.uint32)
+            r = (r - 1) % R
+            perm = np.random.default_rng(99).permutation(R).astype(np.uint32)
             idx.append(perm[r])
         else:
-            idx.append(rng.integers(0, w["R"], size=n, dtype=np.int64).astype(np.uint32))
+            idx.append(rng.integers(0, R, size=n, dtype=np.int64).astype(np.uint32))
     return idx, off
 
 
@@ -206,8 +212,9 @@ def time_torch_embeddingbag(tables_f32, idx, off, budget_s=10.0):
 def host_tables(w, n_tables, seed=1234):
     """Quantised int32 tables as export_emb would make them (U(-1/sqrt(R), 1/sqrt(R)) * 1e9)."""
     rng = np.random.default_rng(seed)
-    lim = int(1e9 / np.sqrt(w["R"]))
-    return [rng.integers(-lim, lim + 1, size=(w["R"], w["D"]), dtype=np.int32) for _ in range(n_tables)]
+    rows = w.get("rows", [w["R"]] * w["T"])
+    return [rng.integers(-int(1e9 / np.sqrt(rows[t])), int(1e9 / np.sqrt(rows[t])) + 1, size=(rows[t], w["D"]),
+                         dtype=np.int32) for t in range(n_tables)]
 
 
 def run_reference(args, w):
@@ -303,10 +310,11 @@ def run_b200(args, w):
 
     # tables: int32 fixed point as export_emb makes them, generated on the device
     gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
-    lim = int(1e9 / np.sqrt(R))
+    rows_t = w.get("rows", [R] * T)
     for t in range(T):
-        a = torch.randint(-lim, lim + 1, (R, D), dtype=torch.int32, device="cuda", generator=gen)
-        emblib.check(lib.emb_populate_table_device(t, R, a.data_ptr(), 0, EMB_TABLE_FIXED, stream.cuda_stream))
+        lim = int(1e9 / np.sqrt(rows_t[t]))
+        a = torch.randint(-lim, lim + 1, (rows_t[t], D), dtype=torch.int32, device="cuda", generator=gen)
+        emblib.check(lib.emb_populate_table_device(t, rows_t[t], a.data_ptr(), 0, EMB_TABLE_FIXED, stream.cuda_stream))
         del a
     torch.cuda.empty_cache()
 
@@ -459,7 +467,7 @@ def run_b200(args, w):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         T_s = min(T, 8)
-        tabs = [emblib.table_read(t, 0, R) for t in range(T_s)]
+        tabs = [emblib.table_read(t, 0, rows_t[t]) for t in range(T_s)]
         sidx, soff = batches[0][0][:T_s], batches[0][1][:T_s]
         ftabs = [x.astype(np.float32) * np.float32(1e-9) for x in tabs]
         tv, tth, treps = time_torch_embeddingbag(ftabs, sidx, soff)
@@ -505,10 +513,17 @@ def run_b200(args, w):
 def main():
     args = parse_args()
     w = WORKLOADS[args.workload]
+    # stdout carries exactly one JSON line: libraries that print banners there (NCCL's version line
+    # with NCCL_DEBUG=VERSION) are sent to stderr for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     if args.impl == "reference":
         run_reference(args, w)
     else:
         run_b200(args, w)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":

@@ -285,13 +285,14 @@ uint32_t lanes_for_dim(uint32_t D)
 /* Which kernel pools a launch, decided when the descriptors are built (the CTA -> bag
  * mapping depends on it). */
 struct Variant {
-    int kind;      // 0 generic, 1 bag-per-sub-warp (any table kind), 2 load-balanced (int32 only)
+    int kind;      // 0 generic, 1 bag-per-sub-warp (any table kind), 2 / 3 load-balanced per CTA / per warp (int32 only)
     int unroll;    // K
     int mult;      // bags per CTA / sub-warps per CTA
     uint32_t bags; // bags per CTA
 };
 
-Variant pick_variant(bool any_float)
+/* avg_pool = lookups per bag of the launch (0 = unknown). */
+Variant pick_variant(bool any_float, double avg_pool = 0.0)
 {
     Variant v;
     uint32_t D = g.shape.nr_cols;
@@ -304,13 +305,23 @@ Variant pick_variant(bool any_float)
         return v;
     }
     v.kind = g.variant ? g.variant : 2;
+    if (v.kind == 3 && lanes > 8)
+        v.kind = 2;  // the warp-autonomous kernel is for rows up to 128 bytes
     if (any_float)
         v.kind = 1;  // fp32 sums keep index order (embedding_lookup_idx.cc:33-77)
     // defaults from the sweeps in profiles/r1_sweeps.md (tools/sweep.py): 64-byte rows want many
     // small CTAs; 256-byte rows 8 rows in flight per lane and 4x the bags per CTA; 512-byte rows 2x
     v.unroll = g.unroll ? g.unroll : (lanes >= 16 ? 8 : 4);
     v.mult = (v.kind == 2) ? (g.bags_mult ? g.bags_mult : (lanes == 16 ? 4 : lanes > 16 ? 2 : 1)) : 1;
+    // one or two lookups per bag (Criteo-style single-index features): a CTA's fixed costs dominate,
+    // give it 4x the bags (C3 lookup shape: 76 -> 56 us, profiles/r1_sweeps.md)
+    if (v.kind == 2 && !g.bags_mult && avg_pool > 0.0 && avg_pool <= 4.0)
+        v.mult = 4;
     v.bags = emb::kThreads / lanes * v.mult;
+    if (v.kind == 3) {
+        v.mult = 1;
+        v.bags = emb::kThreads;  // 32 bags per warp
+    }
     return v;
 }
 
@@ -327,6 +338,19 @@ template <int LANES, int K, int MINB>
 void launch_balanced_k(int mult, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
 {
     constexpr int SUB = emb::kThreads / LANES;
+    static int carve = -2;  // measurement knob: EMB_CARVEOUT = preferred shared-memory carveout in percent
+    if (carve == -2) {
+        const char *e = getenv("EMB_CARVEOUT");
+        carve = e ? atoi(e) : -1;
+        if (carve >= 0) {
+            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB>,
+                                 cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB>,
+                                 cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB>,
+                                 cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        }
+    }
     if (mult == 4)
         emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
     else if (mult == 2)
@@ -345,9 +369,26 @@ void launch_balanced(const Variant &v, uint32_t grid, cudaStream_t s, const BagD
 }
 
 template <int LANES>
+void launch_warp(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+{
+    if constexpr (LANES <= 8) {
+        // no carveout preference on purpose: L1 capacity is what holds the row loads in flight, and
+        // the largest shared-memory carveout halves the throughput (profiles/r1_sweeps.md)
+        if (v.unroll == 8)
+            emb::bag_sum_warp_kernel<LANES, 8, 4><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+        else
+            emb::bag_sum_warp_kernel<LANES, 4, 6><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+    } else {
+        (void)v; (void)grid; (void)s; (void)d; (void)n;
+    }
+}
+
+template <int LANES>
 void launch_for_lanes(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
 {
-    if (v.kind == 2)
+    if (v.kind == 3)
+        launch_warp<LANES>(v, grid, s, d, n);
+    else if (v.kind == 2)
         launch_balanced<LANES>(v, grid, s, d, n);
     else
         launch_ordered<LANES>(v.unroll, grid, s, d, n);
@@ -475,8 +516,9 @@ int emb_set_unroll(int unroll)
 
 int emb_set_tuning(int variant, int unroll, int bags_mult)
 {
-    if (variant < 0 || variant > 2)
-        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp) or 2 (load-balanced)");
+    if (variant < 0 || variant > 3)
+        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp), 2 (load-balanced per CTA) "
+                                "or 3 (load-balanced per warp)");
     if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4)
         return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2 or 4");
     int rc = emb_set_unroll(unroll);
@@ -741,7 +783,14 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
     bool any_float = false;
     for (uint32_t i = 0; i < n; i++)
         any_float |= queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].kind == EMB_TABLE_FLOAT;
-    p->variant = pick_variant(any_float);
+    {
+        uint64_t li = 0, nb = 0;
+        for (uint32_t i = 0; i < n; i++) {
+            li += queries[i].indices_len;
+            nb += queries[i].nr_batches;
+        }
+        p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0);
+    }
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
         if ((rc = fill_desc(queries[i], &p->h[i], (uint32_t)chunk, p->variant.bags, &c))) {
@@ -826,7 +875,12 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
     bool any_float = false;
     for (uint32_t i = 0; i < n; i++)
         any_float |= queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].kind == EMB_TABLE_FLOAT;
-    const Variant variant = pick_variant(any_float);
+    uint64_t tot_li = 0, tot_nb = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        tot_li += queries[i].indices_len;
+        tot_nb += queries[i].nr_batches;
+    }
+    const Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0);
     uint64_t chunk = 0;
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
@@ -1045,7 +1099,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         n_groups = std::min(std::min(T, kMaxGroups), forced_groups);
     if ((rc = ensure_events(3 * n_groups + 2)))
         return rc;
-    const Variant variant = pick_variant(any_float);
+    const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0);
     std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
     {
         const uint64_t total = h2d_payload + d2h_payload;

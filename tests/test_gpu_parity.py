@@ -210,11 +210,11 @@ def test_large_call_pipelines_groups_with_mapped_results(emblib):
         assert np.array_equal(bits(got[t]), bits(want[t])), t
 
 
-TUNINGS = [(1, 4, 0), (1, 8, 0), (2, 4, 1), (2, 8, 1), (2, 4, 2), (2, 8, 4)]
+TUNINGS = [(1, 4, 0), (1, 8, 0), (2, 4, 1), (2, 8, 1), (2, 4, 2), (2, 8, 4), (3, 4, 0), (3, 8, 0)]
 
 
 @pytest.mark.parametrize("tuning", TUNINGS, ids=[f"v{v}k{k}m{m}" for v, k, m in TUNINGS])
-@pytest.mark.parametrize("D", [4, 16, 64, 128])
+@pytest.mark.parametrize("D", [4, 8, 16, 32, 64, 128])
 def test_kernel_variants_agree(emblib, tuning, D):
     """Every kernel variant (bag per sub-warp / load-balanced, rows in flight, bags per CTA)."""
     rng = np.random.default_rng(5)
@@ -235,7 +235,7 @@ def test_kernel_variants_agree(emblib, tuning, D):
         emblib.load().emb_set_tuning(0, 0, 0)
 
 
-@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("variant", [1, 2, 3])
 def test_overlapping_and_backward_bags(emblib, variant):
     """lookup() accepts any offsets: bag i covers [offsets[i], offsets[i+1]) on its own
     (emb_dpu_lookup.c:109-116), so bags may overlap or be empty because they run backwards."""

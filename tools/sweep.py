@@ -32,6 +32,7 @@ def main():
     w = dict(bench.WORKLOADS[args.workload])
     if args.rows:
         w["R"] = args.rows
+        w.pop("rows", None)
     if args.tables:
         w["T"] = args.tables
     T, R, D, B = w["T"], w["R"], w["D"], w["B"]
@@ -42,8 +43,9 @@ def main():
     gen = torch.Generator(device="cuda").manual_seed(1234)
     lim = int(1e9 / np.sqrt(R))
     for t in range(T):
-        a = torch.randint(-lim, lim + 1, (R, D), dtype=torch.int32, device="cuda", generator=gen)
-        emblib.check(lib.emb_populate_table_device(t, R, a.data_ptr(), 0, 1, stream.cuda_stream))
+        Rt = w["rows"][t] if "rows" in w and not args.rows else R
+        a = torch.randint(-lim, lim + 1, (Rt, D), dtype=torch.int32, device="cuda", generator=gen)
+        emblib.check(lib.emb_populate_table_device(t, Rt, a.data_ptr(), 0, 1, stream.cuda_stream))
         del a
     batches = [bench.make_batch(w, seed=123 + k) for k in range(2)]
     dev = [([torch.from_numpy(i.view(np.int32)).cuda() for i in idx], [torch.from_numpy(o.view(np.int32)).cuda() for o in off])
