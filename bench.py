@@ -51,6 +51,13 @@ WORKLOADS = {
                D=16, B=39292, pool=(1, 1), dist="uniform"),
     "c4": dict(name="dim-64 tables: 26 x 1M rows x dim 64, batch 65536, pooling 10, uniform indices",
                T=26, R=1_000_000, D=64, B=65536, pool=(10, 10), dist="uniform"),
+    # configs[3]: Criteo Terabyte cardinalities (tools/visualize.py:964), dim 64, 48 GB of
+    # tables sharded table-wise + row-wise over the ranks (sharded.ShardedTables), GLOBAL batch 65536
+    "c4tb": dict(name="Terabyte-cardinality tables: 26 tables up to 40M rows x dim 64 (48 GB), global batch 65536, "
+                      "pooling 10, uniform indices, table+row-wise sharded", T=26, R=39979771,
+                 rows=[39884406, 39043, 17289, 7420, 20263, 3, 7120, 1543, 63, 38532951, 2953546, 403346, 10, 2208,
+                       11938, 155, 4, 976, 14, 39979771, 25641295, 39664984, 585935, 12972, 108, 36],
+                 D=64, B=65536, pool=(10, 10), dist="uniform", sharded=True),
 }
 N_BATCHES = 4  # distinct index batches rotated through the timed steps
 
@@ -225,6 +232,11 @@ def run_reference(args, w):
     # bounded sample of the workload: the first T_s tables of one batch (same shapes and
     # distributions as the GPU arm); each step = one pass over the sample
     T_s = min(w["T"], 8)
+    if w.get("sharded"):
+        # the 40M-row tables are 10 GB each (plus an fp32 copy): the bounded sample takes the largest
+        # table that is cheap to build on the host (2.95M rows, 756 MB) and seven smaller ones
+        pick = [10, 22, 11, 1, 4, 2, 23, 14]
+        w = dict(w, rows=[w["rows"][t] for t in pick], T=len(pick))
     tabs = host_tables(w, T_s)
     idx, off = make_batch(w, seed=123, n_tables=T_s)
     import torch
@@ -510,6 +522,179 @@ def run_b200(args, w):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------
+# sharded arm (C4): ONE global problem cut over the ranks -- strong scaling
+# ---------------------------------------------------------------------------------------------
+
+def make_table_batch(w, t, seed):
+    """(indices, offsets) of global table t for one global batch; the same on every rank."""
+    rng = np.random.default_rng([seed, t])
+    lo, hi = w["pool"]
+    lens = rng.integers(lo, hi + 1, size=w["B"])
+    off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.uint32)
+    idx = rng.integers(0, w["rows"][t], size=int(lens.sum()), dtype=np.int64).astype(np.uint32)
+    return idx, off
+
+
+def run_sharded(args, w):
+    import torch
+    import torch.distributed as dist
+
+    from pim_embedding_lookup_b200 import emblib, sharding
+    from pim_embedding_lookup_b200.sharded import ShardedTables
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    torch.cuda.set_device(local)
+    if world == 1:  # ShardedTables wants a process group even for one rank
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29533")
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    lib = emblib.load()
+    rows, D, B = w["rows"], w["D"], w["B"]
+    T = len(rows)
+    P = (w["pool"][0] + w["pool"][1]) / 2.0
+    emblib.check(lib.emb_set_tuning(args.variant, args.unroll, args.mult))
+    st = ShardedTables(rows, D, B, lookups=[B * P] * T, hbm_budget=150e9)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+
+    # local shards: int32 fixed point as export_emb makes them, generated on the device
+    gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
+    for slot, sh in enumerate(st.local):
+        lim = int(1e9 / np.sqrt(rows[sh.table]))
+        a = torch.randint(-lim, lim + 1, (sh.rows, D), dtype=torch.int32, device="cuda", generator=gen)
+        st.populate_shard(slot, a, device_src=True, stream=stream)
+        del a
+    torch.cuda.empty_cache()
+
+    need = st.tables_needed()
+    host_batches = [{t: make_table_batch(w, t, 123 + k) for t in need} for k in range(N_BATCHES)]
+    plans, dev = [], []
+    for k, hb in enumerate(host_batches):
+        di = {t: torch.from_numpy(hb[t][0].view(np.int32)).cuda() for t in need}
+        do = {t: torch.from_numpy(hb[t][1].view(np.int32)).cuda() for t in need}
+        dev.append((di, do))
+        plans.append(st.make_plan(di, do, buffer=k % 2))
+    lookups_global = float(T * B * P)  # every (table, index) of the global batch, counted once
+    # algorithmic bytes of THIS rank's launch: every index of its shards' tables is read, a row-range
+    # shard fetches its fraction of the rows, every bag writes one row and reads one offset
+    my_bytes = sum(sharding.shard_cost(B * P, B, D, sh.rows / rows[sh.table]) for sh in st.local)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(k):
+        plans[k % N_BATCHES].launch(stream)
+        st.finish(stream, k % 2)
+
+    for k in range(max(args.warmup, 3)):
+        step(k)
+    sync_all()
+    if lib.emb_check_indices():
+        raise RuntimeError("out-of-range index in the synthetic batch")
+
+    K = args.steps
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = emblib.launch_count()
+    with ClockSampler(local) as clk:
+        sync_all()
+        e0.record(stream)
+        for k in range(K):
+            ev[k][0].record(stream)
+            plans[k % N_BATCHES].launch(stream)
+            ev[k][1].record(stream)
+            st.finish(stream, k % 2)
+        e1.record(stream)
+        sync_all()
+    gpu_launches = emblib.launch_count() - launches0
+    total_ms = e0.elapsed_time(e1)
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    t = torch.tensor([total_ms, kernel_ms, my_bytes / (kernel_ms * 1e-3) / 1e9], dtype=torch.float64, device="cuda")
+    tmax, tsum = t.clone(), t.clone()
+    dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    total_ms_max, kernel_ms_max, agg_gbps = float(tmax[0]), float(tmax[1]), float(tsum[2])
+    value = lookups_global * K / (total_ms_max * 1e-3)
+    peak, peak_src = load_peaks()
+    achieved = my_bytes / (kernel_ms * 1e-3) / 1e9  # rank 0's pooling launch
+
+    # ---- e2e: per step, this rank's index/offset arrays come from page-locked host memory and its
+    # [B/N, T, D] result goes back to page-locked host memory, all inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        pin = [{t: (torch.from_numpy(hb[t][0].view(np.int32)).pin_memory(),
+                    torch.from_numpy(hb[t][1].view(np.int32)).pin_memory()) for t in need} for hb in host_batches[:2]]
+        res_host = torch.empty((st.per, T, D), dtype=torch.float32).pin_memory()
+        h2d = sum(a.numel() * 4 + b.numel() * 4 for a, b in pin[0].values())
+        d2h = res_host.numel() * 4
+
+        def e2e_step(k):
+            di, do = dev[k % 2]
+            for tt in need:
+                di[tt].copy_(pin[k % 2][tt][0], non_blocking=True)
+                do[tt].copy_(pin[k % 2][tt][1], non_blocking=True)
+            plans[k % 2].launch(stream)
+            st.finish(stream, k % 2)
+            res_host.copy_(st.result(k % 2), non_blocking=True)
+            stream.synchronize()
+        for k in range(3):
+            e2e_step(k)
+        sync_all()
+        Ke = max(3, min(K, 50))
+        t0 = time.perf_counter()
+        for k in range(Ke):
+            e2e_step(k)
+        dt = time.perf_counter() - t0
+        te = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        dt = float(te[0])
+        e2e = {"value": lookups_global * Ke / dt, "unit": "lookups/s", "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": dt / Ke * 1e3, "steps": Ke,
+               "call": "ShardedTables.lookup per rank: pinned host indices/offsets -> HBM, pooling launch, peer-slab "
+                       "exchange + barrier, partial reduction, [B/N, T, D] rows -> pinned host; bytes are rank 0's"}
+
+    if rank == 0:
+        split = {str(tt): k for tt, (_, k) in st.split.items()}
+        out = {
+            "metric": "embedding lookups/sec", "value": value, "unit": "lookups/s", "n_gpus": world, "steps": K,
+            "warmup": max(args.warmup, 3), "ms_per_step": total_ms_max / K, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": w["name"], "tables": T, "dim": D, "global_batch": B,
+                       "lookups_per_step_global": int(lookups_global),
+                       "table_bytes_total": int(sum(rows) * D * 4),
+                       "l2": f"inputs larger than L2: {sum(rows) * D * 4 / 1e9:.1f} GB of tables over {world} GPU(s), "
+                             f"{N_BATCHES} rotating index batches",
+                       "exchange": "fused (peer-slab stores from the pooling kernel + barrier + partial reduction)",
+                       "placement": {"shards_on_rank0": len(st.local), "row_split_tables": split,
+                                     "planner_imbalance": round(st.plan.imbalance(), 4),
+                                     "hbm_bytes_per_rank": [int(x) for x in st.plan.hbm_bytes]},
+                       "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult},
+                       "parallelism": f"table-wise + row-wise over {world} rank(s), pooled rows to the sample's rank"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms,
+                         "kernel_ms_max_over_ranks": kernel_ms_max, "algorithmic_bytes_per_launch": my_bytes,
+                         "aggregate_GBps_all_ranks": agg_gbps, "note": "rank 0's pooling launch; bytes = indices + "
+                         "in-range rows + outputs + offsets of its shards (sharding.shard_cost)"},
+            "clocks": clk.summary(), "gpu_launches": int(gpu_launches),
+        }
+        if e2e:
+            out["e2e"] = e2e
+        print(json.dumps(out))
+    sync_all()
+    for p in plans:
+        p.close()
+    st.close()
+    emblib.shutdown()
+    dist.destroy_process_group()
+
+
 def main():
     args = parse_args()
     w = WORKLOADS[args.workload]
@@ -521,6 +706,8 @@ def main():
     sys.stdout = os.fdopen(real_stdout, "w")
     if args.impl == "reference":
         run_reference(args, w)
+    elif w.get("sharded"):
+        run_sharded(args, w)
     else:
         run_b200(args, w)
     sys.stdout.flush()

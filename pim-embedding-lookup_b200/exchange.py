@@ -85,7 +85,10 @@ class _DevView:
 class PeerSlabs:
     """Symmetric output slabs mapped across all ranks of `group` (one node, NVLink/NVSwitch)."""
 
-    def __init__(self, global_bags, tables_per_rank, dim, group=None, n_buffers=1):
+    def __init__(self, global_bags, tables_per_rank, dim, group=None, n_buffers=1, n_cols=None):
+        """tables_per_rank[r] = tables rank r owns (consecutive global ids, rank-major), or None with
+        n_cols = number of D-wide column blocks per sample when the placement is arbitrary
+        (sharded.ShardedTables addresses the blocks itself through out_peer_col)."""
         import torch
         import torch.distributed as dist
         from . import emblib
@@ -93,9 +96,12 @@ class PeerSlabs:
         self.group = group
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
-        assert len(tables_per_rank) == self.world
         self.per = bags_per_rank(global_bags, self.world)
-        self.first_table, self.t_global = table_ranges(tables_per_rank)
+        if tables_per_rank is None:
+            self.first_table, self.t_global = None, int(n_cols)
+        else:
+            assert len(tables_per_rank) == self.world
+            self.first_table, self.t_global = table_ranges(tables_per_rank)
         self.dim = dim
         self.stride = self.t_global * dim  # elements between consecutive samples in a slab
         self.n_buffers = n_buffers
@@ -121,7 +127,14 @@ class PeerSlabs:
     def out_peer(self, local_table: int, buffer: int = 0):
         """Per-rank destination of this rank's `local_table`: pass as emb_dev_query.out_peer with
         out_stride = self.stride and bags_per_rank = self.per."""
-        col = (self.first_table[self.rank] + local_table) * self.dim * 4
+        return self.out_peer_col(self.first_table[self.rank] + local_table, buffer)
+
+    def out_peer_col(self, col_block: int, buffer: int = 0):
+        """Per-rank destination of column block `col_block` (elements [col_block*D, (col_block+1)*D) of
+        every sample row)."""
+        if not 0 <= col_block < self.t_global:
+            raise ValueError(f"column block {col_block} outside the slab's {self.t_global}")
+        col = col_block * self.dim * 4
         return [b + buffer * self.slab_bytes + col for b in self.base]
 
     def local(self, buffer: int = 0, dtype="float32"):

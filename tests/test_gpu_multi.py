@@ -120,3 +120,79 @@ def test_exchange_two_gpus(tmp_path):
     for r in range(2):
         got = eval(open(tmp_path / f"ok{r}").read())
         assert got == {"fused": True, "nccl": True, "rowsplit": True, "no_oob": True}, (r, got)
+
+
+# ---- ShardedTables: planner placement + row-range shards + fused exchange + partial reduction ----
+
+def _sharded_worker(rank, world, port, tmp):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import torch
+    import torch.distributed as dist
+
+    import emb_oracle as eo
+    from pim_embedding_lookup_b200 import emblib
+    from pim_embedding_lookup_b200.sharded import ShardedTables
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                            device_id=torch.device("cuda", rank))
+    ok = {}
+    try:
+        D, B = 16, 2048
+        rows = [30000, 17, 5000, 1, 12000, 640, 26000]  # 30000- and 26000-row tables exceed the slab cap below
+        rng = np.random.default_rng(11)  # same on every rank: the global problem
+        tabs = [rng.integers(-2**31, 2**31, size=(r, D), dtype=np.int64).astype(np.int32) for r in rows]
+        batches = []
+        for k in range(3):
+            idx, off = [], []
+            for r in rows:
+                lens = rng.integers(0, 13, size=B)
+                off.append(np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.uint32))
+                idx.append(rng.integers(0, r, size=int(lens.sum())).astype(np.uint32))
+            batches.append((idx, off))
+        per = B // world
+        st = ShardedTables(rows, D, B, lookups=[B * 6] * len(rows), max_table_bytes=20000 * D * 4)
+        ok["split"] = sorted(st.split) == [0, 6] and all(len(st.plan.of_table(t)) >= 2 for t in (0, 6))
+        for slot, s in enumerate(st.local):
+            st.populate_shard(slot, tabs[s.table][s.row_lo:s.row_hi])
+        stream = torch.cuda.Stream()
+        need = st.tables_needed()
+        plans = []
+        for k, (idx, off) in enumerate(batches):
+            di = {t: torch.from_numpy(idx[t].view(np.int32)).cuda() for t in need}
+            do = {t: torch.from_numpy(off[t].view(np.int32)).cuda() for t in need}
+            plans.append(st.make_plan(di, do, buffer=k % 2))
+        torch.cuda.synchronize()
+        dist.barrier()
+        good = True
+        for k, (idx, off) in enumerate(batches):  # back to back, alternating buffers
+            got = st.lookup(plans[k], stream)
+            stream.synchronize()
+            want = np.stack(eo.lookup_rows(tabs, idx, off), axis=1)[rank * per:(rank + 1) * per]
+            good &= bool(np.array_equal(got.cpu().numpy().view(np.uint32), want.view(np.uint32)))
+        ok["bits"] = good
+        ok["no_oob"] = emblib.load().emb_check_indices() == 0
+        dist.barrier()
+        for p in plans:
+            p.close()
+        st.close()
+        emblib.shutdown()
+    finally:
+        open(os.path.join(tmp, f"ok{rank}"), "w").write(repr(ok))
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_sharded_tables(tmp_path, world):
+    torch = pytest.importorskip("torch")
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_sharded_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        got = eval(open(tmp_path / f"ok{r}").read())
+        assert got == {"split": True, "bits": True, "no_oob": True}, (r, got)

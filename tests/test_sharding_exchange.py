@@ -122,3 +122,18 @@ def test_all_to_all_layout_world2_gloo(tmp_path):
     s.close()
     mp.spawn(_exchange_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert [open(tmp_path / f"ok{r}").read() for r in range(2)] == ["1", "1"]
+
+
+def test_partial_columns_of_split_tables_are_dense_and_rank_independent():
+    from pim_embedding_lookup_b200 import sharding
+    from pim_embedding_lookup_b200.sharded import partial_columns
+    plan = sharding.plan_tables(TERABYTE, 64, 8, bags=65536, lookups=[65536 * 10] * 26, hbm_budget=12e9,
+                                max_table_bytes=6e9)
+    col, first, n = partial_columns(plan)
+    split = sorted({s.table for s in plan.shards if not s.whole})
+    assert sorted(first) == split and n == sum(len(plan.of_table(t)) for t in split)
+    assert sorted(col.values()) == list(range(n))          # every block used exactly once
+    for t in split:                                         # a table's parts are consecutive blocks, in part order
+        c0, k = first[t]
+        assert [col[(t, p)] for p in range(k)] == list(range(c0, c0 + k))
+    assert all((s.table, s.part) in col for s in plan.shards if not s.whole)
