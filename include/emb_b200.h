@@ -242,6 +242,35 @@ int emb_reduce_partials(const void *const *parts_dev, uint32_t n_parts, uint32_t
                         void *out_dev, uint32_t out_stride, uint64_t nr_bags, int is_raw_i32,
                         void *stream);
 
+/* ---- completion step of the fused exchange (one launch per batch) --------------------------- */
+
+/* One row-split table at the receiving rank: out[b*out_stride + j] = combine over s < n_parts of
+ * parts[s][b*part_stride + j], b < nr_bags, j < nr_cols (same arithmetic as emb_reduce_partials). */
+typedef struct emb_reduce_job {
+    const void *parts[EMB_MAX_PEERS]; /* DEVICE                                            */
+    void *out;                        /* DEVICE                                            */
+    uint32_t n_parts;
+    uint32_t part_stride; /* elements; 0 means nr_cols                                     */
+    uint32_t out_stride;  /* elements; 0 means nr_cols                                     */
+    uint32_t is_raw_i32;
+    uint64_t nr_bags;
+} emb_reduce_job;
+
+typedef struct emb_finish emb_finish;
+
+/* flag_blocks[r] = rank r's flag block (EMB_MAX_PEERS uint32, zeroed before first use, in memory
+ * from emb_device_alloc) as mapped in this process (emb_ipc_open for r != my_rank).  jobs may be
+ * NULL when n_jobs == 0 (no row-split table). */
+int emb_finish_create(void *const *flag_blocks, uint32_t n_ranks, uint32_t my_rank,
+                      const emb_reduce_job *jobs, uint32_t n_jobs, emb_finish **out);
+/* ONE kernel on `stream`, after the pooling launch of the same batch: signal every peer's flag
+ * block with `epoch`, wait until every peer has signalled `epoch` here, then run the reduce jobs.
+ * `epoch` must be the same on every rank for the same batch and grow by one per batch (start at
+ * 1).  A peer that has not arrived after 10 s sets the error word (emb_check_indices() != 0)
+ * instead of hanging the GPU. */
+int emb_finish_launch(emb_finish *f, uint32_t epoch, void *stream);
+void emb_finish_destroy(emb_finish *f);
+
 /* ---- memory helpers -------------------------------------------------------------------- */
 
 int emb_device_alloc(void **dev_ptr, size_t nbytes); /* cudaMalloc (IPC-exportable)         */

@@ -935,6 +935,102 @@ int emb_reduce_partials(const void *const *parts_dev, uint32_t n_parts, uint32_t
     return EMB_OK;
 }
 
+/* ---------------------------------------------------------------- exchange completion --- */
+
+}  // extern "C"
+
+struct emb_finish {
+    emb::FlagList flags;
+    uint32_t n_ranks = 0, my_rank = 0, n_jobs = 0, grid = 1;
+    emb::ReduceJob *d_jobs = nullptr;
+};
+
+extern "C" {
+
+int emb_finish_create(void *const *flag_blocks, uint32_t n_ranks, uint32_t my_rank, const emb_reduce_job *jobs,
+                      uint32_t n_jobs, emb_finish **out)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (!flag_blocks || !n_ranks || n_ranks > EMB_MAX_PEERS || my_rank >= n_ranks || !out || (n_jobs && !jobs))
+        return fail(EMB_EINVAL, "emb_finish_create: bad arguments");
+    emb_finish *f = new (std::nothrow) emb_finish();
+    if (!f)
+        return fail(EMB_ENOMEM, "out of host memory");
+    memset(&f->flags, 0, sizeof f->flags);
+    for (uint32_t r = 0; r < n_ranks; r++) {
+        if (!flag_blocks[r]) {
+            delete f;
+            return fail(EMB_EINVAL, "flag_blocks[%u] is NULL", r);
+        }
+        f->flags.p[r] = (uint32_t *)flag_blocks[r];
+    }
+    f->n_ranks = n_ranks;
+    f->my_rank = my_rank;
+    f->n_jobs = n_jobs;
+    const uint32_t D = g.shape.nr_cols;
+    uint64_t work = 0;
+    if (n_jobs) {
+        std::vector<emb::ReduceJob> h(n_jobs);
+        for (uint32_t j = 0; j < n_jobs; j++) {
+            const emb_reduce_job &q = jobs[j];
+            if (!q.n_parts || q.n_parts > EMB_MAX_PEERS || !q.out) {
+                delete f;
+                return fail(EMB_EINVAL, "reduce job %u: bad n_parts/out", j);
+            }
+            memset(&h[j], 0, sizeof h[j]);
+            for (uint32_t s = 0; s < q.n_parts; s++) {
+                if (!q.parts[s]) {
+                    delete f;
+                    return fail(EMB_EINVAL, "reduce job %u: parts[%u] is NULL", j, s);
+                }
+                h[j].parts[s] = (const uint32_t *)q.parts[s];
+            }
+            h[j].out = (uint32_t *)q.out;
+            h[j].n_parts = q.n_parts;
+            h[j].part_stride = q.part_stride ? q.part_stride : D;
+            h[j].out_stride = q.out_stride ? q.out_stride : D;
+            h[j].is_raw = q.is_raw_i32 ? 1u : 0u;
+            h[j].nr_bags = q.nr_bags;
+            work = std::max<uint64_t>(work, q.nr_bags * D);
+        }
+        cudaError_t e = cudaMalloc(&f->d_jobs, n_jobs * sizeof(emb::ReduceJob));
+        if (e == cudaSuccess)
+            e = cudaMemcpy(f->d_jobs, h.data(), n_jobs * sizeof(emb::ReduceJob), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            cudaFree(f->d_jobs);
+            delete f;
+            return fail(EMB_ECUDA, "emb_finish_create: %s", cudaGetErrorString(e));
+        }
+    }
+    // every thread handles ~4 elements of the largest job; one block when there is nothing to reduce
+    f->grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>((work + 1023) / 1024, (uint64_t)g.sm_count * 4));
+    *out = f;
+    return EMB_OK;
+}
+
+int emb_finish_launch(emb_finish *f, uint32_t epoch, void *stream)
+{
+    if (!f)
+        return fail(EMB_EINVAL, "NULL finish object");
+    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    emb::exchange_finish_kernel<<<f->grid, 256, 0, s>>>(f->flags, f->n_ranks, f->my_rank, epoch, f->d_jobs, f->n_jobs,
+                                                        g.shape.nr_cols, g.d_err);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+    return EMB_OK;
+}
+
+void emb_finish_destroy(emb_finish *f)
+{
+    if (!f)
+        return;
+    cudaFree(f->d_jobs);
+    delete f;
+}
+
 /* ---------------------------------------------------------------- host-pointer lookups -- */
 
 /* Shared body of lookup() and emb_lookup_ex().

@@ -802,4 +802,93 @@ __global__ void reduce_partials_kernel(PartList parts, uint32_t n_parts, uint32_
     }
 }
 
+/*
+ * Completion step of the fused exchange, ONE launch per batch: every rank's pooling kernel has
+ * stored its pooled rows (and raw partial sums of row-split tables) into the peers' slabs over
+ * NVLink; this kernel (stream-ordered after the pooling kernel, so those stores have been
+ * performed) tells every peer "my rows of batch `epoch` are in your slab", waits until every peer
+ * has said the same, and then adds up the partial sums of the row-split tables that landed here.
+ * It replaces an NCCL all-reduce of one int (~20 us at 8 ranks) plus one reduction launch per
+ * split table.
+ *
+ * flags.p[r] = rank r's flag block as mapped in THIS process (EMB_MAX_PEERS uint32 slots, slot q
+ * written by rank q).  Epochs only grow, a rank can be at most one epoch ahead of a peer, and the
+ * comparison is "slot - epoch >= 0" in wrap-around arithmetic, so one slot per peer is enough.
+ * Block 0 signals; every block waits on the LOCAL flag block only (blocks of this grid never wait
+ * on each other, so the grid need not be co-resident).  A peer that never arrives trips the
+ * timeout: bit 1 of the error word is set and the kernel returns instead of hanging the GPU.
+ */
+struct FlagList {
+    uint32_t *p[EMB_MAX_PEERS];
+};
+struct ReduceJob {
+    const uint32_t *parts[EMB_MAX_PEERS];
+    uint32_t *out;
+    uint32_t n_parts;
+    uint32_t part_stride;
+    uint32_t out_stride;
+    uint32_t is_raw;
+    uint64_t nr_bags;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t globaltimer_ns()
+{
+    uint64_t t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+__global__ void __launch_bounds__(256)
+exchange_finish_kernel(FlagList flags, uint32_t n_ranks, uint32_t my_rank, uint32_t epoch,
+                       const ReduceJob *__restrict__ jobs, uint32_t n_jobs, uint32_t dim,
+                       uint32_t *__restrict__ err_flag)
+{
+    const uint32_t tid = threadIdx.x;
+    if (blockIdx.x == 0 && tid < n_ranks && tid != my_rank)
+        st_release_sys(flags.p[tid] + my_rank, epoch);
+    if (tid < n_ranks && tid != my_rank) {
+        const uint32_t *slot = flags.p[my_rank] + tid;
+        const uint64_t t0 = globaltimer_ns();
+        while ((int32_t)(ld_acquire_sys(slot) - epoch) < 0) {
+            if (globaltimer_ns() - t0 > 10000000000ull) {  // 10 s: a peer died
+                atomicOr(err_flag, 2u);
+                break;
+            }
+            __nanosleep(64);
+        }
+    }
+    __syncthreads();
+    for (uint32_t j = 0; j < n_jobs; j++) {
+        const ReduceJob *job = jobs + j;
+        const uint64_t n = job->nr_bags * dim;
+        const uint32_t np = job->n_parts, ps = job->part_stride, os = job->out_stride;
+        uint32_t *__restrict__ out = job->out;
+        for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + tid; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+            const uint64_t b = i / dim;
+            const uint32_t c = (uint32_t)(i - b * dim);
+            if (job->is_raw) {
+                uint32_t acc = 0;
+                for (uint32_t s = 0; s < np; s++)
+                    acc += job->parts[s][b * ps + c];
+                out[b * os + c] = __float_as_uint(dequant(acc));
+            } else {
+                float acc = 0.f;
+                for (uint32_t s = 0; s < np; s++)
+                    acc = __fadd_rn(acc, __uint_as_float(job->parts[s][b * ps + c]));
+                out[b * os + c] = __float_as_uint(acc);
+            }
+        }
+    }
+}
+
 }  // namespace emb

@@ -113,6 +113,11 @@ class EmbDevQuery(Structure):
                 ("bags_per_rank", c_uint32), ("out_peer", c_void_p * EMB_MAX_PEERS)]
 
 
+class EmbReduceJob(Structure):  # include/emb_b200.h emb_reduce_job
+    _fields_ = [("parts", c_void_p * EMB_MAX_PEERS), ("out", c_void_p), ("n_parts", c_uint32),
+                ("part_stride", c_uint32), ("out_stride", c_uint32), ("is_raw_i32", c_uint32), ("nr_bags", c_uint64)]
+
+
 class EmbTimings(Structure):
     _fields_ = [("h2d_ms", c_double), ("kernel_ms", c_double), ("d2h_ms", c_double), ("total_ms", c_double),
                 ("h2d_bytes", c_uint64), ("d2h_bytes", c_uint64), ("launches", c_uint64), ("path", c_uint64)]

@@ -17,7 +17,7 @@ import subprocess
 import numpy as np
 
 from .dputypes import (EMB_MAX_PEERS, EMB_Q_RAW_SUMS, EMB_TABLE_FIXED, EMB_TABLE_FLOAT, DpuRuntimeTotals,
-                       EmbDevQuery, EmbIpcHandle, EmbShape, EmbTimings)
+                       EmbDevQuery, EmbIpcHandle, EmbReduceJob, EmbShape, EmbTimings)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "lib", "emblib.so")
@@ -73,6 +73,10 @@ def _declare(lib):
         "emb_check_indices": ([], C.c_int),
         "emb_reduce_partials": ([C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
                                  C.c_uint64, C.c_int, C.c_void_p], C.c_int),
+        "emb_finish_create": ([C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32, C.POINTER(EmbReduceJob), C.c_uint32,
+                               C.POINTER(C.c_void_p)], C.c_int),
+        "emb_finish_launch": ([C.c_void_p, C.c_uint32, C.c_void_p], C.c_int),
+        "emb_finish_destroy": ([C.c_void_p], None),
         "emb_device_alloc": ([C.POINTER(C.c_void_p), C.c_size_t], C.c_int),
         "emb_device_free": ([C.c_void_p], C.c_int),
         "emb_host_alloc": ([C.POINTER(C.c_void_p), C.c_size_t], C.c_int),

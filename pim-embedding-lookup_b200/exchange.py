@@ -106,8 +106,14 @@ class PeerSlabs:
         self.stride = self.t_global * dim  # elements between consecutive samples in a slab
         self.n_buffers = n_buffers
         self.slab_bytes = self.per * self.stride * 4
+        # one allocation: n_buffers slabs, then this rank's flag block (one uint32 slot per peer) for the
+        # completion kernel (emb_finish_launch)
+        self._flag_off = (self.slab_bytes * n_buffers + 255) // 256 * 256
         self._mine = C.c_void_p()
-        emblib.check(self.lib.emb_device_alloc(C.byref(self._mine), self.slab_bytes * n_buffers), "emb_device_alloc")
+        emblib.check(self.lib.emb_device_alloc(C.byref(self._mine), self._flag_off + 256), "emb_device_alloc")
+        zeros = np.zeros(64, dtype=np.uint32)
+        emblib.check(self.lib.emb_memcpy_h2d(C.c_void_p(self._mine.value + self._flag_off), zeros.ctypes.data, 256,
+                                             None), "emb_memcpy_h2d")  # synchronous: zero before any peer maps it
         h = EmbIpcHandle()
         emblib.check(self.lib.emb_ipc_export(self._mine, C.byref(h)), "emb_ipc_export")
         handles = [None] * self.world
@@ -123,6 +129,13 @@ class PeerSlabs:
             emblib.check(self.lib.emb_ipc_open(C.byref(ph), C.byref(p)), "emb_ipc_open")
             self.base.append(int(p.value))
         self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        # transport of the completion barrier: "kernel" = emb_finish_launch (flags in peer memory over
+        # NVLink, one launch), "nccl" = all-reduce of one int (comparator; EMB_BARRIER=nccl)
+        import os
+        self.barrier_kind = os.environ.get("EMB_BARRIER", "kernel")
+        self._epoch = 0
+        self._finishers = []
+        self._plain = self.make_finish([]) if self.barrier_kind == "kernel" else None
 
     def out_peer(self, local_table: int, buffer: int = 0):
         """Per-rank destination of this rank's `local_table`: pass as emb_dev_query.out_peer with
@@ -144,13 +157,57 @@ class PeerSlabs:
                      "<f4" if dtype == "float32" else "<i4")
         return torch.as_tensor(v, device="cuda")
 
-    def barrier(self):
-        """Stream-ordered completion barrier: when it has run on this rank's current stream, every
-        rank's pooling kernel (enqueued before its own barrier call) has finished storing."""
+    def make_finish(self, jobs):
+        """Completion object for this slab set: signal + wait + the given reduce jobs in one launch.
+        jobs: list of dicts(parts=[device addresses], out=address, part_stride, out_stride, nr_bags,
+        is_raw_i32).  All finish objects of one PeerSlabs share its flag block and epoch counter."""
+        from .dputypes import EmbReduceJob
+        from . import emblib
+        arr = (EmbReduceJob * max(1, len(jobs)))()
+        for j, q in enumerate(jobs):
+            for s_, p in enumerate(q["parts"]):
+                arr[j].parts[s_] = int(p)
+            arr[j].out = int(q["out"])
+            arr[j].n_parts = len(q["parts"])
+            arr[j].part_stride = q.get("part_stride", 0)
+            arr[j].out_stride = q.get("out_stride", 0)
+            arr[j].is_raw_i32 = int(q.get("is_raw_i32", 1))
+            arr[j].nr_bags = q["nr_bags"]
+        blocks = (C.c_void_p * self.world)(*[b + self._flag_off for b in self.base])
+        h = C.c_void_p()
+        emblib.check(self.lib.emb_finish_create(blocks, self.world, self.rank, arr if jobs else None, len(jobs),
+                                                C.byref(h)), "emb_finish_create")
+        self._finishers.append(h)
+        return h
+
+    def finish(self, finisher, stream=None):
+        """Launch a completion object on `stream` (default: torch's current stream).  Every rank must
+        call finish()/barrier() the same number of times in the same order."""
+        import torch
+        from . import emblib
+        self._epoch += 1
+        st = stream if stream is not None else torch.cuda.current_stream()
+        emblib.check(self.lib.emb_finish_launch(finisher, self._epoch & 0xffffffff, emblib._stream(st)),
+                     "emb_finish_launch")
+
+    def barrier(self, stream=None):
+        """Stream-ordered completion barrier: when it has run on this rank's stream, every rank's
+        pooling kernel (enqueued before its own barrier call) has finished storing."""
+        if self._plain is not None:
+            self.finish(self._plain, stream)
+            return
+        import torch
         import torch.distributed as dist
-        dist.all_reduce(self._flag, group=self.group)
+        if stream is None:
+            dist.all_reduce(self._flag, group=self.group)
+        else:
+            with torch.cuda.stream(stream):
+                dist.all_reduce(self._flag, group=self.group)
 
     def close(self):
+        for h in self._finishers:
+            self.lib.emb_finish_destroy(h)
+        self._finishers = []
         for r, b in enumerate(self.base):
             if r != self.rank and b:
                 self.lib.emb_ipc_close(C.c_void_p(b))

@@ -72,14 +72,21 @@ class ShardedTables:
         self.parts = (exchange.PeerSlabs(global_bags, None, dim, group=group, n_cols=self.n_part_cols,
                                          n_buffers=n_buffers) if self.n_part_cols else None)
         self._reduce_args = [[] for _ in range(n_buffers)]
-        if self.parts is not None:
-            for b in range(n_buffers):
+        self._finish = [None] * n_buffers
+        for b in range(n_buffers):
+            jobs = []
+            if self.parts is not None:
                 loc = self.parts.base[self.rank] + b * self.parts.slab_bytes
                 for t, (c0, k) in self.split.items():
-                    arr = (C.c_void_p * k)(*[loc + (c0 + p) * dim * 4 for p in range(k)])
+                    parts = [loc + (c0 + p) * dim * 4 for p in range(k)]
                     dst = self.out.base[self.rank] + b * self.out.slab_bytes + t * dim * 4
+                    jobs.append(dict(parts=parts, out=dst, part_stride=self.parts.stride, out_stride=self.out.stride,
+                                     nr_bags=self.per, is_raw_i32=1))
+                    arr = (C.c_void_p * k)(*parts)
                     self._reduce_args[b].append((arr, k, self.parts.stride, C.c_void_p(dst), self.out.stride,
                                                  self.per, 1))
+            if self.out.barrier_kind == "kernel":
+                self._finish[b] = self.out.make_finish(jobs)  # signal + wait + all reductions: one launch
 
     # ---- tables ------------------------------------------------------------------------------
     def populate_shard(self, slot, data, device_src=False, stream=None):
@@ -126,9 +133,10 @@ class ShardedTables:
         """Completion barrier of the fused exchange, then the partial-sum reduction of the split
         tables, both ordered on `stream` (a torch.cuda.Stream, the one the plan was launched on).
         When it has run, result(buffer) holds this rank's samples."""
-        import torch
-        with torch.cuda.stream(stream):
-            self.out.barrier()
+        if self._finish[buffer] is not None:
+            self.out.finish(self._finish[buffer], stream)
+            return
+        self.out.barrier(stream)  # EMB_BARRIER=nccl comparator: all-reduce, then one launch per split table
         st = emblib._stream(stream)
         for arr, k, pstride, dst, ostride, nb, raw in self._reduce_args[buffer]:
             emblib.check(self.lib.emb_reduce_partials(arr, k, pstride, dst, ostride, nb, raw, st),
