@@ -564,7 +564,7 @@ def run_sharded(args, w):
 
     # local shards: int32 fixed point as export_emb makes them, generated on the device
     gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
-    for slot, sh in enumerate(st.local):
+    for slot, sh in enumerate(st.slots):
         lim = int(1e9 / np.sqrt(rows[sh.table]))
         a = torch.randint(-lim, lim + 1, (sh.rows, D), dtype=torch.int32, device="cuda", generator=gen)
         st.populate_shard(slot, a, device_src=True, stream=stream)
@@ -582,7 +582,8 @@ def run_sharded(args, w):
     lookups_global = float(T * B * P)  # every (table, index) of the global batch, counted once
     # algorithmic bytes of THIS rank's launch: every index of its shards' tables is read, a row-range
     # shard fetches its fraction of the rows, every bag writes one row and reads one offset
-    my_bytes = sum(sharding.shard_cost(B * P, B, D, sh.rows / rows[sh.table]) for sh in st.local)
+    my_bytes = sum(sharding.shard_cost(B * P, B, D, 1.0) * (sh.bag_hi - sh.bag_lo) / B if sh.sliced else
+                   sharding.shard_cost(B * P, B, D, sh.rows / rows[sh.table]) for sh in st.local)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -662,6 +663,10 @@ def run_sharded(args, w):
 
     if rank == 0:
         split = {str(tt): k for tt, (_, k) in st.split.items()}
+        sliced = {}
+        for sh in st.plan.shards:
+            if sh.sliced:
+                sliced[str(sh.table)] = sliced.get(str(sh.table), 0) + 1
         out = {
             "metric": "embedding lookups/sec", "value": value, "unit": "lookups/s", "n_gpus": world, "steps": K,
             "warmup": max(args.warmup, 3), "ms_per_step": total_ms_max / K, "higher_is_better": True,
@@ -672,7 +677,7 @@ def run_sharded(args, w):
                        "l2": f"inputs larger than L2: {sum(rows) * D * 4 / 1e9:.1f} GB of tables over {world} GPU(s), "
                              f"{N_BATCHES} rotating index batches",
                        "exchange": "fused (peer-slab stores from the pooling kernel + barrier + partial reduction)",
-                       "placement": {"shards_on_rank0": len(st.local), "row_split_tables": split,
+                       "placement": {"shards_on_rank0": len(st.local), "row_split_tables": split, "bag_sliced_replicas": sliced,
                                      "planner_imbalance": round(st.plan.imbalance(), 4),
                                      "hbm_bytes_per_rank": [int(x) for x in st.plan.hbm_bytes]},
                        "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult},

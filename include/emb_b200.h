@@ -216,6 +216,12 @@ typedef struct emb_dev_query {
      * from the pooling kernel (fused all-to-all). */
     uint32_t bags_per_rank;
     void *out_peer[EMB_MAX_PEERS];
+    /* Bag slice: pool only bags [bag_first, bag_first + bag_count) of the nr_batches bags the arrays
+     * describe (bag_count == 0: all from bag_first on).  Bag numbering, bag bounds and output rows
+     * stay those of the whole batch, so several ranks holding a replica of a small table can each
+     * take a slice of the batch (data-parallel placement, no partial sums). */
+    uint32_t bag_first;
+    uint32_t bag_count;
 } emb_dev_query;
 
 typedef struct emb_plan emb_plan;

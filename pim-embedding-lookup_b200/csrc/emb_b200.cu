@@ -432,6 +432,11 @@ int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, uint32_t
     d->out_stride = q.out_stride ? q.out_stride : D;
     d->bags_per_rank = q.bags_per_rank;
     d->chunk_begin = chunk_begin;
+    if (q.bag_first > q.nr_batches || q.bag_count > q.nr_batches - q.bag_first)
+        return fail(EMB_EINVAL, "bag slice [%u, +%u) outside the %u bags of table %u", q.bag_first, q.bag_count,
+                    q.nr_batches, q.table_id);
+    d->bag_first = q.bag_first;
+    d->bag_end = q.bag_count ? q.bag_first + q.bag_count : q.nr_batches;
     if (d->out_stride < D)
         return fail(EMB_EINVAL, "out_stride %u < NR_COLS %u", d->out_stride, D);
     uint32_t flags = 0;
@@ -464,7 +469,7 @@ int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, uint32_t
     if (vec)
         flags |= emb::kDescVecStore;
     d->flags = flags;
-    *chunks = (q.nr_batches + per - 1) / per;
+    *chunks = (d->bag_end - d->bag_first + per - 1) / per;
     return EMB_OK;
 }
 
@@ -798,7 +803,11 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
             return rc;
         }
         chunk += c;
-        p->bytes += ((uint64_t)queries[i].indices_len + queries[i].nr_batches) * (4 * D + 4);
+        {  // a bag slice reads about its share of the indices (the host cannot see the device offsets)
+            const uint64_t nbq = p->h[i].bag_end - p->h[i].bag_first;
+            const uint64_t liq = queries[i].nr_batches ? (uint64_t)queries[i].indices_len * nbq / queries[i].nr_batches : 0;
+            p->bytes += (liq + nbq) * (4 * D + 4);
+        }
     }
     if (chunk > 0x7fffffffull) {
         delete p;

@@ -49,6 +49,9 @@ struct __align__(16) BagDesc {
     uint32_t bags_per_rank;
     uint32_t flags;
     uint32_t chunk_begin;  // first CTA of this query
+    uint32_t bag_first;    // the query covers bags [bag_first, bag_end) of the nr_batches in the arrays
+    uint32_t bag_end;
+    uint32_t pad_[2];
 };
 
 /* EMB_LD_MODE (build-time experiment switch):
@@ -183,8 +186,8 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__r
 
     const uint32_t B = d->nr_batches;
     const uint32_t ilen = d->indices_len;
-    const uint32_t b0 = (blockIdx.x - d->chunk_begin) * BAGS;
-    const uint32_t nb = min((uint32_t)BAGS, B - b0);
+    const uint32_t b0 = d->bag_first + (blockIdx.x - d->chunk_begin) * BAGS;
+    const uint32_t nb = min((uint32_t)BAGS, d->bag_end - b0);
     const uint32_t *__restrict__ g_idx = d->indices;
     const uint32_t *__restrict__ g_off = d->offsets;
 
@@ -335,8 +338,8 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
 
     const uint32_t B = d->nr_batches;
     const uint32_t ilen = d->indices_len;
-    const uint32_t b0 = (blockIdx.x - d->chunk_begin) * BAGS;
-    const uint32_t nb = min((uint32_t)BAGS, B - b0);
+    const uint32_t b0 = d->bag_first + (blockIdx.x - d->chunk_begin) * BAGS;
+    const uint32_t nb = min((uint32_t)BAGS, d->bag_end - b0);
     const uint32_t *__restrict__ g_idx = d->indices;
     const uint32_t *__restrict__ g_off = d->offsets;
 
@@ -527,10 +530,10 @@ bag_sum_warp_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t
     const BagDesc *__restrict__ d = descs + q;
 
     const uint32_t B = d->nr_batches;
-    const uint32_t b0 = (blockIdx.x - d->chunk_begin) * (WARPS * WB) + warp * WB;
-    if (b0 >= B)
+    const uint32_t b0 = d->bag_first + (blockIdx.x - d->chunk_begin) * (WARPS * WB) + warp * WB;
+    if (b0 >= d->bag_end)
         return;
-    const uint32_t nb = min((uint32_t)WB, B - b0);
+    const uint32_t nb = min((uint32_t)WB, d->bag_end - b0);
     const uint32_t ilen = d->indices_len;
     const uint32_t *__restrict__ g_idx = d->indices;
     const uint32_t *__restrict__ g_off = d->offsets;
@@ -717,9 +720,9 @@ bag_sum_generic_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
     const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
     const BagDesc *__restrict__ d = descs + q;
     const uint32_t B = d->nr_batches;
-    const uint32_t b = (blockIdx.x - d->chunk_begin) * BAGS + threadIdx.x / 32;
+    const uint32_t b = d->bag_first + (blockIdx.x - d->chunk_begin) * BAGS + threadIdx.x / 32;
     const uint32_t lane = threadIdx.x % 32;
-    if (b >= B)
+    if (b >= d->bag_end)
         return;
     const uint32_t ilen = d->indices_len;
     uint32_t start = (b == 0) ? 0u : min(__ldg(d->offsets + b), ilen);

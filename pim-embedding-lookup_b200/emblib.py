@@ -273,7 +273,8 @@ class Plan:
 
     `queries` is a list of dicts with keys table_id, indices, offsets, out (objects with
     .data_ptr(), e.g. torch CUDA tensors, or raw ints), optional indices_len, nr_batches,
-    out_stride, flags, bags_per_rank, out_peer.  The plan keeps references to the tensors."""
+    out_stride, flags, bags_per_rank, out_peer, bag_first, bag_count.  The plan keeps references to the
+    tensors."""
 
     def __init__(self, queries):
         self._keep = queries
@@ -315,6 +316,8 @@ def _query_array(queries):
         e.flags = q.get("flags", 0)
         e.out_stride = q.get("out_stride", 0)
         e.bags_per_rank = q.get("bags_per_rank", 0)
+        e.bag_first = q.get("bag_first", 0)
+        e.bag_count = q.get("bag_count", 0)
         for r, p in enumerate(q.get("out_peer", ())):
             e.out_peer[r] = _addr(p)
     return arr, n

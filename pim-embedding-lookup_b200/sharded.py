@@ -7,6 +7,8 @@ every (table, column) on its own DPU) and the DLRM fork does with whole tables p
 
 * `sharding.plan_tables` places whole tables (table-wise) and contiguous row ranges of big or
   hot tables (row-wise) on the ranks;
+* small tables may be replicated and shared by bags instead (each replica pools a slice of the
+  batch: data-parallel, nothing to add up afterwards);
 * every rank pools the WHOLE global batch for the shards it holds, in ONE launch of the pooling
   kernel; whole tables are dequantised in the kernel's epilogue and stored straight into the
   `[B/N, T, D]` slab of the rank that owns each sample (peer memory over NVLink, the fused
@@ -35,11 +37,11 @@ def partial_columns(plan):
     col, first = {}, {}
     n = 0
     for t in sorted({s.table for s in plan.shards if not s.whole}):
-        parts = plan.of_table(t)
-        first[t] = (n, len(parts))
-        for s in parts:
-            col[(t, s.part)] = n
-            n += 1
+        k = plan.of_table(t)[0].n_parts
+        first[t] = (n, k)
+        for p in range(k):
+            col[(t, p)] = n + p
+        n += k
     return col, first, n
 
 
@@ -58,11 +60,20 @@ class ShardedTables:
         self.per = exchange.bags_per_rank(global_bags, self.world)
         self.plan = sharding.plan_tables(self.rows, dim, self.world, lookups=lookups, bags=global_bags,
                                          hbm_budget=hbm_budget, max_table_bytes=max_table_bytes, level=level)
-        self.local = sorted(self.plan.of_rank(self.rank), key=lambda s: (s.table, s.part))
+        self.local = sorted(self.plan.of_rank(self.rank), key=lambda s: (s.table, s.part, s.bag_lo))
+        # table slots of this rank: one per distinct row range held (several bag slices of a replica
+        # share their slot); slots[i] is a representative shard, slot_of[j] the slot of local shard j
+        self.slots, self.slot_of, seen = [], [], {}
+        for s in self.local:
+            key = (s.table, s.row_lo, s.row_hi)
+            if key not in seen:
+                seen[key] = len(self.slots)
+                self.slots.append(s)
+            self.slot_of.append(seen[key])
         self.part_col, self.split, self.n_part_cols = partial_columns(self.plan)
         self.lib = emblib.load()
         dev = torch.cuda.current_device() if device is None else device
-        emblib.configure(max(1, len(self.local)), dim, 0, 0, device=dev)
+        emblib.configure(max(1, len(self.slots)), dim, 0, 0, device=dev)
         T = len(self.rows)
         # Output slabs are double-buffered: a peer may already be storing batch k+1 into this rank's
         # slab while this rank still reads batch k (the barrier of batch k+1 orders batch k+2 after
@@ -90,9 +101,10 @@ class ShardedTables:
 
     # ---- tables ------------------------------------------------------------------------------
     def populate_shard(self, slot, data, device_src=False, stream=None):
-        """Load local shard `slot` (index into self.local): its rows [row_lo, row_hi) of the global
-        table as int32 fixed point, row-major; `data` is a NumPy array or (device_src) a CUDA tensor."""
-        s = self.local[slot]
+        """Load table slot `slot` (index into self.slots): rows [row_lo, row_hi) of global table
+        slots[slot].table as int32 fixed point, row-major; `data` is a NumPy array or (device_src) a
+        CUDA tensor."""
+        s = self.slots[slot]
         if device_src:
             assert tuple(data.shape) == (s.rows, self.dim)
             emblib.check(self.lib.emb_populate_table_device(slot, s.rows, data.data_ptr(), 0, EMB_TABLE_FIXED,
@@ -113,15 +125,19 @@ class ShardedTables:
         offsets[t] are CUDA int32/uint32 tensors of table t for every t in tables_needed().  The
         pooled rows land in output buffer `buffer` (alternate 0, 1, ... between consecutive batches)."""
         qs = []
-        for slot, s in enumerate(self.local):
-            if s.whole:
-                qs.append(dict(table_id=slot, indices=indices[s.table], offsets=offsets[s.table], out=None,
-                               out_stride=self.out.stride, bags_per_rank=self.per,
-                               out_peer=self.out.out_peer_col(s.table, buffer)))
-            else:
-                qs.append(dict(table_id=slot, indices=indices[s.table], offsets=offsets[s.table], out=None,
-                               out_stride=self.parts.stride, bags_per_rank=self.per, flags=EMB_Q_RAW_SUMS,
-                               out_peer=self.parts.out_peer_col(self.part_col[(s.table, s.part)], buffer)))
+        for j, s in enumerate(self.local):
+            slot = self.slot_of[j]
+            if s.whole:  # all rows here (possibly a replica pooling only its slice of the bags): final rows
+                q = dict(table_id=slot, indices=indices[s.table], offsets=offsets[s.table], out=None,
+                         out_stride=self.out.stride, bags_per_rank=self.per,
+                         out_peer=self.out.out_peer_col(s.table, buffer))
+                if s.sliced:
+                    q.update(bag_first=s.bag_lo, bag_count=s.bag_hi - s.bag_lo)
+            else:        # a row range: raw int32 partial sums, added at the receiver
+                q = dict(table_id=slot, indices=indices[s.table], offsets=offsets[s.table], out=None,
+                         out_stride=self.parts.stride, bags_per_rank=self.per, flags=EMB_Q_RAW_SUMS,
+                         out_peer=self.parts.out_peer_col(self.part_col[(s.table, s.part)], buffer))
+            qs.append(q)
         return qs
 
     def make_plan(self, indices, offsets, buffer=0):

@@ -26,12 +26,18 @@ class Shard:
     row_lo: int     # first global row held
     row_hi: int     # one past the last
     rank: int
-    n_parts: int    # how many shards the table was cut into (1 = whole table)
+    n_parts: int    # how many row ranges the table was cut into (1 = all rows)
     part: int       # this shard's position among them
+    bag_lo: int = 0  # bag slice [bag_lo, bag_hi) of the global batch this shard pools (replicated small
+    bag_hi: int = 0  # table, data-parallel); bag_hi == 0 means every bag
 
     @property
     def rows(self):
         return self.row_hi - self.row_lo
+
+    @property
+    def sliced(self):
+        return self.bag_hi != 0
 
     @property
     def whole(self):
@@ -50,7 +56,7 @@ class Plan:
         return [s for s in self.shards if s.rank == rank]
 
     def of_table(self, table):
-        return sorted((s for s in self.shards if s.table == table), key=lambda s: s.part)
+        return sorted((s for s in self.shards if s.table == table), key=lambda s: (s.part, s.bag_lo))
 
     def imbalance(self):
         """max rank load / mean rank load (1.0 = perfectly level)."""
@@ -66,10 +72,23 @@ def shard_cost(lookups, bags, dim, frac=1.0):
 
 
 def plan_tables(rows, dim, world, lookups=None, bags=0, hbm_budget=150e9, max_table_bytes=None,
-                level=True, tolerance=1.10):
-    """rows[t] = rows of table t; lookups[t] = expected indices per call (default: equal).
-    hbm_budget: table bytes allowed per GPU.  max_table_bytes: largest slab kept whole
-    (default hbm_budget / 2).  level: also cut hot tables until LPT reaches max/mean <= tolerance."""
+                level=True, tolerance=1.01, min_rows=1024, replicate_max_bytes=256e6, bag_align=256):
+    """rows[t] = rows of table t; lookups[t] = expected indices per call (default: equal); bags = bags
+    per table per call (the global batch).  hbm_budget: table bytes allowed per GPU.
+    max_table_bytes: largest slab kept whole (default hbm_budget / 2).
+
+    Placement is longest-processing-time-first on shard_cost().  With level=True a unit that would
+    push the least-loaded rank above the mean load (x tolerance) is cut instead: the rank receives the
+    piece that fills it exactly to the mean and the remainder goes back into the queue
+    (water-filling), so the ranks end up level with about `world` extra cuts.  Two kinds of cut:
+
+    * a table of at most replicate_max_bytes is REPLICATED on the ranks that share it and cut by bags
+      (each replica pools a slice [bag_lo, bag_hi) of the batch, multiples of bag_align): no wasted
+      index reads, no partial sums -- the data-parallel placement of small tables;
+    * a larger table is cut by ROWS (pieces of at least min_rows): every piece reads the whole index
+      list, fetches the rows in its range and emits partial sums that the receiver adds.
+
+    level=False places whole units only."""
     T = len(rows)
     if lookups is None:
         lookups = [1.0] * T
@@ -77,55 +96,105 @@ def plan_tables(rows, dim, world, lookups=None, bags=0, hbm_budget=150e9, max_ta
         raise ValueError("need at least one rank and one table")
     cap = max_table_bytes if max_table_bytes is not None else hbm_budget / 2
     row_bytes = 4 * dim
-    parts = [max(1, -(-int(r * row_bytes) // int(cap))) for r in rows]
-    for t in range(T):
-        if parts[t] > rows[t]:
-            raise ValueError(f"table {t}: a single row does not fit the budget")
+    if row_bytes > cap:
+        raise ValueError("a single row does not fit the budget")
+    do_level = level and world > 1
 
-    def build(parts):
-        units = []
+    def replicable(t):
+        return bags >= 2 * bag_align and rows[t] * row_bytes <= min(replicate_max_bytes, cap)
+
+    # unit = (t, row_lo, row_hi, bag_lo, bag_hi); bag range (0, 0) = every bag
+    def cost(u):
+        t, lo, hi, blo, bhi = u
+        if bhi:
+            return shard_cost(lookups[t], bags, dim, 1.0) * (bhi - blo) / bags
+        return shard_cost(lookups[t], bags, dim, (hi - lo) / rows[t])
+
+    def build(fixed_target):
+        queue = []
         for t in range(T):
-            k = parts[t]
+            k = max(1, -(-int(rows[t] * row_bytes) // int(cap)))
+            if k > rows[t]:
+                raise ValueError(f"table {t}: a single row does not fit the budget")
             for p in range(k):
-                lo, hi = rows[t] * p // k, rows[t] * (p + 1) // k
-                frac = (hi - lo) / rows[t]
-                units.append((shard_cost(lookups[t], bags, dim, frac), (hi - lo) * row_bytes, t, lo, hi, k, p))
-        units.sort(key=lambda u: (-u[0], u[2], u[6]))
-        load, mem, out = [0.0] * world, [0.0] * world, []
-        for cost, nbytes, t, lo, hi, k, p in units:
-            # shards of one table go to distinct ranks when possible (they reuse the index list)
-            taken = {s.rank for s in out if s.table == t}
-            order = sorted(range(world), key=lambda r: (r in taken and k <= world, load[r], r))
-            for r in order:
-                if mem[r] + nbytes <= hbm_budget:
-                    break
-            else:
-                raise MemoryError(f"table {t} rows [{lo},{hi}) does not fit: {world} x {hbm_budget:.3g} B is full")
-            load[r] += cost
-            mem[r] += nbytes
-            out.append(Shard(t, lo, hi, r, k, p))
+                queue.append((t, rows[t] * p // k, rows[t] * (p + 1) // k, 0, 0))
+        load, mem = [0.0] * world, [0.0] * world
+        placed = []  # (unit, rank)
+        held = set()  # (t, row_lo, row_hi, rank): slabs already counted in mem
+
+        def nbytes(u, r):
+            return 0 if (u[0], u[1], u[2], r) in held else (u[2] - u[1]) * row_bytes
+
+        def put(u, r):
+            mem[r] += nbytes(u, r)
+            held.add((u[0], u[1], u[2], r))
+            load[r] += cost(u)
+            placed.append((u, r))
+
+        while queue:
+            # costliest first; among equals the big tables first (whole, each on a rank of its own) and
+            # the replicable ones last: what is left for the end can then be cut by bags, the cheap kind
+            # of cut, to fill the ranks exactly
+            queue.sort(key=lambda u: (-cost(u), replicable(u[0]), -(u[2] - u[1]), u[0], u[1], u[3]))
+            u = queue.pop(0)
+            t, lo, hi, blo, bhi = u
+            n, c = hi - lo, cost(u)
+            target = fixed_target if fixed_target is not None else (sum(load) + c + sum(cost(v) for v in queue)) / world
+            taken = {r for (v, r) in placed if v[0] == t}
+            order = sorted(range(world), key=lambda r: (load[r], r in taken, r))
+            if do_level and load[order[0]] + c > target * tolerance:
+                room = target - load[order[0]]
+                if replicable(t) and n == rows[t]:
+                    b0, b1 = (blo, bhi) if bhi else (0, bags)
+                    take = int(room / (c / (b1 - b0))) // bag_align * bag_align
+                    q = next((q for q in order if mem[q] + nbytes(u, q) <= hbm_budget), None)
+                    if q is not None and bag_align <= take <= (b1 - b0) - bag_align:
+                        put((t, lo, hi, b0, b0 + take), q)
+                        queue.append((t, lo, hi, b0 + take, b1))
+                        continue
+                elif not bhi and n >= 2 * min_rows:
+                    q = next((q for q in order if mem[q] + min_rows * row_bytes <= hbm_budget), None)
+                    if q is None:
+                        raise MemoryError(f"table {t} rows [{lo},{hi}) does not fit: {world} x {hbm_budget:.3g} B is full")
+                    fixed = shard_cost(lookups[t], bags, dim, 0.0)
+                    var = (c - fixed) / n  # per row
+                    take = int((target - load[q] - fixed) / var) if var > 0 else n
+                    take = min(take, int((hbm_budget - mem[q]) // row_bytes), n - min_rows)
+                    if take >= min_rows:
+                        put((t, lo, lo + take, 0, 0), q)
+                        queue.append((t, lo + take, hi, 0, 0))
+                        continue
+            r = next((q for q in order if mem[q] + nbytes(u, q) <= hbm_budget), None)
+            if r is None:
+                # does not fit whole anywhere: give the emptiest rank the rows it can hold
+                q = max(range(world), key=lambda x: hbm_budget - mem[x])
+                take = min(int((hbm_budget - mem[q]) // row_bytes), n)
+                if bhi or take < 1 or take == n:
+                    raise MemoryError(f"table {t} rows [{lo},{hi}) does not fit: {world} x {hbm_budget:.3g} B is full")
+                put((t, lo, lo + take, 0, 0), q)
+                queue.append((t, lo + take, hi, 0, 0))
+                continue
+            put(u, r)
+        out = []
+        for t in range(T):
+            mine = sorted(((v, r) for (v, r) in placed if v[0] == t), key=lambda x: (x[0][1], x[0][3]))
+            ranges = sorted({(v[1], v[2]) for (v, _) in mine})
+            for (v, r) in mine:
+                out.append(Shard(t, v[1], v[2], r, len(ranges), ranges.index((v[1], v[2])), v[3], v[4]))
         return Plan(world, dim, out, load, mem)
 
-    plan = build(parts)
-    if level and world > 1:
-        # cut the costliest still-splittable table in two more pieces until level (or no gain)
-        for _ in range(4 * world):
-            if plan.imbalance() <= tolerance:
+    best = build(None)
+    if do_level:
+        # every cut by rows adds a shard's fixed cost (its index and output traffic), which the running
+        # mean cannot foresee: aim the next pass at the mean the last one ended with
+        plan = best
+        for _ in range(4):
+            if best.imbalance() <= tolerance:
                 break
-            hot = max(range(world), key=lambda r: plan.load[r])
-            cands = [s for s in plan.of_rank(hot) if s.rows >= 2 * 1024]
-            if not cands:
-                break
-            worst = max(cands, key=lambda s: shard_cost(lookups[s.table], bags, dim, s.rows / rows[s.table]))
-            trial = list(parts)
-            trial[worst.table] = min(world, parts[worst.table] * 2)
-            if trial == parts:
-                break
-            new = build(trial)
-            if new.imbalance() >= plan.imbalance() - 1e-9:
-                break
-            parts, plan = trial, new
-    return plan
+            plan = build(sum(plan.load) / world)
+            if plan.imbalance() < best.imbalance() - 1e-9:
+                best = plan
+    return best
 
 
 def bucket_indices(indices, offsets, row_lo, row_hi):

@@ -63,22 +63,23 @@ def test_struct_layouts():
     assert C.sizeof(dt.DpuRuntimeGroup) == 16
     assert C.sizeof(dt.QueryLen) == 8                        # emb_types.h:21-24, packed
     assert C.sizeof(dt.EmbShape) == 16
-    assert C.sizeof(dt.EmbDevQuery) == 16 + 3 * 8 + 8 + 8 * 8
+    assert C.sizeof(dt.EmbDevQuery) == 16 + 3 * 8 + 8 + 8 * 8 + 8
+    assert C.sizeof(dt.EmbReduceJob) == 8 * 8 + 8 + 4 * 4 + 8
     assert C.sizeof(dt.EmbTimings) == 4 * 8 + 4 * 8
     assert C.sizeof(dt.EmbIpcHandle) == 64
 
 
 def test_struct_sizes_agree_with_the_c_compiler(tmp_path):
     src = tmp_path / "sz.c"
-    src.write_text('#include "emb_b200.h"\n#include <stdio.h>\nint main(void){printf("%zu %zu %zu %zu %zu %zu\\n",'
+    src.write_text('#include "emb_b200.h"\n#include <stdio.h>\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu\\n",'
                    "sizeof(dpu_runtime_totals),sizeof(dpu_runtime_group),sizeof(struct query_len),"
-                   "sizeof(emb_dev_query),sizeof(emb_timings),sizeof(emb_shape));return 0;}\n")
+                   "sizeof(emb_dev_query),sizeof(emb_timings),sizeof(emb_shape),sizeof(emb_reduce_job));return 0;}\n")
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-std=gnu11", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True).stdout.split()]
     from pim_embedding_lookup_b200 import dputypes as dt
     want = [C.sizeof(x) for x in (dt.DpuRuntimeTotals, dt.DpuRuntimeGroup, dt.QueryLen, dt.EmbDevQuery,
-                                  dt.EmbTimings, dt.EmbShape)]
+                                  dt.EmbTimings, dt.EmbShape, dt.EmbReduceJob)]
     assert got == want
 
 

@@ -230,3 +230,41 @@ def test_full_size_microbench_properties(emblib):
     torch.cuda.synchronize()
     assert torch.equal(raws[0] + rb, rab)
     p2.close()
+
+
+@pytest.mark.parametrize("D,variant", [(16, 1), (16, 2), (16, 3), (64, 2), (128, 2), (6, 0)])
+def test_bag_slices_cover_the_batch(emblib, D, variant):
+    """bag_first / bag_count: queries that each take a slice of the bags (replicas of a small table on
+    several ranks) together produce exactly the whole batch's result; bags outside a slice are not
+    touched.  Slices include bag 0 (starts at 0 whatever offsets[0] says) and the last bag (ends at
+    indices_len)."""
+    rng = np.random.default_rng(9)
+    R, B = 1500, 777
+    emblib.configure(1, D)
+    assert emblib.load().emb_set_tuning(variant, 0, 0) == 0
+    q = rng.integers(-2**31, 2**31, size=(R, D), dtype=np.int64).astype(np.int32)
+    emblib.populate_table_i32(0, q)
+    i, o = ragged(rng, R, B, 15)
+    o[0] = 3  # ignored (emb_dpu_lookup.c:60-63)
+    want = eo.lookup_rows([q], [i], [o])[0]
+    di, do = u32(i), u32(o)
+    out = torch.full((B, D), float("nan"), dtype=torch.float32, device="cuda")
+    cuts = [0, 1, 64, 65, 300, 776, B]
+    # one plan with all slices (one launch) ...
+    plan = emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=out, bag_first=a, bag_count=b - a)
+                        for a, b in zip(cuts[:-1], cuts[1:])])
+    plan.launch(torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    assert np.array_equal(bits(out.cpu().numpy()), bits(want))
+    plan.close()
+    # ... and a single slice leaves the other bags alone; bag_count 0 = "to the end"
+    out.fill_(float("nan"))
+    plan = emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=out, bag_first=300)])
+    plan.launch(torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert np.isnan(got[:300]).all() and np.array_equal(bits(got[300:]), bits(want[300:]))
+    plan.close()
+    with pytest.raises(emblib.EmbError):
+        emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=out, bag_first=700, bag_count=100)])
+    emblib.load().emb_set_tuning(0, 0, 0)

@@ -151,9 +151,12 @@ def _sharded_worker(rank, world, port, tmp):
                 idx.append(rng.integers(0, r, size=int(lens.sum())).astype(np.uint32))
             batches.append((idx, off))
         per = B // world
-        st = ShardedTables(rows, D, B, lookups=[B * 6] * len(rows), max_table_bytes=20000 * D * 4)
+        hint = [B * 6] * len(rows)
+        hint[4] = B * 60  # planning hint only: a hot small table, which the planner replicates and shares by bags
+        st = ShardedTables(rows, D, B, lookups=hint, max_table_bytes=20000 * D * 4)
         ok["split"] = sorted(st.split) == [0, 6] and all(len(st.plan.of_table(t)) >= 2 for t in (0, 6))
-        for slot, s in enumerate(st.local):
+        ok["sliced"] = world == 1 or any(s.sliced for s in st.plan.shards)  # a replica shared by bags
+        for slot, s in enumerate(st.slots):
             st.populate_shard(slot, tabs[s.table][s.row_lo:s.row_hi])
         stream = torch.cuda.Stream()
         need = st.tables_needed()
@@ -195,4 +198,4 @@ def test_sharded_tables(tmp_path, world):
     mp.spawn(_sharded_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
     for r in range(world):
         got = eval(open(tmp_path / f"ok{r}").read())
-        assert got == {"split": True, "bits": True, "no_oob": True}, (r, got)
+        assert got == {"split": True, "sliced": True, "bits": True, "no_oob": True}, (r, got)

@@ -24,12 +24,24 @@ def test_planner_whole_tables_balanced():
     assert plan.imbalance() < 1.001
 
 
-def test_planner_levels_26_tables_over_8_ranks_by_row_splitting():
+def test_planner_levels_26_tables_over_8_ranks():
     from pim_embedding_lookup_b200 import sharding
     flat = sharding.plan_tables([1_000_000] * 26, 16, 8, bags=65536, level=False)
     assert flat.imbalance() > 1.2          # 4-vs-3 tables
+    # 64 MB tables are replicable: the two left-over tables are shared by bags, 4 replicas each
     plan = sharding.plan_tables([1_000_000] * 26, 16, 8, bags=65536, lookups=[688128] * 26)
-    assert plan.imbalance() < flat.imbalance()
+    assert plan.imbalance() < 1.01
+    sliced = sorted({s.table for s in plan.shards if s.sliced})
+    assert len(sliced) == 2 and all(s.whole for s in plan.shards)
+    for t in sliced:                        # the slices of a table tile the batch, on distinct ranks
+        parts = plan.of_table(t)
+        assert parts[0].bag_lo == 0 and parts[-1].bag_hi == 65536
+        assert all(a.bag_hi == b.bag_lo for a, b in zip(parts, parts[1:]))
+        assert all((s.bag_hi - s.bag_lo) % 256 == 0 for s in parts)
+        assert len({s.rank for s in parts}) == len(parts)
+    # tables too big to replicate are cut by rows instead
+    plan = sharding.plan_tables([1_000_000] * 26, 16, 8, bags=65536, lookups=[688128] * 26, replicate_max_bytes=0)
+    assert plan.imbalance() < flat.imbalance() and not any(s.sliced for s in plan.shards)
     for t in range(26):                     # every row of every table is held exactly once
         parts = plan.of_table(t)
         assert parts[0].row_lo == 0 and parts[-1].row_hi == 1_000_000

@@ -2,7 +2,7 @@
 # quick N-rank check of the two exchange-heavy workloads: tools/multi_gpu_quick.sh N tag [extra bench args]
 N=${1:-2}; TAG=${2:-q}; shift 2
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
-for wl in c4tb c2; do
+for wl in ${WL:-c4tb c2}; do
   timeout 300 $TR bench.py --gpus $N --workload $wl --steps 100 --warmup 10 --no-cpu-baseline --no-e2e "$@" \
       > gpurun_out/${wl}_n${N}_$TAG.json 2> gpurun_out/${wl}_n${N}_$TAG.err
   echo "$wl N=$N rc=$?"; python - <<PY
