@@ -70,6 +70,10 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--layout", default="sample", choices=["table", "sample"],
+                    help="peer-slab layout of the fused exchange: [T][B/N][D] or [B/N][T][D]")
+    ap.add_argument("--no-rotate", action="store_true",
+                    help="fused exchange: every rank walks the destination ranks in the same order (comparator)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--variant", type=int, default=0, help="kernel variant (emb_set_tuning); 0 = default")
@@ -341,7 +345,7 @@ def run_b200(args, w):
     # outputs + plans (descriptors uploaded once; a step is one kernel launch)
     slabs = None
     if world > 1 and args.exchange == "fused":
-        slabs = exchange.PeerSlabs(B, [T] * world, D)
+        slabs = exchange.PeerSlabs(B, [T] * world, D, layout=args.layout)
     per = B // world
     plans, keep = [], []
     for k, (di, do) in enumerate(dev_batches):
@@ -349,7 +353,8 @@ def run_b200(args, w):
         if slabs is not None:
             for t in range(T):
                 qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=None, out_stride=slabs.stride,
-                               bags_per_rank=per, out_peer=slabs.out_peer(t)))
+                               bags_per_rank=per, out_peer=slabs.out_peer(t),
+                               bag_rotate=0 if args.no_rotate else rank * per))
         elif world > 1:  # nccl: send buffer [N, B/N, T_local, D] == bag-major rows of stride T*D
             buf = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
             keep.append(buf)
@@ -498,7 +503,8 @@ def run_b200(args, w):
                        "lookups_per_step_per_gpu": int(np.mean(lookups)),
                        "l2": f"inputs larger than L2: tables {T * R * D * 4 / 1e9:.2f} GB per GPU, "
                              f"{N_BATCHES} rotating index batches",
-                       "exchange": ("none (1 GPU)" if world == 1 else args.exchange),
+                       "exchange": ("none (1 GPU)" if world == 1 else args.exchange +
+                                    (f", {args.layout}-major peer slabs" if args.exchange == "fused" else "")),
                        "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult},
                        "parallelism": f"table-wise x{world}, pooled rows to the sample's rank"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -558,7 +564,8 @@ def run_sharded(args, w):
     T = len(rows)
     P = (w["pool"][0] + w["pool"][1]) / 2.0
     emblib.check(lib.emb_set_tuning(args.variant, args.unroll, args.mult))
-    st = ShardedTables(rows, D, B, lookups=[B * P] * T, hbm_budget=150e9)
+    st = ShardedTables(rows, D, B, lookups=[B * P] * T, hbm_budget=150e9, layout=args.layout,
+                       rotate=not args.no_rotate)
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
 
@@ -632,7 +639,7 @@ def run_sharded(args, w):
     if not args.no_e2e:
         pin = [{t: (torch.from_numpy(hb[t][0].view(np.int32)).pin_memory(),
                     torch.from_numpy(hb[t][1].view(np.int32)).pin_memory()) for t in need} for hb in host_batches[:2]]
-        res_host = torch.empty((st.per, T, D), dtype=torch.float32).pin_memory()
+        res_host = torch.empty(tuple(st.result(0).shape), dtype=torch.float32).pin_memory()
         h2d = sum(a.numel() * 4 + b.numel() * 4 for a, b in pin[0].values())
         d2h = res_host.numel() * 4
 
@@ -676,7 +683,8 @@ def run_sharded(args, w):
                        "table_bytes_total": int(sum(rows) * D * 4),
                        "l2": f"inputs larger than L2: {sum(rows) * D * 4 / 1e9:.1f} GB of tables over {world} GPU(s), "
                              f"{N_BATCHES} rotating index batches",
-                       "exchange": "fused (peer-slab stores from the pooling kernel + barrier + partial reduction)",
+                       "exchange": f"fused: peer-slab stores from the pooling kernel ({args.layout}-major slabs) + one completion "
+                                   "kernel (flag barrier over NVLink + partial reduction)",
                        "placement": {"shards_on_rank0": len(st.local), "row_split_tables": split, "bag_sliced_replicas": sliced,
                                      "planner_imbalance": round(st.plan.imbalance(), 4),
                                      "hbm_bytes_per_rank": [int(x) for x in st.plan.hbm_bytes]},

@@ -222,6 +222,13 @@ typedef struct emb_dev_query {
      * take a slice of the batch (data-parallel placement, no partial sums). */
     uint32_t bag_first;
     uint32_t bag_count;
+    /* Order only, never results: pool the bags starting from bag_rotate (a bag id inside the slice,
+     * rounded down to the launch's bags-per-CTA) and wrap around.  With bags_per_rank set, rank r
+     * passes r * bags_per_rank so that at any moment every destination slab is being written by ONE
+     * sender instead of all of them (all ranks otherwise walk the destinations in the same order and
+     * N-1 senders pile onto one GPU's NVLink ingress). */
+    uint32_t bag_rotate;
+    uint32_t reserved_;
 } emb_dev_query;
 
 typedef struct emb_plan emb_plan;

@@ -470,6 +470,15 @@ int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, uint32_t
         flags |= emb::kDescVecStore;
     d->flags = flags;
     *chunks = (d->bag_end - d->bag_first + per - 1) / per;
+    d->n_chunks = *chunks;
+    // bag_rotate: start at the chunk holding that bag (rounded down to a chunk boundary) and wrap
+    d->chunk_rot = 0;
+    if (q.bag_rotate) {
+        if (q.bag_rotate < d->bag_first || q.bag_rotate >= d->bag_end)
+            return fail(EMB_EINVAL, "bag_rotate %u outside the query's bags [%u, %u)", q.bag_rotate, d->bag_first,
+                        d->bag_end);
+        d->chunk_rot = (q.bag_rotate - d->bag_first) / per;
+    }
     return EMB_OK;
 }
 

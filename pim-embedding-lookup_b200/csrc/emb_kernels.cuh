@@ -51,8 +51,18 @@ struct __align__(16) BagDesc {
     uint32_t chunk_begin;  // first CTA of this query
     uint32_t bag_first;    // the query covers bags [bag_first, bag_end) of the nr_batches in the arrays
     uint32_t bag_end;
-    uint32_t pad_[2];
+    uint32_t n_chunks;     // CTAs of this query
+    uint32_t chunk_rot;    // CTA c pools chunk (c + chunk_rot) mod n_chunks: ranks start at different bags
 };
+
+/* First bag of the chunk CTA `cta` (relative to the query) pools; `per` = bags per CTA. */
+__device__ __forceinline__ uint32_t chunk_first_bag(const BagDesc *d, uint32_t cta, uint32_t per)
+{
+    uint32_t c = cta + d->chunk_rot;
+    if (c >= d->n_chunks)
+        c -= d->n_chunks;
+    return d->bag_first + c * per;
+}
 
 /* EMB_LD_MODE (build-time experiment switch):
  *   0  rows: ld.global.nc.L1::no_allocate                       (default)
@@ -186,7 +196,7 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__r
 
     const uint32_t B = d->nr_batches;
     const uint32_t ilen = d->indices_len;
-    const uint32_t b0 = d->bag_first + (blockIdx.x - d->chunk_begin) * BAGS;
+    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, BAGS);
     const uint32_t nb = min((uint32_t)BAGS, d->bag_end - b0);
     const uint32_t *__restrict__ g_idx = d->indices;
     const uint32_t *__restrict__ g_off = d->offsets;
@@ -338,7 +348,7 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
 
     const uint32_t B = d->nr_batches;
     const uint32_t ilen = d->indices_len;
-    const uint32_t b0 = d->bag_first + (blockIdx.x - d->chunk_begin) * BAGS;
+    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, BAGS);
     const uint32_t nb = min((uint32_t)BAGS, d->bag_end - b0);
     const uint32_t *__restrict__ g_idx = d->indices;
     const uint32_t *__restrict__ g_off = d->offsets;
@@ -530,7 +540,7 @@ bag_sum_warp_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t
     const BagDesc *__restrict__ d = descs + q;
 
     const uint32_t B = d->nr_batches;
-    const uint32_t b0 = d->bag_first + (blockIdx.x - d->chunk_begin) * (WARPS * WB) + warp * WB;
+    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, WARPS * WB) + warp * WB;
     if (b0 >= d->bag_end)
         return;
     const uint32_t nb = min((uint32_t)WB, d->bag_end - b0);
@@ -720,7 +730,7 @@ bag_sum_generic_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
     const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
     const BagDesc *__restrict__ d = descs + q;
     const uint32_t B = d->nr_batches;
-    const uint32_t b = d->bag_first + (blockIdx.x - d->chunk_begin) * BAGS + threadIdx.x / 32;
+    const uint32_t b = chunk_first_bag(d, blockIdx.x - d->chunk_begin, BAGS) + threadIdx.x / 32;
     const uint32_t lane = threadIdx.x % 32;
     if (b >= d->bag_end)
         return;

@@ -111,7 +111,7 @@ class EmbDevQuery(Structure):
     _fields_ = [("table_id", c_uint32), ("nr_batches", c_uint32), ("indices_len", c_uint32), ("flags", c_uint32),
                 ("indices", c_void_p), ("offsets", c_void_p), ("out", c_void_p), ("out_stride", c_uint32),
                 ("bags_per_rank", c_uint32), ("out_peer", c_void_p * EMB_MAX_PEERS),
-                ("bag_first", c_uint32), ("bag_count", c_uint32)]
+                ("bag_first", c_uint32), ("bag_count", c_uint32), ("bag_rotate", c_uint32), ("reserved_", c_uint32)]
 
 
 class EmbReduceJob(Structure):  # include/emb_b200.h emb_reduce_job

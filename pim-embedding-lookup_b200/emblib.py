@@ -273,7 +273,7 @@ class Plan:
 
     `queries` is a list of dicts with keys table_id, indices, offsets, out (objects with
     .data_ptr(), e.g. torch CUDA tensors, or raw ints), optional indices_len, nr_batches,
-    out_stride, flags, bags_per_rank, out_peer, bag_first, bag_count.  The plan keeps references to the
+    out_stride, flags, bags_per_rank, out_peer, bag_first, bag_count, bag_rotate.  The plan keeps references to the
     tensors."""
 
     def __init__(self, queries):
@@ -318,6 +318,7 @@ def _query_array(queries):
         e.bags_per_rank = q.get("bags_per_rank", 0)
         e.bag_first = q.get("bag_first", 0)
         e.bag_count = q.get("bag_count", 0)
+        e.bag_rotate = q.get("bag_rotate", 0)
         for r, p in enumerate(q.get("out_peer", ())):
             e.out_peer[r] = _addr(p)
     return arr, n

@@ -7,11 +7,12 @@ sample's pooled rows must end up on the data-parallel rank that owns the sample
 
 Two transports:
 
-* `PeerSlabs` (fused): every rank owns one output slab [B/N, T_global, D] in cudaMalloc
-  memory, exported with CUDA IPC and mapped by all peers.  The pooling kernel itself stores
-  bag b of table t at slab[b // (B/N)][b % (B/N), t, :] (emb_dev_query.bags_per_rank /
-  out_peer, include/emb_b200.h), so the rows cross NVLink as they are produced and the only
-  collective left is the completion barrier.
+* `PeerSlabs` (fused): every rank owns one output slab [T_global, B/N, D] (or sample-major
+  [B/N, T_global, D]) in cudaMalloc memory, exported with CUDA IPC and mapped by all peers.  The
+  pooling kernel itself stores bag b of table t into the slab of rank b // (B/N), row b % (B/N) of
+  table t (emb_dev_query.bags_per_rank / out_peer, include/emb_b200.h), so the rows cross NVLink
+  as they are produced and the only collective left is the completion step (emb_finish_launch:
+  flags in peer memory).
 * `nccl_all_to_all`: pool into a local [N, B/N, T_local, D] buffer, one
   `all_to_all_single`, comparator and fallback.
 
@@ -85,8 +86,16 @@ class _DevView:
 class PeerSlabs:
     """Symmetric output slabs mapped across all ranks of `group` (one node, NVLink/NVSwitch)."""
 
-    def __init__(self, global_bags, tables_per_rank, dim, group=None, n_buffers=1, n_cols=None):
-        """tables_per_rank[r] = tables rank r owns (consecutive global ids, rank-major), or None with
+    def __init__(self, global_bags, tables_per_rank, dim, group=None, n_buffers=1, n_cols=None, layout="sample"):
+        """layout "sample" (default): slab = [B/N][T_global][D], sample-major rows ready for the
+        interaction.  layout "table": slab = [T_global][B/N][D], one contiguous [B/N, D] block per table
+        -- the list of per-table tensors the DLRM fork's alltoall hands back
+        (extend_distributed.py:418-426).  Measured on C2 (dim 16): with all slabs in LOCAL memory the
+        table-major launch is 8 % faster (0.279 vs 0.301 ms, tools/route_probe.py: the sample-major
+        rows are 64-byte pieces at a 1664-byte stride), but with the slabs on NVLink peers it is the
+        other way round (N=4: 0.307 vs 0.293 ms; profiles/r1_multi_gpu.md), so sample-major is the
+        default for the exchange.
+        tables_per_rank[r] = tables rank r owns (consecutive global ids, rank-major), or None with
         n_cols = number of D-wide column blocks per sample when the placement is arbitrary
         (sharded.ShardedTables addresses the blocks itself through out_peer_col)."""
         import torch
@@ -103,9 +112,13 @@ class PeerSlabs:
             assert len(tables_per_rank) == self.world
             self.first_table, self.t_global = table_ranges(tables_per_rank)
         self.dim = dim
-        self.stride = self.t_global * dim  # elements between consecutive samples in a slab
+        if layout not in ("table", "sample"):
+            raise ValueError("layout must be 'table' or 'sample'")
+        self.layout = layout
+        # elements between consecutive samples of one table in a slab
+        self.stride = self.t_global * dim if layout == "sample" else dim
         self.n_buffers = n_buffers
-        self.slab_bytes = self.per * self.stride * 4
+        self.slab_bytes = self.per * self.t_global * dim * 4
         # one allocation: n_buffers slabs, then this rank's flag block (one uint32 slot per peer) for the
         # completion kernel (emb_finish_launch)
         self._flag_off = (self.slab_bytes * n_buffers + 255) // 256 * 256
@@ -147,15 +160,22 @@ class PeerSlabs:
         every sample row)."""
         if not 0 <= col_block < self.t_global:
             raise ValueError(f"column block {col_block} outside the slab's {self.t_global}")
-        col = col_block * self.dim * 4
+        col = col_block * self.dim * 4 * (1 if self.layout == "sample" else self.per)
         return [b + buffer * self.slab_bytes + col for b in self.base]
 
     def local(self, buffer: int = 0, dtype="float32"):
-        """This rank's slab as a torch tensor [B/N, T_global, D] (no copy)."""
+        """This rank's slab as a torch tensor (no copy): [T_global, B/N, D] for layout "table" (index it
+        by table to get the per-table [B/N, D] tensors the DLRM fork's alltoall returns), [B/N, T_global,
+        D] for layout "sample"."""
         import torch
-        v = _DevView(self.base[self.rank] + buffer * self.slab_bytes, (self.per, self.t_global, self.dim),
-                     "<f4" if dtype == "float32" else "<i4")
+        shape = (self.per, self.t_global, self.dim) if self.layout == "sample" else (self.t_global, self.per, self.dim)
+        v = _DevView(self.base[self.rank] + buffer * self.slab_bytes, shape, "<f4" if dtype == "float32" else "<i4")
         return torch.as_tensor(v, device="cuda")
+
+    def local_sample_major(self, buffer: int = 0):
+        """[B/N, T_global, D] view of this rank's slab whatever the layout (strided for "table")."""
+        x = self.local(buffer)
+        return x if self.layout == "sample" else x.permute(1, 0, 2)
 
     def make_finish(self, jobs):
         """Completion object for this slab set: signal + wait + the given reduce jobs in one launch.

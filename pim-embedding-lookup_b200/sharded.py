@@ -50,16 +50,19 @@ class ShardedTables:
     (the global mini-batch, divisible by the world size)."""
 
     def __init__(self, rows, dim, global_bags, lookups=None, group=None, hbm_budget=150e9,
-                 max_table_bytes=None, level=True, device=None, n_buffers=2):
+                 max_table_bytes=None, level=True, device=None, n_buffers=2, layout="sample", rotate=True,
+                 **plan_kwargs):
         import torch
         import torch.distributed as dist
         self.group = group
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
         self.rows, self.dim, self.bags = list(rows), dim, global_bags
+        self.rotate = rotate  # ranks start pooling at different bags: one sender per destination at a time
         self.per = exchange.bags_per_rank(global_bags, self.world)
         self.plan = sharding.plan_tables(self.rows, dim, self.world, lookups=lookups, bags=global_bags,
-                                         hbm_budget=hbm_budget, max_table_bytes=max_table_bytes, level=level)
+                                         hbm_budget=hbm_budget, max_table_bytes=max_table_bytes, level=level,
+                                         **plan_kwargs)
         self.local = sorted(self.plan.of_rank(self.rank), key=lambda s: (s.table, s.part, s.bag_lo))
         # table slots of this rank: one per distinct row range held (several bag slices of a replica
         # share their slot); slots[i] is a representative shard, slot_of[j] the slot of local shard j
@@ -79,18 +82,18 @@ class ShardedTables:
         # slab while this rank still reads batch k (the barrier of batch k+1 orders batch k+2 after
         # that read, so two buffers are enough).
         self.n_buffers = n_buffers
-        self.out = exchange.PeerSlabs(global_bags, None, dim, group=group, n_cols=T, n_buffers=n_buffers)
+        self.out = exchange.PeerSlabs(global_bags, None, dim, group=group, n_cols=T, n_buffers=n_buffers,
+                                      layout=layout)
         self.parts = (exchange.PeerSlabs(global_bags, None, dim, group=group, n_cols=self.n_part_cols,
-                                         n_buffers=n_buffers) if self.n_part_cols else None)
+                                         n_buffers=n_buffers, layout=layout) if self.n_part_cols else None)
         self._reduce_args = [[] for _ in range(n_buffers)]
         self._finish = [None] * n_buffers
         for b in range(n_buffers):
             jobs = []
             if self.parts is not None:
-                loc = self.parts.base[self.rank] + b * self.parts.slab_bytes
                 for t, (c0, k) in self.split.items():
-                    parts = [loc + (c0 + p) * dim * 4 for p in range(k)]
-                    dst = self.out.base[self.rank] + b * self.out.slab_bytes + t * dim * 4
+                    parts = [self.parts.out_peer_col(c0 + p, b)[self.rank] for p in range(k)]
+                    dst = self.out.out_peer_col(t, b)[self.rank]
                     jobs.append(dict(parts=parts, out=dst, part_stride=self.parts.stride, out_stride=self.out.stride,
                                      nr_bags=self.per, is_raw_i32=1))
                     arr = (C.c_void_p * k)(*parts)
@@ -127,16 +130,19 @@ class ShardedTables:
         qs = []
         for j, s in enumerate(self.local):
             slot = self.slot_of[j]
+            b_lo, b_hi = (s.bag_lo, s.bag_hi) if s.sliced else (0, self.bags)
+            rot = b_lo + (self.rank * self.per) % (b_hi - b_lo) if self.rotate else 0
             if s.whole:  # all rows here (possibly a replica pooling only its slice of the bags): final rows
                 q = dict(table_id=slot, indices=indices[s.table], offsets=offsets[s.table], out=None,
                          out_stride=self.out.stride, bags_per_rank=self.per,
                          out_peer=self.out.out_peer_col(s.table, buffer))
                 if s.sliced:
                     q.update(bag_first=s.bag_lo, bag_count=s.bag_hi - s.bag_lo)
+                q["bag_rotate"] = rot
             else:        # a row range: raw int32 partial sums, added at the receiver
                 q = dict(table_id=slot, indices=indices[s.table], offsets=offsets[s.table], out=None,
                          out_stride=self.parts.stride, bags_per_rank=self.per, flags=EMB_Q_RAW_SUMS,
-                         out_peer=self.parts.out_peer_col(self.part_col[(s.table, s.part)], buffer))
+                         out_peer=self.parts.out_peer_col(self.part_col[(s.table, s.part)], buffer), bag_rotate=rot)
             qs.append(q)
         return qs
 
@@ -165,8 +171,14 @@ class ShardedTables:
         return self.result(plan.buffer)
 
     def result(self, buffer=0):
-        """This rank's pooled rows, torch CUDA tensor [B/N, T, D] fp32 (no copy)."""
+        """This rank's pooled rows, torch CUDA tensor fp32 (no copy): [B/N, T, D] for the default layout
+        "sample"; [T, B/N, D] for layout "table" (result()[t] = table t's [B/N, D], the per-table list
+        the DLRM fork's alltoall returns)."""
         return self.out.local(buffer)
+
+    def result_sample_major(self, buffer=0):
+        """[B/N, T, D] view of result() whatever the layout."""
+        return self.out.local_sample_major(buffer)
 
     def close(self):
         if self.parts is not None:

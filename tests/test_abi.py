@@ -63,7 +63,7 @@ def test_struct_layouts():
     assert C.sizeof(dt.DpuRuntimeGroup) == 16
     assert C.sizeof(dt.QueryLen) == 8                        # emb_types.h:21-24, packed
     assert C.sizeof(dt.EmbShape) == 16
-    assert C.sizeof(dt.EmbDevQuery) == 16 + 3 * 8 + 8 + 8 * 8 + 8
+    assert C.sizeof(dt.EmbDevQuery) == 16 + 3 * 8 + 8 + 8 * 8 + 16
     assert C.sizeof(dt.EmbReduceJob) == 8 * 8 + 8 + 4 * 4 + 8
     assert C.sizeof(dt.EmbTimings) == 4 * 8 + 4 * 8
     assert C.sizeof(dt.EmbIpcHandle) == 64

@@ -265,6 +265,20 @@ def test_bag_slices_cover_the_batch(emblib, D, variant):
     got = out.cpu().numpy()
     assert np.isnan(got[:300]).all() and np.array_equal(bits(got[300:]), bits(want[300:]))
     plan.close()
+    # bag_rotate changes the order the bags are pooled in, never the result
+    for kw in (dict(bag_rotate=300), dict(bag_rotate=B - 1), dict(bag_first=65, bag_count=600, bag_rotate=400)):
+        out.fill_(float("nan"))
+        plan = emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=out, **kw)])
+        plan.launch(torch.cuda.current_stream())
+        torch.cuda.synchronize()
+        got = out.cpu().numpy()
+        a = kw.get("bag_first", 0)
+        b = a + kw["bag_count"] if "bag_count" in kw else B
+        assert np.array_equal(bits(got[a:b]), bits(want[a:b])), kw
+        assert np.isnan(got[:a]).all() and np.isnan(got[b:]).all()
+        plan.close()
     with pytest.raises(emblib.EmbError):
         emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=out, bag_first=700, bag_count=100)])
+    with pytest.raises(emblib.EmbError):
+        emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=out, bag_first=100, bag_count=100, bag_rotate=50)])
     emblib.load().emb_set_tuning(0, 0, 0)

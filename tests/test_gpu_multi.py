@@ -65,7 +65,7 @@ def _worker(rank, world, port, tmp):
         plan.launch(stream)
         slabs.barrier()
         torch.cuda.synchronize()
-        got = slabs.local().cpu().numpy()
+        got = slabs.local_sample_major().cpu().numpy()
         ok["fused"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
         plan.close()
 
@@ -83,15 +83,15 @@ def _worker(rank, world, port, tmp):
         lo, hi = (0, R // 3) if rank == 0 else (R // 3, R)
         emblib.populate_table_i32(T_local, tabs[0][lo:hi])
         emblib.check(emblib.load().emb_table_set_row_base(T_local, lo))
-        parts = exchange.PeerSlabs(B, [1, 1], D)  # slab [B/N, 2, D]: column block r = partial from rank r
+        parts = exchange.PeerSlabs(B, [1, 1], D, layout="table")  # slab [2, B/N, D]: block r = partial from rank r
         di, do = torch.from_numpy(idx[0].view(np.int32)).cuda(), torch.from_numpy(off[0].view(np.int32)).cuda()
         plan = emblib.Plan([dict(table_id=T_local, indices=di, offsets=do, out=None, out_stride=parts.stride,
                                  bags_per_rank=parts.per, out_peer=parts.out_peer(0), flags=EMB_Q_RAW_SUMS)])
         plan.launch(stream)
         parts.barrier()
-        loc = parts.local(dtype="int32")
+        loc = parts.local(dtype="int32")  # [2, B/N, D]: block r = partial from rank r
         res = torch.empty((per, D), dtype=torch.float32, device="cuda")
-        arr = (C.c_void_p * 2)(loc[:, 0, :].data_ptr(), loc[:, 1, :].data_ptr())
+        arr = (C.c_void_p * 2)(loc[0].data_ptr(), loc[1].data_ptr())
         emblib.check(emblib.load().emb_reduce_partials(arr, 2, parts.stride, res.data_ptr(), D, per, 1,
                                                        emblib._stream(stream)))
         torch.cuda.synchronize()
@@ -153,7 +153,8 @@ def _sharded_worker(rank, world, port, tmp):
         per = B // world
         hint = [B * 6] * len(rows)
         hint[4] = B * 60  # planning hint only: a hot small table, which the planner replicates and shares by bags
-        st = ShardedTables(rows, D, B, lookups=hint, max_table_bytes=20000 * D * 4)
+        st = ShardedTables(rows, D, B, lookups=hint, max_table_bytes=20000 * D * 4,
+                           layout="sample" if world == 1 else "table")
         ok["split"] = sorted(st.split) == [0, 6] and all(len(st.plan.of_table(t)) >= 2 for t in (0, 6))
         ok["sliced"] = world == 1 or any(s.sliced for s in st.plan.shards)  # a replica shared by bags
         for slot, s in enumerate(st.slots):
@@ -169,7 +170,8 @@ def _sharded_worker(rank, world, port, tmp):
         dist.barrier()
         good = True
         for k, (idx, off) in enumerate(batches):  # back to back, alternating buffers
-            got = st.lookup(plans[k], stream)
+            st.lookup(plans[k], stream)
+            got = st.result_sample_major(plans[k].buffer)
             stream.synchronize()
             want = np.stack(eo.lookup_rows(tabs, idx, off), axis=1)[rank * per:(rank + 1) * per]
             good &= bool(np.array_equal(got.cpu().numpy().view(np.uint32), want.view(np.uint32)))
