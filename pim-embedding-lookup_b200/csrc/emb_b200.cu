@@ -10,6 +10,8 @@
  */
 #include "emb_kernels.cuh"
 
+#include <cuda.h>  // CUtensorMap types only: cuTensorMapEncodeTiled is fetched with cudaGetDriverEntryPoint
+
 #include <errno.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -35,6 +37,7 @@ struct Table {
     uint64_t row_base = 0;
     int kind = 0;  // 0 = empty, EMB_TABLE_FIXED, EMB_TABLE_FLOAT
     bool sharded = false;
+    void *d_tmap = nullptr;  // CUtensorMap [rows][D] in device memory, built on first use by the TMA kernel
 };
 
 struct Ctx {
@@ -231,6 +234,10 @@ int table_alloc(Table *t, uint64_t rows, int kind)
         cudaFree(t->dev);
         t->dev = nullptr;
     }
+    if (t->d_tmap) {
+        cudaFree(t->d_tmap);
+        t->d_tmap = nullptr;
+    }
     size_t bytes = (size_t)rows * g.shape.nr_cols * 4;
     cudaError_t e = cudaMalloc(&t->dev, bytes);
     if (e != cudaSuccess) {
@@ -272,6 +279,45 @@ int grow(void **p, size_t *cap_elems, size_t want_elems, size_t elem)
     return EMB_OK;
 }
 
+/* 2-D tensor map [rows][D] (4-byte elements, box = one row) for the gather4 kernel.  Encoded on the
+ * host by the driver (entry point fetched through the runtime: no link-time libcuda dependency)
+ * and kept in device memory beside the table. */
+int ensure_tmap(Table *t)
+{
+    if (t->d_tmap)
+        return EMB_OK;
+    typedef CUresult (*EncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeTiled enc = nullptr;
+    if (!enc) {
+        cudaDriverEntryPointQueryResult qr;
+        void *fn = nullptr;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr);
+        if (e != cudaSuccess || !fn)
+            return fail(EMB_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+        enc = (EncodeTiled)fn;
+    }
+    const uint32_t D = g.shape.nr_cols;
+    if (t->rows > 0x7fffffffull)
+        return fail(EMB_EINVAL, "the TMA kernel addresses rows with int32 coordinates: %llu rows is too many",
+                    (unsigned long long)t->rows);
+    CUtensorMap tm;
+    memset(&tm, 0, sizeof tm);
+    cuuint64_t gdim[2] = {D, t->rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)D * 4};
+    cuuint32_t box[2] = {D, 1};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_INT32, 2, t->dev, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(EMB_ECUDA, "cuTensorMapEncodeTiled failed (%d) for a %llu x %u table", (int)r,
+                    (unsigned long long)t->rows, D);
+    CU(cudaMalloc(&t->d_tmap, sizeof tm));
+    CU(cudaMemcpy(t->d_tmap, &tm, sizeof tm, cudaMemcpyHostToDevice));
+    return EMB_OK;
+}
+
 uint32_t lanes_for_dim(uint32_t D)
 {
     if (D % 4 != 0)
@@ -285,7 +331,8 @@ uint32_t lanes_for_dim(uint32_t D)
 /* Which kernel pools a launch, decided when the descriptors are built (the CTA -> bag
  * mapping depends on it). */
 struct Variant {
-    int kind;      // 0 generic, 1 bag-per-sub-warp (any table kind), 2 / 3 load-balanced per CTA / per warp (int32 only)
+    int kind;      // 0 generic, 1 bag-per-sub-warp (any table kind), 2 / 3 load-balanced per CTA / per warp (int32 only),
+                   // 4 TMA gather4 (rows of 64..512 bytes, any table kind)
     int unroll;    // K
     int mult;      // bags per CTA / sub-warps per CTA
     uint32_t bags; // bags per CTA
@@ -307,8 +354,10 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0)
     v.kind = g.variant ? g.variant : 2;
     if (v.kind == 3 && lanes > 8)
         v.kind = 2;  // the warp-autonomous kernel is for rows up to 128 bytes
-    if (any_float)
-        v.kind = 1;  // fp32 sums keep index order (embedding_lookup_idx.cc:33-77)
+    if (v.kind == 4 && lanes < 4)
+        v.kind = 2;  // the TMA kernel is for rows of 64 bytes and more
+    if (any_float && v.kind != 4)
+        v.kind = 1;  // fp32 sums keep index order (embedding_lookup_idx.cc:33-77); kinds 1 and 4 do
     // defaults from the sweeps in profiles/r1_sweeps.md (tools/sweep.py): 64-byte rows want many
     // small CTAs; 256-byte rows 8 rows in flight per lane and 4x the bags per CTA; 512-byte rows 2x
     v.unroll = g.unroll ? g.unroll : (lanes >= 16 ? 8 : 4);
@@ -321,6 +370,10 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0)
     if (v.kind == 3) {
         v.mult = 1;
         v.bags = emb::kThreads;  // 32 bags per warp
+    }
+    if (v.kind == 4) {
+        v.mult = 1;
+        v.bags = (emb::kThreads / 32) * 4 * (32 / lanes);  // 4 bags per sub-warp
     }
     return v;
 }
@@ -384,9 +437,29 @@ void launch_warp(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc 
 }
 
 template <int LANES>
+void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+{
+    if constexpr (LANES >= 4) {
+        constexpr int WARPS = emb::kThreads / 32;
+        constexpr size_t smem = (size_t)WARPS * emb::kTmaStages * emb::kTmaStageBytes + WARPS * emb::kTmaStages * 8 +
+                                WARPS * (4 * (32 / LANES) + 1) * 4;
+        static bool once = false;
+        if (!once) {
+            cudaFuncSetAttribute(emb::bag_sum_tma_kernel<LANES, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            once = true;
+        }
+        emb::bag_sum_tma_kernel<LANES, 3><<<grid, emb::kThreads, smem, s>>>(d, n, g.d_err);
+    } else {
+        (void)grid; (void)s; (void)d; (void)n;
+    }
+}
+
+template <int LANES>
 void launch_for_lanes(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
 {
-    if (v.kind == 3)
+    if (v.kind == 4)
+        launch_tma<LANES>(grid, s, d, n);
+    else if (v.kind == 3)
         launch_warp<LANES>(v, grid, s, d, n);
     else if (v.kind == 2)
         launch_balanced<LANES>(v, grid, s, d, n);
@@ -414,14 +487,21 @@ int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_
 }
 
 /* Fill one descriptor from a query; returns the number of CTAs it needs. */
-int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, uint32_t per, uint32_t *chunks)
+int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, const Variant &variant, uint32_t *chunks)
 {
     if (q.table_id >= g.tables.size() || !g.tables[q.table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", q.table_id);
-    const Table &t = g.tables[q.table_id];
+    Table &t = g.tables[q.table_id];
+    const uint32_t per = variant.bags;
     uint32_t D = g.shape.nr_cols;
     memset(d, 0, sizeof *d);
     d->table = t.dev;
+    if (variant.kind == 4) {
+        int rc = ensure_tmap(&t);
+        if (rc)
+            return rc;
+        d->tmap = t.d_tmap;
+    }
     d->indices = q.indices;
     d->offsets = q.offsets;
     d->out = q.out;
@@ -530,9 +610,9 @@ int emb_set_unroll(int unroll)
 
 int emb_set_tuning(int variant, int unroll, int bags_mult)
 {
-    if (variant < 0 || variant > 3)
-        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp), 2 (load-balanced per CTA) "
-                                "or 3 (load-balanced per warp)");
+    if (variant < 0 || variant > 4)
+        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp), 2 (load-balanced per CTA), "
+                                "3 (load-balanced per warp) or 4 (TMA gather4)");
     if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4)
         return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2 or 4");
     int rc = emb_set_unroll(unroll);
@@ -558,9 +638,12 @@ void emb_shutdown(void)
     if (g.device_ready) {
         cudaSetDevice(g.device);
         cudaDeviceSynchronize();
-        for (Table &t : g.tables)
+        for (Table &t : g.tables) {
             if (t.dev)
                 cudaFree(t.dev);
+            if (t.d_tmap)
+                cudaFree(t.d_tmap);
+        }
         cudaFree(g.d_col);
         cudaFree(g.d_idx);
         cudaFree(g.d_off);
@@ -739,6 +822,7 @@ int emb_free_table(uint32_t table_id)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
     CU(cudaDeviceSynchronize());
     cudaFree(g.tables[table_id].dev);
+    cudaFree(g.tables[table_id].d_tmap);
     g.tables[table_id] = Table();
     return EMB_OK;
 }
@@ -807,7 +891,7 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
     }
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
-        if ((rc = fill_desc(queries[i], &p->h[i], (uint32_t)chunk, p->variant.bags, &c))) {
+        if ((rc = fill_desc(queries[i], &p->h[i], (uint32_t)chunk, p->variant, &c))) {
             delete p;
             return rc;
         }
@@ -902,7 +986,7 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
     uint64_t chunk = 0;
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
-        if ((rc = fill_desc(queries[i], &h[i], (uint32_t)chunk, variant.bags, &c)))
+        if ((rc = fill_desc(queries[i], &h[i], (uint32_t)chunk, variant, &c)))
             return rc;
         chunk += c;
     }
@@ -1246,7 +1330,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             q.out = out_mapped ? (void *)a_out[t] : (void *)(g.d_out + oo * D);
             q.out_stride = D;
             uint32_t c = 0;
-            if ((rc = fill_desc(q, &g.h_descs[t], (uint32_t)chunk, variant.bags, &c)))
+            if ((rc = fill_desc(q, &g.h_descs[t], (uint32_t)chunk, variant, &c)))
                 return rc;
             chunk += c;
             t_io[t] = io;

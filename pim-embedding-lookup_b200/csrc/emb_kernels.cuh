@@ -53,6 +53,8 @@ struct __align__(16) BagDesc {
     uint32_t bag_end;
     uint32_t n_chunks;     // CTAs of this query
     uint32_t chunk_rot;    // CTA c pools chunk (c + chunk_rot) mod n_chunks: ranks start at different bags
+    const void *tmap;      // CUtensorMap of the table in device memory (TMA kernel only), 64-byte aligned
+    uint64_t pad_;
 };
 
 /* First bag of the chunk CTA `cta` (relative to the query) pools; `per` = bags per CTA. */
@@ -700,6 +702,249 @@ bag_sum_warp_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t
         uint32_t row;
         if (bpr) {
             uint32_t rk = b / bpr;
+            obase = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
+            row = b - rk * bpr;
+        } else {
+            obase = reinterpret_cast<uint32_t *>(d->out);
+            row = b;
+        }
+        uint32_t *dst = obase + (size_t)row * out_stride + sl * 4;
+        if (flags & kDescVecStore) {
+            stg_stream16(dst, o);
+        } else {
+            dst[0] = o.x;
+            dst[1] = o.y;
+            dst[2] = o.z;
+            dst[3] = o.w;
+        }
+    }
+}
+
+/* ---- TMA (cp.async.bulk.tensor tile::gather4) variant ------------------------------------------
+ *
+ * bag_sum_tma_kernel: the row gathers are issued to the TMA unit instead of the LSU.  One
+ * `cp.async.bulk.tensor.2d ... tile::gather4` (SASS UTMALDG) fetches FOUR rows, named by four row
+ * coordinates, through a 2-D tensor map [rows][D] of the table into shared memory and signals an
+ * mbarrier with the byte count; rows never pass through registers or L1, so the number of rows in
+ * flight is set by shared memory (8 KB per warp here), not by the L1 miss capacity that bounds the
+ * LDG kernels.  Row ids outside the table -- a bad index, a row of another
+ * shard, the padding of the last group of four -- are simply out-of-bounds coordinates: the TMA
+ * unit zero-fills them, which is exactly "contributes nothing".
+ *
+ * Every warp is autonomous (no CTA barrier): it owns WB = 4 * (32/LANES) consecutive bags, walks their
+ * window of the index stream in stages of NR rows through a ring of STAGES shared-memory buffers,
+ * and each sub-warp of LANES lanes keeps the running sums of its 4 bags in registers, reading the
+ * rows of a bag from shared memory strictly in index order -- so fp32 tables are summed in the same
+ * order as the CPU path (embedding_lookup_idx.cc:33-77) and int32 tables need no atomics.
+ */
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t phase)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(phase)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void tma_gather4(void *dst_smem, const void *tmap, uint32_t r0, uint32_t r1, uint32_t r2,
+                                            uint32_t r3, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes "
+                 "[%0], [%1, {%2, %3, %4, %5, %6}], [%7];" ::"r"(smem_u32(dst_smem)),
+                 "l"(tmap), "r"(0), "r"(r0), "r"(r1), "r"(r2), "r"(r3), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+constexpr int kTmaStages = 4;
+constexpr int kTmaStageBytes = 2048;  // per warp and stage: NR = 2048 / row bytes rows
+
+template <int LANES, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
+bag_sum_tma_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__restrict__ err_flag)
+{
+    constexpr int ROWB = LANES * 16;
+    constexpr int NR = kTmaStageBytes / ROWB;  // rows per stage: 32 (64-byte rows) .. 4 (512-byte rows)
+    constexpr int SUBW = 32 / LANES;           // sub-warps per warp
+    constexpr int WB = 4 * SUBW;               // bags per warp: 4 per sub-warp
+    constexpr int WARPS = kThreads / 32;
+    constexpr int RPP = SUBW;                  // rows a warp reads per pass
+    static_assert(NR % 4 == 0 && NR <= 32, "a stage is a whole number of gather4 groups, one row id per lane");
+    extern __shared__ __align__(128) uint8_t tma_smem[];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t sub = lane / LANES, sl = lane % LANES;
+    uint8_t *buf = tma_smem + (size_t)warp * kTmaStages * kTmaStageBytes;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(tma_smem + (size_t)WARPS * kTmaStages * kTmaStageBytes) + warp * kTmaStages;
+    uint32_t *off = reinterpret_cast<uint32_t *>(tma_smem + (size_t)WARPS * kTmaStages * kTmaStageBytes + WARPS * kTmaStages * 8) +
+                    warp * (WB + 1);
+
+    const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
+    const BagDesc *__restrict__ d = descs + q;
+    const uint32_t B = d->nr_batches;
+    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, WARPS * WB) + warp * WB;
+    if (b0 >= d->bag_end)
+        return;
+    const uint32_t nb = min((uint32_t)WB, d->bag_end - b0);
+    const uint32_t ilen = d->indices_len;
+    const uint32_t *__restrict__ g_idx = d->indices;
+    const uint32_t *__restrict__ g_off = d->offsets;
+    const uint32_t flags = d->flags;
+    const uint32_t rows = d->rows;
+    const uint32_t row_base = d->row_base;
+    const void *tmap = d->tmap;
+    const bool is_float = flags & kDescFloat;
+
+    if (lane == 0) {
+        for (int s = 0; s < kTmaStages; s++)
+            mbar_init(&bars[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    // bag bounds (emb_dpu_lookup.c:60-63,109-110); entries past nb repeat the end of the last bag
+    for (uint32_t i = lane; i <= (uint32_t)WB; i += 32) {
+        const uint32_t b = b0 + min(i, nb);
+        const uint32_t v = (b == 0) ? 0u : (b >= B ? ilen : ldg_stream_u32(g_off + b));
+        off[i] = min(v, ilen);
+    }
+    __syncwarp();
+    bool nonmono = false;
+    for (uint32_t i = lane; i < nb; i += 32)
+        nonmono |= off[i] > off[i + 1];
+    nonmono = __any_sync(0xffffffffu, nonmono);
+
+    uint4 acc[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+        acc[j] = make_uint4(0u, 0u, 0u, 0u);
+    bool bad = false;
+
+    if (!nonmono) {
+        const uint32_t wlo = off[0], whi = off[nb];
+        const uint32_t n_stage = (whi - wlo + NR - 1) / NR;
+
+        auto issue = [&](uint32_t k) {
+            const uint32_t s = k % kTmaStages;
+            const uint32_t p = wlo + k * NR + lane;
+            uint32_t id = 0xffffffffu;  // out of bounds: zero-filled by the TMA unit
+            if (lane < (uint32_t)NR && p < whi) {
+                id = ldg_stream_u32(g_idx + p) - row_base;  // unsigned: rows below the shard wrap high
+                if (id >= rows) {
+                    bad = true;
+                    id = 0xffffffffu;
+                }
+            }
+            if (lane == 0)
+                mbar_expect_tx(&bars[s], kTmaStageBytes);
+            const uint32_t r0 = __shfl_sync(0xffffffffu, id, (lane * 4 + 0) & 31u);
+            const uint32_t r1 = __shfl_sync(0xffffffffu, id, (lane * 4 + 1) & 31u);
+            const uint32_t r2 = __shfl_sync(0xffffffffu, id, (lane * 4 + 2) & 31u);
+            const uint32_t r3 = __shfl_sync(0xffffffffu, id, (lane * 4 + 3) & 31u);
+            if (lane < (uint32_t)(NR / 4))
+                tma_gather4(buf + (size_t)s * kTmaStageBytes + (size_t)lane * 4 * ROWB, tmap, r0, r1, r2, r3, &bars[s]);
+        };
+
+        for (uint32_t k = 0; k < (uint32_t)kTmaStages && k < n_stage; k++)
+            issue(k);
+        uint32_t bag_lo = 0;  // first bag that may still have rows at or after the current stage
+        for (uint32_t k = 0; k < n_stage; k++) {
+            const uint32_t s = k % kTmaStages, phase = (k / kTmaStages) & 1u;
+            uint32_t spins = 0;
+            while (!mbar_try_wait(&bars[s], phase)) {
+                if (++spins > (1u << 24)) {  // the copy never arrived: report, do not hang the GPU
+                    atomicOr(err_flag, 4u);
+                    return;
+                }
+            }
+            const uint32_t p0 = wlo + k * NR, p1 = min(p0 + (uint32_t)NR, whi);
+            const uint8_t *src = buf + (size_t)s * kTmaStageBytes + sl * 16;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint32_t bag = sub + SUBW * j;  // interleaved: neighbouring bags go to different sub-warps
+                const uint32_t lo = max(off[bag], p0), hi = min(off[bag + 1], p1);
+                if (bag < nb) {
+                    for (uint32_t p = lo; p < hi; p++) {
+                        const uint4 v = *reinterpret_cast<const uint4 *>(src + (size_t)(p - p0) * ROWB);
+                        if (!is_float) {  // int32 wrap-around adds (emb_dpu_lookup.c:114)
+                            acc[j].x += v.x;
+                            acc[j].y += v.y;
+                            acc[j].z += v.z;
+                            acc[j].w += v.w;
+                        } else {          // fp32, strictly in index order
+                            acc[j].x = __float_as_uint(__fadd_rn(__uint_as_float(acc[j].x), __uint_as_float(v.x)));
+                            acc[j].y = __float_as_uint(__fadd_rn(__uint_as_float(acc[j].y), __uint_as_float(v.y)));
+                            acc[j].z = __float_as_uint(__fadd_rn(__uint_as_float(acc[j].z), __uint_as_float(v.z)));
+                            acc[j].w = __float_as_uint(__fadd_rn(__uint_as_float(acc[j].w), __uint_as_float(v.w)));
+                        }
+                    }
+                }
+            }
+            (void)bag_lo;
+            (void)RPP;
+            __syncwarp();  // every lane has read stage s: it may be refilled
+            if (k + kTmaStages < n_stage)
+                issue(k + kTmaStages);
+        }
+    } else {
+        // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t bag = sub + SUBW * j;
+            if (bag >= nb)
+                continue;
+            const uint4 *__restrict__ table = reinterpret_cast<const uint4 *>(d->table) + sl;
+            for (uint32_t p = off[bag]; p < off[bag + 1]; p++) {
+                const uint32_t id = __ldg(g_idx + p) - row_base;
+                if (id < rows) {
+                    const uint4 v = ldg_row16(table + (size_t)id * LANES);
+                    if (!is_float) {
+                        acc[j].x += v.x;
+                        acc[j].y += v.y;
+                        acc[j].z += v.z;
+                        acc[j].w += v.w;
+                    } else {
+                        acc[j].x = __float_as_uint(__fadd_rn(__uint_as_float(acc[j].x), __uint_as_float(v.x)));
+                        acc[j].y = __float_as_uint(__fadd_rn(__uint_as_float(acc[j].y), __uint_as_float(v.y)));
+                        acc[j].z = __float_as_uint(__fadd_rn(__uint_as_float(acc[j].z), __uint_as_float(v.z)));
+                        acc[j].w = __float_as_uint(__fadd_rn(__uint_as_float(acc[j].w), __uint_as_float(v.w)));
+                    }
+                } else {
+                    bad = true;
+                }
+            }
+        }
+    }
+    if (bad && !(flags & kDescSharded))
+        atomicOr(err_flag, 1u);
+
+    const uint32_t bpr = d->bags_per_rank;
+    const uint32_t out_stride = d->out_stride;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const uint32_t bag = sub + SUBW * j;
+        if (bag >= nb)
+            continue;
+        uint4 o = acc[j];
+        if (!is_float && !(flags & kDescRaw))  // post_process, emb_host.h:210
+            o = make_uint4(__float_as_uint(dequant(o.x)), __float_as_uint(dequant(o.y)),
+                           __float_as_uint(dequant(o.z)), __float_as_uint(dequant(o.w)));
+        const uint32_t b = b0 + bag;
+        uint32_t *obase;
+        uint32_t row;
+        if (bpr) {
+            const uint32_t rk = b / bpr;
             obase = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
             row = b - rk * bpr;
         } else {

@@ -13,6 +13,8 @@ import emb_oracle as eo
 
 pytestmark = pytest.mark.gpu
 
+torch = pytest.importorskip("torch")
+
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 DPU_FILES = sorted(glob.glob(os.path.join(GOLD, "ref_dpu_*.npz")))
 
@@ -24,6 +26,10 @@ def emblib():
     m.shutdown()
     yield m
     m.shutdown()
+
+
+def u32(a):  # torch has no uint32 arithmetic; carry the bits as int32
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.uint32).view(np.int32)).cuda()
 
 
 def bits(a):
@@ -210,7 +216,7 @@ def test_large_call_pipelines_groups_with_mapped_results(emblib):
         assert np.array_equal(bits(got[t]), bits(want[t])), t
 
 
-TUNINGS = [(1, 4, 0), (1, 8, 0), (2, 4, 1), (2, 8, 1), (2, 4, 2), (2, 8, 4), (3, 4, 0), (3, 8, 0)]
+TUNINGS = [(1, 4, 0), (1, 8, 0), (2, 4, 1), (2, 8, 1), (2, 4, 2), (2, 8, 4), (3, 4, 0), (3, 8, 0), (4, 0, 0)]
 
 
 @pytest.mark.parametrize("tuning", TUNINGS, ids=[f"v{v}k{k}m{m}" for v, k, m in TUNINGS])
@@ -235,7 +241,7 @@ def test_kernel_variants_agree(emblib, tuning, D):
         emblib.load().emb_set_tuning(0, 0, 0)
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4])
 def test_overlapping_and_backward_bags(emblib, variant):
     """lookup() accepts any offsets: bag i covers [offsets[i], offsets[i+1]) on its own
     (emb_dpu_lookup.c:109-116), so bags may overlap or be empty because they run backwards."""
@@ -338,3 +344,58 @@ def test_float_tables_match_reference_apply_emb(emblib):
             np.testing.assert_allclose(got[k], z[f"out{D}_{k}"], rtol=1e-5, atol=1e-7)
             want = eo.bag_sum_f32(z[f"w{D}_{k}"], z[f"idx{D}_{k}"], z[f"off{D}_{k}"])
             assert np.array_equal(bits(got[k]), bits(want))  # same order of adds -> same bits
+
+
+@pytest.mark.parametrize("D", [16, 32, 64, 128])
+def test_tma_kernel_float_tables_row_shards_and_bad_indices(emblib, D):
+    """Variant 4 (cp.async.bulk.tensor tile::gather4): fp32 tables summed in index order (bit-equal to
+    the ordered kernel), a row shard (indices outside contribute nothing: out-of-bounds TMA
+    coordinates are zero-filled), an out-of-range index on a whole table (flagged, contributes
+    nothing), empty bags, a window that is not a multiple of the stage size."""
+    from pim_embedding_lookup_b200.dputypes import EMB_TABLE_FLOAT
+    rng = np.random.default_rng(21)
+    R, B = 5000, 1237
+    emblib.configure(3, D)
+    lib = emblib.load()
+    w = rng.uniform(-1, 1, size=(R, D)).astype(np.float32)
+    q = rng.integers(-2**31, 2**31, size=(R, D), dtype=np.int64).astype(np.int32)
+    emblib.populate_table_f32(0, w, EMB_TABLE_FLOAT)
+    emblib.populate_table_i32(1, q)
+    lo, hi = 1000, 3500
+    emblib.populate_table_i32(2, q[lo:hi])
+    emblib.check(lib.emb_table_set_row_base(2, lo))
+    i, o = ragged(rng, R, B, 23)
+    outs = {}
+    for variant in (1, 4):
+        assert lib.emb_set_tuning(variant, 0, 0) == 0
+        f = torch.empty((B, D), dtype=torch.float32, device="cuda")
+        a = torch.empty((B, D), dtype=torch.float32, device="cuda")
+        s_ = torch.empty((B, D), dtype=torch.int32, device="cuda")
+        plan = emblib.Plan([dict(table_id=0, indices=u32(i), offsets=u32(o), out=f),
+                            dict(table_id=1, indices=u32(i), offsets=u32(o), out=a),
+                            dict(table_id=2, indices=u32(i), offsets=u32(o), out=s_, flags=1)])
+        plan.launch(torch.cuda.current_stream())
+        torch.cuda.synchronize()
+        outs[variant] = (f.cpu().numpy(), a.cpu().numpy(), s_.cpu().numpy())
+        plan.close()
+        assert lib.emb_check_indices() == 0
+    assert np.array_equal(bits(outs[4][0]), bits(outs[1][0]))  # fp32: same order of additions
+    assert np.array_equal(bits(outs[4][1]), bits(eo.lookup_rows([q], [i], [o])[0]))
+    keep = (i >= lo) & (i < hi)
+    masked = q.copy()
+    masked[:lo] = 0
+    masked[hi:] = 0
+    _, sums = eo.lookup_rows([masked], [i], [o], want_sums=True)
+    assert keep.any() and np.array_equal(outs[4][2], sums[0])
+    # one bad index on the whole table: flagged, and the bag gets the sum of its other rows
+    bad = i.copy()
+    bad[7] = R + 5
+    a = torch.empty((B, D), dtype=torch.float32, device="cuda")
+    plan = emblib.Plan([dict(table_id=1, indices=u32(bad), offsets=u32(o), out=a)])
+    plan.launch(torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    assert lib.emb_check_indices() == 1
+    q0 = np.vstack([q, np.zeros((10, D), dtype=np.int32)])
+    assert np.array_equal(bits(a.cpu().numpy()), bits(eo.lookup_rows([q0], [bad], [o])[0]))
+    plan.close()
+    lib.emb_set_tuning(0, 0, 0)
