@@ -1300,14 +1300,23 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0);
     std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
     {
+        // Group sizes grow by a factor r per group: nothing can be pooled before the first group's
+        // indices have crossed PCIe, so a small first group shortens the start-up bubble; but group
+        // g+1's indices must have arrived by the time group g's results have drained, or the result
+        // stream stalls, so r cannot exceed (time to write a group out) / (time to read its indices).
+        // r = 1 is equal groups.  Measurement knob: EMB_GROUP_RATIO (percent, default 100).
         const uint64_t total = h2d_payload + d2h_payload;
-        const uint64_t per_group = (total + n_groups - 1) / n_groups;
+        static const double r = std::max(100u, env_u32("EMB_GROUP_RATIO", 100)) / 100.0;
+        std::vector<double> cum(n_groups);
+        double w = 1.0, sum = 0.0;
+        for (uint32_t i = 0; i < n_groups; i++, w *= r)
+            cum[i] = (sum += w);
         uint64_t acc = 0;
         uint32_t gi = 0;
         g_first[0] = 0;
         for (uint32_t t = 0; t < T; t++) {
             acc += ((uint64_t)indices_len[t] + nr_batches[t]) * 4 + (uint64_t)nr_batches[t] * D * 4;
-            if (acc >= per_group * (gi + 1) && gi + 1 < n_groups && t + 1 < T)
+            if ((double)acc >= (double)total * cum[gi] / sum && gi + 1 < n_groups && t + 1 < T)
                 g_first[++gi] = t + 1;
         }
         n_groups = gi + 1;
