@@ -336,7 +336,16 @@ struct Variant {
     int unroll;    // K
     int mult;      // bags per CTA / sub-warps per CTA
     uint32_t bags; // bags per CTA
+    int threads;   // CTA size of the balanced kernel: 64, 128 or 256
 };
+
+int cta_threads()
+{
+    static int t = -1;  // measurement knob: EMB_CTA_THREADS = 64 / 128 / 256 forces the balanced kernel's CTA size
+    if (t < 0)
+        t = (int)env_u32("EMB_CTA_THREADS", 0);
+    return t;
+}
 
 /* avg_pool = lookups per bag of the launch (0 = unknown). */
 Variant pick_variant(bool any_float, double avg_pool = 0.0)
@@ -367,6 +376,23 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0)
     if (v.kind == 2 && !g.bags_mult && avg_pool > 0.0 && avg_pool <= 4.0)
         v.mult = 4;
     v.bags = emb::kThreads / lanes * v.mult;
+    // CTA size of the balanced kernel.  Small CTAs: the CTA barriers (offsets staged, indices staged,
+    // all pieces pooled) hold fewer warps and the CTAs of an SM drift apart, so more row loads are in
+    // flight at any time.  Same box, 256 / 128 / 64 threads (tools/cta_sweep.sh, profiles/r1_sweeps.md):
+    // C2 0.2995 / 0.287 / 0.2811 ms, C3 0.0577 / 0.0536 / 0.0598, C4 0.674 / 0.664 / 0.662,
+    // C5 0.5288 / 0.5104 (bags_mult 1) / --.
+    v.threads = emb::kThreads;
+    if (v.kind == 2) {
+        const bool short_bags = avg_pool > 0.0 && avg_pool <= 4.0;
+        int want = cta_threads();
+        if (!want)
+            want = lanes >= 32 ? 128 : (lanes == 4 && short_bags) ? 128 : 64;
+        if (want == 128 || (want == 64 && lanes <= 16))
+            v.threads = want;
+        if (!g.bags_mult && lanes >= 32 && v.threads == 128)
+            v.mult = 1;
+        v.bags = v.threads / lanes * v.mult;
+    }
     if (v.kind == 3) {
         v.mult = 1;
         v.bags = emb::kThreads;  // 32 bags per warp
@@ -387,38 +413,53 @@ void launch_ordered(int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d,
         emb::bag_sum_kernel<LANES, 4><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
 }
 
-template <int LANES, int K, int MINB>
+template <int LANES, int K, int MINB, int THREADS>
 void launch_balanced_k(int mult, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
 {
-    constexpr int SUB = emb::kThreads / LANES;
+    constexpr int SUB = THREADS / LANES;
     static int carve = -2;  // measurement knob: EMB_CARVEOUT = preferred shared-memory carveout in percent
     if (carve == -2) {
         const char *e = getenv("EMB_CARVEOUT");
         carve = e ? atoi(e) : -1;
         if (carve >= 0) {
-            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB>,
+            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB, THREADS>,
                                  cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB>,
+            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB, THREADS>,
                                  cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB>,
+            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB, THREADS>,
                                  cudaFuncAttributePreferredSharedMemoryCarveout, carve);
         }
     }
     if (mult == 4)
-        emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+        emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, g.d_err);
     else if (mult == 2)
-        emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+        emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, g.d_err);
     else
-        emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+        emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, g.d_err);
 }
 
+/* CTA sizes of the balanced kernel: 256 threads always; 128 and 64 as well where the sub-warp count
+ * stays >= 2 (rows up to 512 / 256 bytes).  MINB keeps the resident threads per SM the same. */
 template <int LANES>
 void launch_balanced(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
 {
-    if (v.unroll == 8)
-        launch_balanced_k<LANES, 8, 4>(v.mult, grid, s, d, n);
-    else
-        launch_balanced_k<LANES, 4, 6>(v.mult, grid, s, d, n);
+    if (v.unroll == 8) {
+        if constexpr (LANES <= 16) {
+            if (v.threads == 64)
+                return launch_balanced_k<LANES, 8, 16, 64>(v.mult, grid, s, d, n);
+        }
+        if (v.threads == 128)
+            return launch_balanced_k<LANES, 8, 8, 128>(v.mult, grid, s, d, n);
+        launch_balanced_k<LANES, 8, 4, 256>(v.mult, grid, s, d, n);
+    } else {
+        if constexpr (LANES <= 16) {
+            if (v.threads == 64)
+                return launch_balanced_k<LANES, 4, 24, 64>(v.mult, grid, s, d, n);
+        }
+        if (v.threads == 128)
+            return launch_balanced_k<LANES, 4, 12, 128>(v.mult, grid, s, d, n);
+        launch_balanced_k<LANES, 4, 6, 256>(v.mult, grid, s, d, n);
+    }
 }
 
 template <int LANES>
@@ -569,7 +610,7 @@ struct emb_plan {
     BagDesc *d = nullptr;
     uint32_t grid = 0;
     uint64_t bytes = 0;
-    Variant variant = {0, 1, 1, 8};
+    Variant variant = {0, 1, 1, 8, 256};
 };
 
 extern "C" {

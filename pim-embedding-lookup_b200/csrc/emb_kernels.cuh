@@ -333,15 +333,16 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__r
  * Requires monotone offsets inside the CTA's chunk; a chunk that is not monotone (bags that
  * overlap, which lookup() permits) is pooled bag by bag instead.
  */
-template <int LANES, int K, int BAGS, int MINB>
-__global__ void __launch_bounds__(kThreads, MINB)
+template <int LANES, int K, int BAGS, int MINB, int THREADS = kThreads>
+__global__ void __launch_bounds__(THREADS, MINB)
 bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__restrict__ err_flag)
 {
-    constexpr int SUB = kThreads / LANES;  // sub-warps per CTA
+    constexpr int SUB = THREADS / LANES;  // sub-warps per CTA
     constexpr int D = LANES * 4;
     static_assert(BAGS % SUB == 0, "BAGS must be a multiple of the sub-warp count");
     __shared__ uint32_t s_off[BAGS + 1];
-    __shared__ uint32_t s_idx[kIdxStage];
+    constexpr int STAGE = kIdxStage * THREADS / kThreads;  // indices staged per pass
+    __shared__ uint32_t s_idx[STAGE];
     __shared__ __align__(16) uint32_t s_acc[BAGS * D];
 
     const uint32_t tid = threadIdx.x;
@@ -355,16 +356,16 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
     const uint32_t *__restrict__ g_idx = d->indices;
     const uint32_t *__restrict__ g_off = d->offsets;
 
-    for (uint32_t i = tid; i <= nb; i += kThreads) {
+    for (uint32_t i = tid; i <= nb; i += THREADS) {
         uint32_t b = b0 + i;
         uint32_t v = (b == 0) ? 0u : (b >= B ? ilen : ldg_stream_u32(g_off + b));
         s_off[i] = min(v, ilen);
     }
-    for (uint32_t i = tid; i < BAGS * D / 4; i += kThreads)
+    for (uint32_t i = tid; i < BAGS * D / 4; i += THREADS)
         reinterpret_cast<uint4 *>(s_acc)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     bool nonmono = false;
-    for (uint32_t i = tid; i < nb; i += kThreads)
+    for (uint32_t i = tid; i < nb; i += THREADS)
         nonmono |= s_off[i] > s_off[i + 1];
     const bool ordered = __syncthreads_or(nonmono);
 
@@ -378,11 +379,11 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
 
     if (!ordered) {
         const uint32_t wlo = s_off[0], whi = s_off[nb];
-        for (uint32_t base = wlo; base < whi; base += kIdxStage) {
-            const uint32_t n = min((uint32_t)kIdxStage, whi - base);
+        for (uint32_t base = wlo; base < whi; base += STAGE) {
+            const uint32_t n = min((uint32_t)STAGE, whi - base);
             if (base != wlo)
                 __syncthreads();  // everyone is done with the previous pass's s_idx
-            for (uint32_t i = tid; i < n; i += kThreads)
+            for (uint32_t i = tid; i < n; i += THREADS)
                 s_idx[i] = ldg_stream_u32(g_idx + base + i);
             __syncthreads();
             for (uint32_t c = sub * K; c < n; c += SUB * K) {
