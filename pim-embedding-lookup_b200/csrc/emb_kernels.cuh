@@ -782,7 +782,6 @@ bag_sum_tma_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t 
     constexpr int SUBW = 32 / LANES;           // sub-warps per warp
     constexpr int WB = 4 * SUBW;               // bags per warp: 4 per sub-warp
     constexpr int WARPS = kThreads / 32;
-    constexpr int RPP = SUBW;                  // rows a warp reads per pass
     static_assert(NR % 4 == 0 && NR <= 32, "a stage is a whole number of gather4 groups, one row id per lane");
     extern __shared__ __align__(128) uint8_t tma_smem[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -859,7 +858,6 @@ bag_sum_tma_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t 
 
         for (uint32_t k = 0; k < (uint32_t)kTmaStages && k < n_stage; k++)
             issue(k);
-        uint32_t bag_lo = 0;  // first bag that may still have rows at or after the current stage
         for (uint32_t k = 0; k < n_stage; k++) {
             const uint32_t s = k % kTmaStages, phase = (k / kTmaStages) & 1u;
             uint32_t spins = 0;
@@ -892,8 +890,6 @@ bag_sum_tma_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t 
                     }
                 }
             }
-            (void)bag_lo;
-            (void)RPP;
             __syncwarp();  // every lane has read stage s: it may be refilled
             if (k + kTmaStages < n_stage)
                 issue(k + kTmaStages);
