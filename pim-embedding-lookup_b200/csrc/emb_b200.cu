@@ -347,8 +347,9 @@ int cta_threads()
     return t;
 }
 
-/* avg_pool = lookups per bag of the launch (0 = unknown). */
-Variant pick_variant(bool any_float, double avg_pool = 0.0)
+/* avg_pool = lookups per bag of the launch (0 = unknown); max_table_bytes = the largest table the
+ * launch reads (0 = unknown). */
+Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_bytes = 0)
 {
     Variant v;
     uint32_t D = g.shape.nr_cols;
@@ -361,6 +362,16 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0)
         return v;
     }
     v.kind = g.variant ? g.variant : 2;
+    // Tables that stay in L2 while a launch walks them (<= 8 MB each, rows up to 128 bytes): the
+    // warp-autonomous kernel issues ~3x fewer instructions per lookup and wins (26 x 4 MB tables: 0.201
+    // vs 0.236 ms, 8 MB: 0.217 vs 0.238, 16 MB: 0.248 vs 0.242; profiles/r1_sweeps.md).  Its larger
+    // shared-memory footprint costs L1, which is what DRAM-resident tables need.
+    bool auto_warp = false;
+    if (!g.variant && !any_float && lanes <= 8 && max_table_bytes && max_table_bytes <= (8ull << 20) &&
+        !(avg_pool > 0.0 && avg_pool <= 4.0)) {
+        v.kind = 3;
+        auto_warp = true;
+    }
     if (v.kind == 3 && lanes > 8)
         v.kind = 2;  // the warp-autonomous kernel is for rows up to 128 bytes
     if (v.kind == 4 && lanes < 4)
@@ -369,7 +380,7 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0)
         v.kind = 1;  // fp32 sums keep index order (embedding_lookup_idx.cc:33-77); kinds 1 and 4 do
     // defaults from the sweeps in profiles/r1_sweeps.md (tools/sweep.py): 64-byte rows want many
     // small CTAs; 256-byte rows 8 rows in flight per lane and 4x the bags per CTA; 512-byte rows 2x
-    v.unroll = g.unroll ? g.unroll : (lanes >= 16 ? 8 : 4);
+    v.unroll = g.unroll ? g.unroll : (lanes >= 16 || auto_warp ? 8 : 4);
     v.mult = (v.kind == 2) ? (g.bags_mult ? g.bags_mult : (lanes == 16 ? 4 : lanes > 16 ? 2 : 1)) : 1;
     // one or two lookups per bag (Criteo-style single-index features): a CTA's fixed costs dominate,
     // give it 4x the bags (C3 lookup shape: 76 -> 56 us, profiles/r1_sweeps.md)
@@ -525,6 +536,15 @@ int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
     return EMB_OK;
+}
+
+uint64_t max_table_bytes_of(const emb_dev_query *queries, uint32_t n)
+{
+    uint64_t m = 0;
+    for (uint32_t i = 0; i < n; i++)
+        if (queries[i].table_id < g.tables.size())
+            m = std::max<uint64_t>(m, g.tables[queries[i].table_id].rows * (uint64_t)g.shape.nr_cols * 4);
+    return m;
 }
 
 /* Fill one descriptor from a query; returns the number of CTAs it needs. */
@@ -928,7 +948,7 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
             li += queries[i].indices_len;
             nb += queries[i].nr_batches;
         }
-        p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0);
+        p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0, max_table_bytes_of(queries, n));
     }
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
@@ -1023,7 +1043,8 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
         tot_li += queries[i].indices_len;
         tot_nb += queries[i].nr_batches;
     }
-    const Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0);
+    const Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0,
+                                         max_table_bytes_of(queries, n));
     uint64_t chunk = 0;
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
@@ -1338,7 +1359,10 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         n_groups = std::min(std::min(T, kMaxGroups), forced_groups);
     if ((rc = ensure_events(3 * n_groups + 2)))
         return rc;
-    const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0);
+    uint64_t max_tb = 0;
+    for (uint32_t t = 0; t < T; t++)
+        max_tb = std::max<uint64_t>(max_tb, g.tables[t].rows * D * 4ull);
+    const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, max_tb);
     std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
     {
         // Group sizes grow by a factor r per group: nothing can be pooled before the first group's
