@@ -67,6 +67,10 @@ struct Ctx {
     BagDesc *d_descs = nullptr;
     BagDesc *h_descs = nullptr;  // pinned
     uint32_t desc_cap = 0;
+    // bytes d_descs holds (last successful upload): a caller that passes the same arrays call after
+    // call (dlrm_dpu_pytorch.py:484-498 allocates them once) needs no descriptor upload at all
+    std::vector<uint8_t> desc_shadow;
+    bool desc_shadow_ok = false;
     // descriptor ring of emb_lookup_device
     BagDesc *ring_h[4] = {nullptr, nullptr, nullptr, nullptr};
     BagDesc *ring_d[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -75,6 +79,7 @@ struct Ctx {
     int ring_next = 0;
     // page-locked bounce arena for small calls on pageable arrays
     uint8_t *h_bounce = nullptr;
+    uint8_t *d_bounce = nullptr;  // device alias of h_bounce
     size_t bounce_cap = 0;
 
     emb_timings last = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -1260,6 +1265,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         g.d_descs = nullptr;
         g.h_descs = nullptr;
         g.desc_cap = 0;
+        g.desc_shadow_ok = false;
         CU(cudaMalloc(&g.d_descs, T * sizeof(BagDesc)));
         CU(cudaMallocHost(&g.h_descs, T * sizeof(BagDesc)));
         g.desc_cap = T;
@@ -1295,10 +1301,10 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             g.bounce_cap = 0;
             const size_t cap = std::max(need, (size_t)kBounceMaxBytes + 64);
             CU(cudaHostAlloc((void **)&g.h_bounce, cap, cudaHostAllocMapped | cudaHostAllocPortable));
+            CU(cudaHostGetDevicePointer((void **)&g.d_bounce, g.h_bounce, 0));
             g.bounce_cap = cap;
         }
-        uint8_t *dev_base = nullptr;
-        CU(cudaHostGetDevicePointer((void **)&dev_base, g.h_bounce, 0));
+        uint8_t *const dev_base = g.d_bounce;
         size_t pos = 0;
         for (uint32_t t = 0; t < T; t++) {  // indices, then offsets (4-byte items), then 16-byte aligned outputs
             memcpy(g.h_bounce + pos, indices[t], (size_t)indices_len[t] * 4);
@@ -1418,11 +1424,23 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     }
 
     // nothing to stage: descriptors and launch share one stream (fewer CUDA calls per small lookup)
+    // Small calls are bound by host time per CUDA call and by the copy engine's start-up latency in
+    // front of the launch, so nothing is enqueued that the call does not need: the descriptors are
+    // uploaded only when they differ from what d_descs already holds (same arrays, same shapes, same
+    // tables as the previous call -- the reference's caller reuses its buffers), and the begin/end
+    // events exist only where a copy stream has something to time.
     cudaStream_t s_k = g.stream, s_in = in_mapped ? s_k : g.stream_in, s_out = g.stream_out;
     cudaEvent_t *ev = g.ev_pool.data();
     cudaEvent_t ev_begin = ev[3 * n_groups], ev_end = ev[3 * n_groups + 1];
-    CU(cudaEventRecord(ev_begin, s_in));
-    CU(cudaMemcpyAsync(g.d_descs, g.h_descs, T * sizeof(BagDesc), cudaMemcpyHostToDevice, s_in));
+    if (s_in != s_k)
+        CU(cudaEventRecord(ev_begin, s_in));
+    static const bool desc_cache = env_u32("EMB_DESC_CACHE", 1) != 0;  // measurement knob
+    const size_t desc_bytes = (size_t)T * sizeof(BagDesc);
+    const bool desc_same = desc_cache && g.desc_shadow_ok && g.desc_shadow.size() == desc_bytes &&
+                           memcmp(g.desc_shadow.data(), g.h_descs, desc_bytes) == 0;
+    g.desc_shadow_ok = false;  // set again once this call has completed
+    if (!desc_same)
+        CU(cudaMemcpyAsync(g.d_descs, g.h_descs, desc_bytes, cudaMemcpyHostToDevice, s_in));
     uint64_t launches = 0;
     for (uint32_t gi = 0; gi < n_groups; gi++) {
         const uint32_t t0 = g_first[gi], t1 = g_first[gi + 1];
@@ -1453,8 +1471,12 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         }
     }
     cudaStream_t s_last = out_mapped ? s_k : s_out;
-    CU(cudaEventRecord(ev_end, s_last));
+    if (!out_mapped)
+        CU(cudaEventRecord(ev_end, s_last));
     CU(cudaStreamSynchronize(s_last));
+    if (!desc_same)
+        g.desc_shadow.assign((const uint8_t *)g.h_descs, (const uint8_t *)g.h_descs + desc_bytes);
+    g.desc_shadow_ok = true;
     float ms = 0, k_ms = 0;
     g.last.h2d_ms = 0;
     if (s_in != s_k) {
@@ -1476,8 +1498,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     g.last.d2h_bytes = d2h_payload;
     g.last.launches = launches;
     if (bounce) {
-        uint8_t *dev_base = nullptr;
-        CU(cudaHostGetDevicePointer((void **)&dev_base, g.h_bounce, 0));
+        const uint8_t *dev_base = g.d_bounce;
         for (uint32_t t = 0; t < T; t++)
             if (nr_batches[t])
                 memcpy(final_results[t], g.h_bounce + ((uint8_t *)a_out[t] - dev_base), (size_t)nr_batches[t] * D * 4);

@@ -116,6 +116,84 @@ def test_lookup_ex_matches_oracle(emblib, D):
     assert emblib.load().emb_check_indices() == 0
 
 
+def test_repeated_calls_on_the_same_arrays_follow_their_contents(emblib):
+    """The reference's caller allocates its index / offset / result arrays once and refills them per
+    batch (dlrm_dpu_pytorch.py:484-498,1028-1051).  The library then skips the descriptor upload
+    (same addresses, same shapes); the results must still follow the arrays' CONTENTS, and a call
+    with other arrays, other lengths or a re-populated table must not see stale descriptors."""
+    rng = np.random.default_rng(77)
+    T, D, B = 3, 16, 40
+    emblib.configure(T, D)
+    tabs = []
+    for t in range(T):
+        q = rng.integers(-2**31, 2**31, size=(500 + t, D), dtype=np.int64).astype(np.int32)
+        tabs.append(q)
+        emblib.populate_table_i32(t, q)
+    for pinned in (False, True):
+        mk = (lambda n, dt: emblib.pinned_array(n, dt)) if pinned else (lambda n, dt: np.zeros(n, dtype=dt))
+        idxs = [mk(B * 5, np.uint32) for _ in range(T)]
+        offs = [mk(B, np.uint32) for _ in range(T)]
+        res = [mk((B, D), np.float32) for _ in range(T)]
+        call = emblib.HostCall(idxs, offs, res)
+        for rep in range(4):  # same arrays, new contents every time
+            for t in range(T):
+                lens = rng.integers(0, 6, size=B)
+                lens[-1] = 5
+                o = np.concatenate([[0], np.cumsum(lens)[:-1]])
+                offs[t][:] = o
+                idxs[t][:] = rng.integers(0, tabs[t].shape[0], size=B * 5)
+            got = call()
+            want = eo.lookup_rows(tabs, [np.array(i) for i in idxs], [np.array(o) for o in offs])
+            for t in range(T):
+                assert np.array_equal(bits(got[t]), bits(want[t])), (pinned, rep, t)
+        # other lengths through the same library state
+        i2, o2 = zip(*[ragged(rng, tabs[t].shape[0], 17 + t, 9) for t in range(T)])
+        got = emblib.lookup_ex(list(i2), list(o2))
+        want = eo.lookup_rows(tabs, list(i2), list(o2))
+        for t in range(T):
+            assert np.array_equal(bits(got[t]), bits(want[t])), (pinned, "ragged", t)
+        # a table populated again (other size): the next call on the first arrays sees the new table
+        tabs[1] = rng.integers(-2**31, 2**31, size=(900, D), dtype=np.int64).astype(np.int32)
+        emblib.populate_table_i32(1, tabs[1])
+        got = call()
+        want = eo.lookup_rows(tabs, [np.array(i) for i in idxs], [np.array(o) for o in offs])
+        for t in range(T):
+            assert np.array_equal(bits(got[t]), bits(want[t])), (pinned, "repopulated", t)
+        if pinned:
+            for a in idxs + offs + res:
+                emblib.free_pinned(a)
+
+
+def test_c1_shape_mini_batch_one(emblib):
+    """BASELINE.json configs[0]: Kaggle arch, 26 tables x dim 16, mini-batch 1, one
+    index per lookup -- through populate_table_f32 (export_emb's arithmetic on the GPU) and the
+    reference's lookup().  Cardinalities from tools/visualize.py:949, the four multi-million-row
+    tables capped at 300k rows so the oracle's quantise stays sub-second (tools/small_call_latency.py
+    runs the full cardinalities)."""
+    rows = [1460, 583, 10131227, 2202608, 305, 24, 12517, 633, 3, 93145, 5683, 8351593, 3194, 27, 14992, 5461306,
+            10, 5652, 2173, 4, 7046547, 18, 15, 286181, 105, 142572]
+    rows = [min(r, 300_000) for r in rows]
+    rng = np.random.default_rng(123)
+    T, D = len(rows), 16
+    emblib.configure(T, D, 1, 1)
+    W = [rng.uniform(-np.sqrt(1 / n), np.sqrt(1 / n), size=(n, D)).astype(np.float32) for n in rows]
+    for t in range(T):
+        emblib.populate_table_f32(t, W[t])
+    tabs = [eo.quantise_rows(w) for w in W]
+    for trial in range(3):
+        idxs = [np.array([rng.integers(0, n)], dtype=np.uint32) for n in rows]
+        if trial == 2:
+            idxs = [np.array([n - 1], dtype=np.uint32) for n in rows]  # last row of every table
+        offs = [np.zeros(1, dtype=np.uint32) for _ in rows]
+        got = emblib.lookup(idxs, offs)
+        want = eo.lookup_rows(tabs, idxs, offs)
+        for t in range(T):
+            assert got[t].shape == (1, D)
+            assert np.array_equal(bits(got[t]), bits(want[t])), (trial, t)
+            # and it is the float row the CPU path (dlrm_s_pytorch.py:483-488) would return, to 1e-9 steps
+            assert np.abs(got[t][0] - W[t][idxs[t][0]]).max() <= 1e-6
+
+
 @pytest.mark.parametrize("D", [16, 64, 6])
 def test_page_locked_arrays_take_the_mapped_path_and_match(emblib, D):
     """Host arrays in page-locked memory: the pooling kernel reads them and writes the results over
