@@ -421,16 +421,16 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
 }
 
 template <int LANES>
-void launch_ordered(int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+void launch_ordered(int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     if (unroll == 8)
-        emb::bag_sum_kernel<LANES, 8><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+        emb::bag_sum_kernel<LANES, 8><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
     else
-        emb::bag_sum_kernel<LANES, 4><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+        emb::bag_sum_kernel<LANES, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
 }
 
 template <int LANES, int K, int MINB, int THREADS>
-void launch_balanced_k(int mult, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+void launch_balanced_k(int mult, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     constexpr int SUB = THREADS / LANES;
     static int carve = -2;  // measurement knob: EMB_CARVEOUT = preferred shared-memory carveout in percent
@@ -447,54 +447,54 @@ void launch_balanced_k(int mult, uint32_t grid, cudaStream_t s, const BagDesc *d
         }
     }
     if (mult == 4)
-        emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, g.d_err);
+        emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, uni, g.d_err);
     else if (mult == 2)
-        emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, g.d_err);
+        emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, uni, g.d_err);
     else
-        emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, g.d_err);
+        emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, uni, g.d_err);
 }
 
 /* CTA sizes of the balanced kernel: 256 threads always; 128 and 64 as well where the sub-warp count
  * stays >= 2 (rows up to 512 / 256 bytes).  MINB keeps the resident threads per SM the same. */
 template <int LANES>
-void launch_balanced(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+void launch_balanced(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     if (v.unroll == 8) {
         if constexpr (LANES <= 16) {
             if (v.threads == 64)
-                return launch_balanced_k<LANES, 8, 16, 64>(v.mult, grid, s, d, n);
+                return launch_balanced_k<LANES, 8, 16, 64>(v.mult, grid, s, d, n, uni);
         }
         if (v.threads == 128)
-            return launch_balanced_k<LANES, 8, 8, 128>(v.mult, grid, s, d, n);
-        launch_balanced_k<LANES, 8, 4, 256>(v.mult, grid, s, d, n);
+            return launch_balanced_k<LANES, 8, 8, 128>(v.mult, grid, s, d, n, uni);
+        launch_balanced_k<LANES, 8, 4, 256>(v.mult, grid, s, d, n, uni);
     } else {
         if constexpr (LANES <= 16) {
             if (v.threads == 64)
-                return launch_balanced_k<LANES, 4, 24, 64>(v.mult, grid, s, d, n);
+                return launch_balanced_k<LANES, 4, 24, 64>(v.mult, grid, s, d, n, uni);
         }
         if (v.threads == 128)
-            return launch_balanced_k<LANES, 4, 12, 128>(v.mult, grid, s, d, n);
-        launch_balanced_k<LANES, 4, 6, 256>(v.mult, grid, s, d, n);
+            return launch_balanced_k<LANES, 4, 12, 128>(v.mult, grid, s, d, n, uni);
+        launch_balanced_k<LANES, 4, 6, 256>(v.mult, grid, s, d, n, uni);
     }
 }
 
 template <int LANES>
-void launch_warp(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+void launch_warp(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     if constexpr (LANES <= 8) {
         // no carveout preference on purpose: L1 capacity is what holds the row loads in flight, and
         // the largest shared-memory carveout halves the throughput (profiles/r1_sweeps.md)
         if (v.unroll == 8)
-            emb::bag_sum_warp_kernel<LANES, 8, 4><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+            emb::bag_sum_warp_kernel<LANES, 8, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
         else
-            emb::bag_sum_warp_kernel<LANES, 4, 6><<<grid, emb::kThreads, 0, s>>>(d, n, g.d_err);
+            emb::bag_sum_warp_kernel<LANES, 4, 6><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
     } else {
-        (void)v; (void)grid; (void)s; (void)d; (void)n;
+        (void)v; (void)grid; (void)s; (void)d; (void)n; (void)uni;
     }
 }
 
 template <int LANES>
-void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     if constexpr (LANES >= 4) {
         constexpr int WARPS = emb::kThreads / 32;
@@ -505,38 +505,53 @@ void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
             cudaFuncSetAttribute(emb::bag_sum_tma_kernel<LANES, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             once = true;
         }
-        emb::bag_sum_tma_kernel<LANES, 3><<<grid, emb::kThreads, smem, s>>>(d, n, g.d_err);
+        emb::bag_sum_tma_kernel<LANES, 3><<<grid, emb::kThreads, smem, s>>>(d, n, uni, g.d_err);
     } else {
-        (void)grid; (void)s; (void)d; (void)n;
+        (void)grid; (void)s; (void)d; (void)n; (void)uni;
     }
 }
 
 template <int LANES>
-void launch_for_lanes(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n)
+void launch_for_lanes(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     if (v.kind == 4)
-        launch_tma<LANES>(grid, s, d, n);
+        launch_tma<LANES>(grid, s, d, n, uni);
     else if (v.kind == 3)
-        launch_warp<LANES>(v, grid, s, d, n);
+        launch_warp<LANES>(v, grid, s, d, n, uni);
     else if (v.kind == 2)
-        launch_balanced<LANES>(v, grid, s, d, n);
+        launch_balanced<LANES>(v, grid, s, d, n, uni);
     else
-        launch_ordered<LANES>(v.unroll, grid, s, d, n);
+        launch_ordered<LANES>(v.unroll, grid, s, d, n, uni);
 }
 
-int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_t grid, cudaStream_t s)
+/* Every query of the launch owns the same number of CTAs (the usual case: all tables pool the same
+ * batch): CTA c belongs to descriptor c / chunks and no kernel has to search for it. */
+uint32_t uniform_chunks(const BagDesc *h, uint32_t n)
+{
+    static const bool on = env_u32("EMB_UNIFORM_CHUNKS", 1) != 0;  // measurement knob
+    if (!on || n == 0 || h[0].n_chunks == 0 || h[0].chunk_begin != 0)
+        return 0;
+    const uint32_t c = h[0].n_chunks;
+    for (uint32_t i = 0; i < n; i++)
+        if (h[i].n_chunks != c || h[i].chunk_begin != i * c)
+            return 0;
+    return c;
+}
+
+/* `uni` = uniform_chunks() of the n descriptors (0 = search). */
+int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_t uni, uint32_t grid, cudaStream_t s)
 {
     if (grid == 0)
         return EMB_OK;
     uint32_t D = g.shape.nr_cols;
     switch (v.kind ? lanes_for_dim(D) : 0) {
-    case 0: emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, D, g.d_err); break;
-    case 1: launch_for_lanes<1>(v, grid, s, d_descs, n); break;
-    case 2: launch_for_lanes<2>(v, grid, s, d_descs, n); break;
-    case 4: launch_for_lanes<4>(v, grid, s, d_descs, n); break;
-    case 8: launch_for_lanes<8>(v, grid, s, d_descs, n); break;
-    case 16: launch_for_lanes<16>(v, grid, s, d_descs, n); break;
-    default: launch_for_lanes<32>(v, grid, s, d_descs, n); break;
+    case 0: emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, uni, D, g.d_err); break;
+    case 1: launch_for_lanes<1>(v, grid, s, d_descs, n, uni); break;
+    case 2: launch_for_lanes<2>(v, grid, s, d_descs, n, uni); break;
+    case 4: launch_for_lanes<4>(v, grid, s, d_descs, n, uni); break;
+    case 8: launch_for_lanes<8>(v, grid, s, d_descs, n, uni); break;
+    case 16: launch_for_lanes<16>(v, grid, s, d_descs, n, uni); break;
+    default: launch_for_lanes<32>(v, grid, s, d_descs, n, uni); break;
     }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
@@ -634,6 +649,7 @@ struct emb_plan {
     std::vector<BagDesc> h;
     BagDesc *d = nullptr;
     uint32_t grid = 0;
+    uint32_t uni = 0;  // uniform_chunks() of the descriptors
     uint64_t bytes = 0;
     Variant variant = {0, 1, 1, 8, 256};
 };
@@ -973,6 +989,7 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
         return fail(EMB_EINVAL, "too many bags for one launch");
     }
     p->grid = (uint32_t)chunk;
+    p->uni = uniform_chunks(p->h.data(), n);
     cudaError_t e = cudaMalloc(&p->d, n * sizeof(BagDesc));
     if (e == cudaSuccess)
         e = cudaMemcpy(p->d, p->h.data(), n * sizeof(BagDesc), cudaMemcpyHostToDevice);
@@ -989,7 +1006,7 @@ int emb_plan_launch(emb_plan *plan, void *stream)
 {
     if (!plan)
         return fail(EMB_EINVAL, "NULL plan");
-    return launch_bag_sum(plan->variant, plan->d, (uint32_t)plan->h.size(), plan->grid,
+    return launch_bag_sum(plan->variant, plan->d, (uint32_t)plan->h.size(), plan->uni, plan->grid,
                           stream ? (cudaStream_t)stream : g.stream);
 }
 
@@ -1061,7 +1078,7 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
         return fail(EMB_EINVAL, "too many bags for one launch");
     CU(cudaMemcpyAsync(g.ring_d[slot], h, n * sizeof(BagDesc), cudaMemcpyHostToDevice, s));
     CU(cudaEventRecord(g.ring_ev[slot], s));
-    return launch_bag_sum(variant, g.ring_d[slot], n, (uint32_t)chunk, s);
+    return launch_bag_sum(variant, g.ring_d[slot], n, uniform_chunks(h, n), (uint32_t)chunk, s);
 }
 
 int emb_check_indices(void)
@@ -1222,7 +1239,19 @@ void emb_finish_destroy(emb_finish *f)
  * synchronise, because every CUDA call costs several microseconds of host time. */
 constexpr uint64_t kPipelineMinBytes = 4ull << 20;
 constexpr uint64_t kMapInputsMaxBytes = 1ull << 20;  // inputs are read in place below this
-constexpr uint64_t kBounceMaxBytes = 1ull << 20;     // pageable calls up to this size go through the bounce arena
+constexpr uint64_t kBounceMaxBytes = 1ull << 20;     // pageable calls up to this size go through the bounce arena ...
+constexpr uint64_t kBouncePerTable = 128ull << 10;   // ... or up to this much per table (see bounce_limit)
+constexpr uint64_t kBounceCeiling = 8ull << 20;
+constexpr uint64_t kTinyBytes = 64ull << 10;         // below this even page-locked arrays are bounced
+
+/* Pageable arrays cost the staged path 3 cudaMemcpyAsync per table, each ~5.5 us of host time because
+ * the driver stages pageable memory synchronously (RM2 as shipped, upmem/r.sh:6-10: T=32, 1.5 MB per
+ * call -> 628 us staged against 125 us on page-locked arrays; profiles/r1_small_calls.md).  One CPU
+ * memcpy per array into the page-locked arena is cheaper until the bytes outweigh those calls. */
+static uint64_t bounce_limit(uint32_t T)
+{
+    return std::min(kBounceCeiling, std::max(kBounceMaxBytes, (uint64_t)T * kBouncePerTable));
+}
 constexpr uint32_t kMaxGroups = 32;
 
 /* Device-side alias of a host pointer when the GPU can address it directly (memory from
@@ -1275,7 +1304,10 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     // which arrays can the GPU address in place?
     std::vector<const uint32_t *> a_idx(T, nullptr), a_off(T, nullptr);
     std::vector<float *> a_out(T, nullptr);
-    bool out_mapped = g.host_path != EMB_HOST_COPY, in_mapped = out_mapped;
+    // A tiny call (the reference's mini-batch-1 inference) is bounced whatever the arrays
+    // are: copying a few KB costs less host time than asking the driver about 3 T pointers.
+    const bool tiny = g.host_path == EMB_HOST_AUTO && h2d_payload + d2h_payload <= kTinyBytes;
+    bool out_mapped = g.host_path != EMB_HOST_COPY && !tiny, in_mapped = out_mapped;
     for (uint32_t t = 0; t < T && out_mapped; t++)
         if (nr_batches[t] && !(a_out[t] = (float *)mapped_alias(final_results[t])))
             out_mapped = false;
@@ -1291,7 +1323,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     // hundred KB faster than the 3 T cudaMemcpyAsync calls of the staged path cost to enqueue
     // (each CUDA call is several microseconds of host time), and the launch is the mapped one.
     bool bounce = false;
-    if ((g.host_path == EMB_HOST_AUTO && !(in_mapped && out_mapped) && h2d_payload + d2h_payload <= kBounceMaxBytes) ||
+    if ((g.host_path == EMB_HOST_AUTO && !(in_mapped && out_mapped) && h2d_payload + d2h_payload <= bounce_limit(T)) ||
         g.host_path == EMB_HOST_BOUNCE) {
         const size_t need = (size_t)(h2d_payload + d2h_payload) + 64;
         if (g.bounce_cap < need) {
@@ -1299,7 +1331,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
                 cudaFreeHost(g.h_bounce);
             g.h_bounce = nullptr;
             g.bounce_cap = 0;
-            const size_t cap = std::max(need, (size_t)kBounceMaxBytes + 64);
+            const size_t cap = std::max(need, (size_t)bounce_limit(T) + 64);
             CU(cudaHostAlloc((void **)&g.h_bounce, cap, cudaHostAllocMapped | cudaHostAllocPortable));
             CU(cudaHostGetDevicePointer((void **)&g.d_bounce, g.h_bounce, 0));
             g.bounce_cap = cap;
@@ -1458,7 +1490,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             CU(cudaStreamWaitEvent(s_k, ev[3 * gi], 0));
         }
         CU(cudaEventRecord(ev[3 * gi + 1], s_k));
-        if ((rc = launch_bag_sum(variant, g.d_descs + t0, t1 - t0, g_grid[gi], s_k)))
+        if ((rc = launch_bag_sum(variant, g.d_descs + t0, t1 - t0, uniform_chunks(g.h_descs + t0, t1 - t0), g_grid[gi], s_k)))
             return rc;
         launches += g_grid[gi] ? 1 : 0;
         CU(cudaEventRecord(ev[3 * gi + 2], s_k));

@@ -166,8 +166,14 @@ __device__ __forceinline__ int32_t quantise(float w)
     return (int32_t)(uint32_t)(unsigned long long)__float2ll_rn(r);
 }
 
-__device__ __forceinline__ uint32_t find_desc(const BagDesc *__restrict__ descs, uint32_t n, uint32_t chunk)
+/* Descriptor of CTA `chunk`.  uni != 0: every descriptor owns `uni` consecutive CTAs (the host checked,
+ * uniform_chunks()), so this is a division instead of a chain of log2(n) dependent loads in front of
+ * everything else the CTA does. */
+__device__ __forceinline__ uint32_t find_desc(const BagDesc *__restrict__ descs, uint32_t n, uint32_t uni,
+                                              uint32_t chunk)
 {
+    if (uni)
+        return chunk / uni;
     uint32_t lo = 0, hi = n;  // last desc with chunk_begin <= chunk
     while (hi - lo > 1) {
         uint32_t mid = (lo + hi) >> 1;
@@ -186,14 +192,14 @@ __device__ __forceinline__ uint32_t find_desc(const BagDesc *__restrict__ descs,
  */
 template <int LANES, int UNROLL>
 __global__ void __launch_bounds__(kThreads)
-bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__restrict__ err_flag)
+bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
 {
     constexpr int BAGS = kThreads / LANES;
     __shared__ uint32_t s_off[BAGS + 1];
     __shared__ uint32_t s_idx[kIdxStage];
 
     const uint32_t tid = threadIdx.x;
-    const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
+    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
     const BagDesc *__restrict__ d = descs + q;
 
     const uint32_t B = d->nr_batches;
@@ -335,7 +341,7 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__r
  */
 template <int LANES, int K, int BAGS, int MINB, int THREADS = kThreads>
 __global__ void __launch_bounds__(THREADS, MINB)
-bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__restrict__ err_flag)
+bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
 {
     constexpr int SUB = THREADS / LANES;  // sub-warps per CTA
     constexpr int D = LANES * 4;
@@ -346,7 +352,7 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
     __shared__ __align__(16) uint32_t s_acc[BAGS * D];
 
     const uint32_t tid = threadIdx.x;
-    const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
+    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
     const BagDesc *__restrict__ d = descs + q;
 
     const uint32_t B = d->nr_batches;
@@ -521,7 +527,7 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
  */
 template <int LANES, int K, int MINB>
 __global__ void __launch_bounds__(kThreads, MINB)
-bag_sum_warp_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__restrict__ err_flag)
+bag_sum_warp_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
 {
     constexpr int SUB = 32 / LANES;  // sub-warps per warp
     constexpr int D = LANES * 4;
@@ -539,7 +545,7 @@ bag_sum_warp_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t sub = lane / LANES;
     const uint32_t sl = lane % LANES;
-    const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
+    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
     const BagDesc *__restrict__ d = descs + q;
 
     const uint32_t B = d->nr_batches;
@@ -775,7 +781,7 @@ constexpr int kTmaStageBytes = 2048;  // per warp and stage: NR = 2048 / row byt
 
 template <int LANES, int MINB>
 __global__ void __launch_bounds__(kThreads, MINB)
-bag_sum_tma_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t *__restrict__ err_flag)
+bag_sum_tma_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
 {
     constexpr int ROWB = LANES * 16;
     constexpr int NR = kTmaStageBytes / ROWB;  // rows per stage: 32 (64-byte rows) .. 4 (512-byte rows)
@@ -791,7 +797,7 @@ bag_sum_tma_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t 
     uint32_t *off = reinterpret_cast<uint32_t *>(tma_smem + (size_t)WARPS * kTmaStages * kTmaStageBytes + WARPS * kTmaStages * 8) +
                     warp * (WB + 1);
 
-    const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
+    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
     const BagDesc *__restrict__ d = descs + q;
     const uint32_t B = d->nr_batches;
     const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, WARPS * WB) + warp * WB;
@@ -965,11 +971,11 @@ bag_sum_tma_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t 
  * stride over the columns with 4-byte loads.  Correctness path, not a tuned one.
  */
 __global__ void __launch_bounds__(kThreads)
-bag_sum_generic_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t dim,
+bag_sum_generic_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t dim,
                        uint32_t *__restrict__ err_flag)
 {
     constexpr int BAGS = kThreads / 32;
-    const uint32_t q = find_desc(descs, n_desc, blockIdx.x);
+    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
     const BagDesc *__restrict__ d = descs + q;
     const uint32_t B = d->nr_batches;
     const uint32_t b = chunk_first_bag(d, blockIdx.x - d->chunk_begin, BAGS) + threadIdx.x / 32;

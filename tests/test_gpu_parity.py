@@ -164,6 +164,42 @@ def test_repeated_calls_on_the_same_arrays_follow_their_contents(emblib):
                 emblib.free_pinned(a)
 
 
+def test_rm2_preset_on_pageable_arrays_is_bounced_and_tiny_calls_too(emblib):
+    """upmem/r.sh:6-10 (RM2 as shipped): 32 tables x dim 64, 64 bags x 120 indices = 1.5 MB per call in plain
+    NumPy memory.  That is above the 1 MB floor of the bounce rule but below 128 KB per table, so the
+    call is bounced (one launch) instead of staged with 96 copies; and a call of a few KB is bounced
+    even from page-locked arrays.  Both bit-exact against the oracle."""
+    from pim_embedding_lookup_b200.dputypes import EMB_HOST_BOUNCE
+    rng = np.random.default_rng(8)
+    T, D, B, P, R = 32, 64, 64, 120, 3000
+    emblib.configure(T, D, B, P)
+    tabs = [rng.integers(-2**31, 2**31, size=(R, D), dtype=np.int64).astype(np.int32) for _ in range(T)]
+    for t in range(T):
+        emblib.populate_table_i32(t, tabs[t])
+    idxs = [rng.integers(0, R, size=B * P).astype(np.uint32) for _ in range(T)]
+    offs = [(np.arange(B) * P).astype(np.uint32) for _ in range(T)]
+    got = emblib.lookup(idxs, offs)
+    tm = emblib.last_timings()
+    assert tm.path == EMB_HOST_BOUNCE and tm.launches == 1
+    want = eo.lookup_rows(tabs, idxs, offs)
+    for t in range(T):
+        assert np.array_equal(bits(got[t]), bits(want[t])), t
+    # a tiny call on page-locked arrays: 2 bags of table 0..T-1
+    pi = [emblib.pinned_array(6, np.uint32) for _ in range(T)]
+    po = [emblib.pinned_array(2, np.uint32) for _ in range(T)]
+    pr = [emblib.pinned_array((2, D), np.float32) for _ in range(T)]
+    for t in range(T):
+        pi[t][:] = rng.integers(0, R, size=6)
+        po[t][:] = [0, 4]
+    got = emblib.lookup_ex(pi, po, pr)
+    assert emblib.last_timings().path == EMB_HOST_BOUNCE
+    want = eo.lookup_rows(tabs, [np.array(a) for a in pi], [np.array(a) for a in po])
+    for t in range(T):
+        assert np.array_equal(bits(got[t]), bits(want[t])), t
+    for a in pi + po + pr:
+        emblib.free_pinned(a)
+
+
 def test_c1_shape_mini_batch_one(emblib):
     """BASELINE.json configs[0]: Kaggle arch, 26 tables x dim 16, mini-batch 1, one
     index per lookup -- through populate_table_f32 (export_emb's arithmetic on the GPU) and the
