@@ -401,10 +401,19 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
     if (v.kind == 2) {
         const bool short_bags = avg_pool > 0.0 && avg_pool <= 4.0;
         int want = cta_threads();
+        // 64-byte rows: ONE warp per CTA (the CTA barriers cost nothing, 32 CTAs per SM drift apart freely),
+        // 64 registers, so 8 rows in flight per lane and 16 bags per CTA; short bags 4 rows and 32 bags.
+        // Same box, against the 64-thread CTAs above: C2 0.2688 -> 0.2585 ms, C3 0.0517 -> 0.0476 ms
+        // (tools/cta32_sweep.sh, profiles/r1_sweeps.md).
+        const bool one_warp = lanes == 4 && (want == 32 || (!want && !g.unroll && !g.bags_mult));
         if (!want)
-            want = lanes >= 32 ? 128 : (lanes == 4 && short_bags) ? 128 : 64;
-        if (want == 128 || (want == 64 && lanes <= 16))
+            want = one_warp ? 32 : lanes >= 32 ? 128 : 64;
+        if (want == 128 || (want == 64 && lanes <= 16) || (want == 32 && lanes <= 8))
             v.threads = want;
+        if (one_warp && !g.unroll)
+            v.unroll = short_bags ? 4 : 8;
+        if (one_warp && !g.bags_mult)
+            v.mult = short_bags ? 4 : 2;
         if (!g.bags_mult && lanes >= 32 && v.threads == 128)
             v.mult = 1;
         v.bags = v.threads / lanes * v.mult;
@@ -459,6 +468,13 @@ void launch_balanced_k(int mult, uint32_t grid, cudaStream_t s, const BagDesc *d
 template <int LANES>
 void launch_balanced(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
+    if constexpr (LANES <= 8) {  // one warp per CTA: the CTA barriers cost nothing
+        if (v.threads == 32) {
+            if (v.unroll == 8)
+                return launch_balanced_k<LANES, 8, 32, 32>(v.mult, grid, s, d, n, uni);
+            return launch_balanced_k<LANES, 4, 32, 32>(v.mult, grid, s, d, n, uni);
+        }
+    }
     if (v.unroll == 8) {
         if constexpr (LANES <= 16) {
             if (v.threads == 64)

@@ -362,17 +362,36 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
     const uint32_t *__restrict__ g_idx = d->indices;
     const uint32_t *__restrict__ g_off = d->offsets;
 
-    for (uint32_t i = tid; i <= nb; i += THREADS) {
-        uint32_t b = b0 + i;
-        uint32_t v = (b == 0) ? 0u : (b >= B ? ilen : ldg_stream_u32(g_off + b));
-        s_off[i] = min(v, ilen);
+    // Bag bounds (emb_dpu_lookup.c:60-63,109-110: bag 0 starts at 0 whatever offsets[0] is, bag i ends where
+    // bag i+1 starts, the last bag ends at indices_len).  First round: the loads are issued here and looked
+    // at further down.  Every thread also loads its right-hand neighbour's bound (the same cache line): monotonicity is checked on the loaded
+    // values themselves and one barrier closes both the staging and the check.
+    const uint32_t bq = b0 + tid;
+    uint32_t raw0 = 0, raw1 = 0;
+    if (tid <= nb) {
+        if (bq != 0 && bq < B)
+            raw0 = ldg_stream_u32(g_off + bq);
+        if (tid < nb && bq + 1 < B)
+            raw1 = ldg_stream_u32(g_off + bq + 1);
     }
+    // in the shadow of those loads
     for (uint32_t i = tid; i < BAGS * D / 4; i += THREADS)
         reinterpret_cast<uint4 *>(s_acc)[i] = make_uint4(0u, 0u, 0u, 0u);
-    __syncthreads();
+
     bool nonmono = false;
-    for (uint32_t i = tid; i < nb; i += THREADS)
-        nonmono |= s_off[i] > s_off[i + 1];
+    if (tid <= nb) {
+        const uint32_t v = min((bq == 0) ? 0u : (bq >= B ? ilen : raw0), ilen);
+        if (tid < nb)
+            nonmono = v > min((bq + 1 >= B) ? ilen : raw1, ilen);
+        s_off[tid] = v;
+    }
+    for (uint32_t i = tid + THREADS; i <= nb; i += THREADS) {
+        const uint32_t b = b0 + i;
+        const uint32_t v = min((b >= B) ? ilen : ldg_stream_u32(g_off + b), ilen);
+        if (i < nb)
+            nonmono |= v > min((b + 1 >= B) ? ilen : ldg_stream_u32(g_off + b + 1), ilen);
+        s_off[i] = v;
+    }
     const bool ordered = __syncthreads_or(nonmono);
 
     const uint32_t flags = d->flags;
