@@ -66,12 +66,19 @@ __device__ __forceinline__ uint32_t chunk_first_bag(const BagDesc *d, uint32_t c
     return d->bag_first + c * per;
 }
 
-/* EMB_LD_MODE (build-time experiment switch):
- *   0  rows: ld.global.nc.L1::no_allocate                       (default)
- *   1  rows: + L2 evict_last policy; indices/offsets/outputs: L2 evict_first policy
- *   2  rows: + .L2::64B prefetch size      3  rows: + .L2::128B prefetch size */
+/* EMB_LD_MODE (build-time switch; measurements in profiles/r1_sweeps.md):
+ *   4  rows: ld.global.nc -- L1 allocates, L2 default priority                      (default)
+ *   0  rows: ld.global.nc.L1::no_allocate (the first default: "a row is used once, keep it out of L1")
+ *   1  rows: L1::no_allocate + L2 evict_last policy; indices/offsets/outputs: L2 evict_first policy
+ *   2  rows: L1::no_allocate + .L2::64B prefetch size      3  + .L2::128B prefetch size
+ *   5  rows: L1::no_allocate + L2 evict_normal policy      6  L1::no_allocate + L2 evict_last policy (hoisted)
+ * ncu shows every sector of an L1::no_allocate load arriving at L2 as evict_first
+ * (lts__t_sectors_srcunit_tex_op_read_evict_first_*), so the rows of the table being walked were the
+ * first thing L2 dropped.  Plain ld.global.nc is faster on every workload: C2 0.2443 -> 0.2422 ms,
+ * C3 0.0496 -> 0.0456, C4 0.658 -> 0.6088, C5 0.5023 -> 0.4819 (tools/ldmode_ab.sh, same box).
+ * The index / offset streams and the output rows stay L1::no_allocate: they are used once. */
 #ifndef EMB_LD_MODE
-#define EMB_LD_MODE 0
+#define EMB_LD_MODE 4
 #endif
 
 __device__ __forceinline__ uint64_t l2_policy_evict_last()
@@ -90,7 +97,6 @@ __device__ __forceinline__ uint64_t l2_policy_evict_first()
 __device__ __forceinline__ uint4 ldg_row16(const uint4 *p)
 {
     uint4 r;
-    // read-only, streamed: a row is touched once per bag, keep it out of L1
 #if EMB_LD_MODE == 1
     asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
@@ -103,6 +109,20 @@ __device__ __forceinline__ uint4 ldg_row16(const uint4 *p)
     asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                  : "l"(p));
+#elif EMB_LD_MODE == 4
+    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+#elif EMB_LD_MODE == 5 || EMB_LD_MODE == 6
+    uint64_t pol;  // not volatile: one policy per thread, hoisted out of the loops
+#if EMB_LD_MODE == 5
+    asm("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+#else
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+#endif
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p), "l"(pol));
 #else
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)

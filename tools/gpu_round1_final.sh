@@ -1,5 +1,5 @@
 #!/bin/bash
-# One gpurun call: GPU tests, smoke, default-vs-64-thread A/B, small-call latencies, the bench line, the
+# One gpurun call: GPU tests, smoke, the default kernel on every workload shape, small-call latencies, the bench line, the
 # two ncu passes of the recipe (/opt/skills/guides/B200_PROFILING.md).  Usage: tools/gpu_round1_final.sh <tag>
 set -u
 TAG=${1:-r1z}
@@ -11,11 +11,8 @@ tail -6 $OUT/pytest_$TAG.log
 python __graft_entry__.py smoke > $OUT/smoke_$TAG.log 2>&1; echo "smoke rc=$?"; tail -2 $OUT/smoke_$TAG.log
 : > $OUT/ab_$TAG.txt
 for wl in c2 c3 c4 c5; do
-  for t in 0 64 0 64; do
-    echo "workload=$wl EMB_CTA_THREADS=$t" >> $OUT/ab_$TAG.txt
-    if [ $t = 0 ]; then python tools/sweep.py --workload $wl --steps 60 --tunings 0,0,0 >> $OUT/ab_$TAG.txt 2>&1
-    else EMB_CTA_THREADS=$t python tools/sweep.py --workload $wl --steps 60 --tunings 0,0,0 >> $OUT/ab_$TAG.txt 2>&1; fi
-  done
+  echo "workload=$wl default" >> $OUT/ab_$TAG.txt
+  python tools/sweep.py --workload $wl --steps 60 --tunings 0,0,0 >> $OUT/ab_$TAG.txt 2>&1
 done
 cut -c1-200 $OUT/ab_$TAG.txt
 python tools/small_call_latency.py > $OUT/small_$TAG.jsonl 2> $OUT/small_$TAG.err; echo "small rc=$?"; cut -c1-400 $OUT/small_$TAG.jsonl
