@@ -367,12 +367,13 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         return v;
     }
     v.kind = g.variant ? g.variant : 2;
-    // Tables that stay in L2 while a launch walks them (<= 8 MB each, rows up to 128 bytes): the
-    // warp-autonomous kernel issues ~3x fewer instructions per lookup and wins (26 x 4 MB tables: 0.201
-    // vs 0.236 ms, 8 MB: 0.217 vs 0.238, 16 MB: 0.248 vs 0.242; profiles/r1_sweeps.md).  Its larger
-    // shared-memory footprint costs L1, which is what DRAM-resident tables need.
+    // Tables that stay in L2 while a launch walks them (<= 16 MB each, rows up to 128 bytes): the
+    // warp-autonomous kernel issues ~3x fewer instructions per lookup and wins (26 tables of 4 / 8 / 16 MB:
+    // 0.179 / 0.183 / 0.191 ms against 0.187 / 0.191 / 0.197 for the one-warp balanced kernel;
+    // profiles/r1_sweeps.md).  Its larger shared-memory footprint costs L1, which is what DRAM-resident
+    // tables need.
     bool auto_warp = false;
-    if (!g.variant && !any_float && lanes <= 8 && max_table_bytes && max_table_bytes <= (8ull << 20) &&
+    if (!g.variant && !any_float && lanes <= 8 && max_table_bytes && max_table_bytes <= (16ull << 20) &&
         !(avg_pool > 0.0 && avg_pool <= 4.0)) {
         v.kind = 3;
         auto_warp = true;
