@@ -328,9 +328,12 @@ uint64_t emb_launch_count(void);
 int emb_set_unroll(int unroll);
 /* All tuning knobs at once (0 = default): variant 1 = one bag per sub-warp (index-ordered
  * adds; always used when a float table is in the launch), 2 = load-balanced pieces of the
- * index stream with shared-memory int32 accumulators; unroll as above; bags_mult = bags per
- * CTA in units of sub-warps per CTA (1, 2 or 4; variant 2 only).  Takes effect for plans
- * created and host-pointer lookups issued afterwards. */
+ * index stream with shared-memory int32 accumulators, 3 = the same per warp (rows up to 128
+ * bytes), 4 = TMA gather4, 5 = variant 2 with one warp per CTA walking several sub-chunks of
+ * bags, the next sub-chunk's indices copied asynchronously while the current one's rows are
+ * gathered (rows up to 128 bytes); unroll as above; bags_mult = bags per CTA in units of
+ * sub-warps per CTA (1, 2 or 4; variant 2) or sub-chunks per CTA (2, 4 or 8; variant 5).
+ * Takes effect for plans created and host-pointer lookups issued afterwards. */
 int emb_set_tuning(int variant, int unroll, int bags_mult);
 
 #ifdef __cplusplus

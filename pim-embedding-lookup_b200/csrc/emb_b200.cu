@@ -337,11 +337,13 @@ uint32_t lanes_for_dim(uint32_t D)
  * mapping depends on it). */
 struct Variant {
     int kind;      // 0 generic, 1 bag-per-sub-warp (any table kind), 2 / 3 load-balanced per CTA / per warp (int32 only),
-                   // 4 TMA gather4 (rows of 64..512 bytes, any table kind)
+                   // 4 TMA gather4 (rows of 64..512 bytes, any table kind), 5 load-balanced, pipelined sub-chunks
+                   // (int32 only, rows up to 128 bytes)
     int unroll;    // K
     int mult;      // bags per CTA / sub-warps per CTA
     uint32_t bags; // bags per CTA
-    int threads;   // CTA size of the balanced kernel: 64, 128 or 256
+    int threads;   // CTA size of the balanced kernel: 32, 64, 128 or 256
+    int pipe_bags; // pipelined kernel (kind 5): bags per sub-chunk / sub-warps per CTA (2 or 3); mult = sub-chunks per CTA
 };
 
 int cta_threads()
@@ -366,20 +368,24 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         v.bags = emb::kThreads / 32;
         return v;
     }
-    v.kind = g.variant ? g.variant : 2;
+    static const int dflt_kind = (int)env_u32("EMB_DEFAULT_VARIANT", 2);  // measurement knob
+    v.kind = g.variant ? g.variant : (dflt_kind >= 1 && dflt_kind <= 5 ? dflt_kind : 2);
+    v.pipe_bags = 0;
     // Tables that stay in L2 while a launch walks them (<= 16 MB each, rows up to 128 bytes): the
     // warp-autonomous kernel issues ~3x fewer instructions per lookup and wins (26 tables of 4 / 8 / 16 MB:
     // 0.179 / 0.183 / 0.191 ms against 0.187 / 0.191 / 0.197 for the one-warp balanced kernel;
     // profiles/r1_sweeps.md).  Its larger shared-memory footprint costs L1, which is what DRAM-resident
     // tables need.
     bool auto_warp = false;
-    if (!g.variant && !any_float && lanes <= 8 && max_table_bytes && max_table_bytes <= (16ull << 20) &&
+    if (!g.variant && dflt_kind == 2 && !any_float && lanes <= 8 && max_table_bytes && max_table_bytes <= (16ull << 20) &&
         !(avg_pool > 0.0 && avg_pool <= 4.0)) {
         v.kind = 3;
         auto_warp = true;
     }
-    if (v.kind == 3 && lanes > 8)
-        v.kind = 2;  // the warp-autonomous kernel is for rows up to 128 bytes
+    // emb_set_tuning(5, k, 8): 8 sub-chunks per CTA means something only to the pipelined kernel
+    const int bags_mult = (g.bags_mult == 8 && (v.kind != 5 || lanes > 8 || any_float)) ? 0 : g.bags_mult;
+    if ((v.kind == 3 || v.kind == 5) && lanes > 8)
+        v.kind = 2;  // the warp-autonomous and the pipelined kernel are for rows up to 128 bytes
     if (v.kind == 4 && lanes < 4)
         v.kind = 2;  // the TMA kernel is for rows of 64 bytes and more
     if (any_float && v.kind != 4)
@@ -387,10 +393,10 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
     // defaults from the sweeps in profiles/r1_sweeps.md (tools/sweep.py): 64-byte rows want many
     // small CTAs; 256-byte rows 8 rows in flight per lane and 4x the bags per CTA; 512-byte rows 2x
     v.unroll = g.unroll ? g.unroll : (lanes >= 16 || auto_warp ? 8 : 4);
-    v.mult = (v.kind == 2) ? (g.bags_mult ? g.bags_mult : (lanes == 16 ? 4 : lanes > 16 ? 2 : 1)) : 1;
+    v.mult = (v.kind == 2) ? (bags_mult ? bags_mult : (lanes == 16 ? 4 : lanes > 16 ? 2 : 1)) : 1;
     // one or two lookups per bag (Criteo-style single-index features): a CTA's fixed costs dominate,
     // give it 4x the bags (C3 lookup shape: 76 -> 56 us, profiles/r1_sweeps.md)
-    if (v.kind == 2 && !g.bags_mult && avg_pool > 0.0 && avg_pool <= 4.0)
+    if (v.kind == 2 && !bags_mult && avg_pool > 0.0 && avg_pool <= 4.0)
         v.mult = 4;
     v.bags = emb::kThreads / lanes * v.mult;
     // CTA size of the balanced kernel.  Small CTAs: the CTA barriers (offsets staged, indices staged,
@@ -406,22 +412,30 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         // 64 registers, so 8 rows in flight per lane and 16 bags per CTA; short bags 4 rows and 32 bags.
         // Same box, against the 64-thread CTAs above: C2 0.2688 -> 0.2585 ms, C3 0.0517 -> 0.0476 ms
         // (tools/cta32_sweep.sh, profiles/r1_sweeps.md).
-        const bool one_warp = lanes == 4 && (want == 32 || (!want && !g.unroll && !g.bags_mult));
+        const bool one_warp = lanes == 4 && (want == 32 || (!want && !g.unroll && !bags_mult));
         if (!want)
             want = one_warp ? 32 : lanes >= 32 ? 128 : 64;
         if (want == 128 || (want == 64 && lanes <= 16) || (want == 32 && lanes <= 8))
             v.threads = want;
         if (one_warp && !g.unroll)
             v.unroll = short_bags ? 4 : 8;
-        if (one_warp && !g.bags_mult)
+        if (one_warp && !bags_mult)
             v.mult = short_bags ? 4 : 2;
-        if (!g.bags_mult && lanes >= 32 && v.threads == 128)
+        if (!bags_mult && lanes >= 32 && v.threads == 128)
             v.mult = 1;
         v.bags = v.threads / lanes * v.mult;
     }
     if (v.kind == 3) {
         v.mult = 1;
         v.bags = emb::kThreads;  // 32 bags per warp
+    }
+    if (v.kind == 5) {  // one warp per CTA, K = 8, mult = sub-chunks per CTA, pipe_bags x sub-warps bags per sub-chunk
+        static const int pb = (int)env_u32("EMB_PIPE_BAGS", 2);  // measurement knob: 2 or 3
+        v.unroll = 8;
+        v.threads = 32;
+        v.mult = (g.bags_mult == 2 || g.bags_mult == 4 || g.bags_mult == 8) ? g.bags_mult : 4;
+        v.pipe_bags = pb == 3 ? 3 : 2;
+        v.bags = 32 / lanes * v.pipe_bags * v.mult;
     }
     if (v.kind == 4) {
         v.mult = 1;
@@ -510,6 +524,31 @@ void launch_warp(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc 
     }
 }
 
+template <int LANES, int PB>
+void launch_pipe_b(int nch, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+{
+    constexpr int BAGS = 32 / LANES * PB;
+    if (nch == 8)
+        emb::bag_sum_pipe_kernel<LANES, 8, BAGS, 8, 32><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
+    else if (nch == 2)
+        emb::bag_sum_pipe_kernel<LANES, 8, BAGS, 2, 32><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
+    else
+        emb::bag_sum_pipe_kernel<LANES, 8, BAGS, 4, 32><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
+}
+
+template <int LANES>
+void launch_pipe(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+{
+    if constexpr (LANES <= 8) {
+        if (v.pipe_bags == 3)
+            launch_pipe_b<LANES, 3>(v.mult, grid, s, d, n, uni);
+        else
+            launch_pipe_b<LANES, 2>(v.mult, grid, s, d, n, uni);
+    } else {
+        (void)v; (void)grid; (void)s; (void)d; (void)n; (void)uni;
+    }
+}
+
 template <int LANES>
 void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
@@ -531,7 +570,9 @@ void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uin
 template <int LANES>
 void launch_for_lanes(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
-    if (v.kind == 4)
+    if (v.kind == 5)
+        launch_pipe<LANES>(v, grid, s, d, n, uni);
+    else if (v.kind == 4)
         launch_tma<LANES>(grid, s, d, n, uni);
     else if (v.kind == 3)
         launch_warp<LANES>(v, grid, s, d, n, uni);
@@ -668,7 +709,7 @@ struct emb_plan {
     uint32_t grid = 0;
     uint32_t uni = 0;  // uniform_chunks() of the descriptors
     uint64_t bytes = 0;
-    Variant variant = {0, 1, 1, 8, 256};
+    Variant variant = {0, 1, 1, 8, 256, 0};
 };
 
 extern "C" {
@@ -709,11 +750,11 @@ int emb_set_unroll(int unroll)
 
 int emb_set_tuning(int variant, int unroll, int bags_mult)
 {
-    if (variant < 0 || variant > 4)
+    if (variant < 0 || variant > 5)
         return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp), 2 (load-balanced per CTA), "
-                                "3 (load-balanced per warp) or 4 (TMA gather4)");
-    if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4)
-        return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2 or 4");
+                                "3 (load-balanced per warp), 4 (TMA gather4) or 5 (load-balanced, pipelined)");
+    if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4 && !(variant == 5 && bags_mult == 8))
+        return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2 or 4 (variant 5: sub-chunks per CTA, 2, 4 or 8)");
     int rc = emb_set_unroll(unroll);
     if (rc)
         return rc;

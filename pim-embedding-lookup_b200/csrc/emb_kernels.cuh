@@ -548,6 +548,261 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
     }
 }
 
+/* cp.async groups: commit what has been issued, wait until at most N groups are still pending. */
+__device__ __forceinline__ void cp_async_commit()
+{
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group()
+{
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+/*
+ * Pipelined load-balanced sum-pool kernel (variant 5) for int32 fixed-point tables, rows up to 128 bytes.
+ *
+ * bag_sum_balanced_kernel with one warp per CTA spends about half of a CTA's life in front of its first
+ * row load: descriptor -> bag bounds -> indices are three dependent memory round trips, and only then do
+ * rows fly.  Here a CTA (still one warp, still 64 registers, K rows in flight per lane) owns NCH
+ * consecutive sub-chunks of BAGS bags.  The bounds of ALL its bags are loaded in one round trip, and the
+ * index window of sub-chunk j+1 is copied into the other half of a two-buffer shared-memory ring with
+ * cp.async (no registers, no stall at issue) while the rows of sub-chunk j are gathered.  The chain is
+ * paid once per CTA instead of once per BAGS bags; accumulators and the store epilogue stay per
+ * sub-chunk, so shared memory per CTA is about what the balanced kernel uses (L1 capacity is what keeps
+ * row loads in flight).
+ *
+ * Same arithmetic as the balanced kernel: pieces of K lookups dealt round-robin to the sub-warps, int32
+ * wrap-around adds flushed into a shared accumulator at bag boundaries (emb_dpu_lookup.c:114; associative
+ * and commutative, so bit-exact in any order), dequantise + STG.128 epilogue (emb_host.h:207-212).  A
+ * CTA whose bounds are not monotone pools bag by bag like emb_dpu_lookup.c:106-116.
+ */
+template <int LANES, int K, int BAGS, int NCH, int MINB>
+__global__ void __launch_bounds__(32, MINB)
+bag_sum_pipe_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
+{
+    constexpr int SUB = 32 / LANES;  // sub-warps per CTA
+    constexpr int D = LANES * 4;
+    constexpr int ALLB = BAGS * NCH;  // bags per CTA
+    constexpr int SI = BAGS * 16;     // index entries per ring buffer; longer windows take extra passes
+    static_assert(BAGS % SUB == 0, "BAGS must be a multiple of the sub-warp count");
+    __shared__ uint32_t s_off[ALLB + 1];
+    __shared__ uint32_t s_idx[2][SI];
+    __shared__ __align__(16) uint32_t s_acc[BAGS * D];
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
+    const BagDesc *__restrict__ d = descs + q;
+
+    const uint32_t B = d->nr_batches;
+    const uint32_t ilen = d->indices_len;
+    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, ALLB);
+    const uint32_t nb_all = min((uint32_t)ALLB, d->bag_end - b0);
+    const uint32_t *__restrict__ g_idx = d->indices;
+    const uint32_t *__restrict__ g_off = d->offsets;
+
+    // bounds of all the CTA's bags, one round trip (emb_dpu_lookup.c:60-63,109-110: bag 0 starts at 0,
+    // bag i ends where bag i+1 starts, the last bag ends at indices_len); every lane also loads its
+    // right-hand neighbour's bound so that monotonicity is known without a second pass
+    bool nonmono = false;
+    {
+        constexpr int R = (ALLB + 1 + 31) / 32;
+        uint32_t raw0[R], raw1[R];
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const uint32_t i = tid + 32u * r, b = b0 + i;
+            raw0[r] = raw1[r] = 0;
+            if (i <= nb_all) {
+                if (b != 0 && b < B)
+                    raw0[r] = ldg_stream_u32(g_off + b);
+                if (i < nb_all && b + 1 < B)
+                    raw1[r] = ldg_stream_u32(g_off + b + 1);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const uint32_t i = tid + 32u * r, b = b0 + i;
+            if (i <= nb_all) {
+                const uint32_t v = min((b == 0) ? 0u : (b >= B ? ilen : raw0[r]), ilen);
+                if (i < nb_all)
+                    nonmono |= v > min((b + 1 >= B) ? ilen : raw1[r], ilen);
+                s_off[i] = v;
+            }
+        }
+    }
+    const bool ordered = __any_sync(0xffffffffu, nonmono);  // true = NOT monotone (name as in the balanced kernel)
+    __syncwarp();
+
+    const uint32_t flags = d->flags;
+    const uint32_t rows = d->rows;
+    const uint32_t row_base = d->row_base;
+    const uint32_t sub = tid / LANES;
+    const uint32_t lane = tid % LANES;
+    const uint4 *__restrict__ table = reinterpret_cast<const uint4 *>(d->table) + lane;
+    const uint32_t bpr = d->bags_per_rank;
+    const uint32_t out_stride = d->out_stride;
+    const uint32_t nch = (nb_all + BAGS - 1) / BAGS;
+    bool bad = false;
+
+    // index window of sub-chunk j -> ring buffer j & 1 (first SI entries), asynchronously
+    auto issue = [&](uint32_t j) {
+        const uint32_t nbj = min((uint32_t)BAGS, nb_all - j * BAGS);
+        const uint32_t lo = s_off[j * BAGS], hi = s_off[j * BAGS + nbj];
+        const uint32_t n = min((uint32_t)SI, hi - lo);
+        uint32_t *dst = s_idx[j & 1];
+        for (uint32_t i = tid; i < n; i += 32)
+            cp_async_u32(dst + i, g_idx + lo + i);
+        cp_async_commit();
+    };
+    if (!ordered && nch)
+        issue(0);
+
+    // one stretch of n staged lookups (window positions base .. base+n) of sub-chunk bags off[0..nbj]
+    auto pool = [&](const uint32_t *__restrict__ idx, uint32_t n, uint32_t base, const uint32_t *off, uint32_t nbj) {
+        for (uint32_t c = sub * K; c < n; c += SUB * K) {
+            const uint32_t m = min((uint32_t)K, n - c);
+            uint32_t r[K];
+#pragma unroll
+            for (int u = 0; u < K; u++) {
+                uint32_t id = 0xffffffffu;
+                if ((uint32_t)u < m) {
+                    id = idx[c + u] - row_base;  // unsigned: rows below the shard wrap high
+                    bad |= id >= rows;
+                }
+                r[u] = id;
+            }
+            uint4 v[K];
+#pragma unroll
+            for (int u = 0; u < K; u++) {
+                v[u] = make_uint4(0u, 0u, 0u, 0u);
+                if (r[u] < rows)
+                    v[u] = ldg_row16(table + (size_t)r[u] * LANES);
+            }
+            // bag of the piece's first lookup: last i with off[i] <= p (skips empty bags)
+            const uint32_t p0 = base + c;
+            uint32_t lo = 0, hi = nbj;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (off[mid] <= p0)
+                    lo = mid;
+                else
+                    hi = mid;
+            }
+            uint32_t bag = lo, bag_end = off[lo + 1];
+            uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+            for (int u = 0; u < K; u++) {
+                if ((uint32_t)u < m) {
+                    if (p0 + u >= bag_end) {  // crossed into a later bag: flush the partial sum
+                        uint32_t *a = s_acc + bag * D + lane * 4;
+                        atomicAdd(a + 0, acc.x);
+                        atomicAdd(a + 1, acc.y);
+                        atomicAdd(a + 2, acc.z);
+                        atomicAdd(a + 3, acc.w);
+                        acc = make_uint4(0u, 0u, 0u, 0u);
+                        do {
+                            bag++;
+                            bag_end = off[bag + 1];
+                        } while (p0 + u >= bag_end);
+                    }
+                    acc.x += v[u].x;
+                    acc.y += v[u].y;
+                    acc.z += v[u].z;
+                    acc.w += v[u].w;
+                }
+            }
+            uint32_t *a = s_acc + bag * D + lane * 4;
+            atomicAdd(a + 0, acc.x);
+            atomicAdd(a + 1, acc.y);
+            atomicAdd(a + 2, acc.z);
+            atomicAdd(a + 3, acc.w);
+        }
+    };
+
+    for (uint32_t j = 0; j < nch; j++) {
+        const uint32_t nbj = min((uint32_t)BAGS, nb_all - j * BAGS);
+        const uint32_t *off = s_off + j * BAGS;
+        for (uint32_t i = tid; i < BAGS * D / 4; i += 32)
+            reinterpret_cast<uint4 *>(s_acc)[i] = make_uint4(0u, 0u, 0u, 0u);
+        if (!ordered) {
+            const uint32_t wlo = off[0], whi = off[nbj];
+            if (j + 1 < nch) {  // next sub-chunk's indices fly while this one's rows are gathered
+                issue(j + 1);
+                cp_async_wait_group<1>();
+            } else {
+                cp_async_wait_group<0>();
+            }
+            __syncwarp();  // every lane's copies (and the zeroed accumulator) are visible to the warp
+            uint32_t *buf = s_idx[j & 1];
+            pool(buf, min((uint32_t)SI, whi - wlo), wlo, off, nbj);
+            for (uint32_t base = wlo + SI; base < whi; base += SI) {  // windows longer than a ring buffer
+                const uint32_t n = min((uint32_t)SI, whi - base);
+                __syncwarp();
+                for (uint32_t i = tid; i < n; i += 32)
+                    buf[i] = ldg_stream_u32(g_idx + base + i);
+                __syncwarp();
+                pool(buf, n, base, off, nbj);
+            }
+        } else {
+            // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
+            __syncwarp();
+            for (uint32_t bag = sub; bag < nbj; bag += SUB) {
+                const uint32_t start = off[bag], end = off[bag + 1];
+                uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+                for (uint32_t p = start; p < end; p++) {
+                    const uint32_t id = __ldg(g_idx + p) - row_base;
+                    if (id < rows) {
+                        const uint4 v = ldg_row16(table + (size_t)id * LANES);
+                        acc.x += v.x;
+                        acc.y += v.y;
+                        acc.z += v.z;
+                        acc.w += v.w;
+                    } else {
+                        bad = true;
+                    }
+                }
+                reinterpret_cast<uint4 *>(s_acc)[bag * LANES + lane] = acc;
+            }
+        }
+        __syncwarp();
+
+        // post_process (emb_host.h:207-212) for the sub-chunk's bags
+#pragma unroll
+        for (int it = 0; it < BAGS / SUB; it++) {
+            const uint32_t bag = it * SUB + sub;
+            if (bag >= nbj)
+                break;
+            uint4 o = reinterpret_cast<const uint4 *>(s_acc)[bag * LANES + lane];
+            if (!(flags & kDescRaw))
+                o = make_uint4(__float_as_uint(dequant(o.x)), __float_as_uint(dequant(o.y)),
+                               __float_as_uint(dequant(o.z)), __float_as_uint(dequant(o.w)));
+            const uint32_t b = b0 + j * BAGS + bag;
+            uint32_t *obase;
+            uint32_t row;
+            if (bpr) {
+                const uint32_t rk = b / bpr;
+                obase = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
+                row = b - rk * bpr;
+            } else {
+                obase = reinterpret_cast<uint32_t *>(d->out);
+                row = b;
+            }
+            uint32_t *dst = obase + (size_t)row * out_stride + lane * 4;
+            if (flags & kDescVecStore) {
+                stg_stream16(dst, o);
+            } else {
+                dst[0] = o.x;
+                dst[1] = o.y;
+                dst[2] = o.z;
+                dst[3] = o.w;
+            }
+        }
+        __syncwarp();  // accumulator and ring buffer j & 1 are free again
+    }
+    if (bad && !(flags & kDescSharded))
+        atomicOr(err_flag, 1u);
+}
+
 /*
  * Warp-autonomous load-balanced sum-pool kernel for int32 fixed-point tables with short rows
  * (D = 4*LANES <= 32 columns, i.e. rows of 16..128 bytes).
