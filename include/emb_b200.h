@@ -331,9 +331,7 @@ int emb_set_unroll(int unroll);
  * index stream with shared-memory int32 accumulators, 3 = the same per warp (rows up to 128
  * bytes), 4 = TMA gather4, 5 = variant 2 with one warp per CTA walking several sub-chunks of
  * bags, the next sub-chunk's indices copied asynchronously while the current one's rows are
- * gathered (rows up to 128 bytes), 6 = one-warp CTAs in a persistent grid (CTA i pools chunks i,
- * i + G, ...) with the bounds of chunk k+2 and the indices of chunk k+1 in flight while chunk k's
- * rows are gathered (D = 16 or 32); unroll as above; bags_mult = bags per CTA in units of
+ * gathered (rows up to 128 bytes); unroll as above; bags_mult = bags per CTA in units of
  * sub-warps per CTA (1, 2 or 4; variant 2) or sub-chunks per CTA (2, 4 or 8; variant 5).
  * Takes effect for plans created and host-pointer lookups issued afterwards. */
 int emb_set_tuning(int variant, int unroll, int bags_mult);

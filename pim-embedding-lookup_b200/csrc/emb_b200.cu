@@ -338,7 +338,7 @@ uint32_t lanes_for_dim(uint32_t D)
 struct Variant {
     int kind;      // 0 generic, 1 bag-per-sub-warp (any table kind), 2 / 3 load-balanced per CTA / per warp (int32 only),
                    // 4 TMA gather4 (rows of 64..512 bytes, any table kind), 5 load-balanced, pipelined sub-chunks
-                   // (int32 only, rows up to 128 bytes), 6 persistent grid, three-deep pipeline (int32 only, D = 16 / 32)
+                   // (int32 only, rows up to 128 bytes)
     int unroll;    // K
     int mult;      // bags per CTA / sub-warps per CTA
     uint32_t bags; // bags per CTA
@@ -369,7 +369,7 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         return v;
     }
     static const int dflt_kind = (int)env_u32("EMB_DEFAULT_VARIANT", 2);  // measurement knob
-    v.kind = g.variant ? g.variant : (dflt_kind >= 1 && dflt_kind <= 6 ? dflt_kind : 2);
+    v.kind = g.variant ? g.variant : (dflt_kind >= 1 && dflt_kind <= 5 ? dflt_kind : 2);
     v.pipe_bags = 0;
     // Tables that stay in L2 while a launch walks them (<= 16 MB each, rows up to 128 bytes): the
     // warp-autonomous kernel issues ~3x fewer instructions per lookup and wins (26 tables of 4 / 8 / 16 MB:
@@ -386,8 +386,6 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
     const int bags_mult = (g.bags_mult == 8 && (v.kind != 5 || lanes > 8 || any_float)) ? 0 : g.bags_mult;
     if ((v.kind == 3 || v.kind == 5) && lanes > 8)
         v.kind = 2;  // the warp-autonomous and the pipelined kernel are for rows up to 128 bytes
-    if (v.kind == 6 && lanes != 4 && lanes != 8)
-        v.kind = 2;  // the persistent kernel gives one lane to every bag bound of a 16-bag chunk
     if (v.kind == 4 && lanes < 4)
         v.kind = 2;  // the TMA kernel is for rows of 64 bytes and more
     if (any_float && v.kind != 4)
@@ -442,12 +440,6 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
     if (v.kind == 4) {
         v.mult = 1;
         v.bags = (emb::kThreads / 32) * 4 * (32 / lanes);  // 4 bags per sub-warp
-    }
-    if (v.kind == 6) {  // one warp per CTA, K = 8, 16 bags per chunk, grid = resident slots
-        v.unroll = 8;
-        v.threads = 32;
-        v.mult = 1;
-        v.bags = 16;
     }
     return v;
 }
@@ -558,19 +550,6 @@ void launch_pipe(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc 
 }
 
 template <int LANES>
-void launch_persist(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
-{
-    if constexpr (LANES == 4 || LANES == 8) {
-        // one CTA per resident slot (32 one-warp CTAs per SM); CTA i pools chunks i, i + G, i + 2G, ...
-        static const uint32_t per_sm = std::max(1u, std::min(32u, env_u32("EMB_PERSIST_CTAS", 32)));  // measurement knob
-        const uint32_t slots = (uint32_t)g.sm_count * per_sm;
-        emb::bag_sum_persist_kernel<LANES, 8, 16, 32><<<std::min(grid, slots), 32, 0, s>>>(d, n, uni, g.d_err);
-    } else {
-        (void)grid; (void)s; (void)d; (void)n; (void)uni;
-    }
-}
-
-template <int LANES>
 void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     if constexpr (LANES >= 4) {
@@ -591,9 +570,7 @@ void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uin
 template <int LANES>
 void launch_for_lanes(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
-    if (v.kind == 6)
-        launch_persist<LANES>(grid, s, d, n, uni);
-    else if (v.kind == 5)
+    if (v.kind == 5)
         launch_pipe<LANES>(v, grid, s, d, n, uni);
     else if (v.kind == 4)
         launch_tma<LANES>(grid, s, d, n, uni);
@@ -773,10 +750,9 @@ int emb_set_unroll(int unroll)
 
 int emb_set_tuning(int variant, int unroll, int bags_mult)
 {
-    if (variant < 0 || variant > 6)
+    if (variant < 0 || variant > 5)
         return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp), 2 (load-balanced per CTA), "
-                                "3 (load-balanced per warp), 4 (TMA gather4), 5 (load-balanced, pipelined) or "
-                                "6 (load-balanced, persistent grid)");
+                                "3 (load-balanced per warp), 4 (TMA gather4) or 5 (load-balanced, pipelined)");
     if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4 && !(variant == 5 && bags_mult == 8))
         return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2 or 4 (variant 5: sub-chunks per CTA, 2, 4 or 8)");
     int rc = emb_set_unroll(unroll);

@@ -804,265 +804,6 @@ bag_sum_pipe_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t
 }
 
 /*
- * Persistent pipelined sum-pool kernel (variant 6) for int32 fixed-point tables, D = 16 or 32.
- *
- * bag_sum_pipe_kernel hides the bounds -> indices chain but widens the window of rows the resident CTAs
- * gather from (a CTA owns consecutive sub-chunks), which costs more than it saves.  Here the grid is
- * one CTA (one warp) per resident slot and CTA i pools chunks i, i + G, i + 2G, ... (G = gridDim.x), so
- * all CTAs walk the tables together exactly like consecutive CTAs of the balanced kernel do, while
- * each warp runs a three-deep software pipeline: the bounds of chunk k+2 are in flight in two
- * registers and the indices of chunk k+1 in a cp.async ring while the rows of chunk k are gathered.
- * Arithmetic, fallback for non-monotone bounds and epilogue as in bag_sum_pipe_kernel.
- */
-template <int LANES, int K, int BAGS, int MINB>
-__global__ void __launch_bounds__(32, MINB)
-bag_sum_persist_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
-{
-    constexpr int SUB = 32 / LANES;
-    constexpr int D = LANES * 4;
-    constexpr int SI = BAGS * 16;  // index entries per ring buffer; longer windows take extra passes
-    static_assert(BAGS % SUB == 0 && BAGS < 32, "one lane per bag bound");
-    __shared__ uint32_t s_off[2][BAGS + 1];
-    __shared__ uint32_t s_idx[2][SI];
-    __shared__ __align__(16) uint32_t s_acc[BAGS * D];
-
-    const uint32_t tid = threadIdx.x;
-    const uint32_t sub = tid / LANES;
-    const uint32_t lane = tid % LANES;
-    uint32_t total;
-    if (uni) {
-        total = n_desc * uni;
-    } else {
-        const BagDesc *__restrict__ last = descs + (n_desc - 1);
-        total = last->chunk_begin + last->n_chunks;
-    }
-
-    auto locate = [&](uint32_t c, const BagDesc *&dd, uint32_t &bb0, uint32_t &nnb) {
-        dd = descs + find_desc(descs, n_desc, uni, c);
-        bb0 = chunk_first_bag(dd, c - dd->chunk_begin, BAGS);
-        nnb = min((uint32_t)BAGS, dd->bag_end - bb0);
-    };
-
-    // stage A: bounds of chunk c (lane i: bag i and its right-hand neighbour) -> two registers, not looked at
-    uint32_t raw0 = 0, raw1 = 0;
-    auto load_bounds = [&](uint32_t c) {
-        raw0 = raw1 = 0;
-        if (c >= total)
-            return;
-        const BagDesc *dd;
-        uint32_t bb0, nnb;
-        locate(c, dd, bb0, nnb);
-        const uint32_t Bq = dd->nr_batches;
-        const uint32_t *__restrict__ g_off = dd->offsets;
-        const uint32_t b = bb0 + tid;
-        if (tid <= nnb) {
-            if (b != 0 && b < Bq)
-                raw0 = ldg_stream_u32(g_off + b);
-            if (tid < nnb && b + 1 < Bq)
-                raw1 = ldg_stream_u32(g_off + b + 1);
-        }
-    };
-    // stage B: the bounds in raw0/raw1 belong to chunk c: publish them (emb_dpu_lookup.c:60-63,109-110), check
-    // monotonicity, start the asynchronous copy of the chunk's index window.  Always commits one group.
-    auto stage_indices = [&](uint32_t c, uint32_t buf) -> bool {
-        if (c >= total) {
-            cp_async_commit();
-            return false;
-        }
-        const BagDesc *dd;
-        uint32_t bb0, nnb;
-        locate(c, dd, bb0, nnb);
-        const uint32_t Bq = dd->nr_batches, il = dd->indices_len;
-        const uint32_t b = bb0 + tid;
-        bool nm = false;
-        if (tid <= nnb) {
-            const uint32_t v = min((b == 0) ? 0u : (b >= Bq ? il : raw0), il);
-            if (tid < nnb)
-                nm = v > min((b + 1 >= Bq) ? il : raw1, il);
-            s_off[buf][tid] = v;
-        }
-        nm = __any_sync(0xffffffffu, nm);
-        __syncwarp();
-        if (!nm) {
-            const uint32_t lo = s_off[buf][0], hi = s_off[buf][nnb];
-            const uint32_t n = min((uint32_t)SI, hi - lo);
-            const uint32_t *__restrict__ g_idx = dd->indices;
-            for (uint32_t i = tid; i < n; i += 32)
-                cp_async_u32(&s_idx[buf][i], g_idx + lo + i);
-        }
-        cp_async_commit();
-        return nm;
-    };
-
-    // stage C state (per chunk)
-    const uint4 *__restrict__ table = nullptr;
-    uint32_t rows = 0, row_base = 0;
-    bool bad = false, bad_any = false;
-
-    // one stretch of n staged lookups (window positions base .. base+n) of the chunk's bags off[0..nbj]
-    auto pool = [&](const uint32_t *__restrict__ idx, uint32_t n, uint32_t base, const uint32_t *off, uint32_t nbj) {
-        for (uint32_t c = sub * K; c < n; c += SUB * K) {
-            const uint32_t m = min((uint32_t)K, n - c);
-            uint32_t r[K];
-#pragma unroll
-            for (int u = 0; u < K; u++) {
-                uint32_t id = 0xffffffffu;
-                if ((uint32_t)u < m) {
-                    id = idx[c + u] - row_base;  // unsigned: rows below the shard wrap high
-                    bad |= id >= rows;
-                }
-                r[u] = id;
-            }
-            uint4 v[K];
-#pragma unroll
-            for (int u = 0; u < K; u++) {
-                v[u] = make_uint4(0u, 0u, 0u, 0u);
-                if (r[u] < rows)
-                    v[u] = ldg_row16(table + (size_t)r[u] * LANES);
-            }
-            const uint32_t p0 = base + c;  // bag of the piece's first lookup: last i with off[i] <= p0
-            uint32_t lo = 0, hi = nbj;
-            while (hi - lo > 1) {
-                const uint32_t mid = (lo + hi) >> 1;
-                if (off[mid] <= p0)
-                    lo = mid;
-                else
-                    hi = mid;
-            }
-            uint32_t bag = lo, bag_end = off[lo + 1];
-            uint4 acc = make_uint4(0u, 0u, 0u, 0u);
-#pragma unroll
-            for (int u = 0; u < K; u++) {
-                if ((uint32_t)u < m) {
-                    if (p0 + u >= bag_end) {  // crossed into a later bag: flush the partial sum
-                        uint32_t *a = s_acc + bag * D + lane * 4;
-                        atomicAdd(a + 0, acc.x);
-                        atomicAdd(a + 1, acc.y);
-                        atomicAdd(a + 2, acc.z);
-                        atomicAdd(a + 3, acc.w);
-                        acc = make_uint4(0u, 0u, 0u, 0u);
-                        do {
-                            bag++;
-                            bag_end = off[bag + 1];
-                        } while (p0 + u >= bag_end);
-                    }
-                    acc.x += v[u].x;
-                    acc.y += v[u].y;
-                    acc.z += v[u].z;
-                    acc.w += v[u].w;
-                }
-            }
-            uint32_t *a = s_acc + bag * D + lane * 4;
-            atomicAdd(a + 0, acc.x);
-            atomicAdd(a + 1, acc.y);
-            atomicAdd(a + 2, acc.z);
-            atomicAdd(a + 3, acc.w);
-        }
-    };
-
-    const uint32_t G = gridDim.x;
-    uint32_t c = blockIdx.x;
-    load_bounds(c);
-    bool ord_cur = stage_indices(c, 0);  // true = NOT monotone
-    load_bounds(c + G);
-    for (uint32_t k = 0; c < total; k++, c += G) {
-        const uint32_t buf = k & 1;
-        const bool ord_next = stage_indices(c + G, buf ^ 1);  // chunk k+1: bounds arrived during chunk k-1
-        load_bounds(c + 2 * G);                               // chunk k+2: in flight during chunk k
-        for (uint32_t i = tid; i < BAGS * D / 4; i += 32)
-            reinterpret_cast<uint4 *>(s_acc)[i] = make_uint4(0u, 0u, 0u, 0u);
-        cp_async_wait_group<1>();  // chunk k's indices are in the ring
-        __syncwarp();
-
-        const BagDesc *d;
-        uint32_t b0, nb;
-        locate(c, d, b0, nb);
-        const uint32_t flags = d->flags;
-        rows = d->rows;
-        row_base = d->row_base;
-        table = reinterpret_cast<const uint4 *>(d->table) + lane;
-        const uint32_t *off = s_off[buf];
-        bad = false;
-        if (!ord_cur) {
-            const uint32_t wlo = off[0], whi = off[nb];
-            uint32_t *ring = s_idx[buf];
-            pool(ring, min((uint32_t)SI, whi - wlo), wlo, off, nb);
-            const uint32_t *__restrict__ g_idx = d->indices;
-            for (uint32_t base = wlo + SI; base < whi; base += SI) {  // windows longer than a ring buffer
-                const uint32_t n = min((uint32_t)SI, whi - base);
-                __syncwarp();
-                for (uint32_t i = tid; i < n; i += 32)
-                    ring[i] = ldg_stream_u32(g_idx + base + i);
-                __syncwarp();
-                pool(ring, n, base, off, nb);
-            }
-        } else {
-            // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
-            const uint32_t *__restrict__ g_idx = d->indices;
-            for (uint32_t bag = sub; bag < nb; bag += SUB) {
-                const uint32_t start = off[bag], end = off[bag + 1];
-                uint4 acc = make_uint4(0u, 0u, 0u, 0u);
-                for (uint32_t p = start; p < end; p++) {
-                    const uint32_t id = __ldg(g_idx + p) - row_base;
-                    if (id < rows) {
-                        const uint4 v = ldg_row16(table + (size_t)id * LANES);
-                        acc.x += v.x;
-                        acc.y += v.y;
-                        acc.z += v.z;
-                        acc.w += v.w;
-                    } else {
-                        bad = true;
-                    }
-                }
-                reinterpret_cast<uint4 *>(s_acc)[bag * LANES + lane] = acc;
-            }
-        }
-        if (bad && !(flags & kDescSharded))
-            bad_any = true;
-        __syncwarp();
-
-        // post_process (emb_host.h:207-212) for the chunk's bags
-        const uint32_t bpr = d->bags_per_rank;
-        const uint32_t out_stride = d->out_stride;
-#pragma unroll
-        for (int it = 0; it < BAGS / SUB; it++) {
-            const uint32_t bag = it * SUB + sub;
-            if (bag >= nb)
-                break;
-            uint4 o = reinterpret_cast<const uint4 *>(s_acc)[bag * LANES + lane];
-            if (!(flags & kDescRaw))
-                o = make_uint4(__float_as_uint(dequant(o.x)), __float_as_uint(dequant(o.y)),
-                               __float_as_uint(dequant(o.z)), __float_as_uint(dequant(o.w)));
-            const uint32_t b = b0 + bag;
-            uint32_t *obase;
-            uint32_t row;
-            if (bpr) {
-                const uint32_t rk = b / bpr;
-                obase = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
-                row = b - rk * bpr;
-            } else {
-                obase = reinterpret_cast<uint32_t *>(d->out);
-                row = b;
-            }
-            uint32_t *dst = obase + (size_t)row * out_stride + lane * 4;
-            if (flags & kDescVecStore) {
-                stg_stream16(dst, o);
-            } else {
-                dst[0] = o.x;
-                dst[1] = o.y;
-                dst[2] = o.z;
-                dst[3] = o.w;
-            }
-        }
-        __syncwarp();  // accumulator, bounds and ring buffer `buf` are free again
-        ord_cur = ord_next;
-    }
-    cp_async_wait_group<0>();
-    if (bad_any)
-        atomicOr(err_flag, 1u);
-}
-
-/*
  * Warp-autonomous load-balanced sum-pool kernel for int32 fixed-point tables with short rows
  * (D = 4*LANES <= 32 columns, i.e. rows of 16..128 bytes).
  *
