@@ -113,3 +113,33 @@ def test_product_package_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".c", ".h")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "emb_oracle" not in text and "oracle/" not in text, os.path.join(dirpath, f)
+
+
+def test_runtime_interval_csv_is_what_the_reference_plots(tmp_path):
+    """`DPU,Start,Stop` rows (upmem/dputypes.py:87-98) that graph/runtime_intervals/main.py reads with pandas:
+    column 0 the unit, columns 1 and 2 start / stop in milliseconds."""
+    import types
+
+    import pandas as pd
+
+    from pim_embedding_lookup_b200 import dputypes as dt
+    grp = (dt.DpuRuntimeGroup * 2)()
+    keep = []
+    for n, g in enumerate(grp):
+        g.in_use = 2
+        g.length = 2
+        iv = (dt.DpuRuntimeInterval * 2)()
+        keep.append(iv)
+        for i in range(2):
+            iv[i].start.tv_sec, iv[i].start.tv_nsec = 1 + n, 500_000 * i
+            iv[i].stop.tv_sec, iv[i].stop.tv_nsec = 1 + n, 500_000 * i + 250_000
+        g.intervals = iv
+    cfg = types.SimpleNamespace(runtimes=True, runtime_file=str(tmp_path / "runtimes.csv"))
+    dt.write_results(cfg, grp)
+    data = pd.read_csv(cfg.runtime_file)
+    assert list(data.columns) == ["DPU", "Start", "Stop"] and len(data) == 4
+    assert list(data["DPU"]) == [0, 0, 1, 1]
+    assert data["Start"][1] == pytest.approx(1000.5) and data["Stop"][1] == pytest.approx(1000.75)
+    assert (data["Stop"] > data["Start"]).all()
+    dt.write_results(types.SimpleNamespace(runtimes=False, runtime_file=str(tmp_path / "none.csv")), grp)
+    assert not os.path.exists(tmp_path / "none.csv")
