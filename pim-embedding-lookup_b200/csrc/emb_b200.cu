@@ -355,8 +355,9 @@ int cta_threads()
 }
 
 /* avg_pool = lookups per bag of the launch (0 = unknown); max_table_bytes = the largest table the
- * launch reads (0 = unknown). */
-Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_bytes = 0)
+ * launch reads (0 = unknown); pcie_out = the launch stores its results into host memory while the copy
+ * engine brings the next group's indices in (the pipelined host-pointer call). */
+Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_bytes = 0, bool pcie_out = false)
 {
     Variant v;
     uint32_t D = g.shape.nr_cols;
@@ -412,7 +413,12 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         // 64 registers, so 8 rows in flight per lane and 16 bags per CTA; short bags 4 rows and 32 bags.
         // Same box, against the 64-thread CTAs above: C2 0.2688 -> 0.2585 ms, C3 0.0517 -> 0.0476 ms
         // (tools/cta32_sweep.sh, profiles/r1_sweeps.md).
-        const bool one_warp = lanes == 4 && (want == 32 || (!want && !g.unroll && !bags_mult));
+        // Not when the results cross PCIe from inside a pipelined call: the same C2 call through host pointers
+        // takes 2.88-2.92 ms with the 64-thread CTAs and 3.08 ms with the one-warp ones (bench e2e, runs r1y/r1z
+        // against r1v/r1u) -- the faster kernel's result bursts slow the concurrent index copy-in (2.42 -> 2.60 ms).
+        // Measurement knob: EMB_PCIE_OUT_ONE_WARP=1 lifts the exception.
+        static const bool pcie_one_warp = env_u32("EMB_PCIE_OUT_ONE_WARP", 0) != 0;
+        const bool one_warp = lanes == 4 && (want == 32 || (!want && !g.unroll && !bags_mult && (!pcie_out || pcie_one_warp)));
         if (!want)
             want = one_warp ? 32 : lanes >= 32 ? 128 : 64;
         if (want == 128 || (want == 64 && lanes <= 16) || (want == 32 && lanes <= 8))
@@ -1458,7 +1464,8 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     uint64_t max_tb = 0;
     for (uint32_t t = 0; t < T; t++)
         max_tb = std::max<uint64_t>(max_tb, g.tables[t].rows * D * 4ull);
-    const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, max_tb);
+    const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, max_tb,
+                                         out_mapped && !in_mapped && n_groups > 1);
     std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
     {
         // Group sizes grow by a factor r per group: nothing can be pooled before the first group's
