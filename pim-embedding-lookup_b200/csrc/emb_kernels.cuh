@@ -80,6 +80,9 @@ __device__ __forceinline__ uint32_t chunk_first_bag(const BagDesc *d, uint32_t c
 #ifndef EMB_LD_MODE
 #define EMB_LD_MODE 4
 #endif
+#ifndef EMB_CONTIG
+#define EMB_CONTIG 0  // balanced kernel: 1 = contiguous stretch per sub-warp instead of round-robin pieces (experiment)
+#endif
 
 __device__ __forceinline__ uint64_t l2_policy_evict_last()
 {
@@ -431,6 +434,75 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
             for (uint32_t i = tid; i < n; i += THREADS)
                 s_idx[i] = ldg_stream_u32(g_idx + base + i);
             __syncthreads();
+#if EMB_CONTIG
+            // Experiment (build switch, default off; tools/contig_ab.sh): every sub-warp pools ONE contiguous
+            // stretch of the staged window -- one bag search per sub-warp and pass, the running sum kept in
+            // registers across its K-lookup steps, a flush only where a bag ends inside the stretch.
+            {
+                const uint32_t per = (n + SUB - 1) / SUB;
+                const uint32_t cb = min(n, sub * per), ce = min(n, cb + per);
+                uint32_t lo = 0, hi = nb;
+                const uint32_t pfirst = base + cb;
+                while (hi - lo > 1) {  // bag of the stretch's first lookup: last i with s_off[i] <= pfirst
+                    uint32_t mid = (lo + hi) >> 1;
+                    if (s_off[mid] <= pfirst)
+                        lo = mid;
+                    else
+                        hi = mid;
+                }
+                uint32_t bag = lo, bag_end = s_off[lo + 1];
+                uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+                for (uint32_t c = cb; c < ce; c += K) {
+                    const uint32_t m = min((uint32_t)K, ce - c);
+                    uint32_t r[K];
+#pragma unroll
+                    for (int u = 0; u < K; u++) {
+                        uint32_t id = 0xffffffffu;
+                        if ((uint32_t)u < m) {
+                            id = s_idx[c + u] - row_base;
+                            bad |= id >= rows;
+                        }
+                        r[u] = id;
+                    }
+                    uint4 v[K];
+#pragma unroll
+                    for (int u = 0; u < K; u++) {
+                        v[u] = make_uint4(0u, 0u, 0u, 0u);
+                        if (r[u] < rows)
+                            v[u] = ldg_row16(table + (size_t)r[u] * LANES);
+                    }
+                    const uint32_t p0 = base + c;
+#pragma unroll
+                    for (int u = 0; u < K; u++) {
+                        if ((uint32_t)u < m) {
+                            if (p0 + u >= bag_end) {
+                                uint32_t *a = s_acc + bag * D + lane * 4;
+                                atomicAdd(a + 0, acc.x);
+                                atomicAdd(a + 1, acc.y);
+                                atomicAdd(a + 2, acc.z);
+                                atomicAdd(a + 3, acc.w);
+                                acc = make_uint4(0u, 0u, 0u, 0u);
+                                do {
+                                    bag++;
+                                    bag_end = s_off[bag + 1];
+                                } while (p0 + u >= bag_end);
+                            }
+                            acc.x += v[u].x;
+                            acc.y += v[u].y;
+                            acc.z += v[u].z;
+                            acc.w += v[u].w;
+                        }
+                    }
+                }
+                if (cb < ce) {
+                    uint32_t *a = s_acc + bag * D + lane * 4;
+                    atomicAdd(a + 0, acc.x);
+                    atomicAdd(a + 1, acc.y);
+                    atomicAdd(a + 2, acc.z);
+                    atomicAdd(a + 3, acc.w);
+                }
+            }
+#else
             for (uint32_t c = sub * K; c < n; c += SUB * K) {
                 const uint32_t m = min((uint32_t)K, n - c);
                 uint32_t r[K];
@@ -489,6 +561,7 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
                 atomicAdd(a + 2, acc.z);
                 atomicAdd(a + 3, acc.w);
             }
+#endif
         }
     } else {
         // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
