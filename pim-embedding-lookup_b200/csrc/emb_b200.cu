@@ -421,7 +421,7 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         const bool one_warp = lanes == 4 && (want == 32 || (!want && !g.unroll && !bags_mult && (!pcie_out || pcie_one_warp)));
         if (!want)
             want = one_warp ? 32 : lanes >= 32 ? 128 : 64;
-        if (want == 128 || (want == 64 && lanes <= 16) || (want == 32 && lanes <= 8))
+        if (want == 128 || (want == 64 && lanes <= 16) || (want == 32 && lanes <= 16))
             v.threads = want;
         if (one_warp && !g.unroll)
             v.unroll = short_bags ? 4 : 8;
@@ -489,7 +489,7 @@ void launch_balanced_k(int mult, uint32_t grid, cudaStream_t s, const BagDesc *d
 template <int LANES>
 void launch_balanced(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
-    if constexpr (LANES <= 8) {  // one warp per CTA: the CTA barriers cost nothing
+    if constexpr (LANES <= 16) {  // one warp per CTA: the CTA barriers cost nothing (default for LANES 4; EMB_CTA_THREADS=32 otherwise)
         if (v.threads == 32) {
             if (v.unroll == 8)
                 return launch_balanced_k<LANES, 8, 32, 32>(v.mult, grid, s, d, n, uni);
