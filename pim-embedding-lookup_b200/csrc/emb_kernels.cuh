@@ -80,6 +80,9 @@ __device__ __forceinline__ uint32_t chunk_first_bag(const BagDesc *d, uint32_t c
 #ifndef EMB_LD_MODE
 #define EMB_LD_MODE 4
 #endif
+#ifndef EMB_BF_SEARCH
+#define EMB_BF_SEARCH 0  // balanced kernel: 1 = branch-free bag search per piece (experiment; BAGS is a power of two)
+#endif
 #ifndef EMB_CONTIG
 #define EMB_CONTIG 0  // balanced kernel: 1 = contiguous stretch per sub-warp instead of round-robin pieces (experiment)
 #endif
@@ -435,7 +438,7 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
                 s_idx[i] = ldg_stream_u32(g_idx + base + i);
             __syncthreads();
 #if EMB_CONTIG
-            // Experiment (build switch, default off; tools/contig_ab.sh): every sub-warp pools ONE contiguous
+            // Experiment (build switch, default off; tools/piece_loop_ab.sh): every sub-warp pools ONE contiguous
             // stretch of the staged window -- one bag search per sub-warp and pass, the running sum kept in
             // registers across its K-lookup steps, a flush only where a bag ends inside the stretch.
             {
@@ -524,6 +527,16 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
                 }
                 // bag of the piece's first lookup: last i with s_off[i] <= p (skips empty bags)
                 const uint32_t p0 = base + c;
+#if EMB_BF_SEARCH
+                // Experiment (build switch, default off): branch-free binary lifting, log2(BAGS) predicated steps
+                uint32_t lo = 0;
+#pragma unroll
+                for (int step = BAGS / 2; step >= 1; step >>= 1) {
+                    const uint32_t t = lo + step;
+                    if (t < nb && s_off[t] <= p0)
+                        lo = t;
+                }
+#else
                 uint32_t lo = 0, hi = nb;
                 while (hi - lo > 1) {
                     uint32_t mid = (lo + hi) >> 1;
@@ -532,6 +545,7 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
                     else
                         hi = mid;
                 }
+#endif
                 uint32_t bag = lo, bag_end = s_off[lo + 1];
                 uint4 acc = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
