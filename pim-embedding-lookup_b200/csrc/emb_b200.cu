@@ -22,6 +22,7 @@
 #include <algorithm>
 #include <atomic>
 #include <mutex>
+#include <utility>
 #include <vector>
 
 namespace {
@@ -38,6 +39,7 @@ struct Table {
     int kind = 0;  // 0 = empty, EMB_TABLE_FIXED, EMB_TABLE_FLOAT
     bool sharded = false;
     void *d_tmap = nullptr;  // CUtensorMap [rows][D] in device memory, built on first use by the TMA kernel
+    uint32_t generation = 0; // bumped whenever the slab is (re)allocated or freed: plans remember it
 };
 
 struct Ctx {
@@ -227,15 +229,24 @@ int table_slot(uint32_t table_id, Table **out)
     return EMB_OK;
 }
 
-int table_alloc(Table *t, uint64_t rows, int kind)
+/* (Re)allocate the slab of a table slot for `rows` rows.  The slab holds rows + 1 rows: the extra last row is
+ * all zero and is what the stretch kernel gathers for an index that must contribute nothing (out of range, a
+ * row of another shard, padding), so its row loads need no predicate.  Everything this function enqueues goes
+ * on `s`, the stream the caller populates on, so the zero fill is ordered before the caller's copies.  A slot
+ * that is reused forgets that it once was a row shard. */
+int table_alloc(Table *t, uint64_t rows, int kind, cudaStream_t s)
 {
-    if (rows == 0 || rows > 0xffffffffull)
-        return fail(EMB_EINVAL, "nr_rows %llu unsupported (1 .. 2^32-1)", (unsigned long long)rows);
+    if (rows == 0 || rows > 0xfffffffeull)
+        return fail(EMB_EINVAL, "nr_rows %llu unsupported (1 .. 2^32-2)", (unsigned long long)rows);
+    t->row_base = 0;
+    t->sharded = false;
     if (t->dev && t->rows == rows) {
         t->kind = kind;
         return EMB_OK;
     }
     if (t->dev) {
+        // plans made for the old slab may still be running on any stream
+        cudaDeviceSynchronize();
         cudaFree(t->dev);
         t->dev = nullptr;
     }
@@ -243,15 +254,16 @@ int table_alloc(Table *t, uint64_t rows, int kind)
         cudaFree(t->d_tmap);
         t->d_tmap = nullptr;
     }
-    size_t bytes = (size_t)rows * g.shape.nr_cols * 4;
+    t->generation++;
+    size_t bytes = (size_t)(rows + 1) * g.shape.nr_cols * 4;
     cudaError_t e = cudaMalloc(&t->dev, bytes);
     if (e != cudaSuccess) {
         t->dev = nullptr;
         t->kind = 0;
         return fail(EMB_ENOMEM, "cudaMalloc(%zu bytes) for a table: %s", bytes, cudaGetErrorString(e));
     }
-    // columns arrive one populate_mram() call at a time: unwritten ones read as 0
-    e = cudaMemsetAsync(t->dev, 0, bytes, g.stream);
+    // columns arrive one populate_mram() call at a time: unwritten ones read as 0; the last row stays 0
+    e = cudaMemsetAsync(t->dev, 0, bytes, s);
     if (e != cudaSuccess)
         return fail(EMB_ECUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
     t->rows = rows;
@@ -336,14 +348,14 @@ uint32_t lanes_for_dim(uint32_t D)
 /* Which kernel pools a launch, decided when the descriptors are built (the CTA -> bag
  * mapping depends on it). */
 struct Variant {
-    int kind;      // 0 generic, 1 bag-per-sub-warp (any table kind), 2 / 3 load-balanced per CTA / per warp (int32 only),
-                   // 4 TMA gather4 (rows of 64..512 bytes, any table kind), 5 load-balanced, pipelined sub-chunks
-                   // (int32 only, rows up to 128 bytes)
+    int kind;      // 0 generic, 1 bag-per-sub-warp (index-ordered adds, any table kind), 2 / 3 round-1 load-balanced
+                   // kernels per CTA / per warp (int32 only), 4 TMA gather4 (rows of 64..512 bytes, any table kind),
+                   // 6 stretch kernel (load-balanced, no atomics; int32 and fp32)
     int unroll;    // K
     int mult;      // bags per CTA / sub-warps per CTA
     uint32_t bags; // bags per CTA
     int threads;   // CTA size of the balanced kernel: 32, 64, 128 or 256
-    int pipe_bags; // pipelined kernel (kind 5): bags per sub-chunk / sub-warps per CTA (2 or 3); mult = sub-chunks per CTA
+    int stage;     // stretch kernel: lookups staged per pass
 };
 
 int cta_threads()
@@ -357,7 +369,8 @@ int cta_threads()
 /* avg_pool = lookups per bag of the launch (0 = unknown); max_table_bytes = the largest table the
  * launch reads (0 = unknown); pcie_out = the launch stores its results into host memory while the copy
  * engine brings the next group's indices in (the pipelined host-pointer call). */
-Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_bytes = 0, bool pcie_out = false)
+Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_bytes = 0, bool pcie_out = false,
+                     bool all_float = false)
 {
     Variant v;
     uint32_t D = g.shape.nr_cols;
@@ -369,9 +382,9 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         v.bags = emb::kThreads / 32;
         return v;
     }
-    static const int dflt_kind = (int)env_u32("EMB_DEFAULT_VARIANT", 2);  // measurement knob
-    v.kind = g.variant ? g.variant : (dflt_kind >= 1 && dflt_kind <= 5 ? dflt_kind : 2);
-    v.pipe_bags = 0;
+    static const int dflt_kind = (int)env_u32("EMB_DEFAULT_VARIANT", 6);  // measurement knob
+    v.kind = g.variant ? g.variant : ((dflt_kind >= 1 && dflt_kind <= 4) || dflt_kind == 6 ? dflt_kind : 6);
+    v.stage = 0;
     // Tables that stay in L2 while a launch walks them (<= 16 MB each, rows up to 128 bytes): the
     // warp-autonomous kernel issues ~3x fewer instructions per lookup and wins (26 tables of 4 / 8 / 16 MB:
     // 0.179 / 0.183 / 0.191 ms against 0.187 / 0.191 / 0.197 for the one-warp balanced kernel;
@@ -383,14 +396,15 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         v.kind = 3;
         auto_warp = true;
     }
-    // emb_set_tuning(5, k, 8): 8 sub-chunks per CTA means something only to the pipelined kernel
-    const int bags_mult = (g.bags_mult == 8 && (v.kind != 5 || lanes > 8 || any_float)) ? 0 : g.bags_mult;
-    if ((v.kind == 3 || v.kind == 5) && lanes > 8)
-        v.kind = 2;  // the warp-autonomous and the pipelined kernel are for rows up to 128 bytes
+    const int bags_mult = (g.bags_mult == 8 && v.kind != 6) ? 0 : g.bags_mult;  // 8x only means something to the stretch kernel
+    if (v.kind == 3 && lanes > 8)
+        v.kind = 2;  // the warp-autonomous kernel is for rows up to 128 bytes
     if (v.kind == 4 && lanes < 4)
         v.kind = 2;  // the TMA kernel is for rows of 64 bytes and more
-    if (any_float && v.kind != 4)
-        v.kind = 1;  // fp32 sums keep index order (embedding_lookup_idx.cc:33-77); kinds 1 and 4 do
+    if (any_float && v.kind != 4 && !(v.kind == 6 && all_float))
+        v.kind = 1;  // fp32 sums in strict index order (embedding_lookup_idx.cc:33-77): kinds 1 and 4; the stretch
+                     // kernel pools fp32 tables too (deterministic, reassociated at its cut points), but a launch
+                     // is compiled for one element kind
     // defaults from the sweeps in profiles/r1_sweeps.md (tools/sweep.py): 64-byte rows want many
     // small CTAs; 256-byte rows 8 rows in flight per lane and 4x the bags per CTA; 512-byte rows 2x
     v.unroll = g.unroll ? g.unroll : (lanes >= 16 || auto_warp ? 8 : 4);
@@ -435,13 +449,15 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         v.mult = 1;
         v.bags = emb::kThreads;  // 32 bags per warp
     }
-    if (v.kind == 5) {  // one warp per CTA, K = 8, mult = sub-chunks per CTA, pipe_bags x sub-warps bags per sub-chunk
-        static const int pb = (int)env_u32("EMB_PIPE_BAGS", 2);  // measurement knob: 2 or 3
-        v.unroll = 8;
+    if (v.kind == 6) {
+        // one warp per CTA; defaults from the round-2 sweeps (profiles/r2_sweeps.md)
+        const bool short_bags = avg_pool > 0.0 && avg_pool <= 4.0;
         v.threads = 32;
-        v.mult = (g.bags_mult == 2 || g.bags_mult == 4 || g.bags_mult == 8) ? g.bags_mult : 4;
-        v.pipe_bags = pb == 3 ? 3 : 2;
-        v.bags = 32 / lanes * v.pipe_bags * v.mult;
+        v.unroll = g.unroll ? g.unroll : (short_bags && lanes <= 8 ? 4 : 8);
+        v.mult = bags_mult ? bags_mult : (lanes >= 16 ? 4 : short_bags ? 4 : 2);
+        static const int big_stage = (int)env_u32("EMB_STRETCH_STAGE", 0);  // measurement knob: 1 = the larger pass
+        v.stage = big_stage;
+        v.bags = 32 / lanes * v.mult;
     }
     if (v.kind == 4) {
         v.mult = 1;
@@ -530,29 +546,46 @@ void launch_warp(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc 
     }
 }
 
-template <int LANES, int PB>
-void launch_pipe_b(int nch, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+/* Stretch kernel: K rows in flight per lane, BAGS = sub-warps x mult bags per one-warp CTA, STAGE lookups per
+ * pass (the smaller pass keeps shared memory -- and so the L1 the row loads live in -- small; knob
+ * EMB_STRETCH_STAGE=1 doubles it). */
+template <int LANES, int K, int MULT, bool IS_FLOAT>
+void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
-    constexpr int BAGS = 32 / LANES * PB;
-    if (nch == 8)
-        emb::bag_sum_pipe_kernel<LANES, 8, BAGS, 8, 32><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
-    else if (nch == 2)
-        emb::bag_sum_pipe_kernel<LANES, 8, BAGS, 2, 32><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
+    constexpr int SUB = 32 / LANES;
+    constexpr int BAGS = SUB * MULT;
+    constexpr int UNIT = SUB * K;  // a pass is a whole number of K-lookup steps of every sub-warp
+    constexpr int SMALL = (LANES <= 4 ? 256 : 128) < UNIT ? UNIT : (LANES <= 4 ? 256 : 128);
+    constexpr int LARGE = 2 * SMALL;
+    constexpr int MINB = 32;
+    if (big_stage)
+        emb::bag_sum_stretch_kernel<LANES, K, BAGS, LARGE, IS_FLOAT, MINB><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
     else
-        emb::bag_sum_pipe_kernel<LANES, 8, BAGS, 4, 32><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
+        emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, MINB><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
+}
+
+template <int LANES, int K, bool IS_FLOAT>
+void launch_stretch_k(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+{
+    switch (v.mult) {
+    case 1: return launch_stretch_m<LANES, K, 1, IS_FLOAT>(v.stage, grid, s, d, n, uni);
+    case 4: return launch_stretch_m<LANES, K, 4, IS_FLOAT>(v.stage, grid, s, d, n, uni);
+    case 8: return launch_stretch_m<LANES, K, 8, IS_FLOAT>(v.stage, grid, s, d, n, uni);
+    default: return launch_stretch_m<LANES, K, 2, IS_FLOAT>(v.stage, grid, s, d, n, uni);
+    }
 }
 
 template <int LANES>
-void launch_pipe(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+void launch_stretch(const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
-    if constexpr (LANES <= 8) {
-        if (v.pipe_bags == 3)
-            launch_pipe_b<LANES, 3>(v.mult, grid, s, d, n, uni);
-        else
-            launch_pipe_b<LANES, 2>(v.mult, grid, s, d, n, uni);
-    } else {
-        (void)v; (void)grid; (void)s; (void)d; (void)n; (void)uni;
+    if (is_float) {
+        if (v.unroll == 4)
+            return launch_stretch_k<LANES, 4, true>(v, grid, s, d, n, uni);
+        return launch_stretch_k<LANES, 8, true>(v, grid, s, d, n, uni);
     }
+    if (v.unroll == 4)
+        return launch_stretch_k<LANES, 4, false>(v, grid, s, d, n, uni);
+    launch_stretch_k<LANES, 8, false>(v, grid, s, d, n, uni);
 }
 
 template <int LANES>
@@ -574,10 +607,10 @@ void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uin
 }
 
 template <int LANES>
-void launch_for_lanes(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+void launch_for_lanes(const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
-    if (v.kind == 5)
-        launch_pipe<LANES>(v, grid, s, d, n, uni);
+    if (v.kind == 6)
+        launch_stretch<LANES>(v, is_float, grid, s, d, n, uni);
     else if (v.kind == 4)
         launch_tma<LANES>(grid, s, d, n, uni);
     else if (v.kind == 3)
@@ -603,19 +636,20 @@ uint32_t uniform_chunks(const BagDesc *h, uint32_t n)
 }
 
 /* `uni` = uniform_chunks() of the n descriptors (0 = search). */
-int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_t uni, uint32_t grid, cudaStream_t s)
+int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_t uni, uint32_t grid, cudaStream_t s,
+                   bool is_float = false)
 {
     if (grid == 0)
         return EMB_OK;
     uint32_t D = g.shape.nr_cols;
     switch (v.kind ? lanes_for_dim(D) : 0) {
     case 0: emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, uni, D, g.d_err); break;
-    case 1: launch_for_lanes<1>(v, grid, s, d_descs, n, uni); break;
-    case 2: launch_for_lanes<2>(v, grid, s, d_descs, n, uni); break;
-    case 4: launch_for_lanes<4>(v, grid, s, d_descs, n, uni); break;
-    case 8: launch_for_lanes<8>(v, grid, s, d_descs, n, uni); break;
-    case 16: launch_for_lanes<16>(v, grid, s, d_descs, n, uni); break;
-    default: launch_for_lanes<32>(v, grid, s, d_descs, n, uni); break;
+    case 1: launch_for_lanes<1>(v, is_float, grid, s, d_descs, n, uni); break;
+    case 2: launch_for_lanes<2>(v, is_float, grid, s, d_descs, n, uni); break;
+    case 4: launch_for_lanes<4>(v, is_float, grid, s, d_descs, n, uni); break;
+    case 8: launch_for_lanes<8>(v, is_float, grid, s, d_descs, n, uni); break;
+    case 16: launch_for_lanes<16>(v, is_float, grid, s, d_descs, n, uni); break;
+    default: launch_for_lanes<32>(v, is_float, grid, s, d_descs, n, uni); break;
     }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
@@ -711,11 +745,13 @@ int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, const Va
 
 struct emb_plan {
     std::vector<BagDesc> h;
+    std::vector<std::pair<uint32_t, uint32_t>> gen;  // (table slot, Table::generation) of every query
     BagDesc *d = nullptr;
     uint32_t grid = 0;
     uint32_t uni = 0;  // uniform_chunks() of the descriptors
     uint64_t bytes = 0;
     Variant variant = {0, 1, 1, 8, 256, 0};
+    bool all_float = false;
 };
 
 extern "C" {
@@ -756,11 +792,11 @@ int emb_set_unroll(int unroll)
 
 int emb_set_tuning(int variant, int unroll, int bags_mult)
 {
-    if (variant < 0 || variant > 5)
-        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp), 2 (load-balanced per CTA), "
-                                "3 (load-balanced per warp), 4 (TMA gather4) or 5 (load-balanced, pipelined)");
-    if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4 && !(variant == 5 && bags_mult == 8))
-        return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2 or 4 (variant 5: sub-chunks per CTA, 2, 4 or 8)");
+    if (variant < 0 || variant > 6 || variant == 5)
+        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp), 2 (round-1 load-balanced per CTA), "
+                                "3 (round-1 load-balanced per warp), 4 (TMA gather4) or 6 (stretch kernel)");
+    if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4 && !(variant == 6 && bags_mult == 8))
+        return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2 or 4 (variant 6: also 8)");
     int rc = emb_set_unroll(unroll);
     if (rc)
         return rc;
@@ -844,7 +880,7 @@ struct dpu_set_t *populate_mram(uint32_t table_id, uint64_t nr_rows, uint32_t co
         die("populate_mram", EMB_EINVAL);
     }
     Table *t = nullptr;
-    if ((rc = table_slot(table_id, &t)) || (rc = table_alloc(t, nr_rows, EMB_TABLE_FIXED)))
+    if ((rc = table_slot(table_id, &t)) || (rc = table_alloc(t, nr_rows, EMB_TABLE_FIXED, g.stream)))
         die("populate_mram", rc);
     size_t bytes = (size_t)nr_rows * 4;
     size_t cap = g.col_bytes;
@@ -883,7 +919,7 @@ static int populate_whole(uint32_t table_id, uint64_t nr_rows, const void *src, 
     if (kind == EMB_TABLE_FLOAT && !src_f32)
         return fail(EMB_EINVAL, "a float table needs fp32 source data");
     Table *t = nullptr;
-    if ((rc = table_slot(table_id, &t)) || (rc = table_alloc(t, nr_rows, kind)))
+    if ((rc = table_slot(table_id, &t)) || (rc = table_alloc(t, nr_rows, kind, s)))
         return rc;
     uint64_t n = nr_rows * g.shape.nr_cols;
     CU(cudaMemcpyAsync(t->dev, src, n * 4, src_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
@@ -969,7 +1005,9 @@ int emb_free_table(uint32_t table_id)
     CU(cudaDeviceSynchronize());
     cudaFree(g.tables[table_id].dev);
     cudaFree(g.tables[table_id].d_tmap);
+    const uint32_t gen = g.tables[table_id].generation + 1;  // plans made for the freed slab refuse to launch
     g.tables[table_id] = Table();
+    g.tables[table_id].generation = gen;
     return EMB_OK;
 }
 
@@ -1024,16 +1062,21 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
     p->h.resize(n);
     uint64_t chunk = 0;
     const uint64_t D = g.shape.nr_cols;
-    bool any_float = false;
-    for (uint32_t i = 0; i < n; i++)
-        any_float |= queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].kind == EMB_TABLE_FLOAT;
+    bool any_float = false, all_float = true;
+    for (uint32_t i = 0; i < n; i++) {
+        const bool f = queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].kind == EMB_TABLE_FLOAT;
+        any_float |= f;
+        all_float &= f;
+    }
+    p->all_float = all_float;
     {
         uint64_t li = 0, nb = 0;
         for (uint32_t i = 0; i < n; i++) {
             li += queries[i].indices_len;
             nb += queries[i].nr_batches;
         }
-        p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0, max_table_bytes_of(queries, n));
+        p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0, max_table_bytes_of(queries, n), false,
+                                  all_float);
     }
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
@@ -1042,6 +1085,7 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
             return rc;
         }
         chunk += c;
+        p->gen.emplace_back(queries[i].table_id, g.tables[queries[i].table_id].generation);
         {  // a bag slice reads about its share of the indices (the host cannot see the device offsets)
             const uint64_t nbq = p->h[i].bag_end - p->h[i].bag_first;
             const uint64_t liq = queries[i].nr_batches ? (uint64_t)queries[i].indices_len * nbq / queries[i].nr_batches : 0;
@@ -1070,8 +1114,13 @@ int emb_plan_launch(emb_plan *plan, void *stream)
 {
     if (!plan)
         return fail(EMB_EINVAL, "NULL plan");
+    // the descriptors hold raw slab pointers: a table freed or re-allocated since the plan was made would be
+    // read after free
+    for (const auto &tg : plan->gen)
+        if (tg.first >= g.tables.size() || g.tables[tg.first].generation != tg.second || !g.tables[tg.first].kind)
+            return fail(EMB_ESTATE, "plan is stale: table %u was freed or re-allocated after emb_plan_create", tg.first);
     return launch_bag_sum(plan->variant, plan->d, (uint32_t)plan->h.size(), plan->uni, plan->grid,
-                          stream ? (cudaStream_t)stream : g.stream);
+                          stream ? (cudaStream_t)stream : g.stream, plan->all_float);
 }
 
 void emb_plan_destroy(emb_plan *plan)
@@ -1119,18 +1168,21 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
     }
     const int slot = g.ring_next;
     g.ring_next = (g.ring_next + 1) % kRingSlots;
-    CU(cudaEventSynchronize(g.ring_ev[slot]));  // the slot's previous upload has executed
+    CU(cudaEventSynchronize(g.ring_ev[slot]));  // the slot's previous upload AND the kernel reading it have executed
     BagDesc *h = g.ring_h[slot];
-    bool any_float = false;
-    for (uint32_t i = 0; i < n; i++)
-        any_float |= queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].kind == EMB_TABLE_FLOAT;
+    bool any_float = false, all_float = true;
+    for (uint32_t i = 0; i < n; i++) {
+        const bool f = queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].kind == EMB_TABLE_FLOAT;
+        any_float |= f;
+        all_float &= f;
+    }
     uint64_t tot_li = 0, tot_nb = 0;
     for (uint32_t i = 0; i < n; i++) {
         tot_li += queries[i].indices_len;
         tot_nb += queries[i].nr_batches;
     }
     const Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0,
-                                         max_table_bytes_of(queries, n));
+                                         max_table_bytes_of(queries, n), false, all_float);
     uint64_t chunk = 0;
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
@@ -1141,8 +1193,11 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
     if (chunk > 0x7fffffffull)
         return fail(EMB_EINVAL, "too many bags for one launch");
     CU(cudaMemcpyAsync(g.ring_d[slot], h, n * sizeof(BagDesc), cudaMemcpyHostToDevice, s));
+    rc = launch_bag_sum(variant, g.ring_d[slot], n, uniform_chunks(h, n), (uint32_t)chunk, s, all_float);
+    // recorded AFTER the launch: the slot (pinned copy and device copy) is recycled only once the kernel that
+    // reads its descriptors has run, whatever stream the next user of the slot launches on
     CU(cudaEventRecord(g.ring_ev[slot], s));
-    return launch_bag_sum(variant, g.ring_d[slot], n, uniform_chunks(h, n), (uint32_t)chunk, s);
+    return rc;
 }
 
 int emb_check_indices(void)
@@ -1339,7 +1394,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     if (T > g.tables.size())
         return fail(EMB_ESTATE, "lookup over %u tables but only %zu slots exist", T, g.tables.size());
     uint64_t tot_idx = 0, tot_bags = 0;
-    bool any_float = false;
+    bool any_float = false, all_float = true;
     for (uint32_t t = 0; t < T; t++) {
         if (!g.tables[t].kind)
             return fail(EMB_ESTATE, "table %u is not populated", t);
@@ -1348,6 +1403,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         tot_idx += indices_len[t];
         tot_bags += nr_batches[t];
         any_float |= g.tables[t].kind == EMB_TABLE_FLOAT;
+        all_float &= g.tables[t].kind == EMB_TABLE_FLOAT;
     }
     int rc;
     if (g.desc_cap < T) {
@@ -1465,7 +1521,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     for (uint32_t t = 0; t < T; t++)
         max_tb = std::max<uint64_t>(max_tb, g.tables[t].rows * D * 4ull);
     const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, max_tb,
-                                         out_mapped && !in_mapped && n_groups > 1);
+                                         out_mapped && !in_mapped && n_groups > 1, all_float);
     std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
     {
         // Group sizes grow by a factor r per group: nothing can be pooled before the first group's
@@ -1555,7 +1611,8 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             CU(cudaStreamWaitEvent(s_k, ev[3 * gi], 0));
         }
         CU(cudaEventRecord(ev[3 * gi + 1], s_k));
-        if ((rc = launch_bag_sum(variant, g.d_descs + t0, t1 - t0, uniform_chunks(g.h_descs + t0, t1 - t0), g_grid[gi], s_k)))
+        if ((rc = launch_bag_sum(variant, g.d_descs + t0, t1 - t0, uniform_chunks(g.h_descs + t0, t1 - t0), g_grid[gi], s_k,
+                                 all_float)))
             return rc;
         launches += g_grid[gi] ? 1 : 0;
         CU(cudaEventRecord(ev[3 * gi + 2], s_k));

@@ -66,101 +66,38 @@ __device__ __forceinline__ uint32_t chunk_first_bag(const BagDesc *d, uint32_t c
     return d->bag_first + c * per;
 }
 
-/* EMB_LD_MODE (build-time switch; measurements in profiles/r1_sweeps.md):
- *   4  rows: ld.global.nc -- L1 allocates, L2 default priority                      (default)
- *   0  rows: ld.global.nc.L1::no_allocate (the first default: "a row is used once, keep it out of L1")
- *   1  rows: L1::no_allocate + L2 evict_last policy; indices/offsets/outputs: L2 evict_first policy
- *   2  rows: L1::no_allocate + .L2::64B prefetch size      3  + .L2::128B prefetch size
- *   5  rows: L1::no_allocate + L2 evict_normal policy      6  L1::no_allocate + L2 evict_last policy (hoisted)
- * ncu shows every sector of an L1::no_allocate load arriving at L2 as evict_first
- * (lts__t_sectors_srcunit_tex_op_read_evict_first_*), so the rows of the table being walked were the
- * first thing L2 dropped.  Plain ld.global.nc is faster on every workload: C2 0.2443 -> 0.2422 ms,
- * C3 0.0496 -> 0.0456, C4 0.658 -> 0.6088, C5 0.5023 -> 0.4819 (tools/ldmode_ab.sh, same box).
- * The index / offset streams and the output rows stay L1::no_allocate: they are used once. */
-#ifndef EMB_LD_MODE
-#define EMB_LD_MODE 4
-#endif
 #ifndef EMB_BF_SEARCH
-#define EMB_BF_SEARCH 0  // balanced kernel: 1 = branch-free bag search per piece (experiment; BAGS is a power of two)
+#define EMB_BF_SEARCH 0  // old balanced kernel: 1 = branch-free bag search per piece (round-1 experiment switch)
 #endif
 #ifndef EMB_CONTIG
-#define EMB_CONTIG 0  // balanced kernel: 1 = contiguous stretch per sub-warp instead of round-robin pieces (experiment)
+#define EMB_CONTIG 0  // old balanced kernel: 1 = contiguous stretch per sub-warp (round-1 experiment switch)
 #endif
 
-__device__ __forceinline__ uint64_t l2_policy_evict_last()
-{
-    uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_first()
-{
-    uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
-}
-
+/* Row loads are plain ld.global.nc (L1 allocates, L2 default priority).  Measured in round 1 against
+ * L1::no_allocate, L2 evict_last / evict_normal policy operands and the .L2::64B / .L2::128B prefetch sizes
+ * (profiles/r1_sweeps.md): ncu counts every sector of an L1::no_allocate load as evict_first at L2, so the rows
+ * of the table being walked were the first thing L2 dropped; plain ld.global.nc is faster on every workload
+ * (C2 0.2443 -> 0.2422 ms, C3 0.0496 -> 0.0456, C4 0.658 -> 0.6088, C5 0.5023 -> 0.4819).  The index / offset
+ * streams and the output rows stay L1::no_allocate: they are used once. */
 __device__ __forceinline__ uint4 ldg_row16(const uint4 *p)
 {
     uint4 r;
-#if EMB_LD_MODE == 1
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p), "l"(l2_policy_evict_last()));
-#elif EMB_LD_MODE == 2
-    asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-#elif EMB_LD_MODE == 3
-    asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-#elif EMB_LD_MODE == 4
-    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-#elif EMB_LD_MODE == 5 || EMB_LD_MODE == 6
-    uint64_t pol;  // not volatile: one policy per thread, hoisted out of the loops
-#if EMB_LD_MODE == 5
-    asm("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
-#else
-    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-#endif
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p), "l"(pol));
-#else
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-#endif
+    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
 
 __device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t *p)
 {
     uint32_t r;
-#if EMB_LD_MODE == 1
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;"
-                 : "=r"(r)
-                 : "l"(p), "l"(l2_policy_evict_first()));
-#else
     asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
-#endif
     return r;
 }
 
 __device__ __forceinline__ void stg_stream16(void *p, uint4 v)
 {
-#if EMB_LD_MODE == 1
-    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x),
-                 "r"(v.y), "r"(v.z), "r"(v.w), "l"(l2_policy_evict_first())
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+                 "r"(v.w)
                  : "memory");
-#else
-    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
-                 "r"(v.z), "r"(v.w)
-                 : "memory");
-#endif
 }
 
 /* 4-byte asynchronous global->shared copy (LDGSTS): no register, no stall at issue. */
@@ -175,10 +112,19 @@ __device__ __forceinline__ void cp_async_wait_all()
 }
 
 /* emb_host.h:210  (float)s / pow(10,9): int->float RNE, divide in double, round to float.
- * 1e9 is exact in fp32 and double has >= 2*24+2 bits, so this equals one IEEE fp32 divide. */
+ * 1e9 is exact in fp32 and double has >= 2*24+2 bits, so this equals one IEEE fp32 divide x / 1e9f.
+ * That divide is computed here without the division routine: with r = RN(1/1e9), q0 = RN(x*r),
+ * e = x - q0*1e9 (exact in one FMA), q = RN(q0 + e*r) is the correctly rounded quotient (Markstein's
+ * correction step).  Checked exhaustively on the CPU against `/` for every one of the 2^32 int32 inputs
+ * (tests/check_dequant.c, run by tests/test_dequant_exhaustive.py): 0 mismatches.  4 instructions instead of ~12
+ * and no slow-path branch. */
 __device__ __forceinline__ float dequant(uint32_t s)
 {
-    return __fdiv_rn(__int2float_rn((int)s), 1.0e9f);
+    const float x = __int2float_rn((int)s);
+    const float r = 1.0f / 1.0e9f;  // folded at compile time, round to nearest: 0x3089705f
+    const float q0 = __fmul_rn(x, r);
+    const float e = __fmaf_rn(-q0, 1.0e9f, x);
+    return __fmaf_rn(e, r, q0);
 }
 
 /* dlrm_dpu_pytorch.py:318 + :329: float32 product, rint (half-to-even), int64, low 32 bits. */
@@ -635,259 +581,346 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
     }
 }
 
-/* cp.async groups: commit what has been issued, wait until at most N groups are still pending. */
-__device__ __forceinline__ void cp_async_commit()
-{
-    asm volatile("cp.async.commit_group;" ::: "memory");
-}
-template <int N>
-__device__ __forceinline__ void cp_async_wait_group()
-{
-    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
-/*
- * Pipelined load-balanced sum-pool kernel (variant 5) for int32 fixed-point tables, rows up to 128 bytes.
+/* ---- stretch kernel -----------------------------------------------------------------------------
  *
- * bag_sum_balanced_kernel with one warp per CTA spends about half of a CTA's life in front of its first
- * row load: descriptor -> bag bounds -> indices are three dependent memory round trips, and only then do
- * rows fly.  Here a CTA (still one warp, still 64 registers, K rows in flight per lane) owns NCH
- * consecutive sub-chunks of BAGS bags.  The bounds of ALL its bags are loaded in one round trip, and the
- * index window of sub-chunk j+1 is copied into the other half of a two-buffer shared-memory ring with
- * cp.async (no registers, no stall at issue) while the rows of sub-chunk j are gathered.  The chain is
- * paid once per CTA instead of once per BAGS bags; accumulators and the store epilogue stay per
- * sub-chunk, so shared memory per CTA is about what the balanced kernel uses (L1 capacity is what keeps
- * row loads in flight).
+ * bag_sum_stretch_kernel: load-balanced sum pooling with NO atomics and a branch-free inner loop.
  *
- * Same arithmetic as the balanced kernel: pieces of K lookups dealt round-robin to the sub-warps, int32
- * wrap-around adds flushed into a shared accumulator at bag boundaries (emb_dpu_lookup.c:114; associative
- * and commutative, so bit-exact in any order), dequantise + STG.128 epilogue (emb_host.h:207-212).  A
- * CTA whose bounds are not monotone pools bag by bag like emb_dpu_lookup.c:106-116.
+ * The round-1 balanced kernel above spent ~400 warp instructions per 64 lookups (ncu: 57 % of the issue slots,
+ * 19 % of them branch bookkeeping of the divergent flush, one binary search per piece, 4 ATOMS per flush;
+ * profiles/r1_bag_sum_balanced_hotspots.md).  This kernel does the same arithmetic (emb_dpu_lookup.c:106-116,
+ * emb_host.h:207-212) in ~100:
+ *
+ *  - One warp per CTA, BAGS consecutive bags of one table; the bag bounds live in REGISTERS (lane i holds
+ *    bound i), so everything that is derived from them -- monotonicity, the window, which bag a position
+ *    belongs to -- is a shuffle or a ballot, never a dependent shared-memory search.
+ *  - The bags only delimit a window [wlo, whi) of the index stream.  A pass stages up to STAGE lookups of
+ *    the window as 8-byte entries {row id, start marker} in shared memory.  The row id of an index that must
+ *    contribute nothing (out of range, another shard's row, padding) is the table's all-zero extra row
+ *    (table_alloc), so the gather needs no predicate.  Every non-empty bag then writes "bag + 1" into the
+ *    marker of its FIRST lookup: one store per bag, no search per lookup.
+ *  - The pass is cut into SUB equal contiguous stretches, one per sub-warp (SUB = 32 / LANES sub-warps of
+ *    LANES lanes, a lane owns 16 bytes of every row).  A sub-warp walks its stretch K lookups at a time: K
+ *    entry loads (LDS.64), K independent row loads (LDG.128), then K accumulate steps.  An accumulate step
+ *    is straight-line predicated code: if the lookup carries a marker, the running sum is stored (STS.128)
+ *    to where it belongs, the destination moves to the new bag's accumulator and the sum restarts.  The
+ *    first such store of a stretch goes to the sub-warp's HEAD slot: the bag its stretch began in started in
+ *    an earlier stretch and belongs to that sub-warp.  Every other store targets a bag that started inside
+ *    this stretch, which no other sub-warp writes: plain stores, no atomics.
+ *  - After the pass each sub-warp adds its head to the accumulator of the bag it continues (one 16-byte
+ *    read-modify-write per sub-warp; serialised only when one bag spans several stretches).  A bag cut by
+ *    the end of a pass is simply the head of sub-warp 0 in the next pass.
+ *  - Epilogue as before: dequantise (post_process, emb_host.h:210) and STG.128 whole output rows.
+ *
+ * int32 wrap-around sums are exact in any order (bit-exact with the reference).  fp32 tables (IS_FLOAT) are
+ * summed in index order inside a stretch and the pieces of a bag are combined in index order too: the result
+ * is run-to-run deterministic and differs from the strictly sequential CPU sum (embedding_lookup_idx.cc:33-77)
+ * only by the reassociation at the <= SUB-1 cut points of a pass (north_star: <= 1e-5 relative).
+ * Bounds that are not monotone inside the CTA's chunk (overlapping bags, which lookup() permits) are pooled bag
+ * by bag, as emb_dpu_lookup.c:106-116 does.
  */
-template <int LANES, int K, int BAGS, int NCH, int MINB>
-__global__ void __launch_bounds__(32, MINB)
-bag_sum_pipe_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
+/* table + row * ROWB as ONE instruction (IMAD.WIDE.U32 with the 64-bit lane base as the addend) */
+template <int ROWB>
+__device__ __forceinline__ const uint4 *row_ptr(const char *lane_base, uint32_t row)
 {
-    constexpr int SUB = 32 / LANES;  // sub-warps per CTA
-    constexpr int D = LANES * 4;
-    constexpr int ALLB = BAGS * NCH;  // bags per CTA
-    constexpr int SI = BAGS * 16;     // index entries per ring buffer; longer windows take extra passes
-    static_assert(BAGS % SUB == 0, "BAGS must be a multiple of the sub-warp count");
-    __shared__ uint32_t s_off[ALLB + 1];
-    __shared__ uint32_t s_idx[2][SI];
-    __shared__ __align__(16) uint32_t s_acc[BAGS * D];
+    uint64_t a;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(a) : "r"(row), "n"(ROWB), "l"(lane_base));
+    return reinterpret_cast<const uint4 *>(a);
+}
+__device__ __forceinline__ uint2 lds_u64(uint32_t smem_addr)
+{
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(smem_addr));
+    return v;
+}
+__device__ __forceinline__ uint4 lds_u128(uint32_t smem_addr)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_addr));
+    return v;
+}
+__device__ __forceinline__ void sts_u128(uint32_t smem_addr, uint4 v)
+{
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(smem_addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 
-    const uint32_t tid = threadIdx.x;
+/* One accumulate step.  mark != 0: the lookup is the first of bag mark-1 -- store the running sum to dst,
+ * point dst at that bag's accumulator (acc_base + mark * ROWB; acc_base already holds "- ROWB + lane offset")
+ * and restart the sum.  Then add the row.  Predicated, no branch: the sub-warps of a warp meet markers at
+ * different lookups. */
+template <int ROWB, bool IS_FLOAT>
+__device__ __forceinline__ void stretch_step(uint4 &acc, uint32_t &dst, uint32_t mark, uint32_t acc_base, const uint4 &v)
+{
+    uint32_t keep;  // 0 when a new bag starts at this lookup, else 1
+    asm volatile("{\n\t"
+                 ".reg .pred p;\n\t"
+                 "setp.ne.u32 p, %6, 0;\n\t"
+                 "@p st.shared.v4.u32 [%4], {%0,%1,%2,%3};\n\t"
+                 "@p mad.lo.u32 %4, %6, %7, %8;\n\t"
+                 "selp.u32 %5, 0, 1, p;\n\t"
+                 "}"
+                 : "+r"(acc.x), "+r"(acc.y), "+r"(acc.z), "+r"(acc.w), "+r"(dst), "=r"(keep)
+                 : "r"(mark), "n"(ROWB), "r"(acc_base)
+                 : "memory");
+    if (IS_FLOAT) {
+        const float ax = keep ? __uint_as_float(acc.x) : 0.f, ay = keep ? __uint_as_float(acc.y) : 0.f;
+        const float az = keep ? __uint_as_float(acc.z) : 0.f, aw = keep ? __uint_as_float(acc.w) : 0.f;
+        acc.x = __float_as_uint(__fadd_rn(ax, __uint_as_float(v.x)));
+        acc.y = __float_as_uint(__fadd_rn(ay, __uint_as_float(v.y)));
+        acc.z = __float_as_uint(__fadd_rn(az, __uint_as_float(v.z)));
+        acc.w = __float_as_uint(__fadd_rn(aw, __uint_as_float(v.w)));
+    } else {  // int32 wrap-around adds (emb_dpu_lookup.c:114); "restart" folded into one multiply-add per column
+        acc.x = acc.x * keep + v.x;
+        acc.y = acc.y * keep + v.y;
+        acc.z = acc.z * keep + v.z;
+        acc.w = acc.w * keep + v.w;
+    }
+}
+
+template <bool IS_FLOAT>
+__device__ __forceinline__ uint4 add_rows(uint4 a, uint4 b)
+{
+    if (IS_FLOAT)
+        return make_uint4(__float_as_uint(__fadd_rn(__uint_as_float(a.x), __uint_as_float(b.x))),
+                          __float_as_uint(__fadd_rn(__uint_as_float(a.y), __uint_as_float(b.y))),
+                          __float_as_uint(__fadd_rn(__uint_as_float(a.z), __uint_as_float(b.z))),
+                          __float_as_uint(__fadd_rn(__uint_as_float(a.w), __uint_as_float(b.w))));
+    return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+}
+
+template <int LANES, int K, int BAGS, int STAGE, bool IS_FLOAT, int MINB>
+__global__ void __launch_bounds__(32, MINB)
+bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
+{
+    constexpr int SUB = 32 / LANES;  // sub-warps
+    constexpr int D = LANES * 4;
+    constexpr int ROWB = D * 4;      // bytes per row
+    constexpr int NB = (BAGS + 31) / 32;  // bound registers per lane
+    constexpr int NST = STAGE / 32;       // staging rounds per pass
+    static_assert(K == 4 || K == 8, "K is 4 or 8");
+    static_assert(STAGE % (SUB * K) == 0 && STAGE % 32 == 0, "a pass splits evenly");
+    static_assert(BAGS % SUB == 0 && (BAGS <= 32 || BAGS % 32 == 0), "BAGS");
+    // entry i of a pass lives in slot i + i/8: the pad slot after every 8 entries skews the stretches of the
+    // sub-warps (which start a multiple of 8 entries apart) onto different banks
+    __shared__ __align__(16) uint2 s_ent[STAGE + STAGE / 8];
+    __shared__ __align__(16) uint32_t s_acc[BAGS * D];
+    __shared__ __align__(16) uint32_t s_head[SUB * D];
+
+    const uint32_t lane = threadIdx.x;
+    const uint32_t sub = lane / LANES;
+    const uint32_t sl = lane % LANES;
     const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
     const BagDesc *__restrict__ d = descs + q;
 
     const uint32_t B = d->nr_batches;
     const uint32_t ilen = d->indices_len;
-    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, ALLB);
-    const uint32_t nb_all = min((uint32_t)ALLB, d->bag_end - b0);
+    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, BAGS);
+    const uint32_t nb = min((uint32_t)BAGS, d->bag_end - b0);
     const uint32_t *__restrict__ g_idx = d->indices;
     const uint32_t *__restrict__ g_off = d->offsets;
 
-    // bounds of all the CTA's bags, one round trip (emb_dpu_lookup.c:60-63,109-110: bag 0 starts at 0,
-    // bag i ends where bag i+1 starts, the last bag ends at indices_len); every lane also loads its
-    // right-hand neighbour's bound so that monotonicity is known without a second pass
-    bool nonmono = false;
-    {
-        constexpr int R = (ALLB + 1 + 31) / 32;
-        uint32_t raw0[R], raw1[R];
+    // Bag bounds in registers (emb_dpu_lookup.c:60-63,109-110: bag 0 starts at 0 whatever offsets[0] is, bag i
+    // ends where bag i+1 starts, the last bag ends at indices_len): offv[r] = bound of local bag r*32 + lane,
+    // whi = bound nb (the end of the CTA's window), loaded by every lane from one address.
+    uint32_t offv[NB];
 #pragma unroll
-        for (int r = 0; r < R; r++) {
-            const uint32_t i = tid + 32u * r, b = b0 + i;
-            raw0[r] = raw1[r] = 0;
-            if (i <= nb_all) {
-                if (b != 0 && b < B)
-                    raw0[r] = ldg_stream_u32(g_off + b);
-                if (i < nb_all && b + 1 < B)
-                    raw1[r] = ldg_stream_u32(g_off + b + 1);
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < R; r++) {
-            const uint32_t i = tid + 32u * r, b = b0 + i;
-            if (i <= nb_all) {
-                const uint32_t v = min((b == 0) ? 0u : (b >= B ? ilen : raw0[r]), ilen);
-                if (i < nb_all)
-                    nonmono |= v > min((b + 1 >= B) ? ilen : raw1[r], ilen);
-                s_off[i] = v;
-            }
-        }
+    for (int r = 0; r < NB; r++) {
+        const uint32_t i = r * 32 + lane, b = b0 + i;
+        uint32_t v = 0;
+        if (i < nb && b != 0)
+            v = ldg_stream_u32(g_off + b);
+        offv[r] = v;
     }
-    const bool ordered = __any_sync(0xffffffffu, nonmono);  // true = NOT monotone (name as in the balanced kernel)
-    __syncwarp();
+    uint32_t whi = ilen;
+    if (b0 + nb < B)
+        whi = ldg_stream_u32(g_off + b0 + nb);
+    // in the shadow of those loads
+    const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(s_acc);
+    for (uint32_t i = lane; i < BAGS * D / 4; i += 32)
+        sts_u128(acc_s + i * 16, make_uint4(0u, 0u, 0u, 0u));
+    whi = min(whi, ilen);
+    bool nonmono = false;
+#pragma unroll
+    for (int r = 0; r < NB; r++) {
+        const uint32_t i = r * 32 + lane;
+        offv[r] = (i < nb) ? min(offv[r], ilen) : 0xffffffffu;
+    }
+    // bound of the bag after local bag r*32 + lane (the window's end for the last one)
+    auto next_bound = [&](int r) {
+        uint32_t up = __shfl_down_sync(0xffffffffu, offv[r], 1);
+        if (r + 1 < NB) {
+            const uint32_t first_of_next = __shfl_sync(0xffffffffu, offv[r + 1 < NB ? r + 1 : r], 0);
+            if (lane == 31)
+                up = first_of_next;
+        }
+        return (r * 32 + lane + 1 >= nb) ? whi : up;
+    };
+#pragma unroll
+    for (int r = 0; r < NB; r++) {
+        const uint32_t up = next_bound(r);  // shuffles: every lane takes part
+        nonmono |= r * 32 + lane < nb && offv[r] > up;
+    }
+    nonmono = __any_sync(0xffffffffu, nonmono);
+    const uint32_t wlo = __shfl_sync(0xffffffffu, offv[0], 0);
 
     const uint32_t flags = d->flags;
     const uint32_t rows = d->rows;
     const uint32_t row_base = d->row_base;
-    const uint32_t sub = tid / LANES;
-    const uint32_t lane = tid % LANES;
-    const uint4 *__restrict__ table = reinterpret_cast<const uint4 *>(d->table) + lane;
-    const uint32_t bpr = d->bags_per_rank;
-    const uint32_t out_stride = d->out_stride;
-    const uint32_t nch = (nb_all + BAGS - 1) / BAGS;
+    const char *__restrict__ table = reinterpret_cast<const char *>(d->table) + sl * 16;
     bool bad = false;
 
-    // index window of sub-chunk j -> ring buffer j & 1 (first SI entries), asynchronously
-    auto issue = [&](uint32_t j) {
-        const uint32_t nbj = min((uint32_t)BAGS, nb_all - j * BAGS);
-        const uint32_t lo = s_off[j * BAGS], hi = s_off[j * BAGS + nbj];
-        const uint32_t n = min((uint32_t)SI, hi - lo);
-        uint32_t *dst = s_idx[j & 1];
-        for (uint32_t i = tid; i < n; i += 32)
-            cp_async_u32(dst + i, g_idx + lo + i);
-        cp_async_commit();
-    };
-    if (!ordered && nch)
-        issue(0);
-
-    // one stretch of n staged lookups (window positions base .. base+n) of sub-chunk bags off[0..nbj]
-    auto pool = [&](const uint32_t *__restrict__ idx, uint32_t n, uint32_t base, const uint32_t *off, uint32_t nbj) {
-        for (uint32_t c = sub * K; c < n; c += SUB * K) {
-            const uint32_t m = min((uint32_t)K, n - c);
-            uint32_t r[K];
+    if (!nonmono) {
+        const uint32_t ent_s = (uint32_t)__cvta_generic_to_shared(s_ent);
+        const uint32_t head_s = (uint32_t)__cvta_generic_to_shared(s_head) + sub * ROWB + sl * 16;
+        const uint32_t acc_base = acc_s + sl * 16 - ROWB;  // + mark * ROWB = this lane's 16 bytes of bag mark-1
+        for (uint32_t base = wlo; base < whi; base += STAGE) {
+            const uint32_t n = min((uint32_t)STAGE, whi - base);
+            const uint32_t per = K * ((n + SUB * K - 1) / (SUB * K));  // lookups per sub-warp, a multiple of K
+            // ---- stage: all index loads of the pass go out back to back
+            uint32_t raw[NST];
 #pragma unroll
-            for (int u = 0; u < K; u++) {
-                uint32_t id = 0xffffffffu;
-                if ((uint32_t)u < m) {
-                    id = idx[c + u] - row_base;  // unsigned: rows below the shard wrap high
-                    bad |= id >= rows;
-                }
-                r[u] = id;
+            for (int j = 0; j < NST; j++) {
+                const uint32_t i = j * 32 + lane;
+                raw[j] = 0;
+                if (i < n)
+                    raw[j] = ldg_stream_u32(g_idx + base + i);
             }
-            uint4 v[K];
+            // ---- while they fly: the bag each stretch begins in (= the bag its head belongs to): the last bag
+            // whose bound is <= the stretch's first position, counted with one ballot per bound register
+            uint32_t hb = 0;
 #pragma unroll
-            for (int u = 0; u < K; u++) {
-                v[u] = make_uint4(0u, 0u, 0u, 0u);
-                if (r[u] < rows)
-                    v[u] = ldg_row16(table + (size_t)r[u] * LANES);
-            }
-            // bag of the piece's first lookup: last i with off[i] <= p (skips empty bags)
-            const uint32_t p0 = base + c;
-            uint32_t lo = 0, hi = nbj;
-            while (hi - lo > 1) {
-                const uint32_t mid = (lo + hi) >> 1;
-                if (off[mid] <= p0)
-                    lo = mid;
-                else
-                    hi = mid;
-            }
-            uint32_t bag = lo, bag_end = off[lo + 1];
-            uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+            for (int s = 0; s < SUB; s++) {
+                const uint32_t pos = base + s * per;
+                uint32_t cnt = 0;
 #pragma unroll
-            for (int u = 0; u < K; u++) {
-                if ((uint32_t)u < m) {
-                    if (p0 + u >= bag_end) {  // crossed into a later bag: flush the partial sum
-                        uint32_t *a = s_acc + bag * D + lane * 4;
-                        atomicAdd(a + 0, acc.x);
-                        atomicAdd(a + 1, acc.y);
-                        atomicAdd(a + 2, acc.z);
-                        atomicAdd(a + 3, acc.w);
-                        acc = make_uint4(0u, 0u, 0u, 0u);
-                        do {
-                            bag++;
-                            bag_end = off[bag + 1];
-                        } while (p0 + u >= bag_end);
-                    }
-                    acc.x += v[u].x;
-                    acc.y += v[u].y;
-                    acc.z += v[u].z;
-                    acc.w += v[u].w;
-                }
+                for (int r = 0; r < NB; r++)
+                    cnt += __popc(__ballot_sync(0xffffffffu, offv[r] <= pos));  // bounds past nb are 0xffffffff
+                if ((uint32_t)s == sub)
+                    hb = cnt - 1;  // bound 0 = wlo <= base, so cnt >= 1
             }
-            uint32_t *a = s_acc + bag * D + lane * 4;
-            atomicAdd(a + 0, acc.x);
-            atomicAdd(a + 1, acc.y);
-            atomicAdd(a + 2, acc.z);
-            atomicAdd(a + 3, acc.w);
-        }
-    };
-
-    for (uint32_t j = 0; j < nch; j++) {
-        const uint32_t nbj = min((uint32_t)BAGS, nb_all - j * BAGS);
-        const uint32_t *off = s_off + j * BAGS;
-        for (uint32_t i = tid; i < BAGS * D / 4; i += 32)
-            reinterpret_cast<uint4 *>(s_acc)[i] = make_uint4(0u, 0u, 0u, 0u);
-        if (!ordered) {
-            const uint32_t wlo = off[0], whi = off[nbj];
-            if (j + 1 < nch) {  // next sub-chunk's indices fly while this one's rows are gathered
-                issue(j + 1);
-                cp_async_wait_group<1>();
-            } else {
-                cp_async_wait_group<0>();
+            const bool active = sub * per < n;  // idle sub-warps (all padding) have an all-zero head
+#pragma unroll
+            for (int j = 0; j < NST; j++) {
+                const uint32_t i = j * 32 + lane;
+                uint32_t r = raw[j] - row_base;  // unsigned: rows below the shard wrap high
+                const bool in_range = r < rows;
+                bad |= i < n && !in_range;
+                if (i >= n || !in_range)
+                    r = rows;  // the all-zero row behind the table
+                s_ent[i + (i >> 3)] = make_uint2(r, 0u);  // every slot of the pass buffer, padding included
             }
-            __syncwarp();  // every lane's copies (and the zeroed accumulator) are visible to the warp
-            uint32_t *buf = s_idx[j & 1];
-            pool(buf, min((uint32_t)SI, whi - wlo), wlo, off, nbj);
-            for (uint32_t base = wlo + SI; base < whi; base += SI) {  // windows longer than a ring buffer
-                const uint32_t n = min((uint32_t)SI, whi - base);
-                __syncwarp();
-                for (uint32_t i = tid; i < n; i += 32)
-                    buf[i] = ldg_stream_u32(g_idx + base + i);
-                __syncwarp();
-                pool(buf, n, base, off, nbj);
-            }
-        } else {
-            // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
             __syncwarp();
-            for (uint32_t bag = sub; bag < nbj; bag += SUB) {
-                const uint32_t start = off[bag], end = off[bag + 1];
+            // ---- start markers: one store per non-empty bag that begins inside this pass
+#pragma unroll
+            for (int r = 0; r < NB; r++) {
+                const uint32_t i = r * 32 + lane;
+                const uint32_t rel = offv[r] - base;
+                const uint32_t up = next_bound(r);
+                if (i < nb && offv[r] < up && rel < n)  // rel wraps high for bags that began before the pass
+                    s_ent[rel + (rel >> 3)].y = i + 1;
+            }
+            __syncwarp();
+            // ---- gather: every sub-warp walks its stretch, K rows in flight per lane
+            {
+                uint32_t dst = head_s;
                 uint4 acc = make_uint4(0u, 0u, 0u, 0u);
-                for (uint32_t p = start; p < end; p++) {
-                    const uint32_t id = __ldg(g_idx + p) - row_base;
-                    if (id < rows) {
-                        const uint4 v = ldg_row16(table + (size_t)id * LANES);
-                        acc.x += v.x;
-                        acc.y += v.y;
-                        acc.z += v.z;
-                        acc.w += v.w;
-                    } else {
-                        bad = true;
+                const uint32_t c0 = sub * per;  // a multiple of K
+                for (uint32_t c = 0; c < per; c += K) {
+                    const uint32_t e_addr = ent_s + ((c0 + c) + ((c0 + c) >> 3)) * 8;
+                    uint2 e[K];
+#pragma unroll
+                    for (int u = 0; u < K; u++)
+                        e[u] = lds_u64(e_addr + u * 8);
+                    uint4 v[K];
+#pragma unroll
+                    for (int u = 0; u < K; u++)
+                        v[u] = ldg_row16(row_ptr<ROWB>(table, e[u].x));
+#pragma unroll
+                    for (int u = 0; u < K; u++)
+                        stretch_step<ROWB, IS_FLOAT>(acc, dst, e[u].y, acc_base, v[u]);
+                }
+                sts_u128(dst, acc);  // the bag the stretch ends in (or the head, if no bag began in the stretch)
+            }
+            __syncwarp();
+            // ---- heads: the first piece of every stretch belongs to a bag that began earlier
+            {
+                const uint32_t hb_prev = __shfl_up_sync(0xffffffffu, hb, LANES);
+                const bool dup = __any_sync(0xffffffffu, active && sub > 0 && hb == hb_prev);
+                const uint32_t a_addr = acc_s + hb * ROWB + sl * 16;
+                if (!dup) {
+                    if (active)
+                        sts_u128(a_addr, add_rows<IS_FLOAT>(lds_u128(a_addr), lds_u128(head_s)));
+                } else {  // one bag spans several stretches: its pieces are added one after the other, in index order
+                    for (int s = 0; s < SUB; s++) {
+                        if (active && (uint32_t)s == sub)
+                            sts_u128(a_addr, add_rows<IS_FLOAT>(lds_u128(a_addr), lds_u128(head_s)));
+                        __syncwarp();
                     }
                 }
-                reinterpret_cast<uint4 *>(s_acc)[bag * LANES + lane] = acc;
+            }
+            __syncwarp();
+        }
+    } else {
+        // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
+        uint32_t *s_off = reinterpret_cast<uint32_t *>(s_ent);  // BAGS + 1 <= 2 * (STAGE + STAGE / 8) words
+#pragma unroll
+        for (int r = 0; r < NB; r++) {
+            const uint32_t i = r * 32 + lane;
+            const uint32_t up = next_bound(r);
+            if (i < nb) {
+                s_off[2 * i] = offv[r];
+                s_off[2 * i + 1] = up;
             }
         }
         __syncwarp();
-
-        // post_process (emb_host.h:207-212) for the sub-chunk's bags
-#pragma unroll
-        for (int it = 0; it < BAGS / SUB; it++) {
-            const uint32_t bag = it * SUB + sub;
-            if (bag >= nbj)
-                break;
-            uint4 o = reinterpret_cast<const uint4 *>(s_acc)[bag * LANES + lane];
-            if (!(flags & kDescRaw))
-                o = make_uint4(__float_as_uint(dequant(o.x)), __float_as_uint(dequant(o.y)),
-                               __float_as_uint(dequant(o.z)), __float_as_uint(dequant(o.w)));
-            const uint32_t b = b0 + j * BAGS + bag;
-            uint32_t *obase;
-            uint32_t row;
-            if (bpr) {
-                const uint32_t rk = b / bpr;
-                obase = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
-                row = b - rk * bpr;
-            } else {
-                obase = reinterpret_cast<uint32_t *>(d->out);
-                row = b;
+        for (uint32_t bag = sub; bag < nb; bag += SUB) {
+            const uint32_t start = s_off[2 * bag], end = s_off[2 * bag + 1];
+            uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+            for (uint32_t p = start; p < end; p++) {
+                const uint32_t id = __ldg(g_idx + p) - row_base;
+                if (id < rows)
+                    acc = add_rows<IS_FLOAT>(acc, ldg_row16(reinterpret_cast<const uint4 *>(table + (size_t)id * ROWB)));
+                else
+                    bad = true;
             }
-            uint32_t *dst = obase + (size_t)row * out_stride + lane * 4;
-            if (flags & kDescVecStore) {
-                stg_stream16(dst, o);
-            } else {
-                dst[0] = o.x;
-                dst[1] = o.y;
-                dst[2] = o.z;
-                dst[3] = o.w;
-            }
+            sts_u128(acc_s + bag * ROWB + sl * 16, acc);
         }
-        __syncwarp();  // accumulator and ring buffer j & 1 are free again
+        __syncwarp();
     }
     if (bad && !(flags & kDescSharded))
         atomicOr(err_flag, 1u);
+
+    const uint32_t bpr = d->bags_per_rank;
+    const uint32_t out_stride = d->out_stride;
+#pragma unroll 2
+    for (int it = 0; it < BAGS / SUB; it++) {
+        const uint32_t bag = it * SUB + sub;
+        if (bag >= nb)
+            break;
+        uint4 o = lds_u128(acc_s + bag * ROWB + sl * 16);
+        if (!IS_FLOAT && !(flags & kDescRaw))  // post_process, emb_host.h:210
+            o = make_uint4(__float_as_uint(dequant(o.x)), __float_as_uint(dequant(o.y)),
+                           __float_as_uint(dequant(o.z)), __float_as_uint(dequant(o.w)));
+        const uint32_t b = b0 + bag;
+        uint32_t *obase;
+        uint32_t row;
+        if (bpr) {
+            uint32_t rk = b / bpr;
+            obase = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
+            row = b - rk * bpr;
+        } else {
+            obase = reinterpret_cast<uint32_t *>(d->out);
+            row = b;
+        }
+        uint32_t *dstp = obase + (size_t)row * out_stride + sl * 4;
+        if (flags & kDescVecStore) {
+            stg_stream16(dstp, o);
+        } else {
+            dstp[0] = o.x;
+            dstp[1] = o.y;
+            dstp[2] = o.z;
+            dstp[3] = o.w;
+        }
+    }
 }
 
 /*

@@ -330,7 +330,8 @@ def test_large_call_pipelines_groups_with_mapped_results(emblib):
         assert np.array_equal(bits(got[t]), bits(want[t])), t
 
 
-TUNINGS = [(1, 4, 0), (1, 8, 0), (2, 4, 1), (2, 8, 1), (2, 4, 2), (2, 8, 4), (3, 4, 0), (3, 8, 0), (4, 0, 0)]
+TUNINGS = [(1, 4, 0), (1, 8, 0), (2, 4, 1), (2, 8, 1), (2, 4, 2), (2, 8, 4), (3, 4, 0), (3, 8, 0), (4, 0, 0),
+           (6, 8, 1), (6, 8, 2), (6, 4, 4), (6, 8, 8), (6, 4, 1)]
 
 
 @pytest.mark.parametrize("tuning", TUNINGS, ids=[f"v{v}k{k}m{m}" for v, k, m in TUNINGS])
@@ -355,7 +356,7 @@ def test_kernel_variants_agree(emblib, tuning, D):
         emblib.load().emb_set_tuning(0, 0, 0)
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6])
 def test_overlapping_and_backward_bags(emblib, variant):
     """lookup() accepts any offsets: bag i covers [offsets[i], offsets[i+1]) on its own
     (emb_dpu_lookup.c:109-116), so bags may overlap or be empty because they run backwards."""
@@ -452,12 +453,16 @@ def test_float_tables_match_reference_apply_emb(emblib):
         emblib.configure(n, int(D))
         for k in range(n):
             emblib.populate_table_f32(k, z[f"w{D}_{k}"], EMB_TABLE_FLOAT)
-        got = emblib.lookup_ex([z[f"idx{D}_{k}"] for k in range(n)], [z[f"off{D}_{k}"] for k in range(n)])
-        for k in range(n):
-            # north_star: <= 1e-5 relative (fp32 reassociation) vs the reference's CPU lookup
-            np.testing.assert_allclose(got[k], z[f"out{D}_{k}"], rtol=1e-5, atol=1e-7)
-            want = eo.bag_sum_f32(z[f"w{D}_{k}"], z[f"idx{D}_{k}"], z[f"off{D}_{k}"])
-            assert np.array_equal(bits(got[k]), bits(want))  # same order of adds -> same bits
+        for variant in (0, 1):  # the default (stretch kernel: reassociated at its cut points) and the index-ordered kernel
+            assert emblib.load().emb_set_tuning(variant, 0, 0) == 0
+            got = emblib.lookup_ex([z[f"idx{D}_{k}"] for k in range(n)], [z[f"off{D}_{k}"] for k in range(n)])
+            for k in range(n):
+                # north_star: <= 1e-5 relative (fp32 reassociation) vs the reference's CPU lookup
+                np.testing.assert_allclose(got[k], z[f"out{D}_{k}"], rtol=1e-5, atol=1e-7)
+                if variant == 1:
+                    want = eo.bag_sum_f32(z[f"w{D}_{k}"], z[f"idx{D}_{k}"], z[f"off{D}_{k}"])
+                    assert np.array_equal(bits(got[k]), bits(want))  # same order of adds -> same bits
+        emblib.load().emb_set_tuning(0, 0, 0)
 
 
 @pytest.mark.parametrize("D", [16, 32, 64, 128])

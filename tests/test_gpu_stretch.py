@@ -1,0 +1,205 @@
+"""Parity of the stretch kernel (variant 6, bag_sum_stretch_kernel) with the oracle through the C ABI: the cases
+its structure makes interesting -- bags cut by a stretch boundary (heads), one bag spanning several stretches
+(the serialised head merge), windows longer than a pass (a bag cut by the end of a pass becomes the head of the
+next one), empty bags at every position, out-of-range indices and row shards (both gather the all-zero row
+behind the table), fp32 tables (deterministic, <= 1e-5 relative of the sequential CPU sum,
+embedding_lookup_idx.cc:33-77).  int32 results are compared bit for bit (emb_dpu_lookup.c:106-116,
+emb_host.h:207-212)."""
+import numpy as np
+import pytest
+
+import emb_oracle as eo
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture()
+def emblib():
+    from pim_embedding_lookup_b200 import emblib as m
+    m.load()
+    m.shutdown()
+    yield m
+    m.load().emb_set_tuning(0, 0, 0)
+    m.shutdown()
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def u32(a):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.uint32).view(np.int32)).cuda()
+
+
+def table(rng, R, D):
+    return rng.integers(-2**31, 2**31, size=(R, D), dtype=np.int64).astype(np.int32)
+
+
+def offsets_of(lens):
+    return np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.uint32)
+
+
+@pytest.mark.parametrize("D", [4, 8, 16, 32, 64, 128])
+@pytest.mark.parametrize("K,mult", [(8, 1), (8, 2), (4, 4), (8, 8)])
+def test_bag_length_patterns(emblib, D, K, mult):
+    """Bag lengths chosen against the kernel's units: exactly one step, one stretch, one pass, one more than
+    each, runs of empty bags before / between / after, a single giant bag, giant bags back to back."""
+    rng = np.random.default_rng(1000 + D + K + mult)
+    R = 3000
+    emblib.configure(1, D)
+    assert emblib.load().emb_set_tuning(6, K, mult) == 0
+    q = table(rng, R, D)
+    emblib.populate_table_i32(0, q)
+    patterns = [
+        [8] * 64, [7, 9] * 40, [0, 0, 0, 5, 0, 0, 64, 0, 1, 0, 0], [256], [257], [255, 1, 0, 256, 0, 0, 3],
+        [1] * 300, [0] * 100, [0] * 37 + [1] + [0] * 50, [1000, 0, 1000, 1, 2000], [31, 33, 32, 0, 64, 63, 65] * 9,
+        list(rng.integers(0, 40, size=500)), list(rng.integers(0, 3, size=1000)), [2049], [0, 4096, 0],
+    ]
+    for lens in patterns:
+        lens = np.asarray(lens, dtype=np.int64)
+        off = offsets_of(lens)
+        idx = rng.integers(0, R, size=int(lens.sum())).astype(np.uint32)
+        got = emblib.lookup_ex([idx], [off])[0]
+        want = eo.lookup_rows([q], [idx], [off])[0]
+        assert np.array_equal(bits(got), bits(want)), (D, K, mult, lens[:12])
+    assert emblib.load().emb_check_indices() == 0
+
+
+def test_default_kernel_for_fixed_point_tables_is_checked_too(emblib):
+    """Whatever pick_variant chooses by default (no tuning set) on C2's shape in miniature."""
+    rng = np.random.default_rng(77)
+    T, D, R, B = 5, 16, 20000, 4099
+    emblib.configure(T, D)
+    tabs, idxs, offs = [], [], []
+    for t in range(T):
+        q = table(rng, R, D)
+        emblib.populate_table_i32(t, q)
+        lens = rng.integers(1, 21, size=B)
+        tabs.append(q), offs.append(offsets_of(lens)), idxs.append(rng.integers(0, R, size=int(lens.sum())).astype(np.uint32))
+    got = emblib.lookup_ex(idxs, offs)
+    want = eo.lookup_rows(tabs, idxs, offs)
+    for t in range(T):
+        assert np.array_equal(bits(got[t]), bits(want[t])), t
+
+
+@pytest.mark.parametrize("D", [16, 64, 128])
+def test_out_of_range_and_row_shards_use_the_zero_row(emblib, D):
+    """An out-of-range index contributes nothing and raises the error flag; a row shard ignores foreign rows
+    silently; the raw partial sums of the shards add up to the unsharded sums."""
+    from pim_embedding_lookup_b200.dputypes import EMB_Q_RAW_SUMS
+    rng = np.random.default_rng(5 + D)
+    R, B = 1000, 600
+    emblib.configure(3, D)
+    lib = emblib.load()
+    assert lib.emb_set_tuning(6, 0, 0) == 0
+    q = table(rng, R, D)
+    emblib.populate_table_i32(0, q)
+    emblib.populate_table_i32(1, q[:400])
+    emblib.populate_table_i32(2, q[400:])
+    emblib.check(lib.emb_table_set_row_base(1, 0))
+    emblib.check(lib.emb_table_set_row_base(2, 400))
+    lens = rng.integers(0, 30, size=B)
+    off = offsets_of(lens)
+    idx = rng.integers(0, R, size=int(lens.sum())).astype(np.uint32)
+    di, do = u32(idx), u32(off)
+    whole = torch.empty((B, D), dtype=torch.int32, device="cuda")
+    a = torch.empty((B, D), dtype=torch.int32, device="cuda")
+    b = torch.empty((B, D), dtype=torch.int32, device="cuda")
+    plan = emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=whole, flags=EMB_Q_RAW_SUMS),
+                        dict(table_id=1, indices=di, offsets=do, out=a, flags=EMB_Q_RAW_SUMS),
+                        dict(table_id=2, indices=di, offsets=do, out=b, flags=EMB_Q_RAW_SUMS)])
+    plan.launch(torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    assert lib.emb_check_indices() == 0
+    _, sums = eo.lookup_rows([q], [idx], [off], want_sums=True)
+    assert torch.equal(a + b, whole)
+    assert np.array_equal(whole.cpu().numpy(), sums[0])
+    plan.close()
+    # bad indices on a whole table: flagged, contribute nothing
+    bad = idx.copy()
+    bad[::7] = R + 5
+    good = np.ones(len(idx), dtype=bool)
+    good[::7] = False
+    got = emblib.lookup_ex([bad, idx[:0], idx[:0]], [off, off[:0], off[:0]])[0]
+    assert lib.emb_check_indices() == 1
+    # the same bags with the bad lookups removed
+    csum = np.concatenate([[0], np.cumsum(good)])
+    ends = np.concatenate([off[1:], [len(idx)]]).astype(np.int64)
+    keep_lens = csum[ends] - csum[off.astype(np.int64)]
+    want = eo.lookup_rows([q], [idx[good]], [offsets_of(keep_lens)])[0]
+    assert np.array_equal(bits(got), bits(want))
+
+
+@pytest.mark.parametrize("D", [16, 64, 128])
+def test_float_tables_are_deterministic_and_within_tolerance(emblib, D):
+    """fp32 tables on the stretch kernel: <= 1e-5 relative of the sequential sum (north_star), the same bits on
+    every run, and bit-equal to the sequential sum wherever a bag lies inside one stretch (short bags)."""
+    from pim_embedding_lookup_b200.dputypes import EMB_TABLE_FLOAT
+    rng = np.random.default_rng(31 + D)
+    R, B = 5000, 3000
+    emblib.configure(1, D)
+    lib = emblib.load()
+    w = rng.uniform(-R ** -0.5, R ** -0.5, size=(R, D)).astype(np.float32)
+    emblib.populate_table_f32(0, w, EMB_TABLE_FLOAT)
+    lens = rng.integers(0, 41, size=B)
+    off = offsets_of(lens)
+    idx = rng.integers(0, R, size=int(lens.sum())).astype(np.uint32)
+    want = eo.bag_sum_f32(w, idx, off)
+    assert lib.emb_set_tuning(6, 0, 0) == 0
+    runs = [emblib.lookup_ex([idx], [off])[0].copy() for _ in range(3)]
+    assert np.array_equal(bits(runs[0]), bits(runs[1])) and np.array_equal(bits(runs[0]), bits(runs[2]))
+    scale = np.abs(w).max() * np.maximum(lens, 1)[:, None]
+    assert (np.abs(runs[0] - want) <= 1e-5 * scale).all()
+    np.testing.assert_allclose(runs[0], want, rtol=1e-5, atol=1e-5 * float(np.abs(w).max()))
+    # the index-ordered kernel (variant 1) stays available and is bit-equal to the sequential sum
+    assert lib.emb_set_tuning(1, 0, 0) == 0
+    got1 = emblib.lookup_ex([idx], [off])[0]
+    assert np.array_equal(bits(got1), bits(want))
+    # default for float tables = the stretch kernel: same bits as forcing it
+    assert lib.emb_set_tuning(0, 0, 0) == 0
+    got0 = emblib.lookup_ex([idx], [off])[0]
+    assert np.array_equal(bits(got0), bits(runs[0]))
+
+
+def test_repopulating_a_former_row_shard_slot_forgets_the_shard(emblib):
+    """a slot that held a row shard keeps no stale row_base / sharded flag."""
+    rng = np.random.default_rng(3)
+    D, R = 16, 500
+    emblib.configure(1, D)
+    lib = emblib.load()
+    q = table(rng, R, D)
+    emblib.populate_table_i32(0, q[100:300])
+    emblib.check(lib.emb_table_set_row_base(0, 100))
+    emblib.populate_table_i32(0, q)  # a whole table now (different row count)
+    lens = rng.integers(0, 12, size=200)
+    off = offsets_of(lens)
+    idx = rng.integers(0, R, size=int(lens.sum())).astype(np.uint32)
+    got = emblib.lookup_ex([idx], [off])[0]
+    assert np.array_equal(bits(got), bits(eo.lookup_rows([q], [idx], [off])[0]))
+    # same row count as the shard had: the slab is reused, the shard state must still be gone
+    emblib.populate_table_i32(0, q[:200])
+    emblib.check(lib.emb_table_set_row_base(0, 50))
+    emblib.populate_table_i32(0, q[:200])
+    idx2 = rng.integers(0, 200, size=int(lens.sum())).astype(np.uint32)
+    got = emblib.lookup_ex([idx2], [off])[0]
+    assert lib.emb_check_indices() == 0
+    assert np.array_equal(bits(got), bits(eo.lookup_rows([q[:200]], [idx2], [off])[0]))
+
+
+def test_stale_plans_refuse_to_launch(emblib):
+    """a plan made before its table was freed / re-allocated returns EMB_ESTATE."""
+    rng = np.random.default_rng(4)
+    D = 16
+    emblib.configure(1, D)
+    lib = emblib.load()
+    emblib.populate_table_i32(0, table(rng, 100, D))
+    idx, off = u32(np.arange(10)), u32(np.array([0, 5]))
+    out = torch.empty((2, D), dtype=torch.float32, device="cuda")
+    plan = emblib.Plan([dict(table_id=0, indices=idx, offsets=off, out=out)])
+    plan.launch(torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    emblib.populate_table_i32(0, table(rng, 200, D))  # different row count: new slab
+    with pytest.raises(emblib.EmbError):
+        plan.launch(torch.cuda.current_stream())
+    plan.close()
