@@ -450,14 +450,19 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         v.bags = emb::kThreads;  // 32 bags per warp
     }
     if (v.kind == 6) {
-        // one warp per CTA; defaults from the round-2 sweeps (profiles/r2_sweeps.md)
+        // One warp per CTA.  Defaults from the round-2 sweeps on the B200 (tools/r2_quick_ab.sh, profiles/r2_sweeps.md;
+        // K = rows in flight per lane, mult = bags per CTA / sub-warps):
+        //   64-byte rows (C2):   K8 m2 0.2257 ms | K4 m2 0.2360 | K8 m4 0.2545 (two passes) | K8 m1 0.2503
+        //   ... one index per bag (C3): K4 m4 0.0353 | K8 m4 0.0373 | K8 m8 0.0414
+        //   256-byte rows (C4):  K8 m4 0.5761 | K8 m2 0.5924 | K4 m4 0.6148 | K8 m8 0.6206
+        //   512-byte rows (C5):  K8 m1 0.4222 | K8 m2 0.4469 | K8 m4 0.4828
         const bool short_bags = avg_pool > 0.0 && avg_pool <= 4.0;
         v.threads = 32;
         v.unroll = g.unroll ? g.unroll : (short_bags && lanes <= 8 ? 4 : 8);
-        v.mult = bags_mult ? bags_mult : (lanes >= 16 ? 4 : short_bags ? 4 : 2);
+        v.mult = bags_mult ? bags_mult : (lanes >= 32 ? 1 : lanes >= 16 ? 4 : short_bags ? 4 : 2);
         static const int big_stage = (int)env_u32("EMB_STRETCH_STAGE", 0);  // measurement knob: 1 = the larger pass
         v.stage = big_stage;
-        v.bags = 32 / lanes * v.mult;
+        v.bags = std::min<uint32_t>(32 / lanes * v.mult, 64);  // one marker byte per lookup names the bag
     }
     if (v.kind == 4) {
         v.mult = 1;
@@ -553,7 +558,7 @@ template <int LANES, int K, int MULT, bool IS_FLOAT>
 void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     constexpr int SUB = 32 / LANES;
-    constexpr int BAGS = SUB * MULT;
+    constexpr int BAGS = SUB * MULT < 64 ? SUB * MULT : 64;  // stretch_bags() below
     constexpr int UNIT = SUB * K;  // a pass is a whole number of K-lookup steps of every sub-warp
     constexpr int SMALL = (LANES <= 4 ? 256 : 128) < UNIT ? UNIT : (LANES <= 4 ? 256 : 128);
     constexpr int LARGE = 2 * SMALL;

@@ -594,13 +594,14 @@ bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint
  *    bound i), so everything that is derived from them -- monotonicity, the window, which bag a position
  *    belongs to -- is a shuffle or a ballot, never a dependent shared-memory search.
  *  - The bags only delimit a window [wlo, whi) of the index stream.  A pass stages up to STAGE lookups of
- *    the window as 8-byte entries {row id, start marker} in shared memory.  The row id of an index that must
+ *    the window in shared memory: a 4-byte row id and a 1-byte start marker per lookup.  The row id of an index that must
  *    contribute nothing (out of range, another shard's row, padding) is the table's all-zero extra row
  *    (table_alloc), so the gather needs no predicate.  Every non-empty bag then writes "bag + 1" into the
  *    marker of its FIRST lookup: one store per bag, no search per lookup.
  *  - The pass is cut into SUB equal contiguous stretches, one per sub-warp (SUB = 32 / LANES sub-warps of
- *    LANES lanes, a lane owns 16 bytes of every row).  A sub-warp walks its stretch K lookups at a time: K
- *    entry loads (LDS.64), K independent row loads (LDG.128), then K accumulate steps.  An accumulate step
+ *    LANES lanes, a lane owns 16 bytes of every row).  A sub-warp walks its stretch K lookups at a time: the
+ *    K row ids and K markers (three shared-memory loads), K independent row loads (LDG.128), then K accumulate
+ *    steps.  An accumulate step
  *    is straight-line predicated code: if the lookup carries a marker, the running sum is stored (STS.128)
  *    to where it belongs, the destination moves to the new bag's accumulator and the sum restarts.  The
  *    first such store of a stretch goes to the sub-warp's HEAD slot: the bag its stretch began in started in
@@ -630,6 +631,12 @@ __device__ __forceinline__ uint2 lds_u64(uint32_t smem_addr)
 {
     uint2 v;
     asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(smem_addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t smem_addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_addr));
     return v;
 }
 __device__ __forceinline__ uint4 lds_u128(uint32_t smem_addr)
@@ -699,9 +706,10 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
     static_assert(K == 4 || K == 8, "K is 4 or 8");
     static_assert(STAGE % (SUB * K) == 0 && STAGE % 32 == 0, "a pass splits evenly");
     static_assert(BAGS % SUB == 0 && (BAGS <= 32 || BAGS % 32 == 0), "BAGS");
-    // entry i of a pass lives in slot i + i/8: the pad slot after every 8 entries skews the stretches of the
-    // sub-warps (which start a multiple of 8 entries apart) onto different banks
-    __shared__ __align__(16) uint2 s_ent[STAGE + STAGE / 8];
+    // a pass: row ids (4 bytes per lookup) and start markers (1 byte per lookup: bag + 1, or 0)
+    static_assert(BAGS <= 254, "a start marker is one byte");
+    __shared__ __align__(16) uint32_t s_idx[STAGE];
+    __shared__ __align__(16) uint8_t s_mark[STAGE];
     __shared__ __align__(16) uint32_t s_acc[BAGS * D];
     __shared__ __align__(16) uint32_t s_head[SUB * D];
 
@@ -769,7 +777,8 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
     bool bad = false;
 
     if (!nonmono) {
-        const uint32_t ent_s = (uint32_t)__cvta_generic_to_shared(s_ent);
+        const uint32_t idx_s = (uint32_t)__cvta_generic_to_shared(s_idx);
+        const uint32_t mark_s = (uint32_t)__cvta_generic_to_shared(s_mark);
         const uint32_t head_s = (uint32_t)__cvta_generic_to_shared(s_head) + sub * ROWB + sl * 16;
         const uint32_t acc_base = acc_s + sl * 16 - ROWB;  // + mark * ROWB = this lane's 16 bytes of bag mark-1
         for (uint32_t base = wlo; base < whi; base += STAGE) {
@@ -784,6 +793,8 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                 if (i < n)
                     raw[j] = ldg_stream_u32(g_idx + base + i);
             }
+            if (lane < STAGE / 16)
+                sts_u128(mark_s + lane * 16, make_uint4(0u, 0u, 0u, 0u));
             // ---- while they fly: the bag each stretch begins in (= the bag its head belongs to): the last bag
             // whose bound is <= the stretch's first position, counted with one ballot per bound register
             uint32_t hb = 0;
@@ -806,17 +817,17 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                 bad |= i < n && !in_range;
                 if (i >= n || !in_range)
                     r = rows;  // the all-zero row behind the table
-                s_ent[i + (i >> 3)] = make_uint2(r, 0u);  // every slot of the pass buffer, padding included
+                s_idx[i] = r;  // every slot of the pass buffer, padding included
             }
             __syncwarp();
-            // ---- start markers: one store per non-empty bag that begins inside this pass
+            // ---- start markers: one byte store per non-empty bag that begins inside this pass
 #pragma unroll
             for (int r = 0; r < NB; r++) {
                 const uint32_t i = r * 32 + lane;
                 const uint32_t rel = offv[r] - base;
                 const uint32_t up = next_bound(r);
                 if (i < nb && offv[r] < up && rel < n)  // rel wraps high for bags that began before the pass
-                    s_ent[rel + (rel >> 3)].y = i + 1;
+                    s_mark[rel] = (uint8_t)(i + 1);
             }
             __syncwarp();
             // ---- gather: every sub-warp walks its stretch, K rows in flight per lane
@@ -824,20 +835,44 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                 uint32_t dst = head_s;
                 uint4 acc = make_uint4(0u, 0u, 0u, 0u);
                 const uint32_t c0 = sub * per;  // a multiple of K
-                for (uint32_t c = 0; c < per; c += K) {
-                    const uint32_t e_addr = ent_s + ((c0 + c) + ((c0 + c) >> 3)) * 8;
-                    uint2 e[K];
+                // The loop is rotated: the row ids, markers and K row loads of a step are issued at the BOTTOM of
+                // the iteration that consumes the previous step, so the loop's back edge sits between a step's
+                // loads and its accumulate steps.  Written as one straight block, ptxas sinks every row load to
+                // just above the multiply-add that consumes it (one row in flight instead of K; measured 0.374
+                // against 0.238 ms on C2).
+                uint32_t mk[K / 4];  // K start markers, one byte each
+                uint4 v[K];
+                auto load_step = [&](uint32_t c) {
+                    uint32_t id[K];
+#pragma unroll
+                    for (int u4 = 0; u4 < K / 4; u4++) {
+                        const uint4 t = lds_u128(idx_s + (c0 + c + 4 * u4) * 4);
+                        id[4 * u4 + 0] = t.x;
+                        id[4 * u4 + 1] = t.y;
+                        id[4 * u4 + 2] = t.z;
+                        id[4 * u4 + 3] = t.w;
+                    }
+                    if (K == 8) {
+                        const uint2 m = lds_u64(mark_s + c0 + c);
+                        mk[0] = m.x;
+                        mk[K / 4 - 1] = m.y;
+                    } else {
+                        mk[0] = lds_u32(mark_s + c0 + c);
+                    }
 #pragma unroll
                     for (int u = 0; u < K; u++)
-                        e[u] = lds_u64(e_addr + u * 8);
-                    uint4 v[K];
+                        v[u] = ldg_row16(row_ptr<ROWB>(table, id[u]));
+                };
+                load_step(0);
+                for (uint32_t c = K; c < per; c += K) {
 #pragma unroll
                     for (int u = 0; u < K; u++)
-                        v[u] = ldg_row16(row_ptr<ROWB>(table, e[u].x));
-#pragma unroll
-                    for (int u = 0; u < K; u++)
-                        stretch_step<ROWB, IS_FLOAT>(acc, dst, e[u].y, acc_base, v[u]);
+                        stretch_step<ROWB, IS_FLOAT>(acc, dst, (mk[u / 4] >> (8 * (u % 4))) & 0xffu, acc_base, v[u]);
+                    load_step(c);
                 }
+#pragma unroll
+                for (int u = 0; u < K; u++)
+                    stretch_step<ROWB, IS_FLOAT>(acc, dst, (mk[u / 4] >> (8 * (u % 4))) & 0xffu, acc_base, v[u]);
                 sts_u128(dst, acc);  // the bag the stretch ends in (or the head, if no bag began in the stretch)
             }
             __syncwarp();
@@ -861,7 +896,8 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
         }
     } else {
         // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
-        uint32_t *s_off = reinterpret_cast<uint32_t *>(s_ent);  // BAGS + 1 <= 2 * (STAGE + STAGE / 8) words
+        static_assert(2 * BAGS <= STAGE, "the fallback keeps 2 bounds per bag in the pass buffer");
+        uint32_t *s_off = s_idx;
 #pragma unroll
         for (int r = 0; r < NB; r++) {
             const uint32_t i = r * 32 + lane;
