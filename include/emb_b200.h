@@ -326,14 +326,12 @@ int emb_last_timings(emb_timings *out);
 uint64_t emb_launch_count(void);
 /* Tuning knob, mostly for measurement: rows in flight per sub-warp (4 or 8); 0 = default. */
 int emb_set_unroll(int unroll);
-/* All tuning knobs at once (0 = default): variant 1 = one bag per sub-warp (index-ordered
- * adds; always used when a float table is in the launch), 2 = load-balanced pieces of the
- * index stream with shared-memory int32 accumulators, 3 = the same per warp (rows up to 128
- * bytes), 4 = TMA gather4, 5 = variant 2 with one warp per CTA walking several sub-chunks of
- * bags, the next sub-chunk's indices copied asynchronously while the current one's rows are
- * gathered (rows up to 128 bytes); unroll as above; bags_mult = bags per CTA in units of
- * sub-warps per CTA (1, 2 or 4; variant 2) or sub-chunks per CTA (2, 4 or 8; variant 5).
- * Takes effect for plans created and host-pointer lookups issued afterwards. */
+/* All tuning knobs at once (0 = default): variant 1 = one bag per sub-warp (fp32 sums strictly in index
+ * order; also used when a launch mixes fp32 and int32 tables), 4 = TMA gather4 (rows of 64..512 bytes),
+ * 6 = the stretch kernel (default: load-balanced, no atomics; int32 bit-exact, fp32 deterministic and within
+ * 1e-5 relative of the sequential sum); unroll = rows in flight per lane (4 or 8); bags_mult = bags per CTA
+ * in units of sub-warps per CTA (1, 2, 4 or 8; variant 6).  Variants 2, 3 and 5 were round-1 kernels and no
+ * longer exist.  Takes effect for plans created and host-pointer lookups issued afterwards. */
 int emb_set_tuning(int variant, int unroll, int bags_mult);
 
 #ifdef __cplusplus

@@ -87,8 +87,8 @@ struct Ctx {
     emb_timings last = {0, 0, 0, 0, 0, 0, 0, 0};
     // tuning knobs (emb_set_tuning); 0 = default
     int unroll = 0;     // rows in flight per sub-warp: 4 or 8
-    int variant = 0;    // 1 = bag-per-sub-warp kernel, 2 = load-balanced kernel
-    int bags_mult = 0;  // load-balanced kernel: bags per CTA = mult * sub-warps per CTA (1, 2, 4)
+    int variant = 0;    // 1 = bag-per-sub-warp kernel, 4 = TMA gather4, 6 = stretch kernel
+    int bags_mult = 0;  // stretch kernel: bags per CTA = mult * sub-warps per CTA (1, 2, 4, 8)
     int host_path = EMB_HOST_AUTO;  // emb_set_host_path
 };
 
@@ -345,36 +345,26 @@ uint32_t lanes_for_dim(uint32_t D)
     return l;
 }
 
-/* Which kernel pools a launch, decided when the descriptors are built (the CTA -> bag
- * mapping depends on it). */
+/* Which kernel pools a launch, decided when the descriptors are built (the CTA -> bag mapping depends on it). */
 struct Variant {
-    int kind;      // 0 generic, 1 bag-per-sub-warp (index-ordered adds, any table kind), 2 / 3 round-1 load-balanced
-                   // kernels per CTA / per warp (int32 only), 4 TMA gather4 (rows of 64..512 bytes, any table kind),
-                   // 6 stretch kernel (load-balanced, no atomics; int32 and fp32)
-    int unroll;    // K
-    int mult;      // bags per CTA / sub-warps per CTA
+    int kind;      // 0 generic (any D), 1 bag-per-sub-warp (index-ordered adds, any table kind), 4 TMA gather4 (rows of
+                   // 64..512 bytes, any table kind), 6 stretch kernel (load-balanced, no atomics; int32 or fp32 launches)
+    int unroll;    // K: rows in flight per lane
+    int mult;      // stretch kernel: bags per CTA / sub-warps per CTA
     uint32_t bags; // bags per CTA
-    int threads;   // CTA size of the balanced kernel: 32, 64, 128 or 256
-    int stage;     // stretch kernel: lookups staged per pass
+    int stage;     // stretch kernel: 1 = the larger pass buffer (measurement knob)
 };
 
-int cta_threads()
-{
-    static int t = -1;  // measurement knob: EMB_CTA_THREADS = 64 / 128 / 256 forces the balanced kernel's CTA size
-    if (t < 0)
-        t = (int)env_u32("EMB_CTA_THREADS", 0);
-    return t;
-}
-
-/* avg_pool = lookups per bag of the launch (0 = unknown); max_table_bytes = the largest table the
- * launch reads (0 = unknown); pcie_out = the launch stores its results into host memory while the copy
- * engine brings the next group's indices in (the pipelined host-pointer call). */
-Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_bytes = 0, bool pcie_out = false,
-                     bool all_float = false)
+/* avg_pool = lookups per bag of the launch (0 = unknown).  The stretch kernel is the default; it replaced the
+ * round-1 load-balanced kernels (per CTA with atomics, per warp) on every workload (profiles/r2_stretch_ab_rotated.txt).
+ * Variant 1 stays for strictly index-ordered fp32 sums and for launches that mix fp32 and int32 tables, variant 4
+ * (TMA gather4) as the measured alternative north_star asks for. */
+Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = false)
 {
     Variant v;
     uint32_t D = g.shape.nr_cols;
     uint32_t lanes = lanes_for_dim(D);
+    v.stage = 0;
     if (!lanes) {
         v.kind = 0;
         v.unroll = 1;
@@ -383,91 +373,32 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, uint64_t max_table_b
         return v;
     }
     static const int dflt_kind = (int)env_u32("EMB_DEFAULT_VARIANT", 6);  // measurement knob
-    v.kind = g.variant ? g.variant : ((dflt_kind >= 1 && dflt_kind <= 4) || dflt_kind == 6 ? dflt_kind : 6);
-    v.stage = 0;
-    // Tables that stay in L2 while a launch walks them (<= 16 MB each, rows up to 128 bytes): the
-    // warp-autonomous kernel issues ~3x fewer instructions per lookup and wins (26 tables of 4 / 8 / 16 MB:
-    // 0.179 / 0.183 / 0.191 ms against 0.187 / 0.191 / 0.197 for the one-warp balanced kernel;
-    // profiles/r1_sweeps.md).  Its larger shared-memory footprint costs L1, which is what DRAM-resident
-    // tables need.
-    bool auto_warp = false;
-    if (!g.variant && dflt_kind == 2 && !any_float && lanes <= 8 && max_table_bytes && max_table_bytes <= (16ull << 20) &&
-        !(avg_pool > 0.0 && avg_pool <= 4.0)) {
-        v.kind = 3;
-        auto_warp = true;
-    }
-    const int bags_mult = (g.bags_mult == 8 && v.kind != 6) ? 0 : g.bags_mult;  // 8x only means something to the stretch kernel
-    if (v.kind == 3 && lanes > 8)
-        v.kind = 2;  // the warp-autonomous kernel is for rows up to 128 bytes
+    v.kind = g.variant ? g.variant : (dflt_kind == 1 || dflt_kind == 4 ? dflt_kind : 6);
     if (v.kind == 4 && lanes < 4)
-        v.kind = 2;  // the TMA kernel is for rows of 64 bytes and more
+        v.kind = 6;  // the TMA kernel is for rows of 64 bytes and more
     if (any_float && v.kind != 4 && !(v.kind == 6 && all_float))
         v.kind = 1;  // fp32 sums in strict index order (embedding_lookup_idx.cc:33-77): kinds 1 and 4; the stretch
                      // kernel pools fp32 tables too (deterministic, reassociated at its cut points), but a launch
                      // is compiled for one element kind
-    // defaults from the sweeps in profiles/r1_sweeps.md (tools/sweep.py): 64-byte rows want many
-    // small CTAs; 256-byte rows 8 rows in flight per lane and 4x the bags per CTA; 512-byte rows 2x
-    v.unroll = g.unroll ? g.unroll : (lanes >= 16 || auto_warp ? 8 : 4);
-    v.mult = (v.kind == 2) ? (bags_mult ? bags_mult : (lanes == 16 ? 4 : lanes > 16 ? 2 : 1)) : 1;
-    // one or two lookups per bag (Criteo-style single-index features): a CTA's fixed costs dominate,
-    // give it 4x the bags (C3 lookup shape: 76 -> 56 us, profiles/r1_sweeps.md)
-    if (v.kind == 2 && !bags_mult && avg_pool > 0.0 && avg_pool <= 4.0)
-        v.mult = 4;
-    v.bags = emb::kThreads / lanes * v.mult;
-    // CTA size of the balanced kernel.  Small CTAs: the CTA barriers (offsets staged, indices staged,
-    // all pieces pooled) hold fewer warps and the CTAs of an SM drift apart, so more row loads are in
-    // flight at any time.  Same box, 256 / 128 / 64 threads (tools/cta_sweep.sh, profiles/r1_sweeps.md):
-    // C2 0.2995 / 0.287 / 0.2811 ms, C3 0.0577 / 0.0536 / 0.0598, C4 0.674 / 0.664 / 0.662,
-    // C5 0.5288 / 0.5104 (bags_mult 1) / --.
-    v.threads = emb::kThreads;
-    if (v.kind == 2) {
-        const bool short_bags = avg_pool > 0.0 && avg_pool <= 4.0;
-        int want = cta_threads();
-        // 64-byte rows: ONE warp per CTA (the CTA barriers cost nothing, 32 CTAs per SM drift apart freely),
-        // 64 registers, so 8 rows in flight per lane and 16 bags per CTA; short bags 4 rows and 32 bags.
-        // Same box, against the 64-thread CTAs above: C2 0.2688 -> 0.2585 ms, C3 0.0517 -> 0.0476 ms
-        // (tools/cta32_sweep.sh, profiles/r1_sweeps.md).
-        // Not when the results cross PCIe from inside a pipelined call: the same C2 call through host pointers
-        // takes 2.88-2.92 ms with the 64-thread CTAs and 3.08 ms with the one-warp ones (bench e2e, runs r1y/r1z
-        // against r1v/r1u) -- the faster kernel's result bursts slow the concurrent index copy-in (2.42 -> 2.60 ms).
-        // Measurement knob: EMB_PCIE_OUT_ONE_WARP=1 lifts the exception.
-        static const bool pcie_one_warp = env_u32("EMB_PCIE_OUT_ONE_WARP", 0) != 0;
-        const bool one_warp = lanes == 4 && (want == 32 || (!want && !g.unroll && !bags_mult && (!pcie_out || pcie_one_warp)));
-        if (!want)
-            want = one_warp ? 32 : lanes >= 32 ? 128 : 64;
-        if (want == 128 || (want == 64 && lanes <= 16) || (want == 32 && lanes <= 16))
-            v.threads = want;
-        if (one_warp && !g.unroll)
-            v.unroll = short_bags ? 4 : 8;
-        if (one_warp && !bags_mult)
-            v.mult = short_bags ? 4 : 2;
-        if (!bags_mult && lanes >= 32 && v.threads == 128)
-            v.mult = 1;
-        v.bags = v.threads / lanes * v.mult;
-    }
-    if (v.kind == 3) {
-        v.mult = 1;
-        v.bags = emb::kThreads;  // 32 bags per warp
-    }
+    v.unroll = g.unroll ? g.unroll : (lanes >= 16 ? 8 : 4);
+    v.mult = 1;
+    v.bags = emb::kThreads / lanes;  // kind 1: one bag per sub-warp of a 256-thread CTA
     if (v.kind == 6) {
-        // One warp per CTA.  Defaults from the round-2 sweeps on the B200 (tools/r2_quick_ab.sh, profiles/r2_sweeps.md;
-        // K = rows in flight per lane, mult = bags per CTA / sub-warps):
+        // One warp per CTA.  Defaults from the round-2 sweeps on the B200 (tools/r2_quick_ab.sh,
+        // profiles/r2_stretch_ab_rotated.txt; K = rows in flight per lane, mult = bags per CTA / sub-warps):
         //   64-byte rows (C2):   K8 m2 0.2257 ms | K4 m2 0.2360 | K8 m4 0.2545 (two passes) | K8 m1 0.2503
         //   ... one index per bag (C3): K4 m4 0.0353 | K8 m4 0.0373 | K8 m8 0.0414
         //   256-byte rows (C4):  K8 m4 0.5761 | K8 m2 0.5924 | K4 m4 0.6148 | K8 m8 0.6206
         //   512-byte rows (C5):  K8 m1 0.4222 | K8 m2 0.4469 | K8 m4 0.4828
         const bool short_bags = avg_pool > 0.0 && avg_pool <= 4.0;
-        v.threads = 32;
         v.unroll = g.unroll ? g.unroll : (short_bags && lanes <= 8 ? 4 : 8);
-        v.mult = bags_mult ? bags_mult : (lanes >= 32 ? 1 : lanes >= 16 ? 4 : short_bags ? 4 : 2);
+        v.mult = g.bags_mult ? g.bags_mult : (lanes >= 32 ? 1 : lanes >= 16 ? 4 : short_bags ? 4 : 2);
         static const int big_stage = (int)env_u32("EMB_STRETCH_STAGE", 0);  // measurement knob: 1 = the larger pass
         v.stage = big_stage;
         v.bags = std::min<uint32_t>(32 / lanes * v.mult, 64);  // one marker byte per lookup names the bag
     }
-    if (v.kind == 4) {
-        v.mult = 1;
+    if (v.kind == 4)
         v.bags = (emb::kThreads / 32) * 4 * (32 / lanes);  // 4 bags per sub-warp
-    }
     return v;
 }
 
@@ -478,77 +409,6 @@ void launch_ordered(int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d,
         emb::bag_sum_kernel<LANES, 8><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
     else
         emb::bag_sum_kernel<LANES, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
-}
-
-template <int LANES, int K, int MINB, int THREADS>
-void launch_balanced_k(int mult, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
-{
-    constexpr int SUB = THREADS / LANES;
-    static int carve = -2;  // measurement knob: EMB_CARVEOUT = preferred shared-memory carveout in percent
-    if (carve == -2) {
-        const char *e = getenv("EMB_CARVEOUT");
-        carve = e ? atoi(e) : -1;
-        if (carve >= 0) {
-            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB, THREADS>,
-                                 cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB, THREADS>,
-                                 cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-            cudaFuncSetAttribute(emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB, THREADS>,
-                                 cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-        }
-    }
-    if (mult == 4)
-        emb::bag_sum_balanced_kernel<LANES, K, 4 * SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, uni, g.d_err);
-    else if (mult == 2)
-        emb::bag_sum_balanced_kernel<LANES, K, 2 * SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, uni, g.d_err);
-    else
-        emb::bag_sum_balanced_kernel<LANES, K, SUB, MINB, THREADS><<<grid, THREADS, 0, s>>>(d, n, uni, g.d_err);
-}
-
-/* CTA sizes of the balanced kernel: 256 threads always; 128 and 64 as well where the sub-warp count
- * stays >= 2 (rows up to 512 / 256 bytes).  MINB keeps the resident threads per SM the same. */
-template <int LANES>
-void launch_balanced(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
-{
-    if constexpr (LANES <= 16) {  // one warp per CTA: the CTA barriers cost nothing (default for LANES 4; EMB_CTA_THREADS=32 otherwise)
-        if (v.threads == 32) {
-            if (v.unroll == 8)
-                return launch_balanced_k<LANES, 8, 32, 32>(v.mult, grid, s, d, n, uni);
-            return launch_balanced_k<LANES, 4, 32, 32>(v.mult, grid, s, d, n, uni);
-        }
-    }
-    if (v.unroll == 8) {
-        if constexpr (LANES <= 16) {
-            if (v.threads == 64)
-                return launch_balanced_k<LANES, 8, 16, 64>(v.mult, grid, s, d, n, uni);
-        }
-        if (v.threads == 128)
-            return launch_balanced_k<LANES, 8, 8, 128>(v.mult, grid, s, d, n, uni);
-        launch_balanced_k<LANES, 8, 4, 256>(v.mult, grid, s, d, n, uni);
-    } else {
-        if constexpr (LANES <= 16) {
-            if (v.threads == 64)
-                return launch_balanced_k<LANES, 4, 24, 64>(v.mult, grid, s, d, n, uni);
-        }
-        if (v.threads == 128)
-            return launch_balanced_k<LANES, 4, 12, 128>(v.mult, grid, s, d, n, uni);
-        launch_balanced_k<LANES, 4, 6, 256>(v.mult, grid, s, d, n, uni);
-    }
-}
-
-template <int LANES>
-void launch_warp(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
-{
-    if constexpr (LANES <= 8) {
-        // no carveout preference on purpose: L1 capacity is what holds the row loads in flight, and
-        // the largest shared-memory carveout halves the throughput (profiles/r1_sweeps.md)
-        if (v.unroll == 8)
-            emb::bag_sum_warp_kernel<LANES, 8, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
-        else
-            emb::bag_sum_warp_kernel<LANES, 4, 6><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
-    } else {
-        (void)v; (void)grid; (void)s; (void)d; (void)n; (void)uni;
-    }
 }
 
 /* Stretch kernel: K rows in flight per lane, BAGS = sub-warps x mult bags per one-warp CTA, STAGE lookups per
@@ -618,10 +478,6 @@ void launch_for_lanes(const Variant &v, bool is_float, uint32_t grid, cudaStream
         launch_stretch<LANES>(v, is_float, grid, s, d, n, uni);
     else if (v.kind == 4)
         launch_tma<LANES>(grid, s, d, n, uni);
-    else if (v.kind == 3)
-        launch_warp<LANES>(v, grid, s, d, n, uni);
-    else if (v.kind == 2)
-        launch_balanced<LANES>(v, grid, s, d, n, uni);
     else
         launch_ordered<LANES>(v.unroll, grid, s, d, n, uni);
 }
@@ -659,15 +515,6 @@ int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
     return EMB_OK;
-}
-
-uint64_t max_table_bytes_of(const emb_dev_query *queries, uint32_t n)
-{
-    uint64_t m = 0;
-    for (uint32_t i = 0; i < n; i++)
-        if (queries[i].table_id < g.tables.size())
-            m = std::max<uint64_t>(m, g.tables[queries[i].table_id].rows * (uint64_t)g.shape.nr_cols * 4);
-    return m;
 }
 
 /* Fill one descriptor from a query; returns the number of CTAs it needs. */
@@ -755,7 +602,7 @@ struct emb_plan {
     uint32_t grid = 0;
     uint32_t uni = 0;  // uniform_chunks() of the descriptors
     uint64_t bytes = 0;
-    Variant variant = {0, 1, 1, 8, 256, 0};
+    Variant variant = {0, 1, 1, 8, 0};
     bool all_float = false;
 };
 
@@ -797,11 +644,11 @@ int emb_set_unroll(int unroll)
 
 int emb_set_tuning(int variant, int unroll, int bags_mult)
 {
-    if (variant < 0 || variant > 6 || variant == 5)
-        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp), 2 (round-1 load-balanced per CTA), "
-                                "3 (round-1 load-balanced per warp), 4 (TMA gather4) or 6 (stretch kernel)");
-    if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4 && !(variant == 6 && bags_mult == 8))
-        return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2 or 4 (variant 6: also 8)");
+    if (variant != 0 && variant != 1 && variant != 4 && variant != 6)
+        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp, index-ordered), 4 (TMA gather4) or "
+                                "6 (stretch kernel); 2, 3 and 5 were round-1 kernels, removed");
+    if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4 && bags_mult != 8)
+        return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2, 4 or 8");
     int rc = emb_set_unroll(unroll);
     if (rc)
         return rc;
@@ -1080,8 +927,7 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
             li += queries[i].indices_len;
             nb += queries[i].nr_batches;
         }
-        p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0, max_table_bytes_of(queries, n), false,
-                                  all_float);
+        p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0, all_float);
     }
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
@@ -1186,8 +1032,7 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
         tot_li += queries[i].indices_len;
         tot_nb += queries[i].nr_batches;
     }
-    const Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0,
-                                         max_table_bytes_of(queries, n), false, all_float);
+    const Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0, all_float);
     uint64_t chunk = 0;
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
@@ -1522,11 +1367,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         n_groups = std::min(std::min(T, kMaxGroups), forced_groups);
     if ((rc = ensure_events(3 * n_groups + 2)))
         return rc;
-    uint64_t max_tb = 0;
-    for (uint32_t t = 0; t < T; t++)
-        max_tb = std::max<uint64_t>(max_tb, g.tables[t].rows * D * 4ull);
-    const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, max_tb,
-                                         out_mapped && !in_mapped && n_groups > 1, all_float);
+    const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, all_float);
     std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
     {
         // Group sizes grow by a factor r per group: nothing can be pooled before the first group's

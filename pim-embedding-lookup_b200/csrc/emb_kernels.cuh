@@ -66,13 +66,6 @@ __device__ __forceinline__ uint32_t chunk_first_bag(const BagDesc *d, uint32_t c
     return d->bag_first + c * per;
 }
 
-#ifndef EMB_BF_SEARCH
-#define EMB_BF_SEARCH 0  // old balanced kernel: 1 = branch-free bag search per piece (round-1 experiment switch)
-#endif
-#ifndef EMB_CONTIG
-#define EMB_CONTIG 0  // old balanced kernel: 1 = contiguous stretch per sub-warp (round-1 experiment switch)
-#endif
-
 /* Row loads are plain ld.global.nc (L1 allocates, L2 default priority).  Measured in round 1 against
  * L1::no_allocate, L2 evict_last / evict_normal policy operands and the .L2::64B / .L2::128B prefetch sizes
  * (profiles/r1_sweeps.md): ncu counts every sector of an L1::no_allocate load as evict_first at L2, so the rows
@@ -98,17 +91,6 @@ __device__ __forceinline__ void stg_stream16(void *p, uint4 v)
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
                  "r"(v.w)
                  : "memory");
-}
-
-/* 4-byte asynchronous global->shared copy (LDGSTS): no register, no stall at issue. */
-__device__ __forceinline__ void cp_async_u32(uint32_t *smem_dst, const uint32_t *gmem_src)
-{
-    const uint32_t sa = (uint32_t)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gmem_src) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all()
-{
-    asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
 /* emb_host.h:210  (float)s / pow(10,9): int->float RNE, divide in double, round to float.
@@ -293,302 +275,16 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni,
     }
 }
 
-/*
- * Load-balanced sum-pool kernel for int32 fixed-point tables, D = 4*LANES columns.
- *
- * bag_sum_kernel above gives every bag to one sub-warp, so with ragged bags (pooling 1..20)
- * a warp runs as long as its longest bag and the short bags' lanes idle -- fewer row loads in
- * flight than the memory system needs.  Here the CTA's bags only define a window of the index
- * stream; the window is cut into pieces of K consecutive lookups and the pieces are dealt
- * round-robin to the sub-warps.  A sub-warp issues its K row loads back to back (every lane
- * busy whatever the bag lengths), then walks the K rows in order, adding into registers and
- * flushing to a per-CTA shared-memory accumulator whenever the walk crosses a bag boundary.
- * int32 wrap-around addition (emb_dpu_lookup.c:114) is associative and commutative, so the
- * shared-memory atomics reproduce the reference's sums bit for bit in any order.
- *
- * BAGS bags per CTA (a multiple of kThreads/LANES); the window is streamed through the
- * kIdxStage-entry staging buffer in passes, so bags of any length work.
- * Requires monotone offsets inside the CTA's chunk; a chunk that is not monotone (bags that
- * overlap, which lookup() permits) is pooled bag by bag instead.
- */
-template <int LANES, int K, int BAGS, int MINB, int THREADS = kThreads>
-__global__ void __launch_bounds__(THREADS, MINB)
-bag_sum_balanced_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
-{
-    constexpr int SUB = THREADS / LANES;  // sub-warps per CTA
-    constexpr int D = LANES * 4;
-    static_assert(BAGS % SUB == 0, "BAGS must be a multiple of the sub-warp count");
-    __shared__ uint32_t s_off[BAGS + 1];
-    constexpr int STAGE = kIdxStage * THREADS / kThreads;  // indices staged per pass
-    __shared__ uint32_t s_idx[STAGE];
-    __shared__ __align__(16) uint32_t s_acc[BAGS * D];
-
-    const uint32_t tid = threadIdx.x;
-    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
-    const BagDesc *__restrict__ d = descs + q;
-
-    const uint32_t B = d->nr_batches;
-    const uint32_t ilen = d->indices_len;
-    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, BAGS);
-    const uint32_t nb = min((uint32_t)BAGS, d->bag_end - b0);
-    const uint32_t *__restrict__ g_idx = d->indices;
-    const uint32_t *__restrict__ g_off = d->offsets;
-
-    // Bag bounds (emb_dpu_lookup.c:60-63,109-110: bag 0 starts at 0 whatever offsets[0] is, bag i ends where
-    // bag i+1 starts, the last bag ends at indices_len).  First round: the loads are issued here and looked
-    // at further down.  Every thread also loads its right-hand neighbour's bound (the same cache line): monotonicity is checked on the loaded
-    // values themselves and one barrier closes both the staging and the check.
-    const uint32_t bq = b0 + tid;
-    uint32_t raw0 = 0, raw1 = 0;
-    if (tid <= nb) {
-        if (bq != 0 && bq < B)
-            raw0 = ldg_stream_u32(g_off + bq);
-        if (tid < nb && bq + 1 < B)
-            raw1 = ldg_stream_u32(g_off + bq + 1);
-    }
-    // in the shadow of those loads
-    for (uint32_t i = tid; i < BAGS * D / 4; i += THREADS)
-        reinterpret_cast<uint4 *>(s_acc)[i] = make_uint4(0u, 0u, 0u, 0u);
-
-    bool nonmono = false;
-    if (tid <= nb) {
-        const uint32_t v = min((bq == 0) ? 0u : (bq >= B ? ilen : raw0), ilen);
-        if (tid < nb)
-            nonmono = v > min((bq + 1 >= B) ? ilen : raw1, ilen);
-        s_off[tid] = v;
-    }
-    for (uint32_t i = tid + THREADS; i <= nb; i += THREADS) {
-        const uint32_t b = b0 + i;
-        const uint32_t v = min((b >= B) ? ilen : ldg_stream_u32(g_off + b), ilen);
-        if (i < nb)
-            nonmono |= v > min((b + 1 >= B) ? ilen : ldg_stream_u32(g_off + b + 1), ilen);
-        s_off[i] = v;
-    }
-    const bool ordered = __syncthreads_or(nonmono);
-
-    const uint32_t flags = d->flags;
-    const uint32_t rows = d->rows;
-    const uint32_t row_base = d->row_base;
-    const uint32_t sub = tid / LANES;
-    const uint32_t lane = tid % LANES;
-    const uint4 *__restrict__ table = reinterpret_cast<const uint4 *>(d->table) + lane;
-    bool bad = false;
-
-    if (!ordered) {
-        const uint32_t wlo = s_off[0], whi = s_off[nb];
-        for (uint32_t base = wlo; base < whi; base += STAGE) {
-            const uint32_t n = min((uint32_t)STAGE, whi - base);
-            if (base != wlo)
-                __syncthreads();  // everyone is done with the previous pass's s_idx
-            for (uint32_t i = tid; i < n; i += THREADS)
-                s_idx[i] = ldg_stream_u32(g_idx + base + i);
-            __syncthreads();
-#if EMB_CONTIG
-            // Experiment (build switch, default off; tools/piece_loop_ab.sh): every sub-warp pools ONE contiguous
-            // stretch of the staged window -- one bag search per sub-warp and pass, the running sum kept in
-            // registers across its K-lookup steps, a flush only where a bag ends inside the stretch.
-            {
-                const uint32_t per = (n + SUB - 1) / SUB;
-                const uint32_t cb = min(n, sub * per), ce = min(n, cb + per);
-                uint32_t lo = 0, hi = nb;
-                const uint32_t pfirst = base + cb;
-                while (hi - lo > 1) {  // bag of the stretch's first lookup: last i with s_off[i] <= pfirst
-                    uint32_t mid = (lo + hi) >> 1;
-                    if (s_off[mid] <= pfirst)
-                        lo = mid;
-                    else
-                        hi = mid;
-                }
-                uint32_t bag = lo, bag_end = s_off[lo + 1];
-                uint4 acc = make_uint4(0u, 0u, 0u, 0u);
-                for (uint32_t c = cb; c < ce; c += K) {
-                    const uint32_t m = min((uint32_t)K, ce - c);
-                    uint32_t r[K];
-#pragma unroll
-                    for (int u = 0; u < K; u++) {
-                        uint32_t id = 0xffffffffu;
-                        if ((uint32_t)u < m) {
-                            id = s_idx[c + u] - row_base;
-                            bad |= id >= rows;
-                        }
-                        r[u] = id;
-                    }
-                    uint4 v[K];
-#pragma unroll
-                    for (int u = 0; u < K; u++) {
-                        v[u] = make_uint4(0u, 0u, 0u, 0u);
-                        if (r[u] < rows)
-                            v[u] = ldg_row16(table + (size_t)r[u] * LANES);
-                    }
-                    const uint32_t p0 = base + c;
-#pragma unroll
-                    for (int u = 0; u < K; u++) {
-                        if ((uint32_t)u < m) {
-                            if (p0 + u >= bag_end) {
-                                uint32_t *a = s_acc + bag * D + lane * 4;
-                                atomicAdd(a + 0, acc.x);
-                                atomicAdd(a + 1, acc.y);
-                                atomicAdd(a + 2, acc.z);
-                                atomicAdd(a + 3, acc.w);
-                                acc = make_uint4(0u, 0u, 0u, 0u);
-                                do {
-                                    bag++;
-                                    bag_end = s_off[bag + 1];
-                                } while (p0 + u >= bag_end);
-                            }
-                            acc.x += v[u].x;
-                            acc.y += v[u].y;
-                            acc.z += v[u].z;
-                            acc.w += v[u].w;
-                        }
-                    }
-                }
-                if (cb < ce) {
-                    uint32_t *a = s_acc + bag * D + lane * 4;
-                    atomicAdd(a + 0, acc.x);
-                    atomicAdd(a + 1, acc.y);
-                    atomicAdd(a + 2, acc.z);
-                    atomicAdd(a + 3, acc.w);
-                }
-            }
-#else
-            for (uint32_t c = sub * K; c < n; c += SUB * K) {
-                const uint32_t m = min((uint32_t)K, n - c);
-                uint32_t r[K];
-#pragma unroll
-                for (int u = 0; u < K; u++) {
-                    uint32_t id = 0xffffffffu;
-                    if ((uint32_t)u < m) {
-                        id = s_idx[c + u] - row_base;  // unsigned: rows below the shard wrap high
-                        bad |= id >= rows;
-                    }
-                    r[u] = id;
-                }
-                uint4 v[K];
-#pragma unroll
-                for (int u = 0; u < K; u++) {
-                    v[u] = make_uint4(0u, 0u, 0u, 0u);
-                    if (r[u] < rows)
-                        v[u] = ldg_row16(table + (size_t)r[u] * LANES);
-                }
-                // bag of the piece's first lookup: last i with s_off[i] <= p (skips empty bags)
-                const uint32_t p0 = base + c;
-#if EMB_BF_SEARCH
-                // Experiment (build switch, default off): branch-free binary lifting, log2(BAGS) predicated steps
-                uint32_t lo = 0;
-#pragma unroll
-                for (int step = BAGS / 2; step >= 1; step >>= 1) {
-                    const uint32_t t = lo + step;
-                    if (t < nb && s_off[t] <= p0)
-                        lo = t;
-                }
-#else
-                uint32_t lo = 0, hi = nb;
-                while (hi - lo > 1) {
-                    uint32_t mid = (lo + hi) >> 1;
-                    if (s_off[mid] <= p0)
-                        lo = mid;
-                    else
-                        hi = mid;
-                }
-#endif
-                uint32_t bag = lo, bag_end = s_off[lo + 1];
-                uint4 acc = make_uint4(0u, 0u, 0u, 0u);
-#pragma unroll
-                for (int u = 0; u < K; u++) {
-                    if ((uint32_t)u < m) {
-                        if (p0 + u >= bag_end) {  // crossed into a later bag: flush the partial sum
-                            uint32_t *a = s_acc + bag * D + lane * 4;
-                            atomicAdd(a + 0, acc.x);
-                            atomicAdd(a + 1, acc.y);
-                            atomicAdd(a + 2, acc.z);
-                            atomicAdd(a + 3, acc.w);
-                            acc = make_uint4(0u, 0u, 0u, 0u);
-                            do {
-                                bag++;
-                                bag_end = s_off[bag + 1];
-                            } while (p0 + u >= bag_end);
-                        }
-                        acc.x += v[u].x;
-                        acc.y += v[u].y;
-                        acc.z += v[u].z;
-                        acc.w += v[u].w;
-                    }
-                }
-                uint32_t *a = s_acc + bag * D + lane * 4;
-                atomicAdd(a + 0, acc.x);
-                atomicAdd(a + 1, acc.y);
-                atomicAdd(a + 2, acc.z);
-                atomicAdd(a + 3, acc.w);
-            }
-#endif
-        }
-    } else {
-        // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
-        for (uint32_t bag = sub; bag < nb; bag += SUB) {
-            const uint32_t start = s_off[bag], end = s_off[bag + 1];
-            uint4 acc = make_uint4(0u, 0u, 0u, 0u);
-            for (uint32_t p = start; p < end; p++) {
-                uint32_t id = __ldg(g_idx + p) - row_base;
-                if (id < rows) {
-                    uint4 v = ldg_row16(table + (size_t)id * LANES);
-                    acc.x += v.x;
-                    acc.y += v.y;
-                    acc.z += v.z;
-                    acc.w += v.w;
-                } else {
-                    bad = true;
-                }
-            }
-            reinterpret_cast<uint4 *>(s_acc)[bag * LANES + lane] = acc;
-        }
-    }
-    if (bad && !(flags & kDescSharded))
-        atomicOr(err_flag, 1u);
-    __syncthreads();
-
-    const uint32_t bpr = d->bags_per_rank;
-    const uint32_t out_stride = d->out_stride;
-#pragma unroll
-    for (int it = 0; it < BAGS / SUB; it++) {
-        const uint32_t bag = it * SUB + sub;
-        if (bag >= nb)
-            break;
-        uint4 o = reinterpret_cast<const uint4 *>(s_acc)[bag * LANES + lane];
-        if (!(flags & kDescRaw))  // post_process, emb_host.h:210
-            o = make_uint4(__float_as_uint(dequant(o.x)), __float_as_uint(dequant(o.y)),
-                           __float_as_uint(dequant(o.z)), __float_as_uint(dequant(o.w)));
-        const uint32_t b = b0 + bag;
-        uint32_t *base;
-        uint32_t row;
-        if (bpr) {
-            uint32_t rk = b / bpr;
-            base = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
-            row = b - rk * bpr;
-        } else {
-            base = reinterpret_cast<uint32_t *>(d->out);
-            row = b;
-        }
-        uint32_t *dst = base + (size_t)row * out_stride + lane * 4;
-        if (flags & kDescVecStore) {
-            stg_stream16(dst, o);
-        } else {
-            dst[0] = o.x;
-            dst[1] = o.y;
-            dst[2] = o.z;
-            dst[3] = o.w;
-        }
-    }
-}
-
 /* ---- stretch kernel -----------------------------------------------------------------------------
  *
  * bag_sum_stretch_kernel: load-balanced sum pooling with NO atomics and a branch-free inner loop.
  *
- * The round-1 balanced kernel above spent ~400 warp instructions per 64 lookups (ncu: 57 % of the issue slots,
- * 19 % of them branch bookkeeping of the divergent flush, one binary search per piece, 4 ATOMS per flush;
- * profiles/r1_bag_sum_balanced_hotspots.md).  This kernel does the same arithmetic (emb_dpu_lookup.c:106-116,
- * emb_host.h:207-212) in ~100:
+ * The round-1 balanced kernel (pieces of K lookups dealt round-robin to the sub-warps, partial sums flushed into a
+ * shared accumulator with atomicAdd at every bag boundary) spent ~400 warp instructions per 64 lookups (ncu: 57 %
+ * of the issue slots, 19 % of them branch bookkeeping of the divergent flush, one binary search per piece, 4 ATOMS
+ * per flush; profiles/r1_bag_sum_balanced_hotspots.md).  This kernel does the same arithmetic
+ * (emb_dpu_lookup.c:106-116, emb_host.h:207-212) in ~100 and replaced it (and the round-1 warp-autonomous
+ * kernel) on every workload measured (profiles/r2_stretch_ab_rotated.txt):
  *
  *  - One warp per CTA, BAGS consecutive bags of one table; the bag bounds live in REGISTERS (lane i holds
  *    bound i), so everything that is derived from them -- monotonicity, the window, which bag a position
@@ -955,224 +651,6 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
             dstp[1] = o.y;
             dstp[2] = o.z;
             dstp[3] = o.w;
-        }
-    }
-}
-
-/*
- * Warp-autonomous load-balanced sum-pool kernel for int32 fixed-point tables with short rows
- * (D = 4*LANES <= 32 columns, i.e. rows of 16..128 bytes).
- *
- * Same idea as bag_sum_balanced_kernel -- the bags only delimit a window of the index stream
- * and the lookups of the window are dealt evenly to the sub-warps -- but the unit is a WARP, not
- * a CTA: a warp owns 32 consecutive bags (one offset per lane), stages its own index window in
- * its own slice of shared memory and never meets a CTA barrier, so the 8 warps of a CTA drift
- * apart and some are always gathering while others stage or store.  While staging, every lane
- * also finds the bag of "its" lookup (binary search over the warp's 33 offsets, lane-parallel) and
- * stores it beside the index; the sub-warps then walk CONTIGUOUS stretches of the window (K rows
- * in flight, 16-byte shared-memory reads of K indices and K bag ids at a time), keep the running
- * sum in registers across a whole bag and flush to the warp's shared accumulator only when the
- * bag id changes -- about one flush per bag instead of one per K lookups.  int32 wrap-around
- * addition is associative and commutative (emb_dpu_lookup.c:114), so the result is bit-exact.
- */
-template <int LANES, int K, int MINB>
-__global__ void __launch_bounds__(kThreads, MINB)
-bag_sum_warp_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
-{
-    constexpr int SUB = 32 / LANES;  // sub-warps per warp
-    constexpr int D = LANES * 4;
-    constexpr int WB = 32;           // bags per warp
-    constexpr int WARPS = kThreads / 32;
-    constexpr int STAGE = LANES >= 8 ? 256 : (384 % (SUB * K) == 0) ? 384 : 512;  // lookups staged per warp and pass (48 KB static smem)
-    static_assert(K == 4 || K == 8, "K is 4 or 8");
-    static_assert(STAGE % (SUB * K) == 0 && STAGE % 32 == 0, "STAGE must split evenly");
-    __shared__ uint32_t s_off[WARPS][WB + 1];
-    __shared__ __align__(16) uint32_t s_idx[WARPS][STAGE];
-    __shared__ __align__(16) uint8_t s_bag[WARPS][STAGE];
-    __shared__ __align__(16) uint32_t s_acc[WARPS][WB * D];
-
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t warp = threadIdx.x >> 5;
-    const uint32_t sub = lane / LANES;
-    const uint32_t sl = lane % LANES;
-    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
-    const BagDesc *__restrict__ d = descs + q;
-
-    const uint32_t B = d->nr_batches;
-    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, WARPS * WB) + warp * WB;
-    if (b0 >= d->bag_end)
-        return;
-    const uint32_t nb = min((uint32_t)WB, d->bag_end - b0);
-    const uint32_t ilen = d->indices_len;
-    const uint32_t *__restrict__ g_idx = d->indices;
-    const uint32_t *__restrict__ g_off = d->offsets;
-    uint32_t *off = s_off[warp];
-    uint32_t *acc_s = s_acc[warp];
-
-    // bag bounds (emb_dpu_lookup.c:60-63,109-110), one per lane; lane 0 also fetches the end of bag 31
-    {
-        uint32_t b = b0 + lane;
-        uint32_t v = (b == 0) ? 0u : (b >= B ? ilen : ldg_stream_u32(g_off + b));
-        off[lane] = min(v, ilen);
-        if (lane == 0) {
-            b = b0 + WB;
-            off[WB] = (b >= B) ? ilen : min(ldg_stream_u32(g_off + b), ilen);
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < WB * D / 4 / 32; i++)
-        reinterpret_cast<uint4 *>(acc_s)[i * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
-    __syncwarp();
-    const bool nonmono = __any_sync(0xffffffffu, lane < nb && off[lane] > off[lane + 1]);
-
-    const uint32_t flags = d->flags;
-    const uint32_t rows = d->rows;
-    const uint32_t row_base = d->row_base;
-    const uint4 *__restrict__ table = reinterpret_cast<const uint4 *>(d->table) + sl;
-    bool bad = false;
-
-    if (!nonmono) {
-        const uint32_t wlo = off[0], whi = off[nb];
-        for (uint32_t base = wlo; base < whi; base += STAGE) {
-            const uint32_t n = min((uint32_t)STAGE, whi - base);
-            const uint32_t per = ((n + SUB * K - 1) / (SUB * K)) * K;  // lookups per sub-warp, multiple of K
-            const uint32_t n_pad = per * SUB;
-            if (base != wlo)
-                __syncwarp();  // the previous pass's stretches have been walked
-            // all of the pass's index loads go out back to back as asynchronous global->shared copies
-            for (uint32_t i = lane; i < n; i += 32)
-                cp_async_u32(&s_idx[warp][i], g_idx + base + i);
-            cp_async_wait_all();
-            __syncwarp();
-#pragma unroll 4
-            for (uint32_t i = lane; i < n_pad; i += 32) {
-                uint32_t r = 0xffffffffu;
-                const uint32_t p = min(base + i, whi - 1);
-                if (i < n) {
-                    r = s_idx[warp][i] - row_base;  // unsigned: rows below the shard wrap high
-                    if (r >= rows) {
-                        bad = true;
-                        r = 0xffffffffu;
-                    }
-                }
-                // bag of position p: last j < nb with off[j] <= p (empty bags share a start; the last wins)
-                uint32_t lo = 0, hi = nb;
-#pragma unroll
-                for (int it = 0; it < 5; it++) {
-                    const uint32_t mid = (lo + hi) >> 1;
-                    const bool act = hi - lo > 1;
-                    const bool right = off[mid] <= p;
-                    lo = (act && right) ? mid : lo;
-                    hi = (act && !right) ? mid : hi;
-                }
-                s_idx[warp][i] = r;
-                s_bag[warp][i] = (uint8_t)lo;
-            }
-            __syncwarp();
-            const uint32_t c0 = sub * per;
-            if (c0 < n) {
-                uint32_t cur = s_bag[warp][c0];
-                uint4 acc = make_uint4(0u, 0u, 0u, 0u);
-                for (uint32_t c = c0; c < c0 + per; c += K) {
-                    uint32_t r[K], bg[K];
-#pragma unroll
-                    for (int u4 = 0; u4 < K / 4; u4++) {
-                        const uint4 rr = *reinterpret_cast<const uint4 *>(&s_idx[warp][c + 4 * u4]);
-                        const uint32_t bb = *reinterpret_cast<const uint32_t *>(&s_bag[warp][c + 4 * u4]);
-                        r[4 * u4 + 0] = rr.x;
-                        r[4 * u4 + 1] = rr.y;
-                        r[4 * u4 + 2] = rr.z;
-                        r[4 * u4 + 3] = rr.w;
-                        bg[4 * u4 + 0] = bb & 0xffu;
-                        bg[4 * u4 + 1] = (bb >> 8) & 0xffu;
-                        bg[4 * u4 + 2] = (bb >> 16) & 0xffu;
-                        bg[4 * u4 + 3] = bb >> 24;
-                    }
-                    uint4 v[K];
-#pragma unroll
-                    for (int u = 0; u < K; u++) {
-                        v[u] = make_uint4(0u, 0u, 0u, 0u);
-                        if (r[u] != 0xffffffffu)
-                            v[u] = ldg_row16(table + (size_t)r[u] * LANES);
-                    }
-#pragma unroll
-                    for (int u = 0; u < K; u++) {
-                        if (bg[u] != cur) {  // a later bag begins: flush the finished one
-                            uint32_t *a = acc_s + cur * D + sl * 4;
-                            atomicAdd(a + 0, acc.x);
-                            atomicAdd(a + 1, acc.y);
-                            atomicAdd(a + 2, acc.z);
-                            atomicAdd(a + 3, acc.w);
-                            acc = make_uint4(0u, 0u, 0u, 0u);
-                            cur = bg[u];
-                        }
-                        acc.x += v[u].x;
-                        acc.y += v[u].y;
-                        acc.z += v[u].z;
-                        acc.w += v[u].w;
-                    }
-                }
-                uint32_t *a = acc_s + cur * D + sl * 4;
-                atomicAdd(a + 0, acc.x);
-                atomicAdd(a + 1, acc.y);
-                atomicAdd(a + 2, acc.z);
-                atomicAdd(a + 3, acc.w);
-            }
-        }
-    } else {
-        // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
-        for (uint32_t bag = sub; bag < nb; bag += SUB) {
-            const uint32_t start = off[bag], end = off[bag + 1];
-            uint4 acc = make_uint4(0u, 0u, 0u, 0u);
-            for (uint32_t p = start; p < end; p++) {
-                uint32_t id = __ldg(g_idx + p) - row_base;
-                if (id < rows) {
-                    uint4 v = ldg_row16(table + (size_t)id * LANES);
-                    acc.x += v.x;
-                    acc.y += v.y;
-                    acc.z += v.z;
-                    acc.w += v.w;
-                } else {
-                    bad = true;
-                }
-            }
-            reinterpret_cast<uint4 *>(acc_s)[bag * LANES + sl] = acc;
-        }
-    }
-    if (bad && !(flags & kDescSharded))
-        atomicOr(err_flag, 1u);
-    __syncwarp();
-
-    const uint32_t bpr = d->bags_per_rank;
-    const uint32_t out_stride = d->out_stride;
-#pragma unroll
-    for (int it = 0; it < WB / SUB; it++) {
-        const uint32_t bag = it * SUB + sub;
-        if (bag >= nb)
-            break;
-        uint4 o = reinterpret_cast<const uint4 *>(acc_s)[bag * LANES + sl];
-        if (!(flags & kDescRaw))  // post_process, emb_host.h:210
-            o = make_uint4(__float_as_uint(dequant(o.x)), __float_as_uint(dequant(o.y)),
-                           __float_as_uint(dequant(o.z)), __float_as_uint(dequant(o.w)));
-        const uint32_t b = b0 + bag;
-        uint32_t *obase;
-        uint32_t row;
-        if (bpr) {
-            uint32_t rk = b / bpr;
-            obase = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
-            row = b - rk * bpr;
-        } else {
-            obase = reinterpret_cast<uint32_t *>(d->out);
-            row = b;
-        }
-        uint32_t *dst = obase + (size_t)row * out_stride + sl * 4;
-        if (flags & kDescVecStore) {
-            stg_stream16(dst, o);
-        } else {
-            dst[0] = o.x;
-            dst[1] = o.y;
-            dst[2] = o.z;
-            dst[3] = o.w;
         }
     }
 }
