@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- embedding lookups/s of the sum-pool hot path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c4|c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c3|c4|c5|c4tb]
 
 One "step" = one pass of the hot path over one batch: every local table pools its B bags.
 N=1 workload = BASELINE.json configs[1] ("c2"): 26 tables x 1M rows x dim 16, batch 65536,
@@ -13,10 +13,15 @@ pooling kernel over NVLink peer memory (--exchange fused, default) or by one NCC
 all_to_all_single (--exchange nccl).
 
 Numbers: `value` = lookups/s with inputs resident in HBM (CUDA events, max over ranks);
-`e2e` = the same through the host-pointer C-ABI call (emb_lookup_ex: pinned host buffers,
-H2D + kernel + D2H inside the timed region); `roofline` = algorithmic bytes of one pooling
-launch / its mean CUDA-event duration against MEASURED_PEAKS.json; `cpu_baseline` = the
-oracle port (multi-threaded C) on this box's host cores, N=1 only.
+`e2e` = the same from HOST buffers: at N=1 through the host-pointer C-ABI call (emb_lookup_ex), at
+N>1 through the sharded product path (pinned indices -> HBM, pooling launch, peer-slab exchange,
+completion kernel, [B/N, T, D] rows -> pinned host); `roofline` = algorithmic bytes of one pooling
+launch / its CUDA-event duration against MEASURED_PEAKS.json; `cpu_baseline` = the reference's CPU
+path and the oracle port on this box's host cores, N=1 only; `parity` = every pooled row of one batch
+compared bit for bit, on every rank, with a torch index_select / index_add_ restatement computed on the
+rank that owns the table (the run exits non-zero on a mismatch); `extra` = the same measurement on the
+other multi-GPU configs of BASELINE.json (c4tb: Terabyte cardinalities, table + row-wise sharded,
+strong scaling; c5: RM2-like skew) so that they land in the driver's records.
 `--impl reference` times the CPU implementation alone (see DESIGN.md "Reference arm").
 """
 from __future__ import annotations
@@ -43,12 +48,12 @@ WORKLOADS = {
     # configs[4], RM2-like: dim 128, pooling 80, Zipf indices
     "c5": dict(name="RM2-like: 32 tables x 500k rows x dim 128, batch 4096, pooling 80, zipf(1.05) indices",
                T=32, R=500_000, D=128, B=4096, pool=(80, 80), dist="zipf"),
-    # configs[3] shape per GPU (dim 64): uniform, fixed pooling 10
     # configs[2] lookup shape: Kaggle cardinalities (tools/visualize.py:949), dim 16, batch 39292, one index per bag
     "c3": dict(name="Kaggle-cardinality tables x dim 16, batch 39292, pooling 1, uniform indices", T=26, R=10131227,
                rows=[1460, 583, 10131227, 2202608, 305, 24, 12517, 633, 3, 93145, 5683, 8351593, 3194, 27, 14992,
                      5461306, 10, 5652, 2173, 4, 7046547, 18, 15, 286181, 105, 142572],
                D=16, B=39292, pool=(1, 1), dist="uniform"),
+    # configs[3] shape per GPU (dim 64): uniform, fixed pooling 10
     "c4": dict(name="dim-64 tables: 26 x 1M rows x dim 64, batch 65536, pooling 10, uniform indices",
                T=26, R=1_000_000, D=64, B=65536, pool=(10, 10), dist="uniform"),
     # configs[3]: Criteo Terabyte cardinalities (tools/visualize.py:964), dim 64, 48 GB of
@@ -62,7 +67,7 @@ WORKLOADS = {
 N_BATCHES = 4  # distinct index batches rotated through the timed steps
 
 
-def parse_args():
+def parse_args(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
@@ -76,15 +81,35 @@ def parse_args():
                     help="fused exchange: every rank walks the destination ranks in the same order (comparator)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the bit-exact check of one batch on every rank")
+    ap.add_argument("--extras", default="auto",
+                    help="comma-separated workloads measured after the main one and reported under `extra` "
+                         "(auto = c4tb,c5 when the main workload is c2; none = skip)")
+    ap.add_argument("--dtype", default="int32", choices=["int32", "f32"],
+                    help="table element kind: int32 fixed point (the DPU representation) or fp32 (the CPU path)")
+    ap.add_argument("--max-table-bytes", type=float, default=0.0,
+                    help="sharded workloads: largest slab kept whole (forces row cuts below the 10 GB tables)")
     ap.add_argument("--variant", type=int, default=0, help="kernel variant (emb_set_tuning); 0 = default")
     ap.add_argument("--unroll", type=int, default=0)
     ap.add_argument("--mult", type=int, default=0)
-    return ap.parse_args()
+    return ap.parse_args(argv)
 
 
 # ---------------------------------------------------------------------------------------------
 # synthetic inputs: seeded NumPy on the host
 # ---------------------------------------------------------------------------------------------
+
+def reference_bag_indices(R, P, ra):
+    """One bag of the reference's uniform generator, dlrm_data_pytorch.py:1061-1065 (generate_uniform_input_batch,
+    fixed pooling): `r = ra.random(P); sparse_group = np.round(r * (R - 1)).astype(np.int64)` with a seeded
+    np.random.RandomState; duplicates are kept (:1065, the np.unique is commented out).  Pinned against the
+    reference's own function by tests/test_generator.py.  bench.make_batch below draws with
+    default_rng.integers(0, R) instead: same support {0..R-1}, but the reference's rounding gives the two end
+    rows half the probability of the others (a 1-in-R effect, irrelevant to throughput), and a vectorised
+    draw of 17.9 M indices takes 0.2 s where the per-bag loop takes minutes."""
+    r = ra.random(P)
+    return np.round(r * (R - 1)).astype(np.int64)
+
 
 def make_batch(w, seed, n_tables=None):
     """One batch for n_tables tables: lists of uint32 indices [L_t] and offsets [B]."""
@@ -108,9 +133,40 @@ def make_batch(w, seed, n_tables=None):
     return idx, off
 
 
+def make_table_batch(w, t, seed):
+    """(indices, offsets) of global table t for one global batch; the same on every rank."""
+    rng = np.random.default_rng([seed, t])
+    lo, hi = w["pool"]
+    lens = rng.integers(lo, hi + 1, size=w["B"])
+    off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.uint32)
+    idx = rng.integers(0, w["rows"][t], size=int(lens.sum()), dtype=np.int64).astype(np.uint32)
+    return idx, off
+
+
 def algorithmic_bytes(n_lookups, n_bags, D):
     # SURVEY.md 8d: per lookup 4D (row) + 4 (index); per bag 4D (output row) + 4 (offset)
     return (n_lookups + n_bags) * (4 * D + 4)
+
+
+def job_config(w, world, args, sharded):
+    """`config` of the JSON line: what the job IS.  Identical in the B200 arm and the reference arm (the driver
+    compares them); everything that describes HOW an arm ran it lives in other keys."""
+    cfg = {"workload": w["name"], "tables": w["T"], "dim": w["D"], "global_batch": w["B"],
+           "pooling": list(w["pool"]), "index_distribution": w["dist"], "dtype": args.dtype,
+           "index_batches": N_BATCHES,
+           "l2": "no flush between steps: inputs larger than L2 (tables %.2f GB per GPU >> 126 MB, %d rotating index "
+                 "batches of %.0f MB); ncu's cold-cache launch time agrees with the warm event time within 1.5 %% "
+                 "(profiles/r2_launches.txt)" % (
+                     (sum(w.get("rows", [w["R"]] * w["T"])) * w["D"] * 4 / 1e9) / (world if sharded else 1), N_BATCHES,
+                     w["T"] * w["B"] * (w["pool"][0] + w["pool"][1]) / 2 * 4 / 1e6),
+           "parallelism": (f"table-wise + row-wise over {world} rank(s), global batch fixed (strong scaling)" if sharded else
+                           f"table-wise x{world}: every rank owns {w['T']} such tables and pools the whole batch for them "
+                           "(weak scaling); pooled rows to the sample's rank")}
+    if "rows" in w:
+        cfg["rows_per_table"] = "per-table cardinalities, max %d, total %d" % (max(w["rows"]), sum(w["rows"]))
+    else:
+        cfg["rows_per_table"] = w["R"]
+    return cfg
 
 
 # ---------------------------------------------------------------------------------------------
@@ -137,7 +193,8 @@ class ClockSampler:
         nv = self.nv
         while not self._stop:
             try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+                self.samples.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM), util))
                 bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
                 for b, name in self.REASONS.items():
                     if bits & b and name != "gpu_idle":
@@ -160,9 +217,10 @@ class ClockSampler:
     def summary(self):
         if not self.nv:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "error": self.err}
-        s = sorted(self.samples)
-        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons), "samples": len(s)}
+        s = sorted(c for c, _ in self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "sm_mhz_min": s[0] if s else None,
+                "reasons": sorted(self.reasons), "samples": len(s),
+                "window": "warm-up + timed steps + e2e steps (the timed steps alone last a few ms: one NVML sample)"}
 
 
 def load_peaks():
@@ -170,6 +228,13 @@ def load_peaks():
     if os.path.exists(p):
         return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def dist_summary(ms):
+    """mean / median / p10 / p90 of per-launch durations (SURVEY.md 8d asks for the spread, not only the mean)."""
+    a = np.sort(np.asarray(ms, dtype=np.float64))
+    q = lambda f: float(a[min(len(a) - 1, int(round(f * (len(a) - 1))))])  # noqa: E731
+    return {"mean": float(a.mean()), "median": q(0.5), "p10": q(0.1), "p90": q(0.9), "min": float(a[0]), "n": len(a)}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -197,27 +262,31 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def time_torch_embeddingbag(tables_f32, idx, off, budget_s=10.0):
-    """The reference's CPU path: nn.EmbeddingBag(mode="sum") per table (dlrm_s_pytorch.py:483-488)."""
+def torch_bags(tables_f32, idx, off):
+    """The reference's CPU path: nn.EmbeddingBag(mode="sum", sparse=True) per table, fp32 tables, int64 indices /
+    offsets (dlrm_s_pytorch.py:295,483-488).  Returns a function that runs one pass over all tables."""
     import torch
-    torch.set_num_threads(host_cores())
-    bags = [torch.nn.EmbeddingBag.from_pretrained(torch.from_numpy(w), mode="sum", freeze=True) for w in tables_f32]
+    bags = [torch.nn.EmbeddingBag.from_pretrained(torch.from_numpy(x), mode="sum", sparse=True, freeze=True)
+            for x in tables_f32]
     ti = [torch.from_numpy(i.astype(np.int64)) for i in idx]
     to = [torch.from_numpy(o.astype(np.int64)) for o in off]
-    n = sum(len(i) for i in idx)
 
     def one():
         with torch.no_grad():
             for k, e in enumerate(bags):
                 e(ti[k], to[k])
+    return one
+
+
+def time_passes(one, n_lookups, budget_s, min_reps=2, max_reps=50):
     one()
     reps, t_tot = 0, 0.0
-    while reps < 2 or (t_tot < budget_s and reps < 50):
+    while reps < min_reps or (t_tot < budget_s and reps < max_reps):
         t0 = time.perf_counter()
         one()
         t_tot += time.perf_counter() - t0
         reps += 1
-    return n * reps / t_tot, torch.get_num_threads(), reps
+    return n_lookups * reps / t_tot, reps
 
 
 def host_tables(w, n_tables, seed=1234):
@@ -229,60 +298,66 @@ def host_tables(w, n_tables, seed=1234):
 
 
 def run_reference(args, w):
-    """--impl reference: the CPU implementation alone, all host threads, bounded sample."""
+    """--impl reference: the reference's CPU implementation of the path alone (nn.EmbeddingBag(mode=sum) per table
+    on stock torch, dlrm_s_pytorch.py:295,483-488), all host threads, the same job `config` as the B200 arm.
+    A step is one pass over ALL tables of one rank's batch (26 x 65536 bags for c2, ~25 ms), so nothing is
+    sampled for the default workload; the sharded 48 GB workload takes the tables that are cheap to build."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    # bounded sample of the workload: the first T_s tables of one batch (same shapes and
-    # distributions as the GPU arm); each step = one pass over the sample
-    T_s = min(w["T"], 8)
+    world = args.gpus
+    cfg = job_config(w, world, args, bool(w.get("sharded")))
+    scaling = "strong" if w.get("sharded") else "weak"
+    T_s = w["T"]
+    sample_note = f"all {w['T']} tables of one rank's batch"
     if w.get("sharded"):
         # the 40M-row tables are 10 GB each (plus an fp32 copy): the bounded sample takes the largest
         # table that is cheap to build on the host (2.95M rows, 756 MB) and seven smaller ones
         pick = [10, 22, 11, 1, 4, 2, 23, 14]
         w = dict(w, rows=[w["rows"][t] for t in pick], T=len(pick))
+        T_s = len(pick)
+        sample_note = f"{T_s} of 26 tables (the 10 GB ones are left out)"
     tabs = host_tables(w, T_s)
     idx, off = make_batch(w, seed=123, n_tables=T_s)
     import torch
     # torchrun exports OMP_NUM_THREADS=1; the reference arm uses every host core it may run on
     torch.set_num_threads(host_cores())
     n = sum(len(i) for i in idx)
-    # the reference's CPU path: nn.EmbeddingBag(mode="sum", sparse=True) per table, fp32 tables,
-    # int64 indices/offsets (dlrm_s_pytorch.py:295,483-488), all host threads
     ftabs = [t.astype(np.float32) * np.float32(1e-9) for t in tabs]
-    bags = [torch.nn.EmbeddingBag.from_pretrained(torch.from_numpy(x), mode="sum", sparse=True, freeze=True)
-            for x in ftabs]
-    ti = [torch.from_numpy(i.astype(np.int64)) for i in idx]
-    to = [torch.from_numpy(o.astype(np.int64)) for o in off]
-
-    def one():
-        with torch.no_grad():
-            for k, e in enumerate(bags):
-                e(ti[k], to[k])
+    one = torch_bags(ftabs, idx, off)
     for _ in range(max(1, min(args.warmup, 5))):
         one()
     steps = max(1, min(args.steps, 200))
     t0 = time.perf_counter()
     done = 0
-    while done < steps and (done < 3 or time.perf_counter() - t0 < 20.0):
+    while done < steps and (done < 3 or time.perf_counter() - t0 < 30.0):
         one()
         done += 1
     dt = time.perf_counter() - t0
     steps = done
     val = n * steps / dt
-    pv, pcores, _ = time_oracle_port(tabs, idx, off, budget_s=6.0)
-    sample = f"{T_s} of {w['T']} tables x {w['B']} bags ({n} lookups) per step, {steps} steps"
+    cores = torch.get_num_threads()
+    # one thread, for reference (SURVEY.md 8d): a quarter of the tables, a few passes
+    torch.set_num_threads(1)
+    T1 = max(1, T_s // 4)
+    one1 = torch_bags(ftabs[:T1], idx[:T1], off[:T1])
+    v1, reps1 = time_passes(one1, sum(len(i) for i in idx[:T1]), budget_s=4.0, min_reps=1, max_reps=5)
+    torch.set_num_threads(cores)
+    pv, pcores, _ = time_oracle_port(tabs[:8], idx[:8], off[:8], budget_s=4.0)
+    sample = f"{sample_note} x {w['B']} bags ({n} lookups) per step, {steps} steps"
     print(json.dumps({
         "impl": "reference", "metric": "embedding lookups/sec", "value": val, "unit": "lookups/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": dt / steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": w["name"], "sample": sample},
-        "cpu_baseline": {"value": val, "unit": "lookups/s", "cores": torch.get_num_threads(), "kind": "reference",
-                         "sample": sample,
-                         "what": "the reference's CPU lookup path restated call for call: nn.EmbeddingBag(mode=sum) "
-                                 "per table on stock torch (dlrm_s_pytorch.py:295,483-488); its DPU path "
-                                 "(oracle/_ref) is undefined at this shape (B<=512, T*D<=256; SURVEY.md Q3/Q4/Q13)",
-                         "oracle_port": {"value": pv, "unit": "lookups/s", "cores": pcores,
+        "higher_is_better": True, "scaling": scaling,
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+        "cpu_baseline": {"value": val, "unit": "lookups/s", "cores": cores, "kind": "reference", "sample": sample,
+                         "what": "the reference's CPU lookup path restated call for call: nn.EmbeddingBag(mode=sum, "
+                                 "sparse=True) per table on stock torch, fp32 tables, int64 indices "
+                                 "(dlrm_s_pytorch.py:295,483-488); its DPU path (oracle/_ref) is undefined at this shape "
+                                 "(B<=512, T*D<=256; SURVEY.md Q3/Q4/Q13)",
+                         "single_thread": {"value": v1, "unit": "lookups/s", "cores": 1,
+                                           "sample": f"{T1} tables x {reps1} passes"},
+                         "oracle_port": {"value": pv, "unit": "lookups/s", "cores": pcores, "sample": "8 tables",
                                          "what": "fixed-point restatement (oracle/emb_oracle.c), multi-threaded C"}},
         "e2e": {"value": val, "unit": "lookups/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -290,47 +365,155 @@ def run_reference(args, w):
 
 
 # ---------------------------------------------------------------------------------------------
-# GPU arm
+# GPU arm helpers
 # ---------------------------------------------------------------------------------------------
 
-def pinned_u32(lib, n):
-    """n uint32 of cudaHostAlloc memory as a NumPy array (emb_host_alloc)."""
+def pinned_arena(lib, nbytes):
+    """nbytes of cudaHostAlloc memory (emb_host_alloc) as a NumPy uint8 array; one arena per call so that the
+    arrays of consecutive tables are adjacent in host memory (the library then moves them with one copy per
+    group instead of one per table)."""
     p = C.c_void_p()
-    rc = lib.emb_host_alloc(C.byref(p), max(4 * n, 4))
-    if rc:
+    if lib.emb_host_alloc(C.byref(p), max(int(nbytes), 64)):
         raise RuntimeError("emb_host_alloc failed")
-    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint32)), shape=(n,))
+    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(max(int(nbytes), 64),))
 
 
-def run_b200(args, w):
+def carve_u32(arena, pos, n):
+    """n uint32 at byte offset pos of the arena (16-byte aligned start); returns (array, next offset)."""
+    pos = (pos + 15) // 16 * 16
+    return arena[pos:pos + 4 * n].view(np.uint32), pos + 4 * n
+
+
+def table_tensor(lib, slot, D, dtype):
+    """The library's slab of a table slot as a torch tensor [rows, D] (no copy)."""
+    import torch
+
+    from pim_embedding_lookup_b200 import emblib, exchange
+    rows, kind, ptr = C.c_uint64(), C.c_int(), C.c_void_p()
+    emblib.check(lib.emb_table_info(slot, C.byref(rows), C.byref(kind), C.byref(ptr)), "emb_table_info")
+    return torch.as_tensor(exchange._DevView(ptr.value, (rows.value, D), "<i4" if dtype == "int32" else "<f4"),
+                           device="cuda")
+
+
+def torch_pooled(tab, idx, off, B, row_lo=0, raw=False):
+    """What the path must produce for one table, restated with stock torch ops on the GPU -- none of this
+    repo's kernels: gather with index_select, segment sums with index_add_ (int32 adds wrap; fp32 tables are
+    added in fp64 and rounded once), then the reference's dequantise (emb_host.h:210) as an fp32 divide.
+    tab: [rows, D] holding global rows [row_lo, row_lo + rows); idx / off: uint32 bits carried as int32.
+    Returns fp32 [B, D] (raw=True: the int32 sums)."""
+    import torch
+    idx64 = idx.to(torch.int64) & 0xffffffff
+    L = idx64.numel()
+    starts = off.to(torch.int64) & 0xffffffff
+    starts[0] = 0  # emb_dpu_lookup.c:60-63
+    bag_of = torch.searchsorted(starts, torch.arange(L, device=idx.device), right=True) - 1
+    rel = idx64 - row_lo
+    keep = (rel >= 0) & (rel < tab.shape[0])
+    if not bool(keep.all()):
+        rel, bag_of = rel[keep], bag_of[keep]
+    if tab.dtype == torch.float32:
+        sums = torch.zeros((B, tab.shape[1]), dtype=torch.float64, device=tab.device)
+        sums.index_add_(0, bag_of, tab.index_select(0, rel).to(torch.float64))
+        return sums.to(torch.float32)
+    sums = torch.zeros((B, tab.shape[1]), dtype=torch.int32, device=tab.device)
+    sums.index_add_(0, bag_of, tab.index_select(0, rel))
+    if raw:
+        return sums
+    return sums.to(torch.float32) / torch.tensor(1e9, dtype=torch.float32, device=tab.device)
+
+
+def compare_rows(got, want, mag=None):
+    """Number of mismatching elements.  Fixed-point path (mag is None): the bits must be equal.  fp32 tables: within
+    1e-5 of the fp64-accumulated sum relative to `mag`, the sum of the magnitudes of the bag's rows (north_star's
+    reassociation tolerance; an fp32 sum of n terms in any order is within (n-1) * 6e-8 of it)."""
+    import torch
+    if mag is None:
+        return int((got.contiguous().view(torch.int32) != want.contiguous().view(torch.int32)).sum().item())
+    return int(((got - want).abs() > 1e-5 * mag + 1e-30).sum().item())
+
+
+def reduce_over_ranks(vals, world, ops):
+    """vals: list of floats; ops: parallel list of 'max' / 'sum' / 'min'.  All-reduce over the ranks."""
+    if world == 1:
+        return list(vals)
+    import torch
+    import torch.distributed as dist
+    out = []
+    t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+    for op, name in ((dist.ReduceOp.MAX, "max"), (dist.ReduceOp.SUM, "sum"), (dist.ReduceOp.MIN, "min")):
+        if name in ops:
+            r = t.clone()
+            dist.all_reduce(r, op=op)
+            out.append((name, r))
+    res = []
+    for i, op in enumerate(ops):
+        res.append(float(dict(out)[op][i]))
+    return res
+
+
+def measure_copy_floor(h2d_bytes, d2h_bytes, world, reps=8):
+    """Plain concurrent pinned H2D + D2H of a step's byte counts, one big copy each way, on every rank at the same
+    time: what the box's PCIe gives these bytes whatever the code around them does."""
+    import torch
+    import torch.distributed as dist
+    hin = torch.empty(max(h2d_bytes, 4) // 4, dtype=torch.int32).pin_memory()
+    din = torch.empty_like(hin, device="cuda")
+    dout = torch.empty(max(d2h_bytes, 4) // 4, dtype=torch.int32, device="cuda")
+    hout = torch.empty(dout.shape, dtype=torch.int32).pin_memory()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def one():
+        with torch.cuda.stream(s1):
+            din.copy_(hin, non_blocking=True)
+        with torch.cuda.stream(s2):
+            hout.copy_(dout, non_blocking=True)
+        s1.synchronize()
+        s2.synchronize()
+    for _ in range(2):
+        one()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        one()
+    dt = (time.perf_counter() - t0) / reps
+    (dt,) = reduce_over_ranks([dt], world, ["max"])
+    return dt * 1e3
+
+
+# ---------------------------------------------------------------------------------------------
+# table-wise arm: every rank owns T tables and pools the whole batch for them (weak scaling)
+# ---------------------------------------------------------------------------------------------
+
+def bench_tablewise(args, w, steps, warmup):
     import torch
     import torch.distributed as dist
 
     from pim_embedding_lookup_b200 import emblib, exchange
-    from pim_embedding_lookup_b200.dputypes import EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED, EMB_TABLE_FIXED
+    from pim_embedding_lookup_b200.dputypes import EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED, EMB_TABLE_FIXED, EMB_TABLE_FLOAT
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = emblib.load()
     T, R, D, B = w["T"], w["R"], w["D"], w["B"]
+    is_float = args.dtype == "f32"
     emblib.configure(T, D, 0, 0, device=local)
     emblib.check(lib.emb_set_tuning(args.variant, args.unroll, args.mult))
     stream = torch.cuda.Stream()  # a real stream: events and launches are ordered on it
     torch.cuda.set_stream(stream)
 
-    # tables: int32 fixed point as export_emb makes them, generated on the device
+    # tables: int32 fixed point as export_emb makes them (or fp32 U(+-1/sqrt(R))), generated on the device
     gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
     rows_t = w.get("rows", [R] * T)
     for t in range(T):
         lim = int(1e9 / np.sqrt(rows_t[t]))
         a = torch.randint(-lim, lim + 1, (rows_t[t], D), dtype=torch.int32, device="cuda", generator=gen)
-        emblib.check(lib.emb_populate_table_device(t, rows_t[t], a.data_ptr(), 0, EMB_TABLE_FIXED, stream.cuda_stream))
+        if is_float:
+            a = a.to(torch.float32) * 1e-9
+        emblib.check(lib.emb_populate_table_device(t, rows_t[t], a.data_ptr(), 1 if is_float else 0,
+                                                   EMB_TABLE_FLOAT if is_float else EMB_TABLE_FIXED, stream.cuda_stream))
         del a
     torch.cuda.empty_cache()
 
@@ -342,37 +525,47 @@ def run_b200(args, w):
         dev_batches.append(([torch.from_numpy(i.view(np.int32)).cuda() for i in idx],
                             [torch.from_numpy(o.view(np.int32)).cuda() for o in off]))
 
-    # outputs + plans (descriptors uploaded once; a step is one kernel launch)
+    # outputs + plans (descriptors uploaded once; a step is one kernel launch).  The peer slabs are double
+    # buffered: batch k lands in buffer k % 2, so a peer may already store batch k+1 while this rank's consumer
+    # still reads batch k -- the configuration a real caller needs (sharded.ShardedTables does the same).
     slabs = None
     if world > 1 and args.exchange == "fused":
-        slabs = exchange.PeerSlabs(B, [T] * world, D, layout=args.layout)
+        slabs = exchange.PeerSlabs(B, [T] * world, D, layout=args.layout, n_buffers=2)
     per = B // world
-    plans, keep = [], []
-    for k, (di, do) in enumerate(dev_batches):
+
+    def make_plan(di, do, buffer):
         qs = []
+        keep = None
         if slabs is not None:
             for t in range(T):
                 qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=None, out_stride=slabs.stride,
-                               bags_per_rank=per, out_peer=slabs.out_peer(t),
+                               bags_per_rank=per, out_peer=slabs.out_peer(t, buffer),
                                bag_rotate=0 if args.no_rotate else rank * per))
         elif world > 1:  # nccl: send buffer [N, B/N, T_local, D] == bag-major rows of stride T*D
-            buf = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
-            keep.append(buf)
+            keep = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
             for t in range(T):
-                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=buf[:, t, :], out_stride=T * D))
+                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=keep[:, t, :], out_stride=T * D))
         else:  # the reference's layout: one [B, D] result per table (emb_host.h:207-212)
-            buf = torch.empty((T, B, D), dtype=torch.float32, device="cuda")
-            keep.append(buf)
+            keep = torch.empty((T, B, D), dtype=torch.float32, device="cuda")
             for t in range(T):
-                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=buf[t]))
-        plans.append(emblib.Plan(qs))
+                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=keep[t]))
+        return emblib.Plan(qs), keep
+
+    plans, keep = [], []
+    for k, (di, do) in enumerate(dev_batches):
+        p, buf = make_plan(di, do, k % 2)
+        plans.append(p)
+        keep.append(buf)
 
     def step(k):
+        """One step; returns this rank's result tensor [B/N, T_global, D] (N = 1: [T, B, D])."""
         plans[k % N_BATCHES].launch(stream)
         if slabs is not None:
             slabs.barrier()
-        elif world > 1:
-            exchange.nccl_all_to_all(keep[k % N_BATCHES], B, [T] * world, D)
+            return slabs.local_sample_major((k % N_BATCHES) % 2)
+        if world > 1:
+            return exchange.nccl_all_to_all(keep[k % N_BATCHES], B, [T] * world, D)
+        return keep[k % N_BATCHES]
 
     def sync_all():
         torch.cuda.synchronize()
@@ -380,40 +573,74 @@ def run_b200(args, w):
             dist.barrier()
             torch.cuda.synchronize()
 
-    for k in range(max(args.warmup, 3)):
+    for k in range(max(warmup, 3)):
         step(k)
     sync_all()
     if lib.emb_check_indices():
         raise RuntimeError("out-of-range index in the synthetic batch")
 
-    K = args.steps
+    # ---- parity: every pooled row of one batch, on every rank, against stock torch ops on the owning rank
+    parity = {"checked": False}
+    if not args.no_parity:
+        kb = 1  # batch 1 lands in slab buffer 1: the double buffering is part of what is checked
+        got = step(kb).clone()
+        sync_all()
+        di, do = dev_batches[kb]
+        tabs = [table_tensor(lib, t, D, args.dtype) for t in range(T)]
+        def routed(fn):
+            """fn(t) -> [B, D] for local table t; returns what this rank must hold: [T, B, D] (N = 1) or, after the
+            reference's butterfly (extend_distributed.py:389-426) done with NCCL, [B/N, T_global, D]."""
+            if world == 1:
+                return torch.stack([fn(t) for t in range(T)])
+            send = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
+            for t in range(T):
+                send[:, t, :] = fn(t)
+            return exchange.nccl_all_to_all(send, B, [T] * world, D)
+        want = routed(lambda t: torch_pooled(tabs[t], di[t], do[t], B))
+        mag = routed(lambda t: torch_pooled(tabs[t].abs(), di[t], do[t], B)) if is_float else None
+        bad = compare_rows(got, want, mag)
+        del mag
+        # checksum of checksums (wrap-around sum of the raw bits of every row this rank received)
+        chk_got = int(got.contiguous().view(torch.int32).to(torch.int64).sum().item()) & 0xffffffffffffffff
+        chk_want = int(want.contiguous().view(torch.int32).to(torch.int64).sum().item()) & 0xffffffffffffffff
+        rows_checked = got.numel() // D
+        bad_all, rows_all = reduce_over_ranks([float(bad), float(rows_checked)], world, ["sum", "sum"])
+        idx_err = lib.emb_check_indices()
+        parity = {"checked": True, "ranks": world, "rows_checked": int(rows_all), "mismatching_elements": int(bad_all),
+                  "bit_exact": bool(bad_all == 0) if not is_float else None,
+                  "within_1e-5_relative": bool(bad_all == 0) if is_float else None,
+                  "checksum_of_checksums_equal": chk_got == chk_want, "index_errors": int(idx_err),
+                  "against": "torch index_select + index_add_ + fp32 divide on the rank that owns each table, routed with "
+                             "NCCL all_to_all_single (extend_distributed.py:389-426; emb_dpu_lookup.c:106-116, "
+                             "emb_host.h:207-212)"}
+        del got, want, tabs
+        torch.cuda.empty_cache()
+        if bad_all or chk_got != chk_want or idx_err:
+            raise SystemExit(f"PARITY FAILURE on rank {rank}: {json.dumps(parity)}")
+
+    K = steps
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = emblib.launch_count()
-    with ClockSampler(local) as clk:
-        sync_all()
-        e0.record(stream)
-        for k in range(K):
-            ev[k][0].record(stream)
-            plans[k % N_BATCHES].launch(stream)
-            ev[k][1].record(stream)
-            if slabs is not None:
-                slabs.barrier()
-            elif world > 1:
-                exchange.nccl_all_to_all(keep[k % N_BATCHES], B, [T] * world, D)
-        e1.record(stream)
-        sync_all()
+    sync_all()
+    e0.record(stream)
+    for k in range(K):
+        ev[k][0].record(stream)
+        plans[k % N_BATCHES].launch(stream)
+        ev[k][1].record(stream)
+        if slabs is not None:
+            slabs.barrier()
+        elif world > 1:
+            exchange.nccl_all_to_all(keep[k % N_BATCHES], B, [T] * world, D)
+    e1.record(stream)
+    sync_all()
     gpu_launches = emblib.launch_count() - launches0
     total_ms = e0.elapsed_time(e1)
-    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    kdist = dist_summary([a.elapsed_time(b) for a, b in ev])
+    kernel_ms = kdist["mean"]
     n_lookups = sum(lookups[k % N_BATCHES] for k in range(K))
-    t = torch.tensor([total_ms, float(n_lookups), kernel_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        tmax = t.clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone()
-        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        total_ms, n_lookups, kernel_ms = float(tmax[0]), float(tsum[1]), float(tmax[2])
+    total_ms, n_lookups, kernel_ms_max = reduce_over_ranks([total_ms, float(n_lookups), kernel_ms], world,
+                                                           ["max", "sum", "max"])
     value = n_lookups / (total_ms * 1e-3)
 
     # roofline of the pooling kernel on this rank (algorithmic bytes / mean launch duration)
@@ -424,125 +651,204 @@ def run_b200(args, w):
     # DRAM traffic of the same kernel from the committed ncu capture (per launch), if there is one
     traffic, traffic_src = None, None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
-    if world == 1 and os.path.exists(tp):
-        rec = json.load(open(tp)).get(args.workload)
+    if world == 1 and os.path.exists(tp) and not is_float:
+        rec = json.load(open(tp)).get(args.workload if w is WORKLOADS.get(args.workload) else None)
         if rec:
             traffic = rec["dram_bytes_read_per_launch"] + rec["dram_bytes_write_per_launch"]
             traffic_src = rec["source"]
 
-    # ---- e2e: the host-pointer C-ABI call, pinned host buffers, copies inside the timed region
+    # ---- e2e from HOST buffers, copies inside the timed region
     e2e = None
     if not args.no_e2e:
-        host = []
-        for idx, off in batches[:2]:
-            hi = [pinned_u32(lib, len(i)) for i in idx]
-            ho = [pinned_u32(lib, len(o)) for o in off]
-            for a, b in zip(hi + ho, idx + off):
-                a[:] = b
-            host.append((hi, ho))
-        res = [pinned_u32(lib, B * D).view(np.float32).reshape(B, D) for _ in range(T)]
-        # pointer arrays built once per batch, as the reference's caller does (dlrm_dpu_pytorch.py:1028-1051)
-        calls = [emblib.HostCall(hi, ho, res) for hi, ho in host]
-
-        def time_e2e(n_steps):
-            for k in range(3):
-                calls[k % 2]()
-            sync_all()
-            t0 = time.perf_counter()
-            for k in range(n_steps):
-                calls[k % 2]()  # emb_lookup_ex: synchronous, the results are in host memory on return
-            dt = time.perf_counter() - t0
-            tm = emblib.last_timings()
-            n_e = sum(lookups[k % 2] for k in range(n_steps))
-            if world > 1:
-                te = torch.tensor([dt, float(n_e)], dtype=torch.float64, device="cuda")
-                a = te.clone()
-                dist.all_reduce(a, op=dist.ReduceOp.MAX)
-                b = te.clone()
-                dist.all_reduce(b, op=dist.ReduceOp.SUM)
-                dt, n_e = float(a[0]), float(b[1])
-            return n_e / dt, dt / n_steps * 1e3, tm
-
-        PATHS = {1: "staged: cudaMemcpyAsync in, kernel, cudaMemcpyAsync out, pipelined over table groups",
-                 2: "mapped: one launch, the kernel reads indices/offsets and writes pooled rows over PCIe",
-                 3: "inputs staged by the copy engine, pooled rows written to the host arrays by the kernel's "
-                    "store epilogue over PCIe, pipelined over table groups"}
         Ke = max(3, min(K, 50))
-        v, ms, tm = time_e2e(Ke)  # default path (EMB_HOST_AUTO) on page-locked arrays
-        e2e = {"value": v, "unit": "lookups/s", "h2d_bytes_per_step": int(tm.h2d_bytes),
-               "d2h_bytes_per_step": int(tm.d2h_bytes), "ms_per_step": ms, "steps": Ke,
-               "call": "emb_lookup_ex (host pointers in page-locked memory), per rank", "path": PATHS[int(tm.path)],
-               "last_call_ms": {"h2d": tm.h2d_ms, "kernel": tm.kernel_ms, "d2h": tm.d2h_ms, "total": tm.total_ms},
-               "other_paths": {}}
-        for forced in (EMB_HOST_COPY, EMB_HOST_MAPPED):
-            emblib.set_host_path(forced)
-            v2, ms2, tm2 = time_e2e(max(3, Ke // 5))
-            e2e["other_paths"][PATHS[forced].split(":")[0]] = {"value": v2, "ms_per_step": ms2}
-        emblib.set_host_path(EMB_HOST_AUTO)
+        if world == 1:
+            e2e = e2e_host_call(args, lib, emblib, batches, lookups, T, B, D, Ke,
+                                (EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED))
+        else:
+            e2e = e2e_sharded_path(args, lib, emblib, exchange, slabs, batches, lookups, T, B, D, per, rank, world,
+                                   Ke, stream, sync_all)
+        e2e["floor_ms"] = measure_copy_floor(e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"], world)
+        e2e["floor_what"] = ("one pinned H2D copy and one D2H copy of the step's bytes running concurrently, on all "
+                             f"{world} rank(s) at once (max over ranks)")
 
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        import torch as _t
         T_s = min(T, 8)
-        tabs = [emblib.table_read(t, 0, rows_t[t]) for t in range(T_s)]
+        tabs = [emblib.table_read(t, 0, rows_t[t], dtype=np.float32 if is_float else np.int32) for t in range(T_s)]
         sidx, soff = batches[0][0][:T_s], batches[0][1][:T_s]
-        ftabs = [x.astype(np.float32) * np.float32(1e-9) for x in tabs]
-        tv, tth, treps = time_torch_embeddingbag(ftabs, sidx, soff)
-        sample = f"{T_s} of {T} tables x {B} bags ({sum(len(i) for i in sidx)} lookups) x {treps} passes"
-        cpu = {"value": tv, "unit": "lookups/s", "cores": tth, "kind": "reference", "sample": sample,
-               "what": "nn.EmbeddingBag(mode=sum) per table, fp32, stock torch (dlrm_s_pytorch.py:295,483-488)"}
-        v, cores, reps = time_oracle_port(tabs, sidx, soff, budget_s=6.0)
-        cpu["oracle_port"] = {"value": v, "unit": "lookups/s", "cores": cores, "passes": reps, "kind": "port"}
+        ftabs = tabs if is_float else [x.astype(np.float32) * np.float32(1e-9) for x in tabs]
+        _t.set_num_threads(host_cores())
+        ns = sum(len(i) for i in sidx)
+        tv, treps = time_passes(torch_bags(ftabs, sidx, soff), ns, budget_s=8.0)
+        cores = _t.get_num_threads()
+        sample = f"{T_s} of {T} tables x {B} bags ({ns} lookups) x {treps} passes"
+        cpu = {"value": tv, "unit": "lookups/s", "cores": cores, "kind": "reference", "sample": sample,
+               "what": "nn.EmbeddingBag(mode=sum, sparse=True) per table, fp32, stock torch (dlrm_s_pytorch.py:295,483-488)"}
+        _t.set_num_threads(1)
+        n1 = sum(len(i) for i in sidx[:2])
+        v1, r1 = time_passes(torch_bags(ftabs[:2], sidx[:2], soff[:2]), n1, budget_s=3.0, min_reps=1, max_reps=5)
+        _t.set_num_threads(cores)
+        cpu["single_thread"] = {"value": v1, "unit": "lookups/s", "cores": 1, "sample": f"2 tables x {r1} passes"}
+        if not is_float:
+            v, pc, reps = time_oracle_port(tabs, sidx, soff, budget_s=5.0)
+            cpu["oracle_port"] = {"value": v, "unit": "lookups/s", "cores": pc, "passes": reps, "kind": "port"}
 
+    out = None
     if rank == 0:
+        cfg = job_config(w, world, args, False)
         out = {
             "metric": "embedding lookups/sec", "value": value, "unit": "lookups/s", "n_gpus": world, "steps": K,
-            "warmup": max(args.warmup, 3), "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-            "config": {"workload": w["name"], "tables_per_gpu": T, "rows": R, "dim": D, "global_batch": B,
-                       "lookups_per_step_per_gpu": int(np.mean(lookups)),
-                       "l2": f"inputs larger than L2: tables {T * R * D * 4 / 1e9:.2f} GB per GPU, "
-                             f"{N_BATCHES} rotating index batches",
-                       "exchange": ("none (1 GPU)" if world == 1 else args.exchange +
-                                    (f", {args.layout}-major peer slabs" if args.exchange == "fused" else "")),
-                       "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult},
-                       "parallelism": f"table-wise x{world}, pooled rows to the sample's rank"},
+            "warmup": max(warmup, 3), "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": cfg,
+            "run": {"lookups_per_step_per_gpu": int(np.mean(lookups)),
+                    "exchange": ("none (1 GPU)" if world == 1 else args.exchange +
+                                 (f", {args.layout}-major peer slabs, double buffered" if args.exchange == "fused" else "")),
+                    "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult}},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel_ms": kernel_ms,
+                         "kernel_ms_dist": kdist, "kernel_ms_max_over_ranks": kernel_ms_max,
                          "algorithmic_bytes_per_launch": bytes_per_launch,
                          "frac_of_nominal_8000": achieved / 8000.0},
-            "clocks": clk.summary(), "gpu_launches": int(gpu_launches),
+            "parity": parity, "gpu_launches": int(gpu_launches),
         }
         if e2e:
             out["e2e"] = e2e
         if cpu:
             out["cpu_baseline"] = cpu
-        print(json.dumps(out))
     sync_all()
     for p in plans:
         p.close()
     if slabs is not None:
         slabs.close()
     emblib.shutdown()
-    if world > 1:
-        dist.destroy_process_group()
+    torch.cuda.empty_cache()
+    return out
+
+
+def e2e_host_call(args, lib, emblib, batches, lookups, T, B, D, Ke, paths):
+    """N = 1: the reference-facing call, emb_lookup_ex on HOST arrays.  The arrays are page-locked and carved out of
+    one arena per kind, the way a caller that owns its buffers would allocate them (the reference allocates its
+    index / offset / result arrays once, dlrm_dpu_pytorch.py:484-498,1028-1051)."""
+    EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED = paths
+    host = []
+    for idx, off in batches[:2]:
+        arena = pinned_arena(lib, sum(4 * len(i) + 16 for i in idx) + sum(4 * len(o) + 16 for o in off) + 64)
+        pos, hi, ho = 0, [], []
+        for i in idx:
+            a, pos = carve_u32(arena, pos, len(i))
+            a[:] = i
+            hi.append(a)
+        for o in off:
+            a, pos = carve_u32(arena, pos, len(o))
+            a[:] = o
+            ho.append(a)
+        host.append((hi, ho, arena))
+    res_arena = pinned_arena(lib, T * (B * D * 4 + 16) + 64)
+    res, pos = [], 0
+    for _ in range(T):
+        a, pos = carve_u32(res_arena, pos, B * D)
+        res.append(a.view(np.float32).reshape(B, D))
+    # pointer arrays built once per batch, as the reference's caller does
+    calls = [emblib.HostCall(hi, ho, res) for hi, ho, _ in host]
+
+    def time_e2e(n_steps):
+        for k in range(3):
+            calls[k % 2]()
+        t0 = time.perf_counter()
+        for k in range(n_steps):
+            calls[k % 2]()  # emb_lookup_ex: synchronous, the results are in host memory on return
+        dt = time.perf_counter() - t0
+        tm = emblib.last_timings()
+        n_e = sum(lookups[k % 2] for k in range(n_steps))
+        return n_e / dt, dt / n_steps * 1e3, tm
+
+    PATHS = {1: "staged: cudaMemcpyAsync in, kernel, cudaMemcpyAsync out, pipelined over table groups",
+             2: "mapped: one launch, the kernel reads indices/offsets and writes pooled rows over PCIe",
+             3: "inputs staged by the copy engine, pooled rows written to the host arrays by the kernel's "
+                "store epilogue over PCIe, pipelined over table groups"}
+    v, ms, tm = time_e2e(Ke)  # default path (EMB_HOST_AUTO) on page-locked arrays
+    e2e = {"value": v, "unit": "lookups/s", "h2d_bytes_per_step": int(tm.h2d_bytes),
+           "d2h_bytes_per_step": int(tm.d2h_bytes), "ms_per_step": ms, "steps": Ke,
+           "call": "emb_lookup_ex (host pointers, page-locked arrays carved from one arena per kind)",
+           "path": PATHS[int(tm.path)],
+           "last_call_ms": {"h2d": tm.h2d_ms, "kernel": tm.kernel_ms, "d2h": tm.d2h_ms, "total": tm.total_ms},
+           "other_paths": {}}
+    for forced in (EMB_HOST_COPY, EMB_HOST_MAPPED):
+        emblib.set_host_path(forced)
+        v2, ms2, _ = time_e2e(max(3, Ke // 5))
+        e2e["other_paths"][PATHS[forced].split(":")[0]] = {"value": v2, "ms_per_step": ms2}
+    emblib.set_host_path(EMB_HOST_AUTO)
+    return e2e
+
+
+def e2e_sharded_path(args, lib, emblib, exchange, slabs, batches, lookups, T, B, D, per, rank, world, Ke, stream,
+                     sync_all):
+    """N > 1: the sharded product path from host buffers, per step and per rank: this rank's indices + offsets in
+    ONE pinned arena -> one H2D copy into a device arena the plan reads -> pooling launch (rows stored straight
+    into the owners' slabs over NVLink) -> completion kernel -> this rank's [B/N, T_global, D] rows -> one D2H copy
+    into pinned memory -> synchronise."""
+    import torch
+    import torch.distributed as dist
+    sets = []
+    for k, (idx, off) in enumerate(batches[:2]):
+        n_words = sum(len(i) for i in idx) + sum(len(o) for o in off)
+        harena = torch.empty(n_words, dtype=torch.int32).pin_memory()
+        darena = torch.empty(n_words, dtype=torch.int32, device="cuda")
+        pos, di, do = 0, [], []
+        for a in idx:
+            harena[pos:pos + len(a)] = torch.from_numpy(a.view(np.int32))
+            di.append(darena[pos:pos + len(a)])
+            pos += len(a)
+        for a in off:
+            harena[pos:pos + len(a)] = torch.from_numpy(a.view(np.int32))
+            do.append(darena[pos:pos + len(a)])
+            pos += len(a)
+        if slabs is not None:
+            qs = [dict(table_id=t, indices=di[t], offsets=do[t], out=None, out_stride=slabs.stride, bags_per_rank=per,
+                       out_peer=slabs.out_peer(t, k % 2), bag_rotate=0 if args.no_rotate else rank * per)
+                  for t in range(T)]
+            send = None
+        else:
+            send = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
+            qs = [dict(table_id=t, indices=di[t], offsets=do[t], out=send[:, t, :], out_stride=T * D) for t in range(T)]
+        sets.append((harena, darena, emblib.Plan(qs), send))
+    res_host = torch.empty((per, T * world, D), dtype=torch.float32).pin_memory()
+
+    def one(k):
+        harena, darena, plan, send = sets[k % 2]
+        darena.copy_(harena, non_blocking=True)
+        plan.launch(stream)
+        if slabs is not None:
+            slabs.barrier()
+            r = slabs.local_sample_major(k % 2)
+        else:
+            r = exchange.nccl_all_to_all(send, B, [T] * world, D)
+        res_host.copy_(r, non_blocking=True)
+        stream.synchronize()
+    for k in range(4):
+        one(k)
+    sync_all()
+    t0 = time.perf_counter()
+    for k in range(Ke):
+        one(k)
+    dt = time.perf_counter() - t0
+    n_e = sum(lookups[k % 2] for k in range(Ke))
+    dt, n_e = reduce_over_ranks([dt, float(n_e)], world, ["max", "sum"])
+    for _, _, plan, _ in sets:
+        plan.close()
+    return {"value": n_e / dt, "unit": "lookups/s", "h2d_bytes_per_step": int(sets[0][0].numel() * 4),
+            "d2h_bytes_per_step": int(res_host.numel() * 4), "ms_per_step": dt / Ke * 1e3, "steps": Ke,
+            "call": "sharded product path per rank: pinned index/offset arena -> HBM (1 copy), pooling launch with peer-slab "
+                    "stores over NVLink, completion kernel, [B/N, T_global, D] rows -> pinned host (1 copy); bytes are per rank"}
 
 
 # ---------------------------------------------------------------------------------------------
 # sharded arm (C4): ONE global problem cut over the ranks -- strong scaling
 # ---------------------------------------------------------------------------------------------
 
-def make_table_batch(w, t, seed):
-    """(indices, offsets) of global table t for one global batch; the same on every rank."""
-    rng = np.random.default_rng([seed, t])
-    lo, hi = w["pool"]
-    lens = rng.integers(lo, hi + 1, size=w["B"])
-    off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.uint32)
-    idx = rng.integers(0, w["rows"][t], size=int(lens.sum()), dtype=np.int64).astype(np.uint32)
-    return idx, off
-
-
-def run_sharded(args, w):
+def bench_sharded(args, w, steps, warmup):
     import torch
     import torch.distributed as dist
 
@@ -551,21 +857,16 @@ def run_sharded(args, w):
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
-    torch.cuda.set_device(local)
-    if world == 1:  # ShardedTables wants a process group even for one rank
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("MASTER_PORT", "29533")
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
     lib = emblib.load()
     rows, D, B = w["rows"], w["D"], w["B"]
     T = len(rows)
     P = (w["pool"][0] + w["pool"][1]) / 2.0
     emblib.check(lib.emb_set_tuning(args.variant, args.unroll, args.mult))
+    kw = {}
+    if args.max_table_bytes:
+        kw["max_table_bytes"] = args.max_table_bytes
     st = ShardedTables(rows, D, B, lookups=[B * P] * T, hbm_budget=150e9, layout=args.layout,
-                       rotate=not args.no_rotate)
+                       rotate=not args.no_rotate, **kw)
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
 
@@ -587,8 +888,8 @@ def run_sharded(args, w):
         dev.append((di, do))
         plans.append(st.make_plan(di, do, buffer=k % 2))
     lookups_global = float(T * B * P)  # every (table, index) of the global batch, counted once
-    # algorithmic bytes of THIS rank's launch: every index of its shards' tables is read, a row-range
-    # shard fetches its fraction of the rows, every bag writes one row and reads one offset
+    # algorithmic bytes of THIS rank's launch: the indices its shards read, the rows in their ranges, every bag
+    # writes one row and reads one offset
     my_bytes = sum(sharding.shard_cost(B * P, B, D, 1.0) * (sh.bag_hi - sh.bag_lo) / B if sh.sliced else
                    sharding.shard_cost(B * P, B, D, sh.rows / rows[sh.table]) for sh in st.local)
 
@@ -601,58 +902,100 @@ def run_sharded(args, w):
         plans[k % N_BATCHES].launch(stream)
         st.finish(stream, k % 2)
 
-    for k in range(max(args.warmup, 3)):
+    for k in range(max(warmup, 3)):
         step(k)
     sync_all()
     if lib.emb_check_indices():
         raise RuntimeError("out-of-range index in the synthetic batch")
 
-    K = args.steps
+    # ---- parity: every pooled row of one batch on every rank.  Each rank restates, with stock torch ops on ITS
+    # shards, the raw int32 sums they contribute (a row-range shard: only the rows it holds; a bag-sliced replica:
+    # only its bags); the contributions are wrap-added across the ranks with an NCCL all-reduce, dequantised once
+    # (emb_host.h:210) and compared bit for bit with what the fused exchange + completion kernel left in this
+    # rank's [B/N, T, D] slab.
+    parity = {"checked": False}
+    if not args.no_parity:
+        kb = 1
+        step(kb)
+        sync_all()
+        got = st.result_sample_major(kb % 2).clone()
+        di, do = dev[kb]
+        contrib = torch.zeros((T, B, D), dtype=torch.int32, device="cuda")
+        for j, sh in enumerate(st.local):
+            tab = table_tensor(lib, st.slot_of[j], D, "int32")
+            sums = torch_pooled(tab, di[sh.table], do[sh.table], B, row_lo=sh.row_lo, raw=True)
+            lo, hi = (sh.bag_lo, sh.bag_hi) if sh.sliced else (0, B)
+            contrib[sh.table, lo:hi] += sums[lo:hi]
+            del sums
+        dist.all_reduce(contrib, op=dist.ReduceOp.SUM)  # int32: wrap-around, as the reference's adds
+        mine = contrib[:, rank * st.per:(rank + 1) * st.per, :]
+        want = (mine.to(torch.float32) / torch.tensor(1e9, dtype=torch.float32, device="cuda")).permute(1, 0, 2).contiguous()
+        bad = compare_rows(got, want)
+        chk_got = int(got.contiguous().view(torch.int32).to(torch.int64).sum().item()) & 0xffffffffffffffff
+        chk_want = int(want.view(torch.int32).to(torch.int64).sum().item()) & 0xffffffffffffffff
+        bad_all, rows_all, chk_bad = reduce_over_ranks([float(bad), float(got.numel() // D), float(chk_got != chk_want)],
+                                                       world, ["sum", "sum", "sum"])
+        idx_err = lib.emb_check_indices()
+        parity = {"checked": True, "ranks": world, "rows_checked": int(rows_all), "mismatching_elements": int(bad_all),
+                  "bit_exact": bool(bad_all == 0), "checksum_of_checksums_equal": chk_bad == 0, "index_errors": int(idx_err),
+                  "against": "torch index_select + index_add_ on every rank's own shards (raw int32 contributions), NCCL "
+                             "all-reduce (wrap-around sum over shards), one fp32 divide (emb_dpu_lookup.c:106-116, "
+                             "emb_host.h:207-212, extend_distributed.py:389-426)"}
+        del contrib, mine, want, got
+        torch.cuda.empty_cache()
+        if bad_all or chk_bad or idx_err:
+            raise SystemExit(f"PARITY FAILURE (sharded) on rank {rank}: {json.dumps(parity)}")
+
+    K = steps
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = emblib.launch_count()
-    with ClockSampler(local) as clk:
-        sync_all()
-        e0.record(stream)
-        for k in range(K):
-            ev[k][0].record(stream)
-            plans[k % N_BATCHES].launch(stream)
-            ev[k][1].record(stream)
-            st.finish(stream, k % 2)
-        e1.record(stream)
-        sync_all()
+    sync_all()
+    e0.record(stream)
+    for k in range(K):
+        ev[k][0].record(stream)
+        plans[k % N_BATCHES].launch(stream)
+        ev[k][1].record(stream)
+        st.finish(stream, k % 2)
+    e1.record(stream)
+    sync_all()
     gpu_launches = emblib.launch_count() - launches0
     total_ms = e0.elapsed_time(e1)
-    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
-    t = torch.tensor([total_ms, kernel_ms, my_bytes / (kernel_ms * 1e-3) / 1e9], dtype=torch.float64, device="cuda")
-    tmax, tsum = t.clone(), t.clone()
-    dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-    total_ms_max, kernel_ms_max, agg_gbps = float(tmax[0]), float(tmax[1]), float(tsum[2])
+    kdist = dist_summary([a.elapsed_time(b) for a, b in ev])
+    kernel_ms = kdist["mean"]
+    total_ms_max, kernel_ms_max, agg_gbps = reduce_over_ranks(
+        [total_ms, kernel_ms, my_bytes / (kernel_ms * 1e-3) / 1e9], world, ["max", "max", "sum"])
     value = lookups_global * K / (total_ms_max * 1e-3)
     peak, peak_src = load_peaks()
     achieved = my_bytes / (kernel_ms * 1e-3) / 1e9  # rank 0's pooling launch
 
-    # ---- e2e: per step, this rank's index/offset arrays come from page-locked host memory and its
-    # [B/N, T, D] result goes back to page-locked host memory, all inside the timed region
+    # ---- e2e: per step, this rank's index/offset arrays come from ONE page-locked arena and its [B/N, T, D]
+    # result goes back to page-locked host memory, all inside the timed region
     e2e = None
     if not args.no_e2e:
-        pin = [{t: (torch.from_numpy(hb[t][0].view(np.int32)).pin_memory(),
-                    torch.from_numpy(hb[t][1].view(np.int32)).pin_memory()) for t in need} for hb in host_batches[:2]]
+        sets = []
+        for k, hb in enumerate(host_batches[:2]):
+            n_words = sum(len(hb[t][0]) + len(hb[t][1]) for t in need)
+            harena = torch.empty(n_words, dtype=torch.int32).pin_memory()
+            darena = torch.empty(n_words, dtype=torch.int32, device="cuda")
+            pos, di, do = 0, {}, {}
+            for t in need:
+                for arr, dct in ((hb[t][0], di), (hb[t][1], do)):
+                    harena[pos:pos + len(arr)] = torch.from_numpy(arr.view(np.int32))
+                    dct[t] = darena[pos:pos + len(arr)]
+                    pos += len(arr)
+            sets.append((harena, darena, st.make_plan(di, do, buffer=k % 2)))
         res_host = torch.empty(tuple(st.result(0).shape), dtype=torch.float32).pin_memory()
-        h2d = sum(a.numel() * 4 + b.numel() * 4 for a, b in pin[0].values())
-        d2h = res_host.numel() * 4
+        h2d, d2h = sets[0][0].numel() * 4, res_host.numel() * 4
 
         def e2e_step(k):
-            di, do = dev[k % 2]
-            for tt in need:
-                di[tt].copy_(pin[k % 2][tt][0], non_blocking=True)
-                do[tt].copy_(pin[k % 2][tt][1], non_blocking=True)
-            plans[k % 2].launch(stream)
+            harena, darena, plan = sets[k % 2]
+            darena.copy_(harena, non_blocking=True)
+            plan.launch(stream)
             st.finish(stream, k % 2)
             res_host.copy_(st.result(k % 2), non_blocking=True)
             stream.synchronize()
-        for k in range(3):
+        for k in range(4):
             e2e_step(k)
         sync_all()
         Ke = max(3, min(K, 50))
@@ -660,14 +1003,17 @@ def run_sharded(args, w):
         for k in range(Ke):
             e2e_step(k)
         dt = time.perf_counter() - t0
-        te = torch.tensor([dt], dtype=torch.float64, device="cuda")
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        dt = float(te[0])
+        (dt,) = reduce_over_ranks([dt], world, ["max"])
+        for _, _, p in sets:
+            p.close()
         e2e = {"value": lookups_global * Ke / dt, "unit": "lookups/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": dt / Ke * 1e3, "steps": Ke,
-               "call": "ShardedTables.lookup per rank: pinned host indices/offsets -> HBM, pooling launch, peer-slab "
-                       "exchange + barrier, partial reduction, [B/N, T, D] rows -> pinned host; bytes are rank 0's"}
+               "call": "ShardedTables.lookup per rank: pinned index/offset arena -> HBM (1 copy), pooling launch, peer-slab "
+                       "exchange + completion kernel (barrier + partial reduction), [B/N, T, D] rows -> pinned host (1 copy); "
+                       "bytes are rank 0's",
+               "floor_ms": measure_copy_floor(h2d, d2h, world)}
 
+    out = None
     if rank == 0:
         split = {str(tt): k for tt, (_, k) in st.split.items()}
         sliced = {}
@@ -676,36 +1022,93 @@ def run_sharded(args, w):
                 sliced[str(sh.table)] = sliced.get(str(sh.table), 0) + 1
         out = {
             "metric": "embedding lookups/sec", "value": value, "unit": "lookups/s", "n_gpus": world, "steps": K,
-            "warmup": max(args.warmup, 3), "ms_per_step": total_ms_max / K, "higher_is_better": True,
+            "warmup": max(warmup, 3), "ms_per_step": total_ms_max / K, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-            "config": {"workload": w["name"], "tables": T, "dim": D, "global_batch": B,
-                       "lookups_per_step_global": int(lookups_global),
-                       "table_bytes_total": int(sum(rows) * D * 4),
-                       "l2": f"inputs larger than L2: {sum(rows) * D * 4 / 1e9:.1f} GB of tables over {world} GPU(s), "
-                             f"{N_BATCHES} rotating index batches",
-                       "exchange": f"fused: peer-slab stores from the pooling kernel ({args.layout}-major slabs) + one completion "
-                                   "kernel (flag barrier over NVLink + partial reduction)",
-                       "placement": {"shards_on_rank0": len(st.local), "row_split_tables": split, "bag_sliced_replicas": sliced,
-                                     "planner_imbalance": round(st.plan.imbalance(), 4),
-                                     "hbm_bytes_per_rank": [int(x) for x in st.plan.hbm_bytes]},
-                       "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult},
-                       "parallelism": f"table-wise + row-wise over {world} rank(s), pooled rows to the sample's rank"},
+            "config": job_config(w, world, args, True),
+            "run": {"lookups_per_step_global": int(lookups_global), "table_bytes_total": int(sum(rows) * D * 4),
+                    "exchange": f"fused: peer-slab stores from the pooling kernel ({args.layout}-major slabs, double buffered) + "
+                                "one completion kernel (flag barrier over NVLink + partial reduction)",
+                    "placement": {"shards_on_rank0": len(st.local), "row_split_tables": split, "bag_sliced_replicas": sliced,
+                                  "planner_imbalance": round(st.plan.imbalance(), 4),
+                                  "hbm_bytes_per_rank": [int(x) for x in st.plan.hbm_bytes]},
+                    "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult}},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms,
+                         "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms, "kernel_ms_dist": kdist,
                          "kernel_ms_max_over_ranks": kernel_ms_max, "algorithmic_bytes_per_launch": my_bytes,
                          "aggregate_GBps_all_ranks": agg_gbps, "note": "rank 0's pooling launch; bytes = indices + "
                          "in-range rows + outputs + offsets of its shards (sharding.shard_cost)"},
-            "clocks": clk.summary(), "gpu_launches": int(gpu_launches),
+            "parity": parity, "gpu_launches": int(gpu_launches),
         }
         if e2e:
             out["e2e"] = e2e
-        print(json.dumps(out))
     sync_all()
     for p in plans:
         p.close()
     st.close()
     emblib.shutdown()
-    dist.destroy_process_group()
+    torch.cuda.empty_cache()
+    return out
+
+
+def condensed(r):
+    """What an `extra` workload contributes to the main JSON line."""
+    keep = {k: r[k] for k in ("value", "unit", "ms_per_step", "steps", "scaling", "gpu_launches", "parity")}
+    keep["workload"] = r["config"]["workload"]
+    keep["roofline"] = {k: r["roofline"].get(k) for k in ("achieved", "frac", "kernel_ms", "kernel_ms_max_over_ranks",
+                                                           "algorithmic_bytes_per_launch", "aggregate_GBps_all_ranks")}
+    if "placement" in r.get("run", {}):
+        keep["placement"] = r["run"]["placement"]
+    if "e2e" in r:
+        keep["e2e"] = {k: r["e2e"].get(k) for k in ("value", "ms_per_step", "floor_ms", "h2d_bytes_per_step",
+                                                     "d2h_bytes_per_step")}
+    return keep
+
+
+def run_b200(args, w):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    if not torch.cuda.is_available():
+        raise SystemExit("no CUDA device: the B200 arm has no CPU stand-in (use --impl reference for the CPU path)")
+    torch.cuda.set_device(local)
+    extras = args.extras
+    if extras == "auto":
+        extras = "c4tb,c5" if (args.workload == "c2" and args.dtype == "int32") else "none"
+    extras = [e for e in extras.split(",") if e and e != "none"]
+    need_group = world > 1 or bool(w.get("sharded")) or any(WORKLOADS[e].get("sharded") for e in extras)
+    if need_group:
+        if world == 1:  # ShardedTables wants a process group even for one rank
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29533")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+
+    def one(wl, steps, warmup):
+        return bench_sharded(args, wl, steps, warmup) if wl.get("sharded") else bench_tablewise(args, wl, steps, warmup)
+
+    with ClockSampler(local) as clk:
+        out = one(w, args.steps, args.warmup)
+        extra = {}
+        for name in extras:
+            saved = args.no_cpu_baseline
+            args.no_cpu_baseline = True
+            try:
+                r = one(WORKLOADS[name], max(3, min(args.steps, 50)), min(args.warmup, 5))
+            finally:
+                args.no_cpu_baseline = saved
+            if rank == 0:
+                extra[name] = condensed(r)
+    if rank == 0:
+        out["clocks"] = clk.summary()
+        if extra:
+            out["extra"] = extra
+        print(json.dumps(out))
+    if need_group:
+        dist.destroy_process_group()
 
 
 def main():
@@ -719,8 +1122,6 @@ def main():
     sys.stdout = os.fdopen(real_stdout, "w")
     if args.impl == "reference":
         run_reference(args, w)
-    elif w.get("sharded"):
-        run_sharded(args, w)
     else:
         run_b200(args, w)
     sys.stdout.flush()

@@ -154,7 +154,13 @@ class ShardedTables:
     def finish(self, stream, buffer=0):
         """Completion barrier of the fused exchange, then the partial-sum reduction of the split
         tables, both ordered on `stream` (a torch.cuda.Stream, the one the plan was launched on).
-        When it has run, result(buffer) holds this rank's samples."""
+        When it has run, result(buffer) holds this rank's samples.
+
+        Buffer rule (what makes n_buffers = 2 enough): consecutive batches alternate buffers, and whatever
+        CONSUMES result(buffer) of batch k is enqueued on `stream` BEFORE finish() of batch k+1.  A peer can only
+        start storing batch k+2 (same buffer as k) after its own finish(k+1) has seen this rank's epoch k+1
+        signal, which this rank's stream issues after the consumer of batch k.  A consumer on another stream must
+        make `stream` wait for it (event) before the next finish()."""
         if self._finish[buffer] is not None:
             self.out.finish(self._finish[buffer], stream)
             return
@@ -165,7 +171,8 @@ class ShardedTables:
                          "emb_reduce_partials")
 
     def lookup(self, plan, stream):
-        """One call: pooling launch + exchange + reduction.  Returns result(plan.buffer)."""
+        """One call: pooling launch + exchange + reduction.  Returns result(plan.buffer), valid for work enqueued
+        on `stream`; see finish() for the buffer rule when several batches are in flight."""
         plan.launch(stream)
         self.finish(stream, plan.buffer)
         return self.result(plan.buffer)

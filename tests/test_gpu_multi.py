@@ -1,4 +1,5 @@
-"""Two-GPU parity of the pooled-output exchange (skipped on a one-GPU box): both transports --
+"""Multi-GPU parity of the pooled-output exchange (each case skips on a box with fewer GPUs; run with
+`gpurun --gpus N`): ShardedTables at world sizes 1, 2, 4 and 8, and at two GPUs both transports --
 peer-slab stores straight from the pooling kernel over NVLink, and NCCL all_to_all_single --
 must leave on every rank exactly the oracle's pooled rows of that rank's samples, for all
 tables, bit for bit.  Also a row-split table: raw int32 partials from two GPUs added at the
@@ -143,7 +144,7 @@ def _sharded_worker(rank, world, port, tmp):
         rng = np.random.default_rng(11)  # same on every rank: the global problem
         tabs = [rng.integers(-2**31, 2**31, size=(r, D), dtype=np.int64).astype(np.int32) for r in rows]
         batches = []
-        for k in range(3):
+        for k in range(4):
             idx, off = [], []
             for r in rows:
                 lens = rng.integers(0, 13, size=B)
@@ -176,6 +177,22 @@ def _sharded_worker(rank, world, port, tmp):
             want = np.stack(eo.lookup_rows(tabs, idx, off), axis=1)[rank * per:(rank + 1) * per]
             good &= bool(np.array_equal(got.cpu().numpy().view(np.uint32), want.view(np.uint32)))
         ok["bits"] = good
+        # Batches in flight: 8 lookups enqueued back to back with NO host synchronisation in between, each followed
+        # by a device-side copy of result(buffer) on the same stream (the consumer).  Ranks run ahead of each other
+        # here: a peer stores batch k+1 into buffer (k+1) % 2 while this rank's copy of batch k may still be
+        # pending, and the epoch flags of the completion kernel see a peer one epoch ahead.  The rule that makes two
+        # buffers enough: the consumer of result(buffer) is enqueued on the SAME stream before the next finish().
+        wants = [np.stack(eo.lookup_rows(tabs, idx, off), axis=1)[rank * per:(rank + 1) * per] for idx, off in batches]
+        dist.barrier()
+        copies = []
+        for k in range(8):
+            p = plans[k % 4]
+            st.lookup(p, stream)
+            with torch.cuda.stream(stream):
+                copies.append(st.result_sample_major(p.buffer).clone())
+        stream.synchronize()
+        ok["inflight"] = all(bool(np.array_equal(c.cpu().numpy().view(np.uint32), wants[k % 4].view(np.uint32)))
+                             for k, c in enumerate(copies))
         ok["no_oob"] = emblib.load().emb_check_indices() == 0
         dist.barrier()
         for p in plans:
@@ -187,7 +204,7 @@ def _sharded_worker(rank, world, port, tmp):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [1, 2])
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
 def test_sharded_tables(tmp_path, world):
     torch = pytest.importorskip("torch")
     if torch.cuda.device_count() < world:
@@ -200,4 +217,4 @@ def test_sharded_tables(tmp_path, world):
     mp.spawn(_sharded_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
     for r in range(world):
         got = eval(open(tmp_path / f"ok{r}").read())
-        assert got == {"split": True, "sliced": True, "bits": True, "no_oob": True}, (r, got)
+        assert got == {"split": True, "sliced": True, "bits": True, "inflight": True, "no_oob": True}, (r, got)
