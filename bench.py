@@ -379,8 +379,8 @@ def pinned_arena(lib, nbytes):
 
 
 def carve_u32(arena, pos, n):
-    """n uint32 at byte offset pos of the arena (16-byte aligned start); returns (array, next offset)."""
-    pos = (pos + 15) // 16 * 16
+    """n uint32 at byte offset pos of the arena, packed tightly: the arrays of consecutive tables are adjacent in
+    host memory, which lets the library move a group of tables with one copy.  Returns (array, next offset)."""
     return arena[pos:pos + 4 * n].view(np.uint32), pos + 4 * n
 
 

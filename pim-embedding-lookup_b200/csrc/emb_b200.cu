@@ -1370,17 +1370,23 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, all_float);
     std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
     {
-        // Group sizes grow by a factor r per group: nothing can be pooled before the first group's
-        // indices have crossed PCIe, so a small first group shortens the start-up bubble; but group
-        // g+1's indices must have arrived by the time group g's results have drained, or the result
-        // stream stalls, so r cannot exceed (time to write a group out) / (time to read its indices).
-        // r = 1 is equal groups.  Measurement knob: EMB_GROUP_RATIO (percent, default 100).
+        // Group sizes.  Nothing can be pooled before the first group's indices have crossed PCIe and nothing
+        // overlaps the last group's results, so small groups at both ends shorten the two bubbles, while large
+        // groups in the middle keep the copies long (every copy boundary idles the copy engine for a few
+        // microseconds).  EMB_GROUP_SHAPE (measurement knob): 0 = equal groups, 1 = sizes 1,2,4,...,4,2,1 (default),
+        // 2 = equal groups with a half-size last one.
         const uint64_t total = h2d_payload + d2h_payload;
-        static const double r = std::max(100u, env_u32("EMB_GROUP_RATIO", 100)) / 100.0;
+        const uint32_t shape = env_u32("EMB_GROUP_SHAPE", 1);
         std::vector<double> cum(n_groups);
-        double w = 1.0, sum = 0.0;
-        for (uint32_t i = 0; i < n_groups; i++, w *= r)
+        double sum = 0.0;
+        for (uint32_t i = 0; i < n_groups; i++) {
+            double w = 1.0;
+            if (shape == 1)
+                w = (double)std::min(std::min(1u << std::min(i, 16u), 1u << std::min(n_groups - 1 - i, 16u)), 4u);
+            else if (shape == 2 && i + 1 == n_groups)
+                w = 0.5;
             cum[i] = (sum += w);
+        }
         uint64_t acc = 0;
         uint32_t gi = 0;
         g_first[0] = 0;
@@ -1443,15 +1449,30 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     uint64_t launches = 0;
     for (uint32_t gi = 0; gi < n_groups; gi++) {
         const uint32_t t0 = g_first[gi], t1 = g_first[gi + 1];
-        if (!in_mapped)
-            for (uint32_t t = t0; t < t1; t++) {
-                if (indices_len[t])
-                    CU(cudaMemcpyAsync(g.d_idx + t_io[t], indices[t], (size_t)indices_len[t] * 4,
-                                       cudaMemcpyHostToDevice, s_in));
-                if (nr_batches[t] && !off_mapped)
-                    CU(cudaMemcpyAsync(g.d_off + t_oo[t], offsets[t], (size_t)nr_batches[t] * 4,
-                                       cudaMemcpyHostToDevice, s_in));
+        // Arrays of consecutive tables that are ADJACENT in host memory (a caller that carves its arrays out of one
+        // arena) cross PCIe as one copy: the device arenas are contiguous in table order, so a run of adjacent host
+        // arrays maps onto one contiguous device range.  Per-table copies cost the copy engine a start-up gap each
+        // (52 + 26 copies: 66 GB/s both ways against 87 GB/s with one copy each way, profiles/r1_pcie.md).
+        if (!in_mapped) {
+            for (uint32_t t = t0; t < t1;) {  // indices
+                uint32_t e = t + 1;
+                size_t n = indices_len[t];
+                while (e < t1 && indices[e] == indices[t] + n)
+                    n += indices_len[e++];
+                if (n)
+                    CU(cudaMemcpyAsync(g.d_idx + t_io[t], indices[t], n * 4, cudaMemcpyHostToDevice, s_in));
+                t = e;
             }
+            for (uint32_t t = t0; t < t1 && !off_mapped;) {  // offsets
+                uint32_t e = t + 1;
+                size_t n = nr_batches[t];
+                while (e < t1 && offsets[e] == offsets[t] + n)
+                    n += nr_batches[e++];
+                if (n)
+                    CU(cudaMemcpyAsync(g.d_off + t_oo[t], offsets[t], n * 4, cudaMemcpyHostToDevice, s_in));
+                t = e;
+            }
+        }
         if (s_in != s_k) {
             CU(cudaEventRecord(ev[3 * gi], s_in));
             CU(cudaStreamWaitEvent(s_k, ev[3 * gi], 0));
@@ -1464,10 +1485,15 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         CU(cudaEventRecord(ev[3 * gi + 2], s_k));
         if (!out_mapped) {
             CU(cudaStreamWaitEvent(s_out, ev[3 * gi + 2], 0));
-            for (uint32_t t = t0; t < t1; t++)
-                if (nr_batches[t])
-                    CU(cudaMemcpyAsync(final_results[t], g.d_out + t_oo[t] * D, (size_t)nr_batches[t] * D * 4,
-                                       cudaMemcpyDeviceToHost, s_out));
+            for (uint32_t t = t0; t < t1;) {  // adjacent result arrays: one copy
+                uint32_t e = t + 1;
+                size_t n = (size_t)nr_batches[t] * D;
+                while (e < t1 && final_results[e] == final_results[t] + n)
+                    n += (size_t)nr_batches[e++] * D;
+                if (n)
+                    CU(cudaMemcpyAsync(final_results[t], g.d_out + t_oo[t] * D, n * 4, cudaMemcpyDeviceToHost, s_out));
+                t = e;
+            }
         }
     }
     cudaStream_t s_last = out_mapped ? s_k : s_out;
