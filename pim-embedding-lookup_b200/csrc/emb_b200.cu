@@ -1235,6 +1235,32 @@ static void *mapped_alias(const void *p)
     return (a.type == cudaMemoryTypeHost) ? a.devicePointer : nullptr;
 }
 
+/* Start address of the CUDA allocation (cudaHostAlloc / cudaHostRegister range) that holds a host pointer, 0 for
+ * memory the driver does not know (plain malloc).  One cudaMemcpyAsync may not span two page-locked allocations even
+ * when they happen to be adjacent in the address space, so copies of neighbouring arrays are merged only inside one
+ * allocation (or between two arrays of unregistered memory). */
+static uintptr_t alloc_base(const void *p)
+{
+    typedef CUresult (*GetAttr)(void *, CUpointer_attribute, CUdeviceptr);
+    static GetAttr fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        cudaDriverEntryPointQueryResult qr;
+        void *f = nullptr;
+        if (cudaGetDriverEntryPoint("cuPointerGetAttribute", &f, cudaEnableDefault, &qr) == cudaSuccess)
+            fn = (GetAttr)f;
+        else
+            cudaGetLastError();
+    }
+    if (!fn)
+        return (uintptr_t)p;  // cannot tell: every array is its own run
+    CUdeviceptr base = 0;
+    if (fn(&base, CU_POINTER_ATTRIBUTE_RANGE_START_ADDR, (CUdeviceptr)(uintptr_t)p) != CUDA_SUCCESS)
+        return 0;
+    return (uintptr_t)base;
+}
+
 static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_t *const *offsets,
                        const uint32_t *indices_len, const uint32_t *nr_batches,
                        float *const *final_results)
@@ -1332,6 +1358,16 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         return fail(EMB_EINVAL, "EMB_HOST_MAPPED_OUT: a final_results array is not page-locked");
     if (g.host_path == EMB_HOST_MAPPED_OUT)
         in_mapped = false;
+    // AUTO on a large call: both directions go through the copy engines, also when the result arrays are
+    // page-locked.  Measured on C2 (tools/e2e_sweep.py, profiles/r2_host_path.md): 2.75 ms per call with copies
+    // against 2.91 ms with the kernel's store epilogue writing over PCIe (arrays carved from one arena; about equal
+    // with one allocation per table) -- a pooling kernel that stores to host memory is stretched to the PCIe
+    // write rate and holds the SMs the next group's kernel wants.  EMB_AUTO_LARGE=0 (measurement knob) restores
+    // the mapped results.
+    static const bool auto_copy = env_u32("EMB_AUTO_LARGE", 1) != 0;
+    if (g.host_path == EMB_HOST_AUTO && auto_copy && out_mapped && !in_mapped && !bounce &&
+        h2d_payload + d2h_payload >= kPipelineMinBytes)
+        out_mapped = false;
     // MAPPED_OUT: the offsets (4 bytes per bag) are still read in place when they are page-locked:
     // a separate small copy per table costs more on the copy engine than it moves
     bool off_mapped = in_mapped;
@@ -1352,15 +1388,15 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     // Groups of consecutive tables with about equal bytes (one group when nothing is staged).
     // A kernel that stores to host memory only retires when its writes have drained (measured,
     // tools/pcie_mix_probe.py: the same 109 MB take 2.08 ms in 1 launch, 2.13 in 4, 2.46 in 26) and
-    // every copy boundary idles the copy engine for a few microseconds, so groups are large:
-    // ~32 MB with mapped results, ~16 MB when the results are copied out as well (the last
-    // group's copy-out overlaps nothing).  Sweep on C2 (tools/e2e_groups_sweep.sh): 2 / 4 / 6 / 8 /
-    // 13 / 26 groups -> 3.26 / 3.05 / 3.05 / 3.09 / 3.22 / 3.60 ms per call (mapped results).
+    // every copy boundary idles the copy engine for a few microseconds, so groups are large: ~32 MB.
+    // Sweep on C2 (tools/e2e_sweep.py, arrays from one arena, 187 MB per call): copies both ways, equal groups,
+    // 4 / 6 / 8 / 12 groups -> 2.80 / 2.75 / 2.76 / 2.95 ms; mapped results, ramped groups -> 2.91 / 2.92 / 2.98 /
+    // 3.15 ms; floor of the two copies alone, running concurrently: 2.17 ms.
     const uint64_t staged = (in_mapped ? 0 : h2d_payload) + d2h_payload;
     uint32_t n_groups = 1;
     if (!(in_mapped && out_mapped) && staged >= kPipelineMinBytes) {
-        const uint64_t unit = out_mapped ? (32ull << 20) : (16ull << 20);
-        n_groups = std::min(std::min(T, kMaxGroups), std::max(2u, (uint32_t)(staged / unit)));
+        const uint64_t unit = 32ull << 20;  // C2 (187 MB): 6 groups, the sweep's best for copies; 4-8 are within 1 %
+        n_groups = std::min(std::min(T, kMaxGroups), std::max(2u, (uint32_t)((staged + unit / 2) / unit)));
     }
     const uint32_t forced_groups = env_u32("EMB_GROUPS", 0);  // measurement knob
     if (forced_groups && n_groups > 1)
@@ -1373,10 +1409,11 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         // Group sizes.  Nothing can be pooled before the first group's indices have crossed PCIe and nothing
         // overlaps the last group's results, so small groups at both ends shorten the two bubbles, while large
         // groups in the middle keep the copies long (every copy boundary idles the copy engine for a few
-        // microseconds).  EMB_GROUP_SHAPE (measurement knob): 0 = equal groups, 1 = sizes 1,2,4,...,4,2,1 (default),
-        // 2 = equal groups with a half-size last one.
+        // microseconds).  EMB_GROUP_SHAPE (measurement knob): 0 = equal groups (default when the results are copied:
+        // 2.75 ms against 2.80 for the ramp on C2), 1 = sizes 1,2,4,...,4,2,1 (default with mapped results: the
+        // small first kernel starts writing early), 2 = equal groups with a half-size last one.
         const uint64_t total = h2d_payload + d2h_payload;
-        const uint32_t shape = env_u32("EMB_GROUP_SHAPE", 1);
+        const uint32_t shape = env_u32("EMB_GROUP_SHAPE", out_mapped ? 1 : 0);
         std::vector<double> cum(n_groups);
         double sum = 0.0;
         for (uint32_t i = 0; i < n_groups; i++) {
@@ -1457,7 +1494,8 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             for (uint32_t t = t0; t < t1;) {  // indices
                 uint32_t e = t + 1;
                 size_t n = indices_len[t];
-                while (e < t1 && indices[e] == indices[t] + n)
+                const uintptr_t ab = alloc_base(indices[t]);
+                while (e < t1 && indices[e] == indices[t] + n && alloc_base(indices[e]) == ab)
                     n += indices_len[e++];
                 if (n)
                     CU(cudaMemcpyAsync(g.d_idx + t_io[t], indices[t], n * 4, cudaMemcpyHostToDevice, s_in));
@@ -1466,7 +1504,8 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             for (uint32_t t = t0; t < t1 && !off_mapped;) {  // offsets
                 uint32_t e = t + 1;
                 size_t n = nr_batches[t];
-                while (e < t1 && offsets[e] == offsets[t] + n)
+                const uintptr_t ab = alloc_base(offsets[t]);
+                while (e < t1 && offsets[e] == offsets[t] + n && alloc_base(offsets[e]) == ab)
                     n += nr_batches[e++];
                 if (n)
                     CU(cudaMemcpyAsync(g.d_off + t_oo[t], offsets[t], n * 4, cudaMemcpyHostToDevice, s_in));
@@ -1488,7 +1527,8 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             for (uint32_t t = t0; t < t1;) {  // adjacent result arrays: one copy
                 uint32_t e = t + 1;
                 size_t n = (size_t)nr_batches[t] * D;
-                while (e < t1 && final_results[e] == final_results[t] + n)
+                const uintptr_t ab = alloc_base(final_results[t]);
+                while (e < t1 && final_results[e] == final_results[t] + n && alloc_base(final_results[e]) == ab)
                     n += (size_t)nr_batches[e++] * D;
                 if (n)
                     CU(cudaMemcpyAsync(final_results[t], g.d_out + t_oo[t] * D, n * 4, cudaMemcpyDeviceToHost, s_out));

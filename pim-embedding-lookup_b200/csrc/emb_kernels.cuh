@@ -72,10 +72,20 @@ __device__ __forceinline__ uint32_t chunk_first_bag(const BagDesc *d, uint32_t c
  * of the table being walked were the first thing L2 dropped; plain ld.global.nc is faster on every workload
  * (C2 0.2443 -> 0.2422 ms, C3 0.0496 -> 0.0456, C4 0.658 -> 0.6088, C5 0.5023 -> 0.4819).  The index / offset
  * streams and the output rows stay L1::no_allocate: they are used once. */
+/* One 16-byte piece of a table row through the read-only path.  NARROW (rows of 64 bytes or less) adds the L2
+ * prefetch-size hint of 64 bytes: by default an L2 miss fills the whole 128-byte line, so a gather of 64-byte rows
+ * reads twice its bytes from DRAM (C2, ncu dram__bytes_read per launch: 1.329 GB without the hint, 0.909 GB with it;
+ * profiles/r2_row_loads.md).  The kernel's time does not change (0.2215 ms either way: it is not bound by DRAM
+ * bytes), the traffic does.  Table slabs come from cudaMalloc (256-byte aligned), so a 64-byte row never straddles a
+ * 64-byte boundary. */
+template <bool NARROW>
 __device__ __forceinline__ uint4 ldg_row16(const uint4 *p)
 {
     uint4 r;
-    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    if (NARROW)
+        asm volatile("ld.global.nc.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    else
+        asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
 
@@ -218,7 +228,7 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni,
         for (int u = 0; u < UNROLL; u++) {
             v[u] = make_uint4(0u, 0u, 0u, 0u);
             if (r[u] < rows)
-                v[u] = ldg_row16(table + (size_t)r[u] * LANES);
+                v[u] = ldg_row16<(LANES <= 4)>(table + (size_t)r[u] * LANES);
         }
         if (!is_float) {
 #pragma unroll
@@ -557,7 +567,7 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                     }
 #pragma unroll
                     for (int u = 0; u < K; u++)
-                        v[u] = ldg_row16(row_ptr<ROWB>(table, id[u]));
+                        v[u] = ldg_row16<(ROWB <= 64)>(row_ptr<ROWB>(table, id[u]));
                 };
                 load_step(0);
                 for (uint32_t c = K; c < per; c += K) {
@@ -610,7 +620,7 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
             for (uint32_t p = start; p < end; p++) {
                 const uint32_t id = __ldg(g_idx + p) - row_base;
                 if (id < rows)
-                    acc = add_rows<IS_FLOAT>(acc, ldg_row16(reinterpret_cast<const uint4 *>(table + (size_t)id * ROWB)));
+                    acc = add_rows<IS_FLOAT>(acc, ldg_row16<(ROWB <= 64)>(reinterpret_cast<const uint4 *>(table + (size_t)id * ROWB)));
                 else
                     bad = true;
             }
@@ -839,7 +849,7 @@ bag_sum_tma_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t 
             for (uint32_t p = off[bag]; p < off[bag + 1]; p++) {
                 const uint32_t id = __ldg(g_idx + p) - row_base;
                 if (id < rows) {
-                    const uint4 v = ldg_row16(table + (size_t)id * LANES);
+                    const uint4 v = ldg_row16<(LANES <= 4)>(table + (size_t)id * LANES);
                     if (!is_float) {
                         acc[j].x += v.x;
                         acc[j].y += v.y;

@@ -23,6 +23,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--workload", default="c2")
+    ap.add_argument("--quick", action="store_true",
+                    help="arena arrays only: the default path (EMB_HOST_AUTO) against forced copies / mapped results")
     args = ap.parse_args()
     import torch
 
@@ -77,6 +79,22 @@ def main():
         dt = (time.perf_counter() - t0) / n
         return dt * 1e3, emblib.last_timings()
 
+    if args.quick:
+        calls = arrays(True)
+        for path, pname in ((EMB_HOST_AUTO, "auto"), (EMB_HOST_MAPPED_OUT, "mapped_out"), (EMB_HOST_COPY, "copy")):
+            emblib.set_host_path(path)
+            for groups in (0,) if path == EMB_HOST_AUTO else (0, 2, 4, 8):
+                os.environ["EMB_GROUPS"] = str(groups)
+                ms, tm = timed(calls, args.steps)
+                print(json.dumps({"workload": args.workload, "path": pname, "groups": groups,
+                                  "ms_per_call": round(ms, 4), "G_lookups_per_s": round(np.mean(lookups) / ms / 1e6, 3),
+                                  "launches": int(tm.launches), "h2d_ms": round(tm.h2d_ms, 3),
+                                  "kernel_ms": round(tm.kernel_ms, 3), "d2h_ms": round(tm.d2h_ms, 3),
+                                  "chosen_path": int(tm.path), "h2d_bytes": int(tm.h2d_bytes),
+                                  "d2h_bytes": int(tm.d2h_bytes)}), flush=True)
+        emblib.set_host_path(EMB_HOST_AUTO)
+        emblib.shutdown()
+        return
     for packed in (True, False):
         calls = arrays(packed)
         for path, pname in ((EMB_HOST_MAPPED_OUT, "mapped_out"), (EMB_HOST_COPY, "copy")):
