@@ -79,6 +79,9 @@ def parse_args(argv=None):
                     help="peer-slab layout of the fused exchange: [T][B/N][D] or [B/N][T][D]")
     ap.add_argument("--no-rotate", action="store_true",
                     help="fused exchange: every rank walks the destination ranks in the same order (comparator)")
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="plans without EMB_Q_OVERLAP: a pooling launch reads nothing before the kernel in front of it "
+                         "has completed (comparator for the programmatic-dependent-launch overlap)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the bit-exact check of one batch on every rank")
@@ -491,7 +494,8 @@ def bench_tablewise(args, w, steps, warmup):
     import torch.distributed as dist
 
     from pim_embedding_lookup_b200 import emblib, exchange
-    from pim_embedding_lookup_b200.dputypes import EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED, EMB_TABLE_FIXED, EMB_TABLE_FLOAT
+    from pim_embedding_lookup_b200.dputypes import (EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED, EMB_Q_OVERLAP, EMB_TABLE_FIXED,
+                                                    EMB_TABLE_FLOAT)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -533,22 +537,25 @@ def bench_tablewise(args, w, steps, warmup):
         slabs = exchange.PeerSlabs(B, [T] * world, D, layout=args.layout, n_buffers=2)
     per = B // world
 
+    # the index / offset tensors are filled once, before the loop: a launch may gather under its predecessor's tail
+    qflags = 0 if args.no_overlap else EMB_Q_OVERLAP
+
     def make_plan(di, do, buffer):
         qs = []
         keep = None
         if slabs is not None:
             for t in range(T):
                 qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=None, out_stride=slabs.stride,
-                               bags_per_rank=per, out_peer=slabs.out_peer(t, buffer),
+                               bags_per_rank=per, out_peer=slabs.out_peer(t, buffer), flags=qflags,
                                bag_rotate=0 if args.no_rotate else rank * per))
         elif world > 1:  # nccl: send buffer [N, B/N, T_local, D] == bag-major rows of stride T*D
             keep = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
             for t in range(T):
-                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=keep[:, t, :], out_stride=T * D))
+                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=keep[:, t, :], out_stride=T * D, flags=qflags))
         else:  # the reference's layout: one [B, D] result per table (emb_host.h:207-212)
             keep = torch.empty((T, B, D), dtype=torch.float32, device="cuda")
             for t in range(T):
-                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=keep[t]))
+                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=keep[t], flags=qflags))
         return emblib.Plan(qs), keep
 
     plans, keep = [], []
@@ -618,16 +625,14 @@ def bench_tablewise(args, w, steps, warmup):
         if bad_all or chk_got != chk_want or idx_err:
             raise SystemExit(f"PARITY FAILURE on rank {rank}: {json.dumps(parity)}")
 
+    # ---- the timed region: EXACTLY K steps back to back, one event on either side, nothing between the launches
     K = steps
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = emblib.launch_count()
     sync_all()
     e0.record(stream)
     for k in range(K):
-        ev[k][0].record(stream)
         plans[k % N_BATCHES].launch(stream)
-        ev[k][1].record(stream)
         if slabs is not None:
             slabs.barrier()
         elif world > 1:
@@ -636,6 +641,19 @@ def bench_tablewise(args, w, steps, warmup):
     sync_all()
     gpu_launches = emblib.launch_count() - launches0
     total_ms = e0.elapsed_time(e1)
+    # ---- the pooling kernel alone: the same K steps once more, every pooling launch between two events.  (An event
+    # record between two launches also keeps them from overlapping, so this is the duration of an ISOLATED launch;
+    # in the timed region above a launch starts under its predecessor's tail, EMB_Q_OVERLAP.)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    for k in range(K):
+        ev[k][0].record(stream)
+        plans[k % N_BATCHES].launch(stream)
+        ev[k][1].record(stream)
+        if slabs is not None:
+            slabs.barrier()
+        elif world > 1:
+            exchange.nccl_all_to_all(keep[k % N_BATCHES], B, [T] * world, D)
+    sync_all()
     kdist = dist_summary([a.elapsed_time(b) for a, b in ev])
     kernel_ms = kdist["mean"]
     n_lookups = sum(lookups[k % N_BATCHES] for k in range(K))
@@ -709,6 +727,12 @@ def bench_tablewise(args, w, steps, warmup):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel_ms": kernel_ms,
                          "kernel_ms_dist": kdist, "kernel_ms_max_over_ranks": kernel_ms_max,
+                         "kernel_ms_what": "mean duration of one ISOLATED pooling launch: the K steps repeated right "
+                                           "after the timed region with an event on either side of every pooling "
+                                           "launch; in the timed region itself nothing separates the launches and "
+                                           + ("they do not overlap (--no-overlap)" if args.no_overlap else
+                                              "each starts gathering under its predecessor's tail (EMB_Q_OVERLAP), so "
+                                              "ms_per_step can be below kernel_ms"),
                          "algorithmic_bytes_per_launch": bytes_per_launch,
                          "frac_of_nominal_8000": achieved / 8000.0},
             "parity": parity, "gpu_launches": int(gpu_launches),
@@ -886,7 +910,7 @@ def bench_sharded(args, w, steps, warmup):
         di = {t: torch.from_numpy(hb[t][0].view(np.int32)).cuda() for t in need}
         do = {t: torch.from_numpy(hb[t][1].view(np.int32)).cuda() for t in need}
         dev.append((di, do))
-        plans.append(st.make_plan(di, do, buffer=k % 2))
+        plans.append(st.make_plan(di, do, buffer=k % 2, overlap=not args.no_overlap))
     lookups_global = float(T * B * P)  # every (table, index) of the global batch, counted once
     # algorithmic bytes of THIS rank's launch: the indices its shards read, the rows in their ranges, every bag
     # writes one row and reads one offset
@@ -946,21 +970,26 @@ def bench_sharded(args, w, steps, warmup):
         if bad_all or chk_bad or idx_err:
             raise SystemExit(f"PARITY FAILURE (sharded) on rank {rank}: {json.dumps(parity)}")
 
+    # timed region: K steps back to back; then the same K steps with every pooling launch between two events
+    # (an isolated launch -- see bench_tablewise)
     K = steps
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = emblib.launch_count()
     sync_all()
     e0.record(stream)
     for k in range(K):
-        ev[k][0].record(stream)
-        plans[k % N_BATCHES].launch(stream)
-        ev[k][1].record(stream)
-        st.finish(stream, k % 2)
+        step(k)
     e1.record(stream)
     sync_all()
     gpu_launches = emblib.launch_count() - launches0
     total_ms = e0.elapsed_time(e1)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    for k in range(K):
+        ev[k][0].record(stream)
+        plans[k % N_BATCHES].launch(stream)
+        ev[k][1].record(stream)
+        st.finish(stream, k % 2)
+    sync_all()
     kdist = dist_summary([a.elapsed_time(b) for a, b in ev])
     kernel_ms = kdist["mean"]
     total_ms_max, kernel_ms_max, agg_gbps = reduce_over_ranks(

@@ -118,6 +118,13 @@ int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results,
 
 /* emb_dev_query.flags */
 #define EMB_Q_RAW_SUMS 1u /* FIXED tables: write the int32 sums, skip the /1e9 (row shards) */
+/* Plans only, and only when EVERY query of the plan carries it: nothing this launch READS (tables, indices,
+ * offsets) is written by the kernel in front of it on the stream.  The launch may then gather and pool while that
+ * kernel is still running (programmatic dependent launch); only its result stores wait for it to complete.  In a
+ * loop of emb_plan_launch [+ emb_exchange_finish] calls this hides the pooling launch's tail, the launch latency and
+ * the exchange's completion wait behind the next batch's gathers.  Without the flag a launch reads nothing before
+ * the kernel in front of it has completed (stream order as usual). */
+#define EMB_Q_OVERLAP 2u
 
 typedef struct emb_shape {
     uint32_t nr_tables;             /* NR_TABLES                                      */

@@ -414,8 +414,28 @@ void launch_ordered(int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d,
 /* Stretch kernel: K rows in flight per lane, BAGS = sub-warps x mult bags per one-warp CTA, STAGE lookups per
  * pass (the smaller pass keeps shared memory -- and so the L1 the row loads live in -- small; knob
  * EMB_STRETCH_STAGE=1 doubles it). */
+/* Launch with the programmatic-stream-serialization attribute: the kernel may become resident while the kernel in
+ * front of it on the stream is draining (it must order itself with griddepcontrol.wait -- only kernels that do are
+ * launched through here).  EMB_PDL=0 (measurement knob) launches plainly. */
+template <typename... KArgs, typename... Args>
+void launch_dependent(void (*kern)(KArgs...), uint32_t grid, uint32_t block, cudaStream_t s, Args... args)
+{
+    static const bool pdl = env_u32("EMB_PDL", 1) != 0;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.blockDim = dim3(block, 1, 1);
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);  // the caller checks cudaGetLastError
+}
+
 template <int LANES, int K, int MULT, bool IS_FLOAT>
-void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni, uint32_t overlap)
 {
     constexpr int SUB = 32 / LANES;
     constexpr int BAGS = SUB * MULT < 64 ? SUB * MULT : 64;  // stretch_bags() below
@@ -424,33 +444,36 @@ void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDes
     constexpr int LARGE = 2 * SMALL;
     constexpr int MINB = 32;
     if (big_stage)
-        emb::bag_sum_stretch_kernel<LANES, K, BAGS, LARGE, IS_FLOAT, MINB><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
+        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, LARGE, IS_FLOAT, MINB>, grid, 32, s, d, n, uni, g.d_err,
+                         overlap);
     else
-        emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, MINB><<<grid, 32, 0, s>>>(d, n, uni, g.d_err);
+        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, MINB>, grid, 32, s, d, n, uni, g.d_err,
+                         overlap);
 }
 
 template <int LANES, int K, bool IS_FLOAT>
-void launch_stretch_k(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+void launch_stretch_k(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni, uint32_t overlap)
 {
     switch (v.mult) {
-    case 1: return launch_stretch_m<LANES, K, 1, IS_FLOAT>(v.stage, grid, s, d, n, uni);
-    case 4: return launch_stretch_m<LANES, K, 4, IS_FLOAT>(v.stage, grid, s, d, n, uni);
-    case 8: return launch_stretch_m<LANES, K, 8, IS_FLOAT>(v.stage, grid, s, d, n, uni);
-    default: return launch_stretch_m<LANES, K, 2, IS_FLOAT>(v.stage, grid, s, d, n, uni);
+    case 1: return launch_stretch_m<LANES, K, 1, IS_FLOAT>(v.stage, grid, s, d, n, uni, overlap);
+    case 4: return launch_stretch_m<LANES, K, 4, IS_FLOAT>(v.stage, grid, s, d, n, uni, overlap);
+    case 8: return launch_stretch_m<LANES, K, 8, IS_FLOAT>(v.stage, grid, s, d, n, uni, overlap);
+    default: return launch_stretch_m<LANES, K, 2, IS_FLOAT>(v.stage, grid, s, d, n, uni, overlap);
     }
 }
 
 template <int LANES>
-void launch_stretch(const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+void launch_stretch(const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni,
+                    uint32_t overlap)
 {
     if (is_float) {
         if (v.unroll == 4)
-            return launch_stretch_k<LANES, 4, true>(v, grid, s, d, n, uni);
-        return launch_stretch_k<LANES, 8, true>(v, grid, s, d, n, uni);
+            return launch_stretch_k<LANES, 4, true>(v, grid, s, d, n, uni, overlap);
+        return launch_stretch_k<LANES, 8, true>(v, grid, s, d, n, uni, overlap);
     }
     if (v.unroll == 4)
-        return launch_stretch_k<LANES, 4, false>(v, grid, s, d, n, uni);
-    launch_stretch_k<LANES, 8, false>(v, grid, s, d, n, uni);
+        return launch_stretch_k<LANES, 4, false>(v, grid, s, d, n, uni, overlap);
+    launch_stretch_k<LANES, 8, false>(v, grid, s, d, n, uni, overlap);
 }
 
 template <int LANES>
@@ -472,10 +495,11 @@ void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uin
 }
 
 template <int LANES>
-void launch_for_lanes(const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+void launch_for_lanes(const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni,
+                      uint32_t overlap)
 {
-    if (v.kind == 6)
-        launch_stretch<LANES>(v, is_float, grid, s, d, n, uni);
+    if (v.kind == 6)  // the one kernel that orders its result stores itself (EMB_Q_OVERLAP)
+        launch_stretch<LANES>(v, is_float, grid, s, d, n, uni, overlap);
     else if (v.kind == 4)
         launch_tma<LANES>(grid, s, d, n, uni);
     else
@@ -498,19 +522,19 @@ uint32_t uniform_chunks(const BagDesc *h, uint32_t n)
 
 /* `uni` = uniform_chunks() of the n descriptors (0 = search). */
 int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_t uni, uint32_t grid, cudaStream_t s,
-                   bool is_float = false)
+                   bool is_float = false, bool overlap = false)
 {
     if (grid == 0)
         return EMB_OK;
     uint32_t D = g.shape.nr_cols;
     switch (v.kind ? lanes_for_dim(D) : 0) {
     case 0: emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, uni, D, g.d_err); break;
-    case 1: launch_for_lanes<1>(v, is_float, grid, s, d_descs, n, uni); break;
-    case 2: launch_for_lanes<2>(v, is_float, grid, s, d_descs, n, uni); break;
-    case 4: launch_for_lanes<4>(v, is_float, grid, s, d_descs, n, uni); break;
-    case 8: launch_for_lanes<8>(v, is_float, grid, s, d_descs, n, uni); break;
-    case 16: launch_for_lanes<16>(v, is_float, grid, s, d_descs, n, uni); break;
-    default: launch_for_lanes<32>(v, is_float, grid, s, d_descs, n, uni); break;
+    case 1: launch_for_lanes<1>(v, is_float, grid, s, d_descs, n, uni, overlap ? 1u : 0u); break;
+    case 2: launch_for_lanes<2>(v, is_float, grid, s, d_descs, n, uni, overlap ? 1u : 0u); break;
+    case 4: launch_for_lanes<4>(v, is_float, grid, s, d_descs, n, uni, overlap ? 1u : 0u); break;
+    case 8: launch_for_lanes<8>(v, is_float, grid, s, d_descs, n, uni, overlap ? 1u : 0u); break;
+    case 16: launch_for_lanes<16>(v, is_float, grid, s, d_descs, n, uni, overlap ? 1u : 0u); break;
+    default: launch_for_lanes<32>(v, is_float, grid, s, d_descs, n, uni, overlap ? 1u : 0u); break;
     }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
@@ -604,6 +628,7 @@ struct emb_plan {
     uint64_t bytes = 0;
     Variant variant = {0, 1, 1, 8, 0};
     bool all_float = false;
+    bool overlap = false;  // EMB_Q_OVERLAP on every query
 };
 
 extern "C" {
@@ -914,13 +939,15 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
     p->h.resize(n);
     uint64_t chunk = 0;
     const uint64_t D = g.shape.nr_cols;
-    bool any_float = false, all_float = true;
+    bool any_float = false, all_float = true, overlap = true;
     for (uint32_t i = 0; i < n; i++) {
         const bool f = queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].kind == EMB_TABLE_FLOAT;
         any_float |= f;
         all_float &= f;
+        overlap &= (queries[i].flags & EMB_Q_OVERLAP) != 0;
     }
     p->all_float = all_float;
+    p->overlap = overlap;
     {
         uint64_t li = 0, nb = 0;
         for (uint32_t i = 0; i < n; i++) {
@@ -971,7 +998,7 @@ int emb_plan_launch(emb_plan *plan, void *stream)
         if (tg.first >= g.tables.size() || g.tables[tg.first].generation != tg.second || !g.tables[tg.first].kind)
             return fail(EMB_ESTATE, "plan is stale: table %u was freed or re-allocated after emb_plan_create", tg.first);
     return launch_bag_sum(plan->variant, plan->d, (uint32_t)plan->h.size(), plan->uni, plan->grid,
-                          stream ? (cudaStream_t)stream : g.stream, plan->all_float);
+                          stream ? (cudaStream_t)stream : g.stream, plan->all_float, plan->overlap);
 }
 
 void emb_plan_destroy(emb_plan *plan)
@@ -1171,8 +1198,8 @@ int emb_finish_launch(emb_finish *f, uint32_t epoch, void *stream)
     if (!f)
         return fail(EMB_EINVAL, "NULL finish object");
     cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
-    emb::exchange_finish_kernel<<<f->grid, 256, 0, s>>>(f->flags, f->n_ranks, f->my_rank, epoch, f->d_jobs, f->n_jobs,
-                                                        g.shape.nr_cols, g.d_err);
+    launch_dependent(emb::exchange_finish_kernel, f->grid, 256, s, f->flags, f->n_ranks, f->my_rank, epoch, f->d_jobs, f->n_jobs,
+                     g.shape.nr_cols, g.d_err);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
     return EMB_OK;

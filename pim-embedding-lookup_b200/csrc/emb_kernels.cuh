@@ -325,6 +325,13 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni,
  * Bounds that are not monotone inside the CTA's chunk (overlapping bags, which lookup() permits) are pooled bag
  * by bag, as emb_dpu_lookup.c:106-116 does.
  */
+/* Programmatic dependent launch (sm_90+).  A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization
+ * may be made resident as soon as every CTA of the kernel in front of it on the stream has executed
+ * launch_dependents (or exited); `griddep_wait` then blocks until that kernel has completed and its memory
+ * operations are visible.  Without the launch attribute both are no-ops. */
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 /* table + row * ROWB as ONE instruction (IMAD.WIDE.U32 with the 64-bit lane base as the addend) */
 template <int ROWB>
 __device__ __forceinline__ const uint4 *row_ptr(const char *lane_base, uint32_t row)
@@ -402,8 +409,16 @@ __device__ __forceinline__ uint4 add_rows(uint4 a, uint4 b)
 
 template <int LANES, int K, int BAGS, int STAGE, bool IS_FLOAT, int MINB>
 __global__ void __launch_bounds__(32, MINB)
-bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
+bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag,
+                       uint32_t overlap)
 {
+    // The next kernel on the stream may become resident once the last CTA of this launch has started; this launch
+    // itself waits for the kernel in front of it either here or -- `overlap`, EMB_Q_OVERLAP on every query: nothing
+    // this launch READS is written by that kernel -- only in front of its result stores, so that its gathers run
+    // under the tail of the previous pooling launch and under the exchange's completion wait.
+    griddep_launch_dependents();
+    if (!overlap)
+        griddep_wait();
     constexpr int SUB = 32 / LANES;  // sub-warps
     constexpr int D = LANES * 4;
     constexpr int ROWB = D * 4;      // bytes per row
@@ -633,6 +648,8 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
 
     const uint32_t bpr = d->bags_per_rank;
     const uint32_t out_stride = d->out_stride;
+    if (overlap)
+        griddep_wait();
 #pragma unroll 2
     for (int it = 0; it < BAGS / SUB; it++) {
         const uint32_t bag = it * SUB + sub;
@@ -1053,6 +1070,10 @@ exchange_finish_kernel(FlagList flags, uint32_t n_ranks, uint32_t my_rank, uint3
                        uint32_t *__restrict__ err_flag)
 {
     const uint32_t tid = threadIdx.x;
+    // resident early (programmatic dependent launch): the launch latency of this kernel and of the one behind it
+    // overlaps the pooling launch's tail; the signal still follows the COMPLETION of everything in front
+    griddep_launch_dependents();
+    griddep_wait();
     if (blockIdx.x == 0 && tid < n_ranks && tid != my_rank)
         st_release_sys(flags.p[tid] + my_rank, epoch);
     if (tid < n_ranks && tid != my_rank) {

@@ -28,7 +28,7 @@ from __future__ import annotations
 import ctypes as C
 
 from . import emblib, exchange, sharding
-from .dputypes import EMB_Q_RAW_SUMS, EMB_TABLE_FIXED
+from .dputypes import EMB_Q_OVERLAP, EMB_Q_RAW_SUMS, EMB_TABLE_FIXED
 
 
 def partial_columns(plan):
@@ -123,10 +123,15 @@ class ShardedTables:
         return sorted({s.table for s in self.local})
 
     # ---- lookups ------------------------------------------------------------------------------
-    def queries(self, indices, offsets, buffer=0):
+    def queries(self, indices, offsets, buffer=0, overlap=False):
         """Query dicts (emblib.Plan / emblib.lookup_device) for one global batch: indices[t] /
         offsets[t] are CUDA int32/uint32 tensors of table t for every t in tables_needed().  The
-        pooled rows land in output buffer `buffer` (alternate 0, 1, ... between consecutive batches)."""
+        pooled rows land in output buffer `buffer` (alternate 0, 1, ... between consecutive batches).
+
+        overlap=True (EMB_Q_OVERLAP, plans only) is a promise: the index / offset tensors and the tables are not
+        written by whatever kernel runs in front of the pooling launch on its stream (they arrive by copy, or were
+        filled earlier).  The launch then gathers while the previous batch's pooling tail and completion wait are
+        still running and holds back only its stores -- the buffer rule of finish() is unchanged."""
         qs = []
         for j, s in enumerate(self.local):
             slot = self.slot_of[j]
@@ -143,11 +148,13 @@ class ShardedTables:
                 q = dict(table_id=slot, indices=indices[s.table], offsets=offsets[s.table], out=None,
                          out_stride=self.parts.stride, bags_per_rank=self.per, flags=EMB_Q_RAW_SUMS,
                          out_peer=self.parts.out_peer_col(self.part_col[(s.table, s.part)], buffer), bag_rotate=rot)
+            if overlap:
+                q["flags"] = q.get("flags", 0) | EMB_Q_OVERLAP
             qs.append(q)
         return qs
 
-    def make_plan(self, indices, offsets, buffer=0):
-        p = emblib.Plan(self.queries(indices, offsets, buffer))
+    def make_plan(self, indices, offsets, buffer=0, overlap=False):
+        p = emblib.Plan(self.queries(indices, offsets, buffer, overlap))
         p.buffer = buffer
         return p
 

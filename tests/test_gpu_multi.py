@@ -182,20 +182,30 @@ def _sharded_worker(rank, world, port, tmp):
         # here: a peer stores batch k+1 into buffer (k+1) % 2 while this rank's copy of batch k may still be
         # pending, and the epoch flags of the completion kernel see a peer one epoch ahead.  The rule that makes two
         # buffers enough: the consumer of result(buffer) is enqueued on the SAME stream before the next finish().
+        # Run twice: plain plans, then plans made with overlap=True (EMB_Q_OVERLAP: a pooling launch gathers while the
+        # previous batch's completion kernel is still waiting for the peers and stores only once it has finished).
         wants = [np.stack(eo.lookup_rows(tabs, idx, off), axis=1)[rank * per:(rank + 1) * per] for idx, off in batches]
-        dist.barrier()
-        copies = []
-        for k in range(8):
-            p = plans[k % 4]
-            st.lookup(p, stream)
-            with torch.cuda.stream(stream):
-                copies.append(st.result_sample_major(p.buffer).clone())
-        stream.synchronize()
-        ok["inflight"] = all(bool(np.array_equal(c.cpu().numpy().view(np.uint32), wants[k % 4].view(np.uint32)))
-                             for k, c in enumerate(copies))
+        plans_ov = []
+        for k, (idx, off) in enumerate(batches):
+            di = {t: torch.from_numpy(idx[t].view(np.int32)).cuda() for t in need}
+            do = {t: torch.from_numpy(off[t].view(np.int32)).cuda() for t in need}
+            plans_ov.append(st.make_plan(di, do, buffer=k % 2, overlap=True))
+        torch.cuda.synchronize()
+        ok["inflight"] = True
+        for which in (plans, plans_ov):
+            dist.barrier()
+            copies = []
+            for k in range(8):
+                p = which[k % 4]
+                st.lookup(p, stream)
+                with torch.cuda.stream(stream):
+                    copies.append(st.result_sample_major(p.buffer).clone())
+            stream.synchronize()
+            ok["inflight"] &= all(bool(np.array_equal(c.cpu().numpy().view(np.uint32), wants[k % 4].view(np.uint32)))
+                                  for k, c in enumerate(copies))
         ok["no_oob"] = emblib.load().emb_check_indices() == 0
         dist.barrier()
-        for p in plans:
+        for p in plans + plans_ov:
             p.close()
         st.close()
         emblib.shutdown()

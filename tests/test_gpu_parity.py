@@ -303,9 +303,11 @@ def test_page_locked_arrays_take_the_mapped_path_and_match(emblib, D):
     assert emblib.load().emb_check_indices() == 0
 
 
-def test_large_call_pipelines_groups_with_mapped_results(emblib):
-    """Enough bytes for several pipeline groups: staged inputs, results written in place."""
-    from pim_embedding_lookup_b200.dputypes import EMB_HOST_MAPPED_OUT
+def test_large_call_pipelines_groups(emblib):
+    """Enough bytes for several pipeline groups.  EMB_HOST_AUTO on page-locked arrays copies both ways through the
+    copy engines (the faster of the two on C2, profiles/r2_host_path.md); EMB_HOST_MAPPED_OUT stages the inputs and
+    lets the kernel write the results in place.  Same bits either way."""
+    from pim_embedding_lookup_b200.dputypes import EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED_OUT
     rng = np.random.default_rng(5)
     T, D, R, B = 6, 16, 50000, 30000
     emblib.configure(T, D)
@@ -323,11 +325,18 @@ def test_large_call_pipelines_groups_with_mapped_results(emblib):
         poff.append(b)
         pres.append(emblib.pinned_array((B, D), np.float32))
     want = eo.lookup_rows(tabs, pidx, poff)
-    got = emblib.lookup_ex(pidx, poff, pres)
-    tm = emblib.last_timings()
-    assert tm.path == EMB_HOST_MAPPED_OUT and tm.launches > 1
-    for t in range(T):
-        assert np.array_equal(bits(got[t]), bits(want[t])), t
+    try:
+        for forced, expect in ((EMB_HOST_AUTO, EMB_HOST_COPY), (EMB_HOST_MAPPED_OUT, EMB_HOST_MAPPED_OUT)):
+            emblib.set_host_path(forced)
+            for r in pres:
+                r[:] = 0
+            got = emblib.lookup_ex(pidx, poff, pres)
+            tm = emblib.last_timings()
+            assert tm.path == expect and tm.launches > 1, (forced, tm.path, tm.launches)
+            for t in range(T):
+                assert np.array_equal(bits(got[t]), bits(want[t])), (forced, t)
+    finally:
+        emblib.set_host_path(EMB_HOST_AUTO)
 
 
 TUNINGS = [(1, 4, 0), (1, 8, 0), (4, 0, 0), (6, 8, 1), (6, 8, 2), (6, 4, 4), (6, 8, 8), (6, 4, 1), (6, 4, 2), (6, 8, 4)]

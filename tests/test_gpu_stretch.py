@@ -203,3 +203,50 @@ def test_stale_plans_refuse_to_launch(emblib):
     with pytest.raises(emblib.EmbError):
         plan.launch(torch.cuda.current_stream())
     plan.close()
+
+
+@pytest.mark.parametrize("D", [16, 64])
+def test_overlapping_launches_keep_stream_order_for_their_stores(emblib, D):
+    """EMB_Q_OVERLAP (programmatic dependent launch): a launch may gather while the kernel in front of it is still
+    running, but its result stores wait for that kernel.  Two plans write the SAME output buffer alternately and a
+    device-side copy of the buffer sits between every two launches: each copy must hold exactly the rows of the
+    launch in front of it -- a store that ran early would show up in the copy before it."""
+    from pim_embedding_lookup_b200.dputypes import EMB_Q_OVERLAP
+    rng = np.random.default_rng(90 + D)
+    R, B = 50000, 30000
+    emblib.configure(1, D)
+    q = table(rng, R, D)
+    emblib.populate_table_i32(0, q)
+    out = torch.zeros((B, D), dtype=torch.float32, device="cuda")
+    plans, wants = [], []
+    for k in range(2):
+        lens = rng.integers(0, 25, size=B)
+        off = offsets_of(lens)
+        idx = rng.integers(0, R, size=int(lens.sum())).astype(np.uint32)
+        di, do = u32(idx), u32(off)
+        plans.append((emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=out, flags=EMB_Q_OVERLAP)]), di, do))
+        wants.append(eo.lookup_rows([q], [idx], [off])[0])
+    stream = torch.cuda.Stream()
+    copies = []
+    with torch.cuda.stream(stream):
+        for k in range(12):
+            plans[k % 2][0].launch(stream)
+            copies.append(out.clone())  # a kernel that READS the buffer the next launch overwrites
+    stream.synchronize()
+    for k, c in enumerate(copies):
+        assert np.array_equal(bits(c.cpu().numpy()), bits(wants[k % 2])), k
+    # back to back with nothing in between (the launches overlap one another), distinct buffers
+    outs = [torch.zeros((B, D), dtype=torch.float32, device="cuda") for _ in range(2)]
+    plans2 = [emblib.Plan([dict(table_id=0, indices=p[1], offsets=p[2], out=o, flags=EMB_Q_OVERLAP)])
+              for p, o in zip(plans, outs)]
+    with torch.cuda.stream(stream):
+        for k in range(10):
+            plans2[k % 2].launch(stream)
+    stream.synchronize()
+    for k in range(2):
+        assert np.array_equal(bits(outs[k].cpu().numpy()), bits(wants[k]))
+    assert emblib.load().emb_check_indices() == 0
+    for p in plans:
+        p[0].close()
+    for p in plans2:
+        p.close()
