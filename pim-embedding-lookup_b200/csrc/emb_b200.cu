@@ -418,12 +418,11 @@ void launch_ordered(int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d,
  * front of it on the stream is draining (it must order itself with griddepcontrol.wait -- only kernels that do are
  * launched through here).  EMB_PDL=0 (measurement knob) launches plainly. */
 template <typename... KArgs, typename... Args>
-void launch_dependent(void (*kern)(KArgs...), uint32_t grid, uint32_t block, cudaStream_t s, Args... args)
+void launch_dependent(void (*kern)(KArgs...), dim3 grid, uint32_t block, cudaStream_t s, Args... args)
 {
     static const bool pdl = env_u32("EMB_PDL", 1) != 0;
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof cfg);
-    cfg.gridDim = dim3(grid, 1, 1);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
     cfg.blockDim = dim3(block, 1, 1);
     cfg.stream = s;
     cudaLaunchAttribute at[1];
@@ -443,11 +442,14 @@ void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDes
     constexpr int SMALL = (LANES <= 4 ? 256 : 128) < UNIT ? UNIT : (LANES <= 4 ? 256 : 128);
     constexpr int LARGE = 2 * SMALL;
     constexpr int MINB = 32;
+    if (n > 65535)  // gridDim.y limit: search for the query instead
+        uni = 0;
+    const dim3 g2 = uni ? dim3(uni, n, 1) : dim3(grid, 1, 1);  // uniform launches: x = chunk, y = query
     if (big_stage)
-        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, LARGE, IS_FLOAT, MINB>, grid, 32, s, d, n, uni, g.d_err,
+        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, LARGE, IS_FLOAT, MINB>, g2, 32, s, d, n, uni, g.d_err,
                          overlap);
     else
-        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, MINB>, grid, 32, s, d, n, uni, g.d_err,
+        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, MINB>, g2, 32, s, d, n, uni, g.d_err,
                          overlap);
 }
 
@@ -1198,7 +1200,7 @@ int emb_finish_launch(emb_finish *f, uint32_t epoch, void *stream)
     if (!f)
         return fail(EMB_EINVAL, "NULL finish object");
     cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
-    launch_dependent(emb::exchange_finish_kernel, f->grid, 256, s, f->flags, f->n_ranks, f->my_rank, epoch, f->d_jobs, f->n_jobs,
+    launch_dependent(emb::exchange_finish_kernel, dim3(f->grid, 1, 1), 256, s, f->flags, f->n_ranks, f->my_rank, epoch, f->d_jobs, f->n_jobs,
                      g.shape.nr_cols, g.d_err);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());

@@ -96,6 +96,9 @@ __device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t *p)
     return r;
 }
 
+/* Result rows: written once, never read by this kernel.  Cache-streaming (.cs), write-through (.wt), plain stores
+ * and L2 evict_first / evict_last policies all measure the same to four digits on both result layouts
+ * (profiles/r2_scaling.md). */
 __device__ __forceinline__ void stg_stream16(void *p, uint4 v)
 {
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
@@ -437,12 +440,25 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
     const uint32_t lane = threadIdx.x;
     const uint32_t sub = lane / LANES;
     const uint32_t sl = lane % LANES;
-    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
+    // Which (query, chunk) is this CTA?  Uniform launches (every query owns `uni` chunks) use a 2-D grid: blockIdx.y is
+    // the query, blockIdx.x the chunk, no division.  CTAs are handed out x-fastest, so the launch walks the tables one
+    // after the other -- the order everything else was measured against: interleaving the chunks of 2 / 4 / 8
+    // neighbouring tables (so that the 64-byte rows of a sample-major result reach L2 as whole lines) costs
+    // +11 / +30 / +48 % on C2, because the rows being gathered then come from 2 / 4 / 8 tables at once
+    // (profiles/r2_scaling.md).
+    uint32_t q, chunk;
+    if (uni) {
+        q = blockIdx.y;
+        chunk = blockIdx.x;
+    } else {
+        q = find_desc(descs, n_desc, 0, blockIdx.x);
+        chunk = blockIdx.x - __ldg(&descs[q].chunk_begin);
+    }
     const BagDesc *__restrict__ d = descs + q;
 
     const uint32_t B = d->nr_batches;
     const uint32_t ilen = d->indices_len;
-    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, BAGS);
+    const uint32_t b0 = chunk_first_bag(d, chunk, BAGS);
     const uint32_t nb = min((uint32_t)BAGS, d->bag_end - b0);
     const uint32_t *__restrict__ g_idx = d->indices;
     const uint32_t *__restrict__ g_off = d->offsets;

@@ -37,10 +37,11 @@ def main():
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     gen = torch.Generator(device="cuda").manual_seed(1234)
-    lim = int(1e9 / np.sqrt(R))
+    rows_t = w.get("rows", [R] * T)
     for t in range(T):
-        a = torch.randint(-lim, lim + 1, (R, D), dtype=torch.int32, device="cuda", generator=gen)
-        emblib.check(lib.emb_populate_table_device(t, R, a.data_ptr(), 0, 1, stream.cuda_stream))
+        lim = int(1e9 / np.sqrt(rows_t[t]))
+        a = torch.randint(-lim, lim + 1, (rows_t[t], D), dtype=torch.int32, device="cuda", generator=gen)
+        emblib.check(lib.emb_populate_table_device(t, rows_t[t], a.data_ptr(), 0, 1, stream.cuda_stream))
         del a
     batches = [bench.make_batch(w, seed=123 + k) for k in range(2)]
     dev = [([torch.from_numpy(i.view(np.int32)).cuda() for i in idx], [torch.from_numpy(o.view(np.int32)).cuda() for o in off])
