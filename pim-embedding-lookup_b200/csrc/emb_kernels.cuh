@@ -410,7 +410,7 @@ __device__ __forceinline__ uint4 add_rows(uint4 a, uint4 b)
     return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
 }
 
-template <int LANES, int K, int BAGS, int STAGE, bool IS_FLOAT, int MINB>
+template <int LANES, int K, int BAGS, int STAGE, bool IS_FLOAT, int MINB, bool COMPACT = false>
 __global__ void __launch_bounds__(32, MINB)
 bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag,
                        uint32_t overlap)
@@ -489,19 +489,46 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
         const uint32_t i = r * 32 + lane;
         offv[r] = (i < nb) ? min(offv[r], ilen) : 0xffffffffu;
     }
+    // COMPACT (row shards, kDescSharded): the pass machinery below works on the stream of IN-RANGE lookups only.
+    // coff[r] = position in that stream where local bag r*32 + lane starts, known once the index stream has been
+    // read up to the bag's bound (0xffffffff before: "not reached yet", which every comparison below treats
+    // correctly as "beyond everything staged so far"); wend = its total length, known when the window is exhausted.
+    uint32_t coff[COMPACT ? NB : 1];
+    uint32_t wend = COMPACT ? 0xffffffffu : whi;
+#pragma unroll
+    for (int r = 0; r < (COMPACT ? NB : 1); r++)
+        coff[r] = 0xffffffffu;
+    auto bound = [&](int r) -> uint32_t {
+        if constexpr (COMPACT)
+            return coff[r];
+        else
+            return offv[r];
+    };
     // bound of the bag after local bag r*32 + lane (the window's end for the last one)
     auto next_bound = [&](int r) {
-        uint32_t up = __shfl_down_sync(0xffffffffu, offv[r], 1);
+        uint32_t up = __shfl_down_sync(0xffffffffu, bound(r), 1);
         if (r + 1 < NB) {
-            const uint32_t first_of_next = __shfl_sync(0xffffffffu, offv[r + 1 < NB ? r + 1 : r], 0);
+            const uint32_t first_of_next = __shfl_sync(0xffffffffu, bound(r + 1 < NB ? r + 1 : r), 0);
             if (lane == 31)
                 up = first_of_next;
         }
-        return (r * 32 + lane + 1 >= nb) ? whi : up;
+        return (r * 32 + lane + 1 >= nb) ? wend : up;
     };
 #pragma unroll
     for (int r = 0; r < NB; r++) {
-        const uint32_t up = next_bound(r);  // shuffles: every lane takes part
+        uint32_t up;  // shuffles: every lane takes part
+        if constexpr (COMPACT) {
+            up = __shfl_down_sync(0xffffffffu, offv[r], 1);
+            if (r + 1 < NB) {
+                const uint32_t first_of_next = __shfl_sync(0xffffffffu, offv[r + 1 < NB ? r + 1 : r], 0);
+                if (lane == 31)
+                    up = first_of_next;
+            }
+            if (r * 32 + lane + 1 >= nb)
+                up = whi;
+        } else {
+            up = next_bound(r);
+        }
         nonmono |= r * 32 + lane < nb && offv[r] > up;
     }
     nonmono = __any_sync(0xffffffffu, nonmono);
@@ -518,52 +545,113 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
         const uint32_t mark_s = (uint32_t)__cvta_generic_to_shared(s_mark);
         const uint32_t head_s = (uint32_t)__cvta_generic_to_shared(s_head) + sub * ROWB + sl * 16;
         const uint32_t acc_base = acc_s + sl * 16 - ROWB;  // + mark * ROWB = this lane's 16 bytes of bag mark-1
-        for (uint32_t base = wlo; base < whi; base += STAGE) {
-            const uint32_t n = min((uint32_t)STAGE, whi - base);
-            const uint32_t per = K * ((n + SUB * K - 1) / (SUB * K));  // lookups per sub-warp, a multiple of K
-            // ---- stage: all index loads of the pass go out back to back
-            uint32_t raw[NST];
-#pragma unroll
-            for (int j = 0; j < NST; j++) {
-                const uint32_t i = j * 32 + lane;
-                raw[j] = 0;
-                if (i < n)
-                    raw[j] = ldg_stream_u32(g_idx + base + i);
-            }
-            if (lane < STAGE / 16)
-                sts_u128(mark_s + lane * 16, make_uint4(0u, 0u, 0u, 0u));
-            // ---- while they fly: the bag each stretch begins in (= the bag its head belongs to): the last bag
-            // whose bound is <= the stretch's first position, counted with one ballot per bound register
+        // base = first position of the pass, in the coordinates of the bounds (index stream; COMPACT: stream of
+        // in-range lookups); src = next position of the index stream to read (COMPACT only)
+        uint32_t src = wlo;
+        for (uint32_t base = COMPACT ? 0u : wlo;;) {
+            uint32_t n, per;
             uint32_t hb = 0;
+            auto head_bags = [&]() {
+                // the bag each stretch begins in (= the bag its head belongs to): the last bag whose bound is <= the
+                // stretch's first position, counted with one ballot per bound register
 #pragma unroll
-            for (int s = 0; s < SUB; s++) {
-                const uint32_t pos = base + s * per;
-                uint32_t cnt = 0;
+                for (int s = 0; s < SUB; s++) {
+                    const uint32_t pos = base + s * per;
+                    uint32_t cnt = 0;
 #pragma unroll
-                for (int r = 0; r < NB; r++)
-                    cnt += __popc(__ballot_sync(0xffffffffu, offv[r] <= pos));  // bounds past nb are 0xffffffff
-                if ((uint32_t)s == sub)
-                    hb = cnt - 1;  // bound 0 = wlo <= base, so cnt >= 1
+                    for (int r = 0; r < NB; r++)
+                        cnt += __popc(__ballot_sync(0xffffffffu, bound(r) <= pos));  // bounds past nb are 0xffffffff
+                    if ((uint32_t)s == sub)
+                        hb = cnt - 1;  // bound 0 <= base, so cnt >= 1
+                }
+            };
+            if constexpr (!COMPACT) {
+                if (base >= whi)
+                    break;
+                n = min((uint32_t)STAGE, whi - base);
+                per = K * ((n + SUB * K - 1) / (SUB * K));  // lookups per sub-warp, a multiple of K
+                // ---- stage: all index loads of the pass go out back to back
+                uint32_t raw[NST];
+#pragma unroll
+                for (int j = 0; j < NST; j++) {
+                    const uint32_t i = j * 32 + lane;
+                    raw[j] = 0;
+                    if (i < n)
+                        raw[j] = ldg_stream_u32(g_idx + base + i);
+                }
+                if (lane < STAGE / 16)
+                    sts_u128(mark_s + lane * 16, make_uint4(0u, 0u, 0u, 0u));
+                head_bags();  // while they fly
+#pragma unroll
+                for (int j = 0; j < NST; j++) {
+                    const uint32_t i = j * 32 + lane;
+                    uint32_t r = raw[j] - row_base;  // unsigned: rows below the shard wrap high
+                    const bool in_range = r < rows;
+                    bad |= i < n && !in_range;
+                    if (i >= n || !in_range)
+                        r = rows;  // the all-zero row behind the table
+                    s_idx[i] = r;  // every slot of the pass buffer, padding included
+                }
+            } else {
+                // ---- stage: read the index stream 32 positions at a time (up to 4 loads in flight) and keep the
+                // rows of this shard, in order, until the pass buffer is full or the window ends.  A ballot per round
+                // gives every kept lookup its slot and every bag bound inside the round its place in the kept stream.
+                if (lane < STAGE / 16)
+                    sts_u128(mark_s + lane * 16, make_uint4(0u, 0u, 0u, 0u));
+                n = 0;
+                while (src < whi && n + 32 <= (uint32_t)STAGE) {
+                    const uint32_t G = min(4u, ((uint32_t)STAGE - n) / 32);
+                    uint32_t raw[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t i = src + j * 32 + lane;
+                        raw[j] = 0xffffffffu;
+                        if ((uint32_t)j < G && i < whi)
+                            raw[j] = ldg_stream_u32(g_idx + i);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        if ((uint32_t)j >= G)
+                            break;
+                        const uint32_t p0 = src + j * 32;
+                        const uint32_t r = raw[j] - row_base;  // unsigned: rows below the shard wrap high
+                        const bool keep = p0 + lane < whi && r < rows;
+                        const uint32_t m = __ballot_sync(0xffffffffu, keep);
+                        if (keep)
+                            s_idx[n + __popc(m & ((1u << lane) - 1u))] = r;
+#pragma unroll
+                        for (int rr = 0; rr < NB; rr++) {
+                            const uint32_t o = offv[rr] - p0;  // bounds past nb are 0xffffffff: never inside a round
+                            if (o < 32)
+                                coff[rr] = base + n + __popc(m & ((1u << o) - 1u));
+                        }
+                        n += __popc(m);
+                    }
+                    src += 32 * G;
+                }
+                if (src >= whi) {  // window exhausted: the kept stream ends here, and so do the bags not reached
+                    wend = base + n;
+#pragma unroll
+                    for (int rr = 0; rr < NB; rr++)
+                        if (rr * 32 + lane < nb && coff[rr] == 0xffffffffu)
+                            coff[rr] = wend;
+                }
+                if (n == 0)
+                    break;  // nothing kept: only possible once the window is exhausted
+                per = K * ((n + SUB * K - 1) / (SUB * K));
+                for (uint32_t i = n + lane; i < SUB * per; i += 32)
+                    s_idx[i] = rows;  // padding gathers the all-zero row behind the table
+                head_bags();
             }
             const bool active = sub * per < n;  // idle sub-warps (all padding) have an all-zero head
-#pragma unroll
-            for (int j = 0; j < NST; j++) {
-                const uint32_t i = j * 32 + lane;
-                uint32_t r = raw[j] - row_base;  // unsigned: rows below the shard wrap high
-                const bool in_range = r < rows;
-                bad |= i < n && !in_range;
-                if (i >= n || !in_range)
-                    r = rows;  // the all-zero row behind the table
-                s_idx[i] = r;  // every slot of the pass buffer, padding included
-            }
             __syncwarp();
             // ---- start markers: one byte store per non-empty bag that begins inside this pass
 #pragma unroll
             for (int r = 0; r < NB; r++) {
                 const uint32_t i = r * 32 + lane;
-                const uint32_t rel = offv[r] - base;
+                const uint32_t rel = bound(r) - base;
                 const uint32_t up = next_bound(r);
-                if (i < nb && offv[r] < up && rel < n)  // rel wraps high for bags that began before the pass
+                if (i < nb && bound(r) < up && rel < n)  // rel wraps high for bags that began before the pass
                     s_mark[rel] = (uint8_t)(i + 1);
             }
             __syncwarp();
@@ -630,6 +718,13 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                 }
             }
             __syncwarp();
+            if constexpr (COMPACT) {
+                base += n;
+                if (src >= whi)
+                    break;
+            } else {
+                base += STAGE;
+            }
         }
     } else {
         // bags overlap or run backwards: pool each bag on its own, as emb_dpu_lookup.c:106-116 does
@@ -638,7 +733,14 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
 #pragma unroll
         for (int r = 0; r < NB; r++) {
             const uint32_t i = r * 32 + lane;
-            const uint32_t up = next_bound(r);
+            uint32_t up = __shfl_down_sync(0xffffffffu, offv[r], 1);  // (next_bound speaks COMPACT coordinates)
+            if (r + 1 < NB) {
+                const uint32_t first_of_next = __shfl_sync(0xffffffffu, offv[r + 1 < NB ? r + 1 : r], 0);
+                if (lane == 31)
+                    up = first_of_next;
+            }
+            if (i + 1 >= nb)
+                up = whi;
             if (i < nb) {
                 s_off[2 * i] = offv[r];
                 s_off[2 * i + 1] = up;

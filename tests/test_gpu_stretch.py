@@ -250,3 +250,62 @@ def test_overlapping_launches_keep_stream_order_for_their_stores(emblib, D):
         p[0].close()
     for p in plans2:
         p.close()
+
+
+@pytest.mark.parametrize("D", [4, 16, 64, 128])
+@pytest.mark.parametrize("parts", [2, 3, 8])
+def test_row_shards_pool_only_their_own_lookups(emblib, D, parts):
+    """Row shards in a plan go through the compacting instantiation (bag_sum_stretch_kernel<..., COMPACT>): a
+    shard stages only the lookups of its row range.  Bag patterns against its units: windows longer than a pass
+    of KEPT lookups, bags with no lookup in the shard, bounds on round (32) and pass boundaries, runs of empty
+    bags, a window with nothing in range at all.  The int32 partial sums of the parts must add up (wrap-around) to
+    the oracle's sums, bit for bit, also in a plan that mixes a whole table with the shards and with EMB_Q_OVERLAP."""
+    from pim_embedding_lookup_b200.dputypes import EMB_Q_OVERLAP, EMB_Q_RAW_SUMS
+    rng = np.random.default_rng(400 + 10 * D + parts)
+    R = 4000
+    emblib.configure(parts + 1, D)
+    lib = emblib.load()
+    q = table(rng, R, D)
+    cuts = np.concatenate([[0], np.sort(rng.choice(np.arange(1, R), size=parts - 1, replace=False)), [R]])
+    emblib.populate_table_i32(0, q)
+    for p in range(parts):
+        emblib.populate_table_i32(1 + p, q[cuts[p]:cuts[p + 1]])
+        emblib.check(lib.emb_table_set_row_base(1 + p, int(cuts[p])))
+    patterns = [
+        list(rng.integers(0, 40, size=700)), [32] * 64, [31, 33, 0, 0, 64, 1] * 30, [5000], [0] * 90 + [3000] + [0] * 90,
+        [1] * 1000, [0] * 300, [256, 0, 257, 0, 0, 255, 1] * 5, list(rng.integers(0, 3, size=2000)), [700, 700, 700],
+    ]
+    stream = torch.cuda.current_stream()
+    for pi, lens in enumerate(patterns):
+        lens = np.asarray(lens, dtype=np.int64)
+        B = len(lens)
+        off = offsets_of(lens)
+        idx = rng.integers(0, R, size=int(lens.sum())).astype(np.uint32)
+        if pi == 3:  # one giant bag that never touches part 0
+            idx = rng.integers(int(cuts[1]), R, size=int(lens.sum())).astype(np.uint32)
+        di, do = u32(idx), u32(off)
+        _, sums = eo.lookup_rows([q], [idx], [off], want_sums=True)
+        for flags in (EMB_Q_RAW_SUMS, EMB_Q_RAW_SUMS | EMB_Q_OVERLAP):
+            outs = [torch.full((B, D), 7, dtype=torch.int32, device="cuda") for _ in range(parts + 1)]
+            qs = [dict(table_id=1 + p, indices=di, offsets=do, out=outs[1 + p], flags=flags) for p in range(parts)]
+            plan = emblib.Plan(qs)  # shards only
+            plan.launch(stream)
+            torch.cuda.synchronize()
+            tot = outs[1].clone()
+            for p in range(1, parts):
+                tot += outs[1 + p]
+            assert np.array_equal(tot.cpu().numpy(), sums[0]), (D, parts, pi, "shards")
+            plan.close()
+            plan = emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=outs[0], flags=flags)] + qs)  # mixed
+            for o in outs:
+                o.fill_(9)
+            plan.launch(stream)
+            plan.launch(stream)
+            torch.cuda.synchronize()
+            tot = outs[1].clone()
+            for p in range(1, parts):
+                tot += outs[1 + p]
+            assert np.array_equal(tot.cpu().numpy(), sums[0]), (D, parts, pi, "mixed")
+            assert np.array_equal(outs[0].cpu().numpy(), sums[0]), (D, parts, pi, "whole")
+            plan.close()
+    assert lib.emb_check_indices() == 0
