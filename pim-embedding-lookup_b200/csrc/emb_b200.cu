@@ -445,7 +445,7 @@ void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDes
     if (n > 65535)  // gridDim.y limit: search for the query instead
         uni = 0;
     const dim3 g2 = uni ? dim3(uni, n, 1) : dim3(grid, 1, 1);  // uniform launches: x = chunk, y = query
-    // bit 1 of `overlap`: the descriptors are row shards -> the instantiation that stages only the shard's own
+    // bit 1 of `overlap`: row shards among the descriptors -> the instantiation that stages only a shard's own
     // lookups (COMPACT; fixed-point tables, K = 8).  Anything else pools shards with the plain kernel, where a
     // foreign index gathers the all-zero row.
     if constexpr (!IS_FLOAT && K == 8) {
@@ -646,11 +646,9 @@ struct emb_plan {
     Variant variant = {0, 1, 1, 8, 0};
     bool all_float = false;
     bool overlap = false;  // EMB_Q_OVERLAP on every query
-    // Row shards of fixed-point tables are a second launch with their own descriptors h[n_whole..): the kernel
-    // instantiation that stages only a shard's own lookups (bag_sum_stretch_kernel<..., COMPACT>).
-    uint32_t n_whole = 0;
-    uint32_t grid_shards = 0, uni_shards = 0;
-    Variant variant_shards = {0, 1, 1, 8, 0};
+    // The plan holds row shards of fixed-point tables: launched with the kernel instantiation that stages only a
+    // shard's own lookups (bag_sum_stretch_kernel<..., COMPACT>; whole tables in the same launch are staged as usual).
+    bool compact = false;
 };
 
 extern "C" {
@@ -977,52 +975,39 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
         }
         p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0, all_float);
     }
-    // Two groups, each in query order: whole tables (and everything the compacting kernel does not cover), then the
-    // row shards of fixed-point tables.  EMB_SHARD_COMPACT=0 (measurement knob) keeps one group.
+    // Row shards of fixed-point tables: the compacting instantiation (K = 8).  EMB_SHARD_COMPACT=0 (measurement
+    // knob) pools them with the plain kernel, where a foreign index gathers the all-zero row.
     static const bool compact_on = env_u32("EMB_SHARD_COMPACT", 1) != 0;
-    std::vector<uint32_t> order, shard_q;
+    if (compact_on && p->variant.kind == 6 && lanes_for_dim((uint32_t)D) && !any_float)
+        for (uint32_t i = 0; i < n; i++)
+            p->compact |= queries[i].table_id < g.tables.size() && g.tables[queries[i].table_id].sharded;
+    if (p->compact && p->variant.unroll != 8) {
+        p->variant.unroll = 8;
+        if (p->variant.mult > 2)
+            p->variant.mult = 2;
+        p->variant.bags = std::min<uint32_t>(32 / lanes_for_dim((uint32_t)D) * p->variant.mult, 64);
+    }
+    uint64_t chunk = 0;
     for (uint32_t i = 0; i < n; i++) {
-        const bool shard = compact_on && p->variant.kind == 6 && lanes_for_dim((uint32_t)D) && queries[i].table_id < g.tables.size() &&
-                           g.tables[queries[i].table_id].sharded && g.tables[queries[i].table_id].kind == EMB_TABLE_FIXED;
-        (shard ? shard_q : order).push_back(i);
-    }
-    p->n_whole = (uint32_t)order.size();
-    order.insert(order.end(), shard_q.begin(), shard_q.end());
-    // A shard keeps ~1/parts of the lookups of its bags: more bags per CTA, K = 8 (the compacting instantiation)
-    p->variant_shards = p->variant;
-    if (!shard_q.empty()) {
-        const uint32_t lanes = lanes_for_dim((uint32_t)D);
-        p->variant_shards.unroll = 8;
-        p->variant_shards.mult = (int)env_u32("EMB_SHARD_MULT", 8);
-        if (p->variant_shards.mult != 1 && p->variant_shards.mult != 2 && p->variant_shards.mult != 4)
-            p->variant_shards.mult = 8;
-        p->variant_shards.bags = std::min<uint32_t>(32 / lanes * p->variant_shards.mult, 64);
-    }
-    uint64_t chunks[2] = {0, 0};  // CTAs of the two launches; chunk numbers start at 0 in each
-    for (uint32_t k = 0; k < n; k++) {
-        const uint32_t i = order[k];
-        const int grp = k >= p->n_whole;
         uint32_t c = 0;
-        if ((rc = fill_desc(queries[i], &p->h[k], (uint32_t)chunks[grp], grp ? p->variant_shards : p->variant, &c))) {
+        if ((rc = fill_desc(queries[i], &p->h[i], (uint32_t)chunk, p->variant, &c))) {
             delete p;
             return rc;
         }
-        chunks[grp] += c;
+        chunk += c;
         p->gen.emplace_back(queries[i].table_id, g.tables[queries[i].table_id].generation);
         {  // a bag slice reads about its share of the indices (the host cannot see the device offsets)
-            const uint64_t nbq = p->h[k].bag_end - p->h[k].bag_first;
+            const uint64_t nbq = p->h[i].bag_end - p->h[i].bag_first;
             const uint64_t liq = queries[i].nr_batches ? (uint64_t)queries[i].indices_len * nbq / queries[i].nr_batches : 0;
             p->bytes += (liq + nbq) * (4 * D + 4);
         }
     }
-    if (chunks[0] > 0x7fffffffull || chunks[1] > 0x7fffffffull) {
+    if (chunk > 0x7fffffffull) {
         delete p;
         return fail(EMB_EINVAL, "too many bags for one launch");
     }
-    p->grid = (uint32_t)chunks[0];
-    p->grid_shards = (uint32_t)chunks[1];
-    p->uni = uniform_chunks(p->h.data(), p->n_whole);
-    p->uni_shards = uniform_chunks(p->h.data() + p->n_whole, n - p->n_whole);
+    p->grid = (uint32_t)chunk;
+    p->uni = uniform_chunks(p->h.data(), n);
     cudaError_t e = cudaMalloc(&p->d, n * sizeof(BagDesc));
     if (e == cudaSuccess)
         e = cudaMemcpy(p->d, p->h.data(), n * sizeof(BagDesc), cudaMemcpyHostToDevice);
@@ -1044,13 +1029,8 @@ int emb_plan_launch(emb_plan *plan, void *stream)
     for (const auto &tg : plan->gen)
         if (tg.first >= g.tables.size() || g.tables[tg.first].generation != tg.second || !g.tables[tg.first].kind)
             return fail(EMB_ESTATE, "plan is stale: table %u was freed or re-allocated after emb_plan_create", tg.first);
-    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
-    const uint32_t n = (uint32_t)plan->h.size();
-    int rc = launch_bag_sum(plan->variant, plan->d, plan->n_whole, plan->uni, plan->grid, s, plan->all_float, plan->overlap);
-    if (rc == EMB_OK && n > plan->n_whole)  // the row shards: own launch, filling the first one's tail (same rules)
-        rc = launch_bag_sum(plan->variant_shards, plan->d + plan->n_whole, n - plan->n_whole, plan->uni_shards,
-                            plan->grid_shards, s, false, plan->overlap, true);
-    return rc;
+    return launch_bag_sum(plan->variant, plan->d, (uint32_t)plan->h.size(), plan->uni, plan->grid,
+                          stream ? (cudaStream_t)stream : g.stream, plan->all_float, plan->overlap, plan->compact);
 }
 
 void emb_plan_destroy(emb_plan *plan)
@@ -1062,7 +1042,7 @@ void emb_plan_destroy(emb_plan *plan)
 }
 
 uint64_t emb_plan_bytes(const emb_plan *plan) { return plan ? plan->bytes : 0; }
-uint32_t emb_plan_grid(const emb_plan *plan) { return plan ? plan->grid + plan->grid_shards : 0; }
+uint32_t emb_plan_grid(const emb_plan *plan) { return plan ? plan->grid : 0; }
 
 /* One-shot, stream-ordered and asynchronous: the descriptors go through a small ring of
  * page-locked slots (each guarded by an event so a slot is not rewritten before its upload has

@@ -95,6 +95,14 @@ __device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t *p)
     asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
     return r;
 }
+/* The partial sums a peer stored into this rank's slab are read once, AFTER an acquire on the peer's flag: the
+ * coherent path, not ld.global.nc. */
+__device__ __forceinline__ uint4 ldg_stream16(const uint4 *p)
+{
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
 
 /* Result rows: written once, never read by this kernel.  Cache-streaming (.cs), write-through (.wt), plain stores
  * and L2 evict_first / evict_last policies all measure the same to four digits on both result layouts
@@ -327,6 +335,15 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni,
  * only by the reassociation at the <= SUB-1 cut points of a pass (north_star: <= 1e-5 relative).
  * Bounds that are not monotone inside the CTA's chunk (overlapping bags, which lookup() permits) are pooled bag
  * by bag, as emb_dpu_lookup.c:106-116 does.
+ *
+ * COMPACT (plans that hold row shards, kDescSharded): a shard owns rows [row_base, row_base + rows) of its table and
+ * is handed the table's whole index list.  Its CTAs read the index stream 32 positions at a time, keep the rows of
+ * the shard with one ballot per round (slot = running count + popc of the lower lanes) and translate every bag
+ * bound inside the round to its place in the KEPT stream the same way; markers, stretches and heads then work on the
+ * kept stream exactly as above, so a foreign lookup costs 4 bytes of index traffic and a share of a ballot -- no
+ * gather, no accumulate step.  Whole tables in the same launch keep the plain staging.  (Without COMPACT a foreign
+ * index gathers the all-zero row behind the table: correct, L1-resident, but a full accumulate step per lookup.)
+ * profiles/r2_row_shards.md has the measurements.
  */
 /* Programmatic dependent launch (sm_90+).  A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization
  * may be made resident as soon as every CTA of the kernel in front of it on the stream has executed
@@ -493,11 +510,13 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
     // coff[r] = position in that stream where local bag r*32 + lane starts, known once the index stream has been
     // read up to the bag's bound (0xffffffff before: "not reached yet", which every comparison below treats
     // correctly as "beyond everything staged so far"); wend = its total length, known when the window is exhausted.
+    // A whole table in a COMPACT launch keeps stream coordinates (coff = offv) and the usual staging.
+    const bool compacting = COMPACT && (d->flags & kDescSharded);
     uint32_t coff[COMPACT ? NB : 1];
-    uint32_t wend = COMPACT ? 0xffffffffu : whi;
+    uint32_t wend = compacting ? 0xffffffffu : whi;
 #pragma unroll
     for (int r = 0; r < (COMPACT ? NB : 1); r++)
-        coff[r] = 0xffffffffu;
+        coff[r] = compacting ? 0xffffffffu : offv[r];
     auto bound = [&](int r) -> uint32_t {
         if constexpr (COMPACT)
             return coff[r];
@@ -548,7 +567,7 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
         // base = first position of the pass, in the coordinates of the bounds (index stream; COMPACT: stream of
         // in-range lookups); src = next position of the index stream to read (COMPACT only)
         uint32_t src = wlo;
-        for (uint32_t base = COMPACT ? 0u : wlo;;) {
+        for (uint32_t base = compacting ? 0u : wlo;;) {
             uint32_t n, per;
             uint32_t hb = 0;
             auto head_bags = [&]() {
@@ -565,7 +584,7 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                         hb = cnt - 1;  // bound 0 <= base, so cnt >= 1
                 }
             };
-            if constexpr (!COMPACT) {
+            if (!compacting) {
                 if (base >= whi)
                     break;
                 n = min((uint32_t)STAGE, whi - base);
@@ -592,7 +611,7 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                         r = rows;  // the all-zero row behind the table
                     s_idx[i] = r;  // every slot of the pass buffer, padding included
                 }
-            } else {
+            } else if constexpr (COMPACT) {
                 // ---- stage: read the index stream 32 positions at a time (up to 4 loads in flight) and keep the
                 // rows of this shard, in order, until the pass buffer is full or the window ends.  A ballot per round
                 // gives every kept lookup its slot and every bag bound inside the round its place in the kept stream.
@@ -718,7 +737,7 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                 }
             }
             __syncwarp();
-            if constexpr (COMPACT) {
+            if (compacting) {
                 base += n;
                 if (src >= whi)
                     break;
@@ -1211,6 +1230,41 @@ exchange_finish_kernel(FlagList flags, uint32_t n_ranks, uint32_t my_rank, uint3
         const uint64_t n = job->nr_bags * dim;
         const uint32_t np = job->n_parts, ps = job->part_stride, os = job->out_stride;
         uint32_t *__restrict__ out = job->out;
+        if (dim % 4 == 0 && ps % 4 == 0 && os % 4 == 0 && n / 4 < 0xffffffffull) {
+            // 16 bytes per thread per part, the parts' loads independent of each other, 32-bit index arithmetic
+            const uint32_t q = dim / 4, n4 = (uint32_t)(n / 4), ps4 = ps / 4, os4 = os / 4;
+            const uint4 *pp[EMB_MAX_PEERS];
+#pragma unroll
+            for (int s = 0; s < EMB_MAX_PEERS; s++)
+                pp[s] = reinterpret_cast<const uint4 *>(job->parts[s < (int)np ? s : 0]);
+            const bool raw = job->is_raw != 0;
+            for (uint32_t i = blockIdx.x * blockDim.x + tid; i < n4; i += gridDim.x * blockDim.x) {
+                const uint32_t b = i / q, c = i - b * q;
+                const size_t src = (size_t)b * ps4 + c;
+                uint4 v[EMB_MAX_PEERS];
+#pragma unroll
+                for (int s = 0; s < EMB_MAX_PEERS; s++)
+                    if (s < (int)np)
+                        v[s] = ldg_stream16(pp[s] + src);
+                uint4 acc = v[0];
+#pragma unroll
+                for (int s = 1; s < EMB_MAX_PEERS; s++)
+                    if (s < (int)np) {
+                        if (raw)
+                            acc = make_uint4(acc.x + v[s].x, acc.y + v[s].y, acc.z + v[s].z, acc.w + v[s].w);
+                        else
+                            acc = make_uint4(__float_as_uint(__fadd_rn(__uint_as_float(acc.x), __uint_as_float(v[s].x))),
+                                             __float_as_uint(__fadd_rn(__uint_as_float(acc.y), __uint_as_float(v[s].y))),
+                                             __float_as_uint(__fadd_rn(__uint_as_float(acc.z), __uint_as_float(v[s].z))),
+                                             __float_as_uint(__fadd_rn(__uint_as_float(acc.w), __uint_as_float(v[s].w))));
+                    }
+                if (raw)
+                    acc = make_uint4(__float_as_uint(dequant(acc.x)), __float_as_uint(dequant(acc.y)),
+                                     __float_as_uint(dequant(acc.z)), __float_as_uint(dequant(acc.w)));
+                stg_stream16(reinterpret_cast<uint4 *>(out) + (size_t)b * os4 + c, acc);
+            }
+            continue;
+        }
         for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + tid; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
             const uint64_t b = i / dim;
             const uint32_t c = (uint32_t)(i - b * dim);
