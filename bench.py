@@ -807,6 +807,40 @@ def e2e_host_call(args, lib, emblib, batches, lookups, T, B, D, Ke, paths):
     return e2e
 
 
+def run_host_pipeline(torch, stream, n_steps, copy_in, launch, finish, copy_out):
+    """N > 1 e2e: n_steps steps from host buffers with TWO steps in flight.  Step k's host->device copy runs on its
+    own stream while step k-1 pools and step k-1's / k-2's rows drain to the host on a third stream: both PCIe
+    directions busy, as in the one-GPU host call's table groups (a [B/N, T, D] sample-major result cannot be cut by
+    tables, so here the overlap is between steps).  Every copy of every step is inside the caller's timed region.
+    Ordering: the copy-in of step k waits for the launch that read its device arena two steps ago; finish(k) waits for
+    the copy-out of step k-1 (the buffer rule of ShardedTables.finish: the consumer of result(buffer) is ordered
+    before the next finish); the host never has more than two steps enqueued."""
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    in_done = [torch.cuda.Event() for _ in range(2)]
+    comp_done = [torch.cuda.Event() for _ in range(2)]
+    out_done = [torch.cuda.Event() for _ in range(2)]
+    for k in range(n_steps):
+        slot = k % 2
+        if k >= 2:
+            out_done[slot].synchronize()
+            s_in.wait_event(comp_done[slot])
+        with torch.cuda.stream(s_in):
+            copy_in(k)
+            in_done[slot].record(s_in)
+        stream.wait_event(in_done[slot])
+        launch(k)
+        if k >= 1:
+            stream.wait_event(out_done[(k - 1) % 2])
+        finish(k)
+        comp_done[slot].record(stream)
+        s_out.wait_event(comp_done[slot])
+        with torch.cuda.stream(s_out):
+            copy_out(k)
+            out_done[slot].record(s_out)
+    s_out.synchronize()
+    stream.synchronize()
+
+
 def e2e_sharded_path(args, lib, emblib, exchange, slabs, batches, lookups, T, B, D, per, rank, world, Ke, stream,
                      sync_all):
     """N > 1: the sharded product path from host buffers, per step and per rank: this rank's indices + offsets in
@@ -838,34 +872,40 @@ def e2e_sharded_path(args, lib, emblib, exchange, slabs, batches, lookups, T, B,
             send = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
             qs = [dict(table_id=t, indices=di[t], offsets=do[t], out=send[:, t, :], out_stride=T * D) for t in range(T)]
         sets.append((harena, darena, emblib.Plan(qs), send))
-    res_host = torch.empty((per, T * world, D), dtype=torch.float32).pin_memory()
+    res_host = [torch.empty((per, T * world, D), dtype=torch.float32).pin_memory() for _ in range(2)]
+    a2a = {}
 
-    def one(k):
-        harena, darena, plan, send = sets[k % 2]
+    def copy_in(k):
+        harena, darena, _, _ = sets[k % 2]
         darena.copy_(harena, non_blocking=True)
-        plan.launch(stream)
+
+    def launch(k):
+        sets[k % 2][2].launch(stream)
+
+    def finish(k):
         if slabs is not None:
             slabs.barrier()
-            r = slabs.local_sample_major(k % 2)
         else:
-            r = exchange.nccl_all_to_all(send, B, [T] * world, D)
-        res_host.copy_(r, non_blocking=True)
-        stream.synchronize()
-    for k in range(4):
-        one(k)
+            a2a[k % 2] = exchange.nccl_all_to_all(sets[k % 2][3], B, [T] * world, D)
+
+    def copy_out(k):
+        r = slabs.local_sample_major(k % 2) if slabs is not None else a2a[k % 2]
+        res_host[k % 2].copy_(r, non_blocking=True)
+
+    run_host_pipeline(torch, stream, 4, copy_in, launch, finish, copy_out)
     sync_all()
     t0 = time.perf_counter()
-    for k in range(Ke):
-        one(k)
+    run_host_pipeline(torch, stream, Ke, copy_in, launch, finish, copy_out)
     dt = time.perf_counter() - t0
     n_e = sum(lookups[k % 2] for k in range(Ke))
     dt, n_e = reduce_over_ranks([dt, float(n_e)], world, ["max", "sum"])
     for _, _, plan, _ in sets:
         plan.close()
     return {"value": n_e / dt, "unit": "lookups/s", "h2d_bytes_per_step": int(sets[0][0].numel() * 4),
-            "d2h_bytes_per_step": int(res_host.numel() * 4), "ms_per_step": dt / Ke * 1e3, "steps": Ke,
+            "d2h_bytes_per_step": int(res_host[0].numel() * 4), "ms_per_step": dt / Ke * 1e3, "steps": Ke,
             "call": "sharded product path per rank: pinned index/offset arena -> HBM (1 copy), pooling launch with peer-slab "
-                    "stores over NVLink, completion kernel, [B/N, T_global, D] rows -> pinned host (1 copy); bytes are per rank"}
+                    "stores over NVLink, completion kernel, [B/N, T_global, D] rows -> pinned host (1 copy); two steps in "
+                    "flight (copy-in, pooling and copy-out of neighbouring steps overlap); bytes are per rank"}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -1017,20 +1057,16 @@ def bench_sharded(args, w, steps, warmup):
         res_host = torch.empty(tuple(st.result(0).shape), dtype=torch.float32).pin_memory()
         h2d, d2h = sets[0][0].numel() * 4, res_host.numel() * 4
 
-        def e2e_step(k):
-            harena, darena, plan = sets[k % 2]
-            darena.copy_(harena, non_blocking=True)
-            plan.launch(stream)
-            st.finish(stream, k % 2)
-            res_host.copy_(st.result(k % 2), non_blocking=True)
-            stream.synchronize()
-        for k in range(4):
-            e2e_step(k)
+        res_hosts = [res_host, torch.empty_like(res_host).pin_memory()]
+        steps_e2e = (lambda k: sets[k % 2][1].copy_(sets[k % 2][0], non_blocking=True),
+                     lambda k: sets[k % 2][2].launch(stream),
+                     lambda k: st.finish(stream, k % 2),
+                     lambda k: res_hosts[k % 2].copy_(st.result(k % 2), non_blocking=True))
+        run_host_pipeline(torch, stream, 4, *steps_e2e)
         sync_all()
         Ke = max(3, min(K, 50))
         t0 = time.perf_counter()
-        for k in range(Ke):
-            e2e_step(k)
+        run_host_pipeline(torch, stream, Ke, *steps_e2e)
         dt = time.perf_counter() - t0
         (dt,) = reduce_over_ranks([dt], world, ["max"])
         for _, _, p in sets:
@@ -1039,7 +1075,7 @@ def bench_sharded(args, w, steps, warmup):
                "d2h_bytes_per_step": int(d2h), "ms_per_step": dt / Ke * 1e3, "steps": Ke,
                "call": "ShardedTables.lookup per rank: pinned index/offset arena -> HBM (1 copy), pooling launch, peer-slab "
                        "exchange + completion kernel (barrier + partial reduction), [B/N, T, D] rows -> pinned host (1 copy); "
-                       "bytes are rank 0's",
+                       "two steps in flight; bytes are rank 0's",
                "floor_ms": measure_copy_floor(h2d, d2h, world)}
 
     out = None

@@ -24,6 +24,10 @@ except Exception as e:
 PY
   grep -i -E "error|Traceback" -A6 gpurun_out/c4tb_n${N}_${name}_$TAG.err | head -12
 }
+if [ "${QUICK:-0}" = 1 ]; then  # the one line the planner's own placement (bench.py's c4tb extra) does not give
+  run rowcut2_compact "EMB_SHARD_COMPACT=1" --max-table-bytes 6000000000
+  exit 0
+fi
 run planner "EMB_X=0"
 run rowcut_compact "EMB_SHARD_COMPACT=1" --max-table-bytes 3000000000
 run rowcut_scan "EMB_SHARD_COMPACT=0" --max-table-bytes 3000000000
