@@ -75,8 +75,9 @@ def parse_args(argv=None):
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"])
-    ap.add_argument("--layout", default="sample", choices=["table", "sample"],
-                    help="peer-slab layout of the fused exchange: [T][B/N][D] or [B/N][T][D]")
+    ap.add_argument("--layout", default="table", choices=["table", "sample"],
+                    help="peer-slab layout of the fused exchange: [T][B/N][D] (default: the per-table list the interaction "
+                         "concatenates) or [B/N][T][D] (thrashes peer address translation at 8 ranks, profiles/r2_scaling.md)")
     ap.add_argument("--no-rotate", action="store_true",
                     help="fused exchange: every rank walks the destination ranks in the same order (comparator)")
     ap.add_argument("--no-overlap", action="store_true",
@@ -872,7 +873,8 @@ def e2e_sharded_path(args, lib, emblib, exchange, slabs, batches, lookups, T, B,
             send = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
             qs = [dict(table_id=t, indices=di[t], offsets=do[t], out=send[:, t, :], out_stride=T * D) for t in range(T)]
         sets.append((harena, darena, emblib.Plan(qs), send))
-    res_host = [torch.empty((per, T * world, D), dtype=torch.float32).pin_memory() for _ in range(2)]
+    res_shape = tuple(slabs.local(0).shape) if slabs is not None else (per, T * world, D)  # the slab as it lies
+    res_host = [torch.empty(res_shape, dtype=torch.float32).pin_memory() for _ in range(2)]
     a2a = {}
 
     def copy_in(k):
@@ -889,7 +891,7 @@ def e2e_sharded_path(args, lib, emblib, exchange, slabs, batches, lookups, T, B,
             a2a[k % 2] = exchange.nccl_all_to_all(sets[k % 2][3], B, [T] * world, D)
 
     def copy_out(k):
-        r = slabs.local_sample_major(k % 2) if slabs is not None else a2a[k % 2]
+        r = slabs.local(k % 2) if slabs is not None else a2a[k % 2]
         res_host[k % 2].copy_(r, non_blocking=True)
 
     run_host_pipeline(torch, stream, 4, copy_in, launch, finish, copy_out)

@@ -86,15 +86,19 @@ class _DevView:
 class PeerSlabs:
     """Symmetric output slabs mapped across all ranks of `group` (one node, NVLink/NVSwitch)."""
 
-    def __init__(self, global_bags, tables_per_rank, dim, group=None, n_buffers=1, n_cols=None, layout="sample"):
-        """layout "sample" (default): slab = [B/N][T_global][D], sample-major rows ready for the
-        interaction.  layout "table": slab = [T_global][B/N][D], one contiguous [B/N, D] block per table
-        -- the list of per-table tensors the DLRM fork's alltoall hands back
-        (extend_distributed.py:418-426).  Measured on C2 (dim 16): with all slabs in LOCAL memory the
-        table-major launch is 8 % faster (0.279 vs 0.301 ms, tools/route_probe.py: the sample-major
-        rows are 64-byte pieces at a 1664-byte stride), but with the slabs on NVLink peers it is the
-        other way round (N=4: 0.307 vs 0.293 ms; profiles/r1_multi_gpu.md), so sample-major is the
-        default for the exchange.
+    def __init__(self, global_bags, tables_per_rank, dim, group=None, n_buffers=1, n_cols=None, layout="table"):
+        """layout "table" (default): slab = [T_global][B/N][D], one contiguous [B/N, D] block per table -- the list
+        of per-table tensors `interact_features` concatenates (dlrm_s_pytorch.py:480-488; on one GPU apply_emb
+        returns exactly that list).  layout "sample": slab = [B/N][T_global][D], sample-major rows.
+
+        Why table-major is the default (profiles/r2_scaling.md): a pooling launch walks the tables one after the
+        other, so with table-major slabs the rows in flight land in a narrow window of every peer's slab, while with
+        sample-major slabs they are 64-byte pieces spread over the WHOLE slab of every peer.  Once the peer memory
+        written into that way (all peers, all buffers that alternate) passes ~1 GB the stores thrash the GPU's
+        address translation for peer mappings: C2 at 8 ranks, double buffered (7 x 2 x 109 MB) 0.479 ms per launch
+        against 0.226 ms table-major and 0.258 ms single buffered; dim-64 tables at 8 ranks (7 x 2 x 436 MB) 18 ms.
+        tools/slab_reach_probe.py reproduces it on two GPUs with artificially wide slabs.  Sample-major stays
+        available for small slabs (it also costs 3.7 % on one GPU: partial-line writes).
         tables_per_rank[r] = tables rank r owns (consecutive global ids, rank-major), or None with
         n_cols = number of D-wide column blocks per sample when the placement is arbitrary
         (sharded.ShardedTables addresses the blocks itself through out_peer_col)."""

@@ -50,7 +50,7 @@ class ShardedTables:
     (the global mini-batch, divisible by the world size)."""
 
     def __init__(self, rows, dim, global_bags, lookups=None, group=None, hbm_budget=150e9,
-                 max_table_bytes=None, level=True, device=None, n_buffers=2, layout="sample", rotate=True,
+                 max_table_bytes=None, level=True, device=None, n_buffers=2, layout="table", rotate=True,
                  **plan_kwargs):
         import torch
         import torch.distributed as dist
@@ -185,9 +185,9 @@ class ShardedTables:
         return self.result(plan.buffer)
 
     def result(self, buffer=0):
-        """This rank's pooled rows, torch CUDA tensor fp32 (no copy): [B/N, T, D] for the default layout
-        "sample"; [T, B/N, D] for layout "table" (result()[t] = table t's [B/N, D], the per-table list
-        the DLRM fork's alltoall returns)."""
+        """This rank's pooled rows, torch CUDA tensor fp32 (no copy): [T, B/N, D] for the default layout "table"
+        (result()[t] = table t's [B/N, D]: the per-table list interact_features concatenates,
+        dlrm_s_pytorch.py:480-488); [B/N, T, D] for layout "sample" (see exchange.PeerSlabs for when that is safe)."""
         return self.out.local(buffer)
 
     def result_sample_major(self, buffer=0):

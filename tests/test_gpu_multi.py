@@ -55,20 +55,25 @@ def _worker(rank, world, port, tmp):
             dev.append((torch.from_numpy(idx[t].view(np.int32)).cuda(), torch.from_numpy(off[t].view(np.int32)).cuda()))
         stream = torch.cuda.current_stream()
 
-        # (1) fused: the kernel stores into every rank's slab
-        slabs = exchange.PeerSlabs(B, tables_per_rank, D)
-        slabs.local().zero_()
-        torch.cuda.synchronize()
-        dist.barrier()
-        plan = emblib.Plan([dict(table_id=lt, indices=dev[lt][0], offsets=dev[lt][1], out=None,
-                                 out_stride=slabs.stride, bags_per_rank=slabs.per, out_peer=slabs.out_peer(lt))
-                            for lt in range(T_local)])
-        plan.launch(stream)
-        slabs.barrier()
-        torch.cuda.synchronize()
-        got = slabs.local_sample_major().cpu().numpy()
-        ok["fused"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
-        plan.close()
+        # (1) fused: the kernel stores into every rank's slab, table-major (default) and sample-major
+        ok["fused"] = True
+        for layout in ("table", "sample"):
+            slabs = exchange.PeerSlabs(B, tables_per_rank, D, layout=layout)
+            slabs.local().zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            plan = emblib.Plan([dict(table_id=lt, indices=dev[lt][0], offsets=dev[lt][1], out=None,
+                                     out_stride=slabs.stride, bags_per_rank=slabs.per, out_peer=slabs.out_peer(lt))
+                                for lt in range(T_local)])
+            plan.launch(stream)
+            slabs.barrier()
+            torch.cuda.synchronize()
+            got = np.ascontiguousarray(slabs.local_sample_major().cpu().numpy())
+            ok["fused"] &= bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
+            plan.close()
+            dist.barrier()
+            if layout == "table":
+                slabs.close()
 
         # (2) NCCL all_to_all_single of a [N, B/N, T_local, D] send buffer
         send = torch.empty((B, T_local, D), dtype=torch.float32, device="cuda")

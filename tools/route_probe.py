@@ -26,6 +26,9 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--ranks", type=int, default=8)
     ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--wide", type=int, nargs="*", default=[],
+                    help="extra modes: sample-major rows as wide as this many tables (the stride an N-rank exchange has: "
+                         "N x T tables), only the first T columns written")
     args = ap.parse_args()
     import torch
 
@@ -52,10 +55,17 @@ def main():
     btd = torch.empty((B, T, D), dtype=torch.float32, device="cuda")
     slabs = [torch.empty((per, T, D), dtype=torch.float32, device="cuda") for _ in range(N)]
 
+    wide = {f"wide{k}": torch.empty((B // min(8, max(1, k // T)), k, D), dtype=torch.float32, device="cuda") for k in args.wide}
+
     def queries(mode, di, do):
         qs = []
         for t in range(T):
-            if mode == "tbd":
+            if mode in wide:  # rows of a [B/N][k][D] slab: the bags wrap around it (addresses, not values, matter here)
+                buf = wide[mode]
+                nb = buf.shape[0]
+                qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=None, out_stride=buf.shape[1] * D,
+                               bags_per_rank=nb, out_peer=[buf[:, t, :]] * (B // nb)))
+            elif mode == "tbd":
                 qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=tbd[t]))
             elif mode == "btd":
                 qs.append(dict(table_id=t, indices=di[t], offsets=do[t], out=btd[:, t, :], out_stride=T * D))
@@ -66,7 +76,7 @@ def main():
 
     nl = np.mean([sum(len(i) for i in b[0]) for b in batches])
     ref = None
-    for mode in ("tbd", "btd", "slabs", "tbd"):
+    for mode in ["tbd", "btd", "slabs"] + list(wide) + ["tbd"]:
         plans = [emblib.Plan(queries(mode, di, do)) for di, do in dev]
         for i in range(5):
             plans[i % 2].launch(stream)
@@ -78,8 +88,11 @@ def main():
             ev[i][1].record(stream)
         torch.cuda.synchronize()
         ms = sorted(a.elapsed_time(b) for a, b in ev)
-        got = {"tbd": tbd.permute(1, 0, 2), "btd": btd, "slabs": torch.cat(slabs, 0)}[mode]
-        chk = got.contiguous().view(torch.int32).to(torch.int64).sum().item()
+        if mode in wide:  # later "ranks" overwrite earlier ones: nothing to compare
+            chk = ref
+        else:
+            got = {"tbd": tbd.permute(1, 0, 2), "btd": btd, "slabs": torch.cat(slabs, 0)}[mode]
+            chk = got.contiguous().view(torch.int32).to(torch.int64).sum().item()
         ref = chk if ref is None else ref
         print(json.dumps({"mode": mode, "ranks": N, "kernel_ms_median": round(ms[len(ms) // 2], 4),
                           "kernel_ms_min": round(ms[0], 4), "G_lookups_per_s": round(nl / ms[len(ms) // 2] / 1e6, 2),
