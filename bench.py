@@ -617,13 +617,14 @@ def bench_tablewise(args, w, steps, warmup):
         parity = {"checked": True, "ranks": world, "rows_checked": int(rows_all), "mismatching_elements": int(bad_all),
                   "bit_exact": bool(bad_all == 0) if not is_float else None,
                   "within_1e-5_relative": bool(bad_all == 0) if is_float else None,
-                  "checksum_of_checksums_equal": chk_got == chk_want, "index_errors": int(idx_err),
+                  # fp32 tables are compared within the stated tolerance: their bits, and so the checksum, may differ
+                  "checksum_of_checksums_equal": None if is_float else chk_got == chk_want, "index_errors": int(idx_err),
                   "against": "torch index_select + index_add_ + fp32 divide on the rank that owns each table, routed with "
                              "NCCL all_to_all_single (extend_distributed.py:389-426; emb_dpu_lookup.c:106-116, "
                              "emb_host.h:207-212)"}
         del got, want, tabs
         torch.cuda.empty_cache()
-        if bad_all or chk_got != chk_want or idx_err:
+        if bad_all or (not is_float and chk_got != chk_want) or idx_err:
             raise SystemExit(f"PARITY FAILURE on rank {rank}: {json.dumps(parity)}")
 
     # ---- the timed region: EXACTLY K steps back to back, one event on either side, nothing between the launches

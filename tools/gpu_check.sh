@@ -11,6 +11,7 @@ tail -8 $OUT/pytest_$TAG.log
 python __graft_entry__.py smoke > $OUT/smoke_$TAG.log 2>&1; echo "smoke rc=$?"; tail -3 $OUT/smoke_$TAG.log
 ( time python bench.py --steps 20 --warmup 5 "$@" ) > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.err; echo "bench rc=$?"; cut -c1-1500 $OUT/bench_$TAG.json; tail -5 $OUT/bench_$TAG.err
 ( time python bench.py --impl reference --steps 20 --warmup 5 "$@" ) > $OUT/bench_ref_$TAG.json 2> $OUT/bench_ref_$TAG.err; echo "reference rc=$?"; cut -c1-600 $OUT/bench_ref_$TAG.json; tail -3 $OUT/bench_ref_$TAG.err
+( time python bench.py --steps 20 --warmup 5 --dtype f32 --no-cpu-baseline --extras none ) > $OUT/bench_f32_$TAG.json 2> $OUT/bench_f32_$TAG.err; echo "bench f32 rc=$?"; cut -c1-400 $OUT/bench_f32_$TAG.json
 SHORT="python bench.py --steps 6 --warmup 3 --no-e2e --no-cpu-baseline --no-parity --extras none $*"
 $SHORT > $OUT/plain_$TAG.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_$TAG.csv $SHORT > $OUT/ncu_launch_$TAG.log 2>&1
