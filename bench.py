@@ -771,13 +771,18 @@ def e2e_host_call(args, lib, emblib, batches, lookups, T, B, D, Ke, paths):
             a[:] = o
             ho.append(a)
         host.append((hi, ho, arena))
-    res_arena = pinned_arena(lib, T * (B * D * 4 + 16) + 64)
-    res, pos = [], 0
-    for _ in range(T):
-        a, pos = carve_u32(res_arena, pos, B * D)
-        res.append(a.view(np.float32).reshape(B, D))
+    # one result arena per batch in flight (two calls in flight write different arrays)
+    res_sets, res_arenas = [], []
+    for _ in range(2):
+        res_arena = pinned_arena(lib, T * (B * D * 4 + 16) + 64)
+        res, pos = [], 0
+        for _ in range(T):
+            a, pos = carve_u32(res_arena, pos, B * D)
+            res.append(a.view(np.float32).reshape(B, D))
+        res_sets.append(res)
+        res_arenas.append(res_arena)
     # pointer arrays built once per batch, as the reference's caller does
-    calls = [emblib.HostCall(hi, ho, res) for hi, ho, _ in host]
+    calls = [emblib.HostCall(hi, ho, res_sets[k]) for k, (hi, ho, _) in enumerate(host)]
 
     def time_e2e(n_steps):
         for k in range(3):
@@ -790,14 +795,47 @@ def e2e_host_call(args, lib, emblib, batches, lookups, T, B, D, Ke, paths):
         n_e = sum(lookups[k % 2] for k in range(n_steps))
         return n_e / dt, dt / n_steps * 1e3, tm
 
+    def time_e2e_in_flight(n_steps):
+        """The same calls through emb_lookup_ex_async / emb_lookup_wait, TWO in flight: call k+1 is issued before
+        call k is waited for, so its copy-in crosses PCIe while call k is pooled and its rows drain.  Every call's
+        copies are inside the timed region; the region ends when the last call's rows are in host memory."""
+        def run(n):
+            calls[0].start()
+            for k in range(n):
+                if k + 1 < n:
+                    calls[(k + 1) % 2].start()
+                calls[k % 2].wait()
+        run(4)
+        t0 = time.perf_counter()
+        run(n_steps)
+        dt = time.perf_counter() - t0
+        n_e = sum(lookups[k % 2] for k in range(n_steps))
+        return n_e / dt, dt / n_steps * 1e3
+
     PATHS = {1: "staged: cudaMemcpyAsync in, kernel, cudaMemcpyAsync out, pipelined over table groups",
              2: "mapped: one launch, the kernel reads indices/offsets and writes pooled rows over PCIe",
              3: "inputs staged by the copy engine, pooled rows written to the host arrays by the kernel's "
                 "store epilogue over PCIe, pipelined over table groups"}
     v, ms, tm = time_e2e(Ke)  # default path (EMB_HOST_AUTO) on page-locked arrays
-    e2e = {"value": v, "unit": "lookups/s", "h2d_bytes_per_step": int(tm.h2d_bytes),
-           "d2h_bytes_per_step": int(tm.d2h_bytes), "ms_per_step": ms, "steps": Ke,
-           "call": "emb_lookup_ex (host pointers, page-locked arrays carved from one arena per kind)",
+    # the synchronous result of the last call is the check for the calls in flight: same batch, same bits
+    want_bits = [r.view(np.uint32).copy() for r in calls[(Ke - 1) % 2].results[:2]]
+    for r in calls[(Ke - 1) % 2].results[:2]:
+        r[:] = 0
+    va, msa = time_e2e_in_flight(Ke)
+    for r, wb in zip(calls[(Ke - 1) % 2].results[:2], want_bits):
+        if not np.array_equal(r.view(np.uint32), wb):
+            raise SystemExit("PARITY FAILURE: emb_lookup_ex_async rows differ from emb_lookup_ex rows")
+    in_flight = va >= v  # the headline is the better of the two ways to call; both are in the line
+    e2e = {"value": va if in_flight else v, "unit": "lookups/s", "h2d_bytes_per_step": int(tm.h2d_bytes),
+           "d2h_bytes_per_step": int(tm.d2h_bytes), "ms_per_step": msa if in_flight else ms, "steps": Ke,
+           "calls_in_flight": 2 if in_flight else 1,
+           "call": ("emb_lookup_ex_async + emb_lookup_wait (host pointers, page-locked arrays carved from one arena per "
+                    "kind), two calls in flight: call k+1 is issued before call k is waited for; wall clock from the "
+                    "first issue to the last call's rows in host memory") if in_flight else
+                   "emb_lookup_ex (host pointers, page-locked arrays carved from one arena per kind)",
+           "two_calls_in_flight": {"value": va, "ms_per_step": msa, "call": "emb_lookup_ex_async + emb_lookup_wait"},
+           "synchronous_call": {"value": v, "ms_per_step": ms, "call": "emb_lookup_ex, one call at a time (what an "
+                                "unmodified caller of lookup() gets)"},
            "path": PATHS[int(tm.path)],
            "last_call_ms": {"h2d": tm.h2d_ms, "kernel": tm.kernel_ms, "d2h": tm.d2h_ms, "total": tm.total_ms},
            "other_paths": {}}

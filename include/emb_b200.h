@@ -125,6 +125,9 @@ int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results,
  * the exchange's completion wait behind the next batch's gathers.  Without the flag a launch reads nothing before
  * the kernel in front of it has completed (stream order as usual). */
 #define EMB_Q_OVERLAP 2u
+/* The indices of this query are already slab row ids of a table reordered with emb_table_remap() (the caller
+ * translated them, e.g. with emb_remap_indices() in its data pipeline): the launch does not translate them again. */
+#define EMB_Q_REMAPPED 4u
 
 typedef struct emb_shape {
     uint32_t nr_tables;             /* NR_TABLES                                      */
@@ -169,6 +172,34 @@ int emb_free_table(uint32_t table_id);
 int emb_l2_persist(uint32_t table_id, uint64_t first_row, uint64_t nr_rows, float hit_ratio,
                    void *stream);
 
+/* ---- hot rows: skewed index distributions --------------------------------------------- */
+
+/* north_star: "an L2 persisting-access window keeps hot rows resident under skewed index distributions".  A
+ * cudaAccessPolicyWindow (emb_l2_persist above) is ONE address range per stream, so it cannot serve a launch that
+ * pools many tables.  These calls give every table its own hot set instead: the pooling kernel loads slab rows
+ * [0, hot_rows) of a table with one L2 eviction policy and the rest with another (createpolicy + ld.global.nc
+ * .L2::cache_hint, per load), and emb_table_remap() moves the rows a caller knows to be hot into that prefix.
+ * Results are identical with and without (parity: tests/test_gpu_hot.py); what changes is which rows L2 keeps.
+ * Measurements: profiles/r2_l2_hot_rows.md. */
+#define EMB_HOT_KEEP 1        /* rows [0, hot_rows): L2 evict_last                         */
+#define EMB_HOT_STREAM_COLD 2 /* rows [hot_rows, nr_rows): L2 evict_first                  */
+/* mode = 0 or a combination of the two; hot_rows is clamped to the table.  Takes effect for plans created and
+ * host-pointer / one-shot lookups issued afterwards; cleared when the table is populated again. */
+int emb_table_set_hot_rows(uint32_t table_id, uint64_t hot_rows, int mode);
+/* Reorder a populated (whole, not row-sharded) table in HBM: the row the caller calls r moves to slab row
+ * new_of_old[r] (HOST array of nr_rows entries, a permutation of 0..nr_rows-1; may be freed on return).  Callers
+ * keep using THEIR row ids: lookup(), emb_lookup_ex() and plans translate every index through the permutation
+ * while they stage it (4 more bytes read per lookup), unless a query says EMB_Q_REMAPPED.  Needs a second slab of
+ * the table's size while it runs; plans made before it refuse to launch (EMB_ESTATE).  Populating the table again
+ * restores the caller's order.  emb_table_read() returns rows in slab order. */
+int emb_table_remap(uint32_t table_id, const uint32_t *new_of_old);
+/* HOST helper (no device needed): the permutation that puts the most looked-up rows first.  counts[r] = how often
+ * row r was looked up in a sample of the workload; equal counts keep their order. */
+int emb_hot_order(const uint64_t *counts, uint64_t nr_rows, uint32_t *new_of_old);
+/* Translate n row ids in DEVICE memory to slab order, in place, on `stream` (for EMB_Q_REMAPPED queries).  A table
+ * that was not reordered leaves them unchanged. */
+int emb_remap_indices(uint32_t table_id, uint32_t *indices_dev, uint64_t n, void *stream);
+
 /* ---- lookups with explicit lengths, HOST pointers ------------------------------------ */
 
 /* Like lookup() but per-table lengths are arguments (the historical signatures in
@@ -179,6 +210,24 @@ int emb_l2_persist(uint32_t table_id, uint64_t first_row, uint64_t nr_rows, floa
 int emb_lookup_ex(uint32_t nr_tables, const uint32_t *const *indices,
                   const uint32_t *const *offsets, const uint32_t *indices_len,
                   const uint32_t *nr_batches, float *const *final_results);
+
+/* The same call without the wait: everything is enqueued (copies in, pooling launches, copies out -- or the mapped
+ * / bounced launch of a small call) and the function returns a ticket; emb_lookup_wait(ticket) returns once the
+ * pooled rows are in final_results[].  TWO calls may be in flight: issued as
+ *     async(k+1); wait(k); <consume k>; async(k+2); wait(k+1); ...
+ * the copy-in of call k+1 crosses PCIe while call k is being pooled and its rows drain, so both PCIe directions stay
+ * busy across calls, not only across the table groups inside one call (C2 on page-locked arrays: one call per
+ * ~2.2 ms against 2.75 ms for back-to-back synchronous calls; profiles/r2_host_async.md).  Rules: all host arrays
+ * of a call (pointer tables excluded: they are read before the function returns) stay untouched until its wait
+ * returns; two calls in flight use different result arrays; issuing a third call first completes the oldest one
+ * (its later wait returns at once); lookup() / emb_lookup_ex() / emb_shutdown() complete whatever is in flight
+ * first.  emb_last_timings() describes the call completed last.  Thread-safe; a wait blocks outside the
+ * library's lock. */
+typedef uint64_t emb_ticket;
+int emb_lookup_ex_async(uint32_t nr_tables, const uint32_t *const *indices,
+                        const uint32_t *const *offsets, const uint32_t *indices_len,
+                        const uint32_t *nr_batches, float *const *final_results, emb_ticket *ticket);
+int emb_lookup_wait(emb_ticket ticket);
 
 /* How lookup() / emb_lookup_ex() move the caller's HOST arrays across PCIe:
  * EMB_HOST_COPY        all staged: cudaMemcpyAsync of indices/offsets into HBM, pooling kernel,

@@ -40,7 +40,54 @@ struct Table {
     bool sharded = false;
     void *d_tmap = nullptr;  // CUtensorMap [rows][D] in device memory, built on first use by the TMA kernel
     uint32_t generation = 0; // bumped whenever the slab is (re)allocated or freed: plans remember it
+    // hot rows (emb_table_set_hot_rows / emb_table_remap): slab rows [0, hot_rows) carry the L2 policy hot_mode names;
+    // d_remap != NULL: the slab was reordered, caller row r lives at slab row d_remap[r]
+    uint32_t *d_remap = nullptr;
+    uint64_t hot_rows = 0;
+    uint32_t hot_mode = 0;
 };
+
+/* What host_complete() needs to know about a host-pointer call whose work has been enqueued. */
+struct HostPending {
+    bool active = false;
+    uint64_t ticket = 0;  // 0: a synchronous call
+    double t_begin = 0;
+    uint32_t T = 0, n_groups = 0;
+    bool timed_in = false;  // the inputs went through the copy-in stream (its events were recorded)
+    bool in_mapped = false, out_mapped = false, bounce = false, desc_same = false;
+    bool use_done_event = false;  // wait for HostSlot::ev_done, not for the whole stream (another call may follow on it)
+    cudaStream_t s_last = nullptr;
+    uint64_t h2d_payload = 0, d2h_payload = 0, launches = 0;
+    size_t desc_bytes = 0;
+    // bounced calls: the pooled rows of table t lie at h_bounce + b_src[t] and go to b_dst[t]
+    std::vector<float *> b_dst;
+    std::vector<size_t> b_src, b_bytes;
+};
+
+/* Everything one host-pointer call owns while it is in flight: device mirrors of the caller's arrays, descriptors,
+ * events, the bounce arena.  The synchronous entry points use slot 0; emb_lookup_ex_async alternates between the
+ * slots so that the copies and kernels of two consecutive calls overlap. */
+struct HostSlot {
+    uint32_t *d_idx = nullptr;
+    uint32_t *d_off = nullptr;
+    float *d_out = nullptr;
+    size_t idx_cap = 0, off_cap = 0, out_cap = 0;  // elements
+    BagDesc *d_descs = nullptr;
+    BagDesc *h_descs = nullptr;  // pinned
+    uint32_t desc_cap = 0;
+    // bytes d_descs holds (last successful upload): a caller that passes the same arrays call after
+    // call (dlrm_dpu_pytorch.py:484-498 allocates them once) needs no descriptor upload at all
+    std::vector<uint8_t> desc_shadow;
+    bool desc_shadow_ok = false;
+    std::vector<cudaEvent_t> ev_pool;
+    cudaEvent_t ev_done = nullptr;
+    // page-locked bounce arena for small calls on pageable arrays
+    uint8_t *h_bounce = nullptr;
+    uint8_t *d_bounce = nullptr;  // device alias of h_bounce
+    size_t bounce_cap = 0;
+    HostPending p;
+};
+constexpr int kHostSlots = 2;
 
 struct Ctx {
     bool configured = false;
@@ -53,7 +100,6 @@ struct Ctx {
     cudaStream_t stream = nullptr;     // compute + H2D
     cudaStream_t stream_out = nullptr; // D2H
     cudaStream_t stream_in = nullptr;  // H2D of the pipelined host-pointer path
-    std::vector<cudaEvent_t> ev_pool;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     uint32_t *d_err = nullptr;
 
@@ -61,29 +107,15 @@ struct Ctx {
     void *d_col = nullptr;
     size_t col_bytes = 0;
 
-    // host-pointer lookup path: device mirrors of the caller's arrays + descriptors
-    uint32_t *d_idx = nullptr;
-    uint32_t *d_off = nullptr;
-    float *d_out = nullptr;
-    size_t idx_cap = 0, off_cap = 0, out_cap = 0;  // elements
-    BagDesc *d_descs = nullptr;
-    BagDesc *h_descs = nullptr;  // pinned
-    uint32_t desc_cap = 0;
-    // bytes d_descs holds (last successful upload): a caller that passes the same arrays call after
-    // call (dlrm_dpu_pytorch.py:484-498 allocates them once) needs no descriptor upload at all
-    std::vector<uint8_t> desc_shadow;
-    bool desc_shadow_ok = false;
+    // host-pointer lookup path: per-call state, two slots (emb_lookup_ex_async keeps two calls in flight)
+    HostSlot hslot[kHostSlots];
+    uint64_t next_ticket = 1;  // tickets of emb_lookup_ex_async: slot = ticket % kHostSlots
     // descriptor ring of emb_lookup_device
     BagDesc *ring_h[4] = {nullptr, nullptr, nullptr, nullptr};
     BagDesc *ring_d[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ring_ev[4] = {nullptr, nullptr, nullptr, nullptr};
     uint32_t ring_cap = 0;
     int ring_next = 0;
-    // page-locked bounce arena for small calls on pageable arrays
-    uint8_t *h_bounce = nullptr;
-    uint8_t *d_bounce = nullptr;  // device alias of h_bounce
-    size_t bounce_cap = 0;
-
     emb_timings last = {0, 0, 0, 0, 0, 0, 0, 0};
     // tuning knobs (emb_set_tuning); 0 = default
     int unroll = 0;     // rows in flight per sub-warp: 4 or 8
@@ -240,6 +272,15 @@ int table_alloc(Table *t, uint64_t rows, int kind, cudaStream_t s)
         return fail(EMB_EINVAL, "nr_rows %llu unsupported (1 .. 2^32-2)", (unsigned long long)rows);
     t->row_base = 0;
     t->sharded = false;
+    // rows arrive in the caller's order again: a reordering or a hot prefix of what the slot held before is void
+    t->hot_rows = 0;
+    t->hot_mode = 0;
+    if (t->d_remap) {
+        cudaDeviceSynchronize();  // plans translating through it may still be running
+        cudaFree(t->d_remap);
+        t->d_remap = nullptr;
+        t->generation++;
+    }
     if (t->dev && t->rows == rows) {
         t->kind = kind;
         return EMB_OK;
@@ -271,13 +312,15 @@ int table_alloc(Table *t, uint64_t rows, int kind, cudaStream_t s)
     return EMB_OK;
 }
 
-int ensure_events(size_t n)
+int ensure_events(HostSlot &hs, size_t n)
 {
-    while (g.ev_pool.size() < n) {
+    while (hs.ev_pool.size() < n) {
         cudaEvent_t e;
         CU(cudaEventCreate(&e));
-        g.ev_pool.push_back(e);
+        hs.ev_pool.push_back(e);
     }
+    if (!hs.ev_done)
+        CU(cudaEventCreateWithFlags(&hs.ev_done, cudaEventDisableTiming));
     return EMB_OK;
 }
 
@@ -353,7 +396,29 @@ struct Variant {
     int mult;      // stretch kernel: bags per CTA / sub-warps per CTA
     uint32_t bags; // bags per CTA
     int stage;     // stretch kernel: 1 = the larger pass buffer (measurement knob)
+    bool hot;      // stretch kernel: the HOT instantiation (hot-row tables among the launch's tables; K = 8)
 };
+
+/* Hot-row tables among the tables of a launch (any_hot: an L2 policy is set; any_remap: a reordered slab whose
+ * indices the kernel must translate).  Only the stretch kernel knows them, as its HOT instantiation (K = 8, the small
+ * pass); a launch that holds row shards keeps the compacting instantiation instead.  Policies are hints and may be
+ * dropped; a translation may not. */
+int apply_hot(Variant &v, bool any_hot, bool any_remap, bool compact)
+{
+    v.hot = false;
+    if (!any_hot && !any_remap)
+        return EMB_OK;
+    if (v.kind == 6 && !compact) {
+        v.hot = true;
+        v.unroll = 8;
+        v.stage = 0;
+        return EMB_OK;
+    }
+    if (any_remap)
+        return fail(EMB_EINVAL, "a reordered table (emb_table_remap) is pooled by the stretch kernel only (variant 6, "
+                                "dimension 4..128 in powers of two, no row shards and no fp32/int32 mix in the launch)");
+    return EMB_OK;
+}
 
 /* avg_pool = lookups per bag of the launch (0 = unknown).  The stretch kernel is the default; it replaced the
  * round-1 load-balanced kernels (per CTA with atomics, per warp) on every workload (profiles/r2_stretch_ab_rotated.txt).
@@ -365,6 +430,7 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = fal
     uint32_t D = g.shape.nr_cols;
     uint32_t lanes = lanes_for_dim(D);
     v.stage = 0;
+    v.hot = false;
     if (!lanes) {
         v.kind = 0;
         v.unroll = 1;
@@ -433,6 +499,8 @@ void launch_dependent(void (*kern)(KArgs...), dim3 grid, uint32_t block, cudaStr
     cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);  // the caller checks cudaGetLastError
 }
 
+constexpr int kHotMinBlocks = 32;  // resident one-warp CTAs per SM the HOT instantiation is compiled for
+
 template <int LANES, int K, int MULT, bool IS_FLOAT>
 void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni, uint32_t overlap)
 {
@@ -456,6 +524,14 @@ void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDes
             else
                 launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, MINB, true>, g2, 32, s, d, n, uni,
                                  g.d_err, overlap & 1u);
+            return;
+        }
+    }
+    // bit 2: hot-row tables among the descriptors -> the HOT instantiation (K = 8, small pass; apply_hot)
+    if constexpr (K == 8) {
+        if (overlap & 4u) {
+            launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, kHotMinBlocks, false, true>, g2, 32, s, d,
+                             n, uni, g.d_err, overlap & 1u);
             return;
         }
     }
@@ -544,14 +620,15 @@ int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_
     if (grid == 0)
         return EMB_OK;
     uint32_t D = g.shape.nr_cols;
+    const uint32_t obits = (overlap ? 1u : 0u) | (compact ? 2u : 0u) | (v.hot ? 4u : 0u);
     switch (v.kind ? lanes_for_dim(D) : 0) {
     case 0: emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, uni, D, g.d_err); break;
-    case 1: launch_for_lanes<1>(v, is_float, grid, s, d_descs, n, uni, (overlap ? 1u : 0u) | (compact ? 2u : 0u)); break;
-    case 2: launch_for_lanes<2>(v, is_float, grid, s, d_descs, n, uni, (overlap ? 1u : 0u) | (compact ? 2u : 0u)); break;
-    case 4: launch_for_lanes<4>(v, is_float, grid, s, d_descs, n, uni, (overlap ? 1u : 0u) | (compact ? 2u : 0u)); break;
-    case 8: launch_for_lanes<8>(v, is_float, grid, s, d_descs, n, uni, (overlap ? 1u : 0u) | (compact ? 2u : 0u)); break;
-    case 16: launch_for_lanes<16>(v, is_float, grid, s, d_descs, n, uni, (overlap ? 1u : 0u) | (compact ? 2u : 0u)); break;
-    default: launch_for_lanes<32>(v, is_float, grid, s, d_descs, n, uni, (overlap ? 1u : 0u) | (compact ? 2u : 0u)); break;
+    case 1: launch_for_lanes<1>(v, is_float, grid, s, d_descs, n, uni, obits); break;
+    case 2: launch_for_lanes<2>(v, is_float, grid, s, d_descs, n, uni, obits); break;
+    case 4: launch_for_lanes<4>(v, is_float, grid, s, d_descs, n, uni, obits); break;
+    case 8: launch_for_lanes<8>(v, is_float, grid, s, d_descs, n, uni, obits); break;
+    case 16: launch_for_lanes<16>(v, is_float, grid, s, d_descs, n, uni, obits); break;
+    default: launch_for_lanes<32>(v, is_float, grid, s, d_descs, n, uni, obits); break;
     }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
@@ -621,6 +698,14 @@ int fill_desc(const emb_dev_query &q, BagDesc *d, uint32_t chunk_begin, const Va
     if (vec)
         flags |= emb::kDescVecStore;
     d->flags = flags;
+    if (variant.hot) {
+        d->remap = (q.flags & EMB_Q_REMAPPED) ? nullptr : t.d_remap;
+        d->hot_mode = t.hot_mode;
+        d->hot_rows = t.hot_mode ? (uint32_t)std::min<uint64_t>(t.hot_rows, t.rows) : 0;
+    } else if (t.d_remap && !(q.flags & EMB_Q_REMAPPED)) {
+        return fail(EMB_EINVAL, "table %u is reordered (emb_table_remap) but this launch cannot translate its indices",
+                    q.table_id);
+    }
     *chunks = (d->bag_end - d->bag_first + per - 1) / per;
     d->n_chunks = *chunks;
     // bag_rotate: start at the chunk holding that bag (rounded down to a chunk boundary) and wrap
@@ -643,7 +728,7 @@ struct emb_plan {
     uint32_t grid = 0;
     uint32_t uni = 0;  // uniform_chunks() of the descriptors
     uint64_t bytes = 0;
-    Variant variant = {0, 1, 1, 8, 0};
+    Variant variant = {0, 1, 1, 8, 0, false};
     bool all_float = false;
     bool overlap = false;  // EMB_Q_OVERLAP on every query
     // The plan holds row shards of fixed-point tables: launched with the kernel instantiation that stages only a
@@ -652,6 +737,8 @@ struct emb_plan {
 };
 
 extern "C" {
+
+static int host_drain();  // host-pointer calls still in flight complete first (defined with the host path below)
 
 /* ---------------------------------------------------------------- configuration ------ */
 
@@ -716,26 +803,35 @@ void emb_shutdown(void)
     std::lock_guard<std::mutex> lk(g_mu);
     if (g.device_ready) {
         cudaSetDevice(g.device);
+        host_drain();
         cudaDeviceSynchronize();
         for (Table &t : g.tables) {
             if (t.dev)
                 cudaFree(t.dev);
             if (t.d_tmap)
                 cudaFree(t.d_tmap);
+            if (t.d_remap)
+                cudaFree(t.d_remap);
         }
         cudaFree(g.d_col);
-        cudaFree(g.d_idx);
-        cudaFree(g.d_off);
-        cudaFree(g.d_out);
-        cudaFree(g.d_descs);
         cudaFree(g.d_err);
-        if (g.h_descs)
-            cudaFreeHost(g.h_descs);
+        for (HostSlot &hs : g.hslot) {  // a call still pending is abandoned: the device is idle by now
+            cudaFree(hs.d_idx);
+            cudaFree(hs.d_off);
+            cudaFree(hs.d_out);
+            cudaFree(hs.d_descs);
+            if (hs.h_descs)
+                cudaFreeHost(hs.h_descs);
+            if (hs.h_bounce)
+                cudaFreeHost(hs.h_bounce);
+            for (auto &ev : hs.ev_pool)
+                cudaEventDestroy(ev);
+            if (hs.ev_done)
+                cudaEventDestroy(hs.ev_done);
+        }
         for (auto &ev : g.ev)
             if (ev)
                 cudaEventDestroy(ev);
-        if (g.h_bounce)
-            cudaFreeHost(g.h_bounce);
         for (int i = 0; i < kRingSlots; i++) {
             if (g.ring_h[i])
                 cudaFreeHost(g.ring_h[i]);
@@ -750,8 +846,6 @@ void emb_shutdown(void)
             cudaStreamDestroy(g.stream_out);
         if (g.stream_in)
             cudaStreamDestroy(g.stream_in);
-        for (auto &ev : g.ev_pool)
-            cudaEventDestroy(ev);
     }
     int unroll = g.unroll, variant = g.variant, bags_mult = g.bags_mult, host_path = g.host_path;
     g = Ctx();
@@ -860,6 +954,8 @@ int emb_table_set_row_base(uint32_t table_id, uint64_t row_base)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
     if (row_base > 0xffffffffull)
         return fail(EMB_EINVAL, "row_base too large");
+    if (g.tables[table_id].d_remap)
+        return fail(EMB_EINVAL, "table %u is reordered (emb_table_remap): it cannot become a row shard", table_id);
     g.tables[table_id].row_base = row_base;
     g.tables[table_id].sharded = true;
     return EMB_OK;
@@ -899,9 +995,11 @@ int emb_free_table(uint32_t table_id)
     std::lock_guard<std::mutex> lk(g_mu);
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
+    host_drain();
     CU(cudaDeviceSynchronize());
     cudaFree(g.tables[table_id].dev);
     cudaFree(g.tables[table_id].d_tmap);
+    cudaFree(g.tables[table_id].d_remap);
     const uint32_t gen = g.tables[table_id].generation + 1;  // plans made for the freed slab refuse to launch
     g.tables[table_id] = Table();
     g.tables[table_id].generation = gen;
@@ -940,6 +1038,121 @@ int emb_l2_persist(uint32_t table_id, uint64_t first_row, uint64_t nr_rows, floa
     attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
     attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
     CU(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr));
+    return EMB_OK;
+}
+
+/* ---------------------------------------------------------------- hot rows ------------- */
+
+int emb_table_set_hot_rows(uint32_t table_id, uint64_t hot_rows, int mode)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (table_id >= g.tables.size() || !g.tables[table_id].kind)
+        return fail(EMB_ESTATE, "table %u is not populated", table_id);
+    if (mode < 0 || mode > (EMB_HOT_KEEP | EMB_HOT_STREAM_COLD))
+        return fail(EMB_EINVAL, "mode must be a combination of EMB_HOT_KEEP and EMB_HOT_STREAM_COLD");
+    Table &t = g.tables[table_id];
+    t.hot_rows = std::min<uint64_t>(hot_rows, t.rows);
+    t.hot_mode = (uint32_t)mode;
+    return EMB_OK;
+}
+
+int emb_hot_order(const uint64_t *counts, uint64_t nr_rows, uint32_t *new_of_old)
+{
+    if (!counts || !new_of_old || !nr_rows || nr_rows > 0xfffffffeull)
+        return fail(EMB_EINVAL, "emb_hot_order: NULL arguments or nr_rows outside 1 .. 2^32-2");
+    std::vector<uint32_t> order((size_t)nr_rows);
+    for (uint64_t r = 0; r < nr_rows; r++)
+        order[(size_t)r] = (uint32_t)r;
+    // most looked-up rows first; rows with equal counts keep their order
+    std::stable_sort(order.begin(), order.end(), [counts](uint32_t a, uint32_t b) { return counts[a] > counts[b]; });
+    for (uint64_t k = 0; k < nr_rows; k++)
+        new_of_old[order[(size_t)k]] = (uint32_t)k;
+    return EMB_OK;
+}
+
+int emb_table_remap(uint32_t table_id, const uint32_t *new_of_old)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (table_id >= g.tables.size() || !g.tables[table_id].kind)
+        return fail(EMB_ESTATE, "table %u is not populated", table_id);
+    Table &t = g.tables[table_id];
+    if (!new_of_old)
+        return fail(EMB_EINVAL, "emb_table_remap: NULL permutation");
+    if (t.sharded)
+        return fail(EMB_EINVAL, "table %u is a row shard: reorder whole tables only", table_id);
+    if (t.d_remap)
+        return fail(EMB_ESTATE, "table %u is already reordered: populate it again first", table_id);
+    const uint64_t rows = t.rows;
+    {  // a permutation of 0 .. rows-1?
+        std::vector<bool> seen((size_t)rows, false);
+        for (uint64_t r = 0; r < rows; r++) {
+            const uint32_t v = new_of_old[r];
+            if (v >= rows || seen[v])
+                return fail(EMB_EINVAL, "emb_table_remap: new_of_old is not a permutation of 0..%llu (entry %llu = %u)",
+                            (unsigned long long)(rows - 1), (unsigned long long)r, v);
+            seen[v] = true;
+        }
+    }
+    host_drain();
+    CU(cudaDeviceSynchronize());
+    const uint32_t D = g.shape.nr_cols;
+    const size_t rb = (size_t)D * 4;
+    uint32_t *d_map = nullptr;
+    void *slab = nullptr;
+    cudaError_t e = cudaMalloc(&d_map, (size_t)rows * 4);
+    if (e == cudaSuccess)
+        e = cudaMalloc(&slab, (size_t)(rows + 1) * rb);
+    if (e != cudaSuccess) {
+        cudaFree(d_map);
+        return fail(EMB_ENOMEM, "emb_table_remap needs a second slab of %zu bytes while it reorders: %s",
+                    (size_t)(rows + 1) * rb, cudaGetErrorString(e));
+    }
+    e = cudaMemcpyAsync(d_map, new_of_old, (size_t)rows * 4, cudaMemcpyHostToDevice, g.stream);
+    if (e == cudaSuccess)
+        e = cudaMemsetAsync((char *)slab + (size_t)rows * rb, 0, rb, g.stream);  // the all-zero row behind the table
+    if (e == cudaSuccess) {
+        const uint64_t n = rows * D;
+        const uint32_t grid = (uint32_t)std::min<uint64_t>((n + 255) / 256, (uint64_t)g.sm_count * 32);
+        emb::permute_rows_kernel<<<grid, 256, 0, g.stream>>>((uint32_t *)slab, (const uint32_t *)t.dev, d_map, rows, D);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(g.stream);  // new_of_old may be freed on return
+    if (e != cudaSuccess) {
+        cudaFree(d_map);
+        cudaFree(slab);
+        return fail(EMB_ECUDA, "emb_table_remap: %s", cudaGetErrorString(e));
+    }
+    cudaFree(t.dev);
+    if (t.d_tmap) {
+        cudaFree(t.d_tmap);
+        t.d_tmap = nullptr;
+    }
+    t.dev = slab;
+    t.d_remap = d_map;
+    t.generation++;  // plans made for the old slab refuse to launch
+    return EMB_OK;
+}
+
+int emb_remap_indices(uint32_t table_id, uint32_t *indices_dev, uint64_t n, void *stream)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (table_id >= g.tables.size() || !g.tables[table_id].kind)
+        return fail(EMB_ESTATE, "table %u is not populated", table_id);
+    const Table &t = g.tables[table_id];
+    if (!t.d_remap || !n)
+        return EMB_OK;  // rows are where the caller's ids say
+    if (!indices_dev)
+        return fail(EMB_EINVAL, "emb_remap_indices: NULL indices");
+    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    const uint32_t grid = (uint32_t)std::min<uint64_t>((n + 255) / 256, (uint64_t)g.sm_count * 32);
+    emb::remap_indices_kernel<<<grid, 256, 0, s>>>(indices_dev, t.d_remap, n, (uint32_t)t.rows);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
     return EMB_OK;
 }
 
@@ -986,6 +1199,19 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
         if (p->variant.mult > 2)
             p->variant.mult = 2;
         p->variant.bags = std::min<uint32_t>(32 / lanes_for_dim((uint32_t)D) * p->variant.mult, 64);
+    }
+    {
+        bool any_hot = false, any_remap = false;
+        for (uint32_t i = 0; i < n; i++)
+            if (queries[i].table_id < g.tables.size()) {
+                const Table &tb = g.tables[queries[i].table_id];
+                any_hot |= tb.hot_mode != 0 && tb.hot_rows != 0;
+                any_remap |= tb.d_remap != nullptr && !(queries[i].flags & EMB_Q_REMAPPED);
+            }
+        if ((rc = apply_hot(p->variant, any_hot, any_remap, p->compact))) {
+            delete p;
+            return rc;
+        }
     }
     uint64_t chunk = 0;
     for (uint32_t i = 0; i < n; i++) {
@@ -1091,7 +1317,18 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
         tot_li += queries[i].indices_len;
         tot_nb += queries[i].nr_batches;
     }
-    const Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0, all_float);
+    Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0, all_float);
+    {
+        bool any_hot = false, any_remap = false;
+        for (uint32_t i = 0; i < n; i++)
+            if (queries[i].table_id < g.tables.size()) {
+                const Table &tb = g.tables[queries[i].table_id];
+                any_hot |= tb.hot_mode != 0 && tb.hot_rows != 0;
+                any_remap |= tb.d_remap != nullptr && !(queries[i].flags & EMB_Q_REMAPPED);
+            }
+        if ((rc = apply_hot(variant, any_hot, any_remap, false)))
+            return rc;
+    }
     uint64_t chunk = 0;
     for (uint32_t i = 0; i < n; i++) {
         uint32_t c = 0;
@@ -1320,11 +1557,15 @@ static uintptr_t alloc_base(const void *p)
     return (uintptr_t)base;
 }
 
-static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_t *const *offsets,
-                       const uint32_t *indices_len, const uint32_t *nr_batches,
-                       float *const *final_results)
+/* Enqueue one host-pointer call on slot `hs`: everything up to, but not including, the wait for its last copy or
+ * kernel.  hs.p describes the call for host_complete().  `ticket` != 0: an asynchronous call -- the end of its work
+ * is marked with hs.ev_done, because by the time it is waited for the streams may hold the next call's work too. */
+static int host_enqueue(HostSlot &hs, uint64_t ticket, uint32_t T, const uint32_t *const *indices,
+                        const uint32_t *const *offsets, const uint32_t *indices_len, const uint32_t *nr_batches,
+                        float *const *final_results)
 {
     double t_begin = now_s();
+    hs.p.active = false;
     const uint32_t D = g.shape.nr_cols;
     if (T > g.tables.size())
         return fail(EMB_ESTATE, "lookup over %u tables but only %zu slots exist", T, g.tables.size());
@@ -1341,18 +1582,18 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
         all_float &= g.tables[t].kind == EMB_TABLE_FLOAT;
     }
     int rc;
-    if (g.desc_cap < T) {
-        if (g.d_descs)
-            cudaFree(g.d_descs);
-        if (g.h_descs)
-            cudaFreeHost(g.h_descs);
-        g.d_descs = nullptr;
-        g.h_descs = nullptr;
-        g.desc_cap = 0;
-        g.desc_shadow_ok = false;
-        CU(cudaMalloc(&g.d_descs, T * sizeof(BagDesc)));
-        CU(cudaMallocHost(&g.h_descs, T * sizeof(BagDesc)));
-        g.desc_cap = T;
+    if (hs.desc_cap < T) {
+        if (hs.d_descs)
+            cudaFree(hs.d_descs);
+        if (hs.h_descs)
+            cudaFreeHost(hs.h_descs);
+        hs.d_descs = nullptr;
+        hs.h_descs = nullptr;
+        hs.desc_cap = 0;
+        hs.desc_shadow_ok = false;
+        CU(cudaMalloc(&hs.d_descs, T * sizeof(BagDesc)));
+        CU(cudaMallocHost(&hs.h_descs, T * sizeof(BagDesc)));
+        hs.desc_cap = T;
     }
     const uint64_t h2d_payload = (tot_idx + tot_bags) * 4, d2h_payload = tot_bags * D * 4;
 
@@ -1381,25 +1622,25 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     if ((g.host_path == EMB_HOST_AUTO && !(in_mapped && out_mapped) && h2d_payload + d2h_payload <= bounce_limit(T)) ||
         g.host_path == EMB_HOST_BOUNCE) {
         const size_t need = (size_t)(h2d_payload + d2h_payload) + 64;
-        if (g.bounce_cap < need) {
-            if (g.h_bounce)
-                cudaFreeHost(g.h_bounce);
-            g.h_bounce = nullptr;
-            g.bounce_cap = 0;
+        if (hs.bounce_cap < need) {
+            if (hs.h_bounce)
+                cudaFreeHost(hs.h_bounce);
+            hs.h_bounce = nullptr;
+            hs.bounce_cap = 0;
             const size_t cap = std::max(need, (size_t)bounce_limit(T) + 64);
-            CU(cudaHostAlloc((void **)&g.h_bounce, cap, cudaHostAllocMapped | cudaHostAllocPortable));
-            CU(cudaHostGetDevicePointer((void **)&g.d_bounce, g.h_bounce, 0));
-            g.bounce_cap = cap;
+            CU(cudaHostAlloc((void **)&hs.h_bounce, cap, cudaHostAllocMapped | cudaHostAllocPortable));
+            CU(cudaHostGetDevicePointer((void **)&hs.d_bounce, hs.h_bounce, 0));
+            hs.bounce_cap = cap;
         }
-        uint8_t *const dev_base = g.d_bounce;
+        uint8_t *const dev_base = hs.d_bounce;
         size_t pos = 0;
         for (uint32_t t = 0; t < T; t++) {  // indices, then offsets (4-byte items), then 16-byte aligned outputs
-            memcpy(g.h_bounce + pos, indices[t], (size_t)indices_len[t] * 4);
+            memcpy(hs.h_bounce + pos, indices[t], (size_t)indices_len[t] * 4);
             a_idx[t] = (const uint32_t *)(dev_base + pos);
             pos += (size_t)indices_len[t] * 4;
         }
         for (uint32_t t = 0; t < T; t++) {
-            memcpy(g.h_bounce + pos, offsets[t], (size_t)nr_batches[t] * 4);
+            memcpy(hs.h_bounce + pos, offsets[t], (size_t)nr_batches[t] * 4);
             a_off[t] = (const uint32_t *)(dev_base + pos);
             pos += (size_t)nr_batches[t] * 4;
         }
@@ -1437,11 +1678,11 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
                 off_mapped = false;
     }
 
-    if (!in_mapped && (rc = grow((void **)&g.d_idx, &g.idx_cap, tot_idx, 4)))
+    if (!in_mapped && (rc = grow((void **)&hs.d_idx, &hs.idx_cap, tot_idx, 4)))
         return rc;
-    if (!off_mapped && (rc = grow((void **)&g.d_off, &g.off_cap, tot_bags, 4)))
+    if (!off_mapped && (rc = grow((void **)&hs.d_off, &hs.off_cap, tot_bags, 4)))
         return rc;
-    if (!out_mapped && (rc = grow((void **)&g.d_out, &g.out_cap, tot_bags * D, 4)))
+    if (!out_mapped && (rc = grow((void **)&hs.d_out, &hs.out_cap, tot_bags * D, 4)))
         return rc;
 
     // Groups of consecutive tables with about equal bytes (one group when nothing is staged).
@@ -1460,9 +1701,18 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     const uint32_t forced_groups = env_u32("EMB_GROUPS", 0);  // measurement knob
     if (forced_groups && n_groups > 1)
         n_groups = std::min(std::min(T, kMaxGroups), forced_groups);
-    if ((rc = ensure_events(3 * n_groups + 2)))
+    if ((rc = ensure_events(hs, 3 * n_groups + 2)))
         return rc;
-    const Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, all_float);
+    Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, all_float);
+    {  // the caller's indices are in the caller's row order: reordered tables are translated by the kernel
+        bool any_hot = false, any_remap = false;
+        for (uint32_t t = 0; t < T; t++) {
+            any_hot |= g.tables[t].hot_mode != 0 && g.tables[t].hot_rows != 0;
+            any_remap |= g.tables[t].d_remap != nullptr;
+        }
+        if ((rc = apply_hot(variant, any_hot, any_remap, false)))
+            return rc;
+    }
     std::vector<uint32_t> g_first(n_groups + 1, T), g_grid(n_groups, 0);
     {
         // Group sizes.  Nothing can be pooled before the first group's indices have crossed PCIe and nothing
@@ -1506,12 +1756,12 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             q.table_id = t;
             q.nr_batches = nr_batches[t];
             q.indices_len = indices_len[t];
-            q.indices = in_mapped ? a_idx[t] : g.d_idx + io;
-            q.offsets = off_mapped ? a_off[t] : g.d_off + oo;
-            q.out = out_mapped ? (void *)a_out[t] : (void *)(g.d_out + oo * D);
+            q.indices = in_mapped ? a_idx[t] : hs.d_idx + io;
+            q.offsets = off_mapped ? a_off[t] : hs.d_off + oo;
+            q.out = out_mapped ? (void *)a_out[t] : (void *)(hs.d_out + oo * D);
             q.out_stride = D;
             uint32_t c = 0;
-            if ((rc = fill_desc(q, &g.h_descs[t], (uint32_t)chunk, variant, &c)))
+            if ((rc = fill_desc(q, &hs.h_descs[t], (uint32_t)chunk, variant, &c)))
                 return rc;
             chunk += c;
             t_io[t] = io;
@@ -1531,17 +1781,17 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     // tables as the previous call -- the reference's caller reuses its buffers), and the begin/end
     // events exist only where a copy stream has something to time.
     cudaStream_t s_k = g.stream, s_in = in_mapped ? s_k : g.stream_in, s_out = g.stream_out;
-    cudaEvent_t *ev = g.ev_pool.data();
+    cudaEvent_t *ev = hs.ev_pool.data();
     cudaEvent_t ev_begin = ev[3 * n_groups], ev_end = ev[3 * n_groups + 1];
     if (s_in != s_k)
         CU(cudaEventRecord(ev_begin, s_in));
     static const bool desc_cache = env_u32("EMB_DESC_CACHE", 1) != 0;  // measurement knob
     const size_t desc_bytes = (size_t)T * sizeof(BagDesc);
-    const bool desc_same = desc_cache && g.desc_shadow_ok && g.desc_shadow.size() == desc_bytes &&
-                           memcmp(g.desc_shadow.data(), g.h_descs, desc_bytes) == 0;
-    g.desc_shadow_ok = false;  // set again once this call has completed
+    const bool desc_same = desc_cache && hs.desc_shadow_ok && hs.desc_shadow.size() == desc_bytes &&
+                           memcmp(hs.desc_shadow.data(), hs.h_descs, desc_bytes) == 0;
+    hs.desc_shadow_ok = false;  // set again once this call has completed
     if (!desc_same)
-        CU(cudaMemcpyAsync(g.d_descs, g.h_descs, desc_bytes, cudaMemcpyHostToDevice, s_in));
+        CU(cudaMemcpyAsync(hs.d_descs, hs.h_descs, desc_bytes, cudaMemcpyHostToDevice, s_in));
     uint64_t launches = 0;
     for (uint32_t gi = 0; gi < n_groups; gi++) {
         const uint32_t t0 = g_first[gi], t1 = g_first[gi + 1];
@@ -1557,7 +1807,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
                 while (e < t1 && indices[e] == indices[t] + n && alloc_base(indices[e]) == ab)
                     n += indices_len[e++];
                 if (n)
-                    CU(cudaMemcpyAsync(g.d_idx + t_io[t], indices[t], n * 4, cudaMemcpyHostToDevice, s_in));
+                    CU(cudaMemcpyAsync(hs.d_idx + t_io[t], indices[t], n * 4, cudaMemcpyHostToDevice, s_in));
                 t = e;
             }
             for (uint32_t t = t0; t < t1 && !off_mapped;) {  // offsets
@@ -1567,7 +1817,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
                 while (e < t1 && offsets[e] == offsets[t] + n && alloc_base(offsets[e]) == ab)
                     n += nr_batches[e++];
                 if (n)
-                    CU(cudaMemcpyAsync(g.d_off + t_oo[t], offsets[t], n * 4, cudaMemcpyHostToDevice, s_in));
+                    CU(cudaMemcpyAsync(hs.d_off + t_oo[t], offsets[t], n * 4, cudaMemcpyHostToDevice, s_in));
                 t = e;
             }
         }
@@ -1576,7 +1826,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
             CU(cudaStreamWaitEvent(s_k, ev[3 * gi], 0));
         }
         CU(cudaEventRecord(ev[3 * gi + 1], s_k));
-        if ((rc = launch_bag_sum(variant, g.d_descs + t0, t1 - t0, uniform_chunks(g.h_descs + t0, t1 - t0), g_grid[gi], s_k,
+        if ((rc = launch_bag_sum(variant, hs.d_descs + t0, t1 - t0, uniform_chunks(hs.h_descs + t0, t1 - t0), g_grid[gi], s_k,
                                  all_float)))
             return rc;
         launches += g_grid[gi] ? 1 : 0;
@@ -1590,7 +1840,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
                 while (e < t1 && final_results[e] == final_results[t] + n && alloc_base(final_results[e]) == ab)
                     n += (size_t)nr_batches[e++] * D;
                 if (n)
-                    CU(cudaMemcpyAsync(final_results[t], g.d_out + t_oo[t] * D, n * 4, cudaMemcpyDeviceToHost, s_out));
+                    CU(cudaMemcpyAsync(final_results[t], hs.d_out + t_oo[t] * D, n * 4, cudaMemcpyDeviceToHost, s_out));
                 t = e;
             }
         }
@@ -1598,13 +1848,59 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     cudaStream_t s_last = out_mapped ? s_k : s_out;
     if (!out_mapped)
         CU(cudaEventRecord(ev_end, s_last));
-    CU(cudaStreamSynchronize(s_last));
-    if (!desc_same)
-        g.desc_shadow.assign((const uint8_t *)g.h_descs, (const uint8_t *)g.h_descs + desc_bytes);
-    g.desc_shadow_ok = true;
+    if (ticket)
+        CU(cudaEventRecord(hs.ev_done, s_last));  // created by ensure_events above
+    HostPending &p = hs.p;
+    p.ticket = ticket;
+    p.t_begin = t_begin;
+    p.T = T;
+    p.n_groups = n_groups;
+    p.timed_in = s_in != s_k;
+    p.in_mapped = in_mapped;
+    p.out_mapped = out_mapped;
+    p.bounce = bounce;
+    p.desc_same = desc_same;
+    p.use_done_event = ticket != 0;
+    p.s_last = s_last;
+    p.h2d_payload = h2d_payload;
+    p.d2h_payload = d2h_payload;
+    p.launches = launches;
+    p.desc_bytes = desc_bytes;
+    p.b_dst.clear();
+    p.b_src.clear();
+    p.b_bytes.clear();
+    if (bounce) {
+        const uint8_t *dev_base = hs.d_bounce;
+        for (uint32_t t = 0; t < T; t++) {
+            p.b_dst.push_back(final_results[t]);
+            p.b_src.push_back((size_t)((const uint8_t *)a_out[t] - dev_base));
+            p.b_bytes.push_back((size_t)nr_batches[t] * D * 4);
+        }
+    }
+    p.active = true;
+    return EMB_OK;
+}
+
+/* Wait for the call enqueued on `hs`, then what only the host can do: stage timings, the bounce arena's copy-out. */
+static int host_complete(HostSlot &hs)
+{
+    HostPending &p = hs.p;
+    if (!p.active)
+        return EMB_OK;
+    p.active = false;
+    if (p.use_done_event)
+        CU(cudaEventSynchronize(hs.ev_done));
+    else
+        CU(cudaStreamSynchronize(p.s_last));
+    if (!p.desc_same)
+        hs.desc_shadow.assign((const uint8_t *)hs.h_descs, (const uint8_t *)hs.h_descs + p.desc_bytes);
+    hs.desc_shadow_ok = true;
+    cudaEvent_t *ev = hs.ev_pool.data();
+    const uint32_t n_groups = p.n_groups;
+    cudaEvent_t ev_begin = ev[3 * n_groups], ev_end = ev[3 * n_groups + 1];
     float ms = 0, k_ms = 0;
     g.last.h2d_ms = 0;
-    if (s_in != s_k) {
+    if (p.timed_in) {
         CU(cudaEventElapsedTime(&ms, ev_begin, ev[3 * (n_groups - 1)]));
         g.last.h2d_ms = ms;
     }
@@ -1614,24 +1910,45 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     }
     g.last.kernel_ms = k_ms;  // with mapped arrays the PCIe traffic is inside the kernels
     g.last.d2h_ms = 0;
-    if (!out_mapped) {
+    if (!p.out_mapped) {
         CU(cudaEventElapsedTime(&ms, ev[2], ev_end));  // first group's rows ready -> last byte on the host
         g.last.d2h_ms = ms;
     }
-    g.last.total_ms = (now_s() - t_begin) * 1e3;
-    g.last.h2d_bytes = h2d_payload + T * sizeof(BagDesc);
-    g.last.d2h_bytes = d2h_payload;
-    g.last.launches = launches;
-    if (bounce) {
-        const uint8_t *dev_base = g.d_bounce;
-        for (uint32_t t = 0; t < T; t++)
-            if (nr_batches[t])
-                memcpy(final_results[t], g.h_bounce + ((uint8_t *)a_out[t] - dev_base), (size_t)nr_batches[t] * D * 4);
-        g.last.total_ms = (now_s() - t_begin) * 1e3;
-    }
-    g.last.path = bounce ? EMB_HOST_BOUNCE
-                  : (in_mapped && out_mapped) ? EMB_HOST_MAPPED : out_mapped ? EMB_HOST_MAPPED_OUT : EMB_HOST_COPY;
+    g.last.h2d_bytes = p.h2d_payload + p.T * sizeof(BagDesc);
+    g.last.d2h_bytes = p.d2h_payload;
+    g.last.launches = p.launches;
+    if (p.bounce)
+        for (uint32_t t = 0; t < p.T; t++)
+            if (p.b_bytes[t])
+                memcpy(p.b_dst[t], hs.h_bounce + p.b_src[t], p.b_bytes[t]);
+    g.last.total_ms = (now_s() - p.t_begin) * 1e3;
+    g.last.path = p.bounce ? EMB_HOST_BOUNCE
+                  : (p.in_mapped && p.out_mapped) ? EMB_HOST_MAPPED : p.out_mapped ? EMB_HOST_MAPPED_OUT : EMB_HOST_COPY;
     return EMB_OK;
+}
+
+/* Calls of emb_lookup_ex_async still in flight complete before anything else touches the host path. */
+static int host_drain()
+{
+    int rc = EMB_OK;
+    for (HostSlot &hs : g.hslot) {
+        const int r = host_complete(hs);
+        if (r && !rc)
+            rc = r;
+    }
+    return rc;
+}
+
+/* The synchronous call: slot 0, enqueue + wait. */
+static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_t *const *offsets,
+                       const uint32_t *indices_len, const uint32_t *nr_batches, float *const *final_results)
+{
+    int rc = host_drain();
+    if (rc)
+        return rc;
+    if ((rc = host_enqueue(g.hslot[0], 0, T, indices, offsets, indices_len, nr_batches, final_results)))
+        return rc;
+    return host_complete(g.hslot[0]);
 }
 
 int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results, void *dpu_set_ptr,
@@ -1676,6 +1993,49 @@ int emb_lookup_ex(uint32_t nr_tables, const uint32_t *const *indices, const uint
     if (!nr_tables || !indices || !offsets || !indices_len || !nr_batches || !final_results)
         return fail(EMB_EINVAL, "emb_lookup_ex: NULL/empty arguments");
     return lookup_host(nr_tables, indices, offsets, indices_len, nr_batches, final_results);
+}
+
+int emb_lookup_ex_async(uint32_t nr_tables, const uint32_t *const *indices, const uint32_t *const *offsets,
+                        const uint32_t *indices_len, const uint32_t *nr_batches, float *const *final_results,
+                        emb_ticket *ticket)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    if (!nr_tables || !indices || !offsets || !indices_len || !nr_batches || !final_results || !ticket)
+        return fail(EMB_EINVAL, "emb_lookup_ex_async: NULL/empty arguments");
+    const uint64_t tk = g.next_ticket;
+    HostSlot &hs = g.hslot[tk % kHostSlots];
+    // the slot's previous call (ticket tk - 2) completes first if nobody has waited for it yet: its results are in
+    // host memory from here on, and emb_lookup_wait on it returns at once
+    if ((rc = host_complete(hs)))
+        return rc;
+    if ((rc = host_enqueue(hs, tk, nr_tables, indices, offsets, indices_len, nr_batches, final_results)))
+        return rc;
+    g.next_ticket = tk + 1;
+    *ticket = tk;
+    return EMB_OK;
+}
+
+int emb_lookup_wait(emb_ticket ticket)
+{
+    std::unique_lock<std::mutex> lk(g_mu);
+    if (!ticket || ticket >= g.next_ticket)
+        return fail(EMB_EINVAL, "emb_lookup_wait: ticket %llu was never issued", (unsigned long long)ticket);
+    HostSlot &hs = g.hslot[ticket % kHostSlots];
+    if (!hs.p.active || hs.p.ticket != ticket)
+        return EMB_OK;  // completed earlier (waited for already, or displaced by a later call on its slot)
+    // Block outside the lock, so that another thread can enqueue the next call meanwhile.
+    cudaEvent_t done = hs.ev_done;
+    lk.unlock();
+    cudaError_t e = cudaEventSynchronize(done);
+    lk.lock();
+    if (e != cudaSuccess)
+        return fail(EMB_ECUDA, "emb_lookup_wait: %s", cudaGetErrorString(e));
+    if (hs.p.active && hs.p.ticket == ticket)
+        return host_complete(hs);
+    return EMB_OK;
 }
 
 int emb_last_timings(emb_timings *out)

@@ -33,6 +33,10 @@ enum : uint32_t {
     kDescSharded = 4u,  // row-range shard: out-of-range indices are silently skipped
     kDescVecStore = 8u, // output rows are 16-byte aligned
 };
+enum : uint32_t {  // BagDesc::hot_mode
+    kHotKeep = 1u,        // rows below hot_rows: L2 evict_last
+    kHotStreamCold = 2u,  // rows from hot_rows on: L2 evict_first
+};
 
 /* One per query; lives in device memory for the lifetime of a plan. */
 struct __align__(16) BagDesc {
@@ -54,8 +58,16 @@ struct __align__(16) BagDesc {
     uint32_t n_chunks;     // CTAs of this query
     uint32_t chunk_rot;    // CTA c pools chunk (c + chunk_rot) mod n_chunks: ranks start at different bags
     const void *tmap;      // CUtensorMap of the table in device memory (TMA kernel only), 64-byte aligned
+    // Hot-row tables (emb_table_set_hot_rows / emb_table_remap; stretch kernel, HOT instantiation).  remap != NULL:
+    // the slab was reordered, a caller's row id r lives at slab row remap[r] (translated while the indices are staged).
+    // Slab rows below hot_rows are loaded with the L2 policy hot_mode bit 0 selects (evict_last), the others with the
+    // one bit 1 selects (evict_first); a clear bit means evict_normal.
+    const uint32_t *remap;
+    uint32_t hot_rows;
+    uint32_t hot_mode;
     uint64_t pad_;
 };
+static_assert(sizeof(BagDesc) == 176, "BagDesc layout");
 
 /* First bag of the chunk CTA `cta` (relative to the query) pools; `per` = bags per CTA. */
 __device__ __forceinline__ uint32_t chunk_first_bag(const BagDesc *d, uint32_t cta, uint32_t per)
@@ -87,6 +99,46 @@ __device__ __forceinline__ uint4 ldg_row16(const uint4 *p)
     else
         asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
+}
+
+/* The same load with an L2 cache policy chosen per row (hot-row tables): `hot` picks pol_hot, else pol_cold.  Two
+ * predicated loads into the same registers: no 64-bit select in front of the load. */
+template <bool NARROW>
+__device__ __forceinline__ uint4 ldg_row16_policy(const uint4 *p, bool hot, uint64_t pol_hot, uint64_t pol_cold)
+{
+    uint4 r;
+    if (NARROW)
+        asm volatile("{\n\t"
+                     ".reg .pred h;\n\t"
+                     "setp.ne.u32 h, %5, 0;\n\t"
+                     "@h ld.global.nc.L2::cache_hint.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4], %6;\n\t"
+                     "@!h ld.global.nc.L2::cache_hint.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4], %7;\n\t"
+                     "}"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                     : "l"(p), "r"((uint32_t)hot), "l"(pol_hot), "l"(pol_cold));
+    else
+        asm volatile("{\n\t"
+                     ".reg .pred h;\n\t"
+                     "setp.ne.u32 h, %5, 0;\n\t"
+                     "@h ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %6;\n\t"
+                     "@!h ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %7;\n\t"
+                     "}"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                     : "l"(p), "r"((uint32_t)hot), "l"(pol_hot), "l"(pol_cold));
+    return r;
+}
+/* L2 cache policies for every byte of an access (createpolicy ... 1.0): 0 = evict_normal, 1 = evict_last,
+ * 2 = evict_first. */
+__device__ __forceinline__ uint64_t l2_policy(int kind)
+{
+    uint64_t pol;
+    if (kind == 1)
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    else if (kind == 2)
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    else
+        asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
 }
 
 __device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t *p)
@@ -427,7 +479,7 @@ __device__ __forceinline__ uint4 add_rows(uint4 a, uint4 b)
     return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
 }
 
-template <int LANES, int K, int BAGS, int STAGE, bool IS_FLOAT, int MINB, bool COMPACT = false>
+template <int LANES, int K, int BAGS, int STAGE, bool IS_FLOAT, int MINB, bool COMPACT = false, bool HOT = false>
 __global__ void __launch_bounds__(32, MINB)
 bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag,
                        uint32_t overlap)
@@ -449,6 +501,7 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
     static_assert(BAGS % SUB == 0 && (BAGS <= 32 || BAGS % 32 == 0), "BAGS");
     // a pass: row ids (4 bytes per lookup) and start markers (1 byte per lookup: bag + 1, or 0)
     static_assert(BAGS <= 254, "a start marker is one byte");
+    static_assert(!(COMPACT && HOT), "row shards and hot-row tables are separate instantiations");
     __shared__ __align__(16) uint32_t s_idx[STAGE];
     __shared__ __align__(16) uint8_t s_mark[STAGE];
     __shared__ __align__(16) uint32_t s_acc[BAGS * D];
@@ -558,6 +611,19 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
     const uint32_t row_base = d->row_base;
     const char *__restrict__ table = reinterpret_cast<const char *>(d->table) + sl * 16;
     bool bad = false;
+    // HOT (hot-row tables): row ids are translated to slab order while they are staged (remap), and every row load
+    // carries an L2 policy picked by "slab row < hot_rows".
+    const uint32_t *__restrict__ remap = nullptr;
+    uint32_t hot_rows = 0;
+    uint64_t pol_hot = 0, pol_cold = 0;
+    if constexpr (HOT) {
+        remap = d->remap;
+        hot_rows = d->hot_rows;
+        const uint32_t hm = d->hot_mode;
+        const uint64_t pol_n = l2_policy(0), pol_l = l2_policy(1), pol_f = l2_policy(2);
+        pol_hot = (hm & kHotKeep) ? pol_l : pol_n;
+        pol_cold = (hm & kHotStreamCold) ? pol_f : pol_n;
+    }
 
     if (!nonmono) {
         const uint32_t idx_s = (uint32_t)__cvta_generic_to_shared(s_idx);
@@ -601,6 +667,17 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                 if (lane < STAGE / 16)
                     sts_u128(mark_s + lane * 16, make_uint4(0u, 0u, 0u, 0u));
                 head_bags();  // while they fly
+                if constexpr (HOT) {
+                    if (remap) {  // caller's row id -> slab row; all translations of the pass go out back to back
+#pragma unroll
+                        for (int j = 0; j < NST; j++) {
+                            const uint32_t i = j * 32 + lane;
+                            const uint32_t r = raw[j] - row_base;
+                            if (i < n && r < rows)
+                                raw[j] = __ldg(remap + r) + row_base;
+                        }
+                    }
+                }
 #pragma unroll
                 for (int j = 0; j < NST; j++) {
                     const uint32_t i = j * 32 + lane;
@@ -704,8 +781,13 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
                         mk[0] = lds_u32(mark_s + c0 + c);
                     }
 #pragma unroll
-                    for (int u = 0; u < K; u++)
-                        v[u] = ldg_row16<(ROWB <= 64)>(row_ptr<ROWB>(table, id[u]));
+                    for (int u = 0; u < K; u++) {
+                        if constexpr (HOT)
+                            v[u] = ldg_row16_policy<(ROWB <= 64)>(row_ptr<ROWB>(table, id[u]), id[u] < hot_rows, pol_hot,
+                                                                  pol_cold);
+                        else
+                            v[u] = ldg_row16<(ROWB <= 64)>(row_ptr<ROWB>(table, id[u]));
+                    }
                 };
                 load_step(0);
                 for (uint32_t c = K; c < per; c += K) {
@@ -770,11 +852,16 @@ bag_sum_stretch_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint3
             const uint32_t start = s_off[2 * bag], end = s_off[2 * bag + 1];
             uint4 acc = make_uint4(0u, 0u, 0u, 0u);
             for (uint32_t p = start; p < end; p++) {
-                const uint32_t id = __ldg(g_idx + p) - row_base;
-                if (id < rows)
+                uint32_t id = __ldg(g_idx + p) - row_base;
+                if (id < rows) {
+                    if constexpr (HOT) {
+                        if (remap)
+                            id = __ldg(remap + id);
+                    }
                     acc = add_rows<IS_FLOAT>(acc, ldg_row16<(ROWB <= 64)>(reinterpret_cast<const uint4 *>(table + (size_t)id * ROWB)));
-                else
+                } else {
                     bad = true;
+                }
             }
             sts_u128(acc_s + bag * ROWB + sl * 16, acc);
         }
@@ -1119,6 +1206,32 @@ __global__ void scatter_column_kernel(uint32_t *__restrict__ slab, const uint32_
 
 /* export_emb (dlrm_dpu_pytorch.py:318-320) on the GPU; the slab is already row-major so
  * the reference's transpose disappears.  dst may alias src. */
+/* emb_table_remap: row r of the slab moves to row new_of_old[r] of a new slab (4-byte elements, any dim). */
+__global__ void permute_rows_kernel(uint32_t *__restrict__ dst, const uint32_t *__restrict__ src,
+                                    const uint32_t *__restrict__ new_of_old, uint64_t nr_rows, uint32_t dim)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t step = (uint64_t)gridDim.x * blockDim.x, n = nr_rows * dim;
+    for (; i < n; i += step) {
+        const uint64_t r = i / dim;
+        dst[(uint64_t)new_of_old[r] * dim + (i - r * dim)] = src[i];
+    }
+}
+
+/* emb_remap_indices: caller row ids -> slab row ids, in place; ids outside the table are left as they are (and are
+ * still reported by the pooling launch). */
+__global__ void remap_indices_kernel(uint32_t *__restrict__ idx, const uint32_t *__restrict__ new_of_old,
+                                     uint64_t n, uint32_t nr_rows)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += step) {
+        const uint32_t r = idx[i];
+        if (r < nr_rows)
+            idx[i] = __ldg(new_of_old + r);
+    }
+}
+
 __global__ void quantise_kernel(int32_t *dst, const float *src, uint64_t n)
 {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -94,6 +94,8 @@ EMB_TABLE_FIXED = 1
 EMB_TABLE_FLOAT = 2
 EMB_Q_RAW_SUMS = 1
 EMB_Q_OVERLAP = 2  # plans: the launch reads nothing the kernel in front of it writes (include/emb_b200.h)
+EMB_Q_REMAPPED = 4  # the query's indices are slab row ids of a reordered table already
+EMB_HOT_KEEP, EMB_HOT_STREAM_COLD = 1, 2  # emb_table_set_hot_rows modes
 EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED, EMB_HOST_MAPPED_OUT, EMB_HOST_BOUNCE = 0, 1, 2, 3, 4
 EMB_IPC_HANDLE_BYTES = 64
 

@@ -63,7 +63,14 @@ def _declare(lib):
         "emb_table_info": ([C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_int), C.POINTER(C.c_void_p)], C.c_int),
         "emb_free_table": ([C.c_uint32], C.c_int),
         "emb_l2_persist": ([C.c_uint32, C.c_uint64, C.c_uint64, C.c_float, C.c_void_p], C.c_int),
+        "emb_table_set_hot_rows": ([C.c_uint32, C.c_uint64, C.c_int], C.c_int),
+        "emb_table_remap": ([C.c_uint32, u32p], C.c_int),
+        "emb_hot_order": ([C.POINTER(C.c_uint64), C.c_uint64, u32p], C.c_int),
+        "emb_remap_indices": ([C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p], C.c_int),
         "emb_lookup_ex": ([C.c_uint32, C.POINTER(u32p), C.POINTER(u32p), u32p, u32p, C.POINTER(f32p)], C.c_int),
+        "emb_lookup_ex_async": ([C.c_uint32, C.POINTER(u32p), C.POINTER(u32p), u32p, u32p, C.POINTER(f32p),
+                                 C.POINTER(C.c_uint64)], C.c_int),
+        "emb_lookup_wait": ([C.c_uint64], C.c_int),
         "emb_plan_create": ([C.POINTER(EmbDevQuery), C.c_uint32, C.POINTER(C.c_void_p)], C.c_int),
         "emb_plan_launch": ([C.c_void_p, C.c_void_p], C.c_int),
         "emb_plan_destroy": ([C.c_void_p], None),
@@ -186,6 +193,30 @@ def table_read(table_id: int, row0: int, n: int, dtype=np.int32) -> np.ndarray:
     return out
 
 
+def hot_order(counts) -> np.ndarray:
+    """emb_hot_order: new_of_old permutation that puts the most looked-up rows first (host only)."""
+    c = np.ascontiguousarray(counts, dtype=np.uint64)
+    out = np.empty(c.size, dtype=np.uint32)
+    check(load().emb_hot_order(c.ctypes.data_as(C.POINTER(C.c_uint64)), c.size, _p(out, u32p)), "emb_hot_order")
+    return out
+
+
+def remap_table(table_id: int, new_of_old) -> None:
+    """emb_table_remap: reorder the slab; callers keep their row ids."""
+    m = np.ascontiguousarray(new_of_old, dtype=np.uint32)
+    check(load().emb_table_remap(table_id, _p(m, u32p)), "emb_table_remap")
+
+
+def set_hot_rows(table_id: int, hot_rows: int, mode: int) -> None:
+    check(load().emb_table_set_hot_rows(table_id, hot_rows, mode), "emb_table_set_hot_rows")
+
+
+def remap_indices(table_id: int, indices_dev, stream=None) -> None:
+    """emb_remap_indices on a device tensor of row ids (int32 bits of uint32), in place."""
+    check(load().emb_remap_indices(table_id, _addr(indices_dev), _numel(indices_dev), _stream(stream)),
+          "emb_remap_indices")
+
+
 def pinned_array(shape, dtype=np.uint32) -> np.ndarray:
     """NumPy array in page-locked host memory (emb_host_alloc): lookup()/lookup_ex() on such arrays
     take the EMB_HOST_MAPPED path (no staging copies).  Freed with free_pinned()."""
@@ -255,6 +286,22 @@ class HostCall:
         rc = self._fn(*self._args)
         if rc:
             check(rc, "emb_lookup_ex")
+        return self.results
+
+    def start(self) -> int:
+        """emb_lookup_ex_async: enqueue the call, return its ticket.  The arrays must stay untouched until wait()."""
+        tk = C.c_uint64(0)
+        rc = load().emb_lookup_ex_async(*self._args, C.byref(tk))
+        if rc:
+            check(rc, "emb_lookup_ex_async")
+        self._ticket = tk.value
+        return tk.value
+
+    def wait(self):
+        """emb_lookup_wait on the ticket of the last start(); the results are in host memory on return."""
+        rc = load().emb_lookup_wait(self._ticket)
+        if rc:
+            check(rc, "emb_lookup_wait")
         return self.results
 
 
