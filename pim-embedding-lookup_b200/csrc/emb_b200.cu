@@ -1560,7 +1560,7 @@ static uintptr_t alloc_base(const void *p)
 /* Enqueue one host-pointer call on slot `hs`: everything up to, but not including, the wait for its last copy or
  * kernel.  hs.p describes the call for host_complete().  `ticket` != 0: an asynchronous call -- the end of its work
  * is marked with hs.ev_done, because by the time it is waited for the streams may hold the next call's work too. */
-static int host_enqueue(HostSlot &hs, uint64_t ticket, uint32_t T, const uint32_t *const *indices,
+static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t T, const uint32_t *const *indices,
                         const uint32_t *const *offsets, const uint32_t *indices_len, const uint32_t *nr_batches,
                         float *const *final_results)
 {
@@ -1699,6 +1699,13 @@ static int host_enqueue(HostSlot &hs, uint64_t ticket, uint32_t T, const uint32_
         n_groups = std::min(std::min(T, kMaxGroups), std::max(2u, (uint32_t)((staged + unit / 2) / unit)));
     }
     const uint32_t forced_groups = env_u32("EMB_GROUPS", 0);  // measurement knob
+    // `overlapped`: an asynchronous call issued while the previous one is still in flight.  The overlap that the
+    // groups create inside one call is then there ACROSS calls (this call's copy-in runs under the previous call's
+    // kernels and copy-out), and every group boundary only idles a copy engine: one group.  C2, two calls in flight
+    // (tools/e2e_sweep.py --in-flight, profiles/r2_host_async.md): 1 / 2 / 3 / 6 groups -> 2.17 / 2.29 / 2.31 / 2.41 ms
+    // per call; one call at a time wants the groups: 3.62 / 3.09 / 2.88 / 2.75 ms.
+    if (overlapped && !forced_groups)
+        n_groups = 1;
     if (forced_groups && n_groups > 1)
         n_groups = std::min(std::min(T, kMaxGroups), forced_groups);
     if ((rc = ensure_events(hs, 3 * n_groups + 2)))
@@ -1946,7 +1953,7 @@ static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_
     int rc = host_drain();
     if (rc)
         return rc;
-    if ((rc = host_enqueue(g.hslot[0], 0, T, indices, offsets, indices_len, nr_batches, final_results)))
+    if ((rc = host_enqueue(g.hslot[0], 0, false, T, indices, offsets, indices_len, nr_batches, final_results)))
         return rc;
     return host_complete(g.hslot[0]);
 }
@@ -2011,7 +2018,8 @@ int emb_lookup_ex_async(uint32_t nr_tables, const uint32_t *const *indices, cons
     // host memory from here on, and emb_lookup_wait on it returns at once
     if ((rc = host_complete(hs)))
         return rc;
-    if ((rc = host_enqueue(hs, tk, nr_tables, indices, offsets, indices_len, nr_batches, final_results)))
+    const bool overlapped = g.hslot[(tk + 1) % kHostSlots].p.active;  // the previous call has not been waited for
+    if ((rc = host_enqueue(hs, tk, overlapped, nr_tables, indices, offsets, indices_len, nr_batches, final_results)))
         return rc;
     g.next_ticket = tk + 1;
     *ticket = tk;

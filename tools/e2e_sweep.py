@@ -23,6 +23,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--workload", default="c2")
+    ap.add_argument("--in-flight", action="store_true",
+                    help="arena arrays, copies both ways: emb_lookup_ex one call at a time against emb_lookup_ex_async "
+                         "with two calls in flight, per group count")
     ap.add_argument("--quick", action="store_true",
                     help="arena arrays only: the default path (EMB_HOST_AUTO) against forced copies / mapped results")
     args = ap.parse_args()
@@ -79,6 +82,36 @@ def main():
         dt = (time.perf_counter() - t0) / n
         return dt * 1e3, emblib.last_timings()
 
+    if args.in_flight:
+        calls = arrays(True)
+        # the second call in flight needs result arrays of its own
+        ra2 = bench.pinned_arena(lib, T * B * D * 4 + 64)
+        res2 = [ra2[t * B * D * 4:(t + 1) * B * D * 4].view(np.float32).reshape(B, D) for t in range(T)]
+        calls[1] = emblib.HostCall(calls[1].indices, calls[1].offsets, res2)
+
+        def timed_in_flight(n):
+            def run(m):
+                calls[0].start()
+                for k in range(m):
+                    if k + 1 < m:
+                        calls[(k + 1) % 2].start()
+                    calls[k % 2].wait()
+            run(4)
+            t0 = time.perf_counter()
+            run(n)
+            return (time.perf_counter() - t0) / n * 1e3
+
+        emblib.set_host_path(EMB_HOST_AUTO)
+        for groups in (0, 1, 2, 3, 4, 6, 8, 12):
+            os.environ["EMB_GROUPS"] = str(groups)
+            ms, tm = timed(calls, args.steps)
+            ms2 = timed_in_flight(args.steps)
+            print(json.dumps({"workload": args.workload, "groups": groups, "launches_per_call": int(tm.launches),
+                              "sync_ms_per_call": round(ms, 4), "two_in_flight_ms_per_call": round(ms2, 4),
+                              "G_lookups_per_s_in_flight": round(np.mean(lookups) / ms2 / 1e6, 3)}), flush=True)
+        os.environ["EMB_GROUPS"] = "0"
+        emblib.shutdown()
+        return
     if args.quick:
         calls = arrays(True)
         for path, pname in ((EMB_HOST_AUTO, "auto"), (EMB_HOST_MAPPED_OUT, "mapped_out"), (EMB_HOST_COPY, "copy")):

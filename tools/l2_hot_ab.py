@@ -43,6 +43,18 @@ def draw_ranks(torch, cdf, n, gen):
     return torch.searchsorted(cdf, u).clamp_(max=cdf.numel() - 1)
 
 
+def mix_cdf(torch, R, hot_rows, hot_frac, device):
+    """Two classes: a fraction hot_frac of the lookups falls uniformly on the first hot_rows ranks, the rest uniformly
+    on all the others -- a hot set with NO reuse between its members and a cold stream with none at all, the case in
+    which LRU-like replacement lets the stream push the hot set out once the cold bytes between two uses of a hot
+    row approach the cache size."""
+    w = torch.empty(R, dtype=torch.float64, device=device)
+    w[:hot_rows] = hot_frac / hot_rows
+    w[hot_rows:] = (1.0 - hot_frac) / (R - hot_rows)
+    cdf = torch.cumsum(w, 0)
+    return cdf / cdf[-1]
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--tables", type=int, default=32)
@@ -51,6 +63,11 @@ def main():
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--pool", type=int, default=80)
     ap.add_argument("--alpha", type=float, default=1.05)
+    ap.add_argument("--dist", default="zipf", choices=["zipf", "mix"],
+                    help="zipf: rank^-alpha; mix: --hot-frac of the lookups uniformly on a hot set of --hot-set-mb "
+                         "(all tables together), the rest uniformly on the other rows")
+    ap.add_argument("--hot-frac", type=float, default=0.5)
+    ap.add_argument("--hot-set-mb", type=float, default=48.0)
     ap.add_argument("--hot-mb", type=float, nargs="*", default=[32.0, 64.0, 96.0])
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--sample-batches", type=int, default=4, help="batches of the separate sample the order is estimated from")
@@ -75,7 +92,14 @@ def main():
         del a
     torch.cuda.empty_cache()
 
-    cdf = zipf_cdf(torch, R, args.alpha, "cuda")
+    if args.dist == "zipf":
+        cdf = zipf_cdf(torch, R, args.alpha, "cuda")
+        dist_name = f"rank^-{args.alpha:g}"
+    else:
+        hs_rows = max(1, int(args.hot_set_mb * 1e6 / (T * D * 4)))
+        cdf = mix_cdf(torch, R, hs_rows, args.hot_frac, "cuda")
+        dist_name = (f"{args.hot_frac:g} of the lookups uniform on a hot set of {hs_rows} rows per table "
+                     f"({args.hot_set_mb:g} MB in all), the rest uniform on the other rows")
     perms = [torch.randperm(R, device="cuda", generator=gen) for _ in range(T)]
     n = B * P
     off = (torch.arange(B, dtype=torch.int64, device="cuda") * P).to(torch.int32)
@@ -145,6 +169,11 @@ def main():
             emblib.remap_indices(t, b[t], stream)
     torch.cuda.synchronize()
     measure("remap+pre", pre, EMB_Q_REMAPPED, "rows reordered hot-first; ids translated by the caller")
+    # the cost of the load FORM alone: one hot row per table, so that every load carries a policy operand
+    # (evict_normal for all but that row) and nothing else changes
+    for t in range(T):
+        emblib.set_hot_rows(t, 1, EMB_HOT_KEEP)
+    measure("remap+pre+form", pre, EMB_Q_REMAPPED, "every row load carries an L2 policy operand, all of them evict_normal")
     modes = [("keep", EMB_HOT_KEEP), ("stream", EMB_HOT_STREAM_COLD), ("both", EMB_HOT_KEEP | EMB_HOT_STREAM_COLD)]
     if args.arms == "quick":
         modes = modes[2:]
@@ -159,7 +188,7 @@ def main():
             measure(f"remap+{modes[-1][0]}@{mb:g}MB", batches, 0,
                     f"the same with the kernel translating the ids, mode {modes[-1][0]}")
     base = results[0]["kernel_ms_median"]
-    cfg = f"{T} x {R} rows x dim {D}, batch {B}, pooling {P}, rank^-{args.alpha:g}; tables {T * R * D * 4 / 1e9:.1f} GB"
+    cfg = f"{T} x {R} rows x dim {D}, batch {B}, pooling {P}, {dist_name}; tables {T * R * D * 4 / 1e9:.1f} GB"
     print(f"\n### {args.tag or 'l2_hot_ab'}: {cfg}\n")
     print("| arm | kernel ms (median) | vs plain | G lookups/s | algorithmic GB/s | same bits |")
     print("|---|---|---|---|---|---|")

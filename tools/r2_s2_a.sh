@@ -7,8 +7,6 @@ TAG=${1:-s2a}; OUT=gpurun_out; mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw,memory.total --format=csv > $OUT/smi_$TAG.txt 2>&1
 ( time timeout 300 python -m pytest tests/test_gpu_async.py tests/test_gpu_hot.py -m gpu -q ) > $OUT/pytest_new_$TAG.log 2>&1
 echo "pytest new rc=$?"; tail -15 $OUT/pytest_new_$TAG.log
-( time timeout 900 python -m pytest tests -m gpu -q --deselect tests/test_gpu_async.py --deselect tests/test_gpu_hot.py ) > $OUT/pytest_all_$TAG.log 2>&1
-echo "pytest all rc=$?"; tail -8 $OUT/pytest_all_$TAG.log
 ( time timeout 400 python bench.py --steps 20 --warmup 5 --extras none --no-cpu-baseline ) > $OUT/bench_quick_$TAG.json 2> $OUT/bench_quick_$TAG.err
 echo "bench rc=$?"; tail -3 $OUT/bench_quick_$TAG.err
 python - <<PY
@@ -25,6 +23,9 @@ PY
 HOT=$OUT/l2_hot_$TAG.txt; : > $HOT
 run() { echo "## $*" >> $HOT; timeout 420 "$@" >> $HOT 2>&1; echo "rc=$?" >> $HOT; }
 run python tools/l2_hot_ab.py --tag big_dim128 --steps 30
+grep -E "^\||^###|rc=|Error|error" $HOT | cut -c1-200
+( time timeout 600 python -m pytest tests -m gpu -q --deselect tests/test_gpu_async.py --deselect tests/test_gpu_hot.py ) > $OUT/pytest_all_$TAG.log 2>&1
+echo "pytest all rc=$?"; tail -8 $OUT/pytest_all_$TAG.log
 run python tools/l2_hot_ab.py --tag c5_as_benched --rows 500000 --arms quick --steps 30
 run python tools/l2_hot_ab.py --tag narrow_dim16 --tables 26 --rows 4000000 --dim 16 --batch 65536 --pool 10 --arms quick --steps 30
 grep -E "^\||^###|rc=|Error|error" $HOT | cut -c1-200
