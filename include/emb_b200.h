@@ -143,6 +143,27 @@ int emb_configure(uint32_t nr_tables, uint32_t nr_cols, uint32_t max_nr_batches,
                   uint32_t max_indices_per_batch, int device);
 int emb_get_shape(emb_shape *out);
 int emb_device(void);
+
+/* Several GPUs of one box behind the reference's two entry points (the reference spreads its tables over all DPU
+ * ranks of the machine the same way; emb_host.h:136-183 allocates NR_TABLES*NR_COLS DPUs).  A DEVICE GROUP places
+ * whole tables on its GPUs -- table t on GPU table_device[t] of the group, or t % n_devices when table_device is NULL
+ * -- and then
+ *   - populate_mram / emb_populate_table_* / emb_table_* / emb_free_table act on the GPU that holds the table;
+ *   - lookup / emb_lookup_ex / emb_lookup_ex_async cut a call by GPU, enqueue every part, then wait: each GPU moves
+ *     its tables' indices in and pooled rows out over its own PCIe link at the same time as the others.  The
+ *     reference's per-table result arrays need no exchange, so there is no collective;
+ *   - emb_check_indices / emb_shutdown cover every GPU; emb_last_timings reports the slowest GPU's stage times and
+ *     the summed bytes and launches.
+ * Device-resident entry points (plans, emb_lookup_device, the exchange, emb_device_alloc ...) act on the group's FIRST
+ * GPU only; several GPUs with device-resident data are one process per GPU (ShardedTables).
+ * An unmodified caller gets a group from the environment: EMB_DEVICES="0,1,2,3" or EMB_NGPUS=4, read where the shape
+ * variables are read.  The group can change only after emb_shutdown().  devices[] may name a GPU more than once (two
+ * contexts on one GPU: of use for tests only). */
+int emb_configure_devices(uint32_t nr_tables, uint32_t nr_cols, uint32_t max_nr_batches,
+                          uint32_t max_indices_per_batch, const int *devices, uint32_t n_devices,
+                          const uint32_t *table_device);
+int emb_group_size(void);                /* GPUs in the group (1 by default)                  */
+int emb_table_device(uint32_t table_id); /* CUDA device that holds (or will hold) the table   */
 /* Frees every table, buffer, plan-independent resource; the next call re-initialises.
  * (The reference never frees its DPU set, emb_host.h:156-160.) */
 void emb_shutdown(void);

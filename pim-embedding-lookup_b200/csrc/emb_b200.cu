@@ -109,7 +109,6 @@ struct Ctx {
 
     // host-pointer lookup path: per-call state, two slots (emb_lookup_ex_async keeps two calls in flight)
     HostSlot hslot[kHostSlots];
-    uint64_t next_ticket = 1;  // tickets of emb_lookup_ex_async: slot = ticket % kHostSlots
     // descriptor ring of emb_lookup_device
     BagDesc *ring_h[4] = {nullptr, nullptr, nullptr, nullptr};
     BagDesc *ring_d[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -117,14 +116,33 @@ struct Ctx {
     uint32_t ring_cap = 0;
     int ring_next = 0;
     emb_timings last = {0, 0, 0, 0, 0, 0, 0, 0};
-    // tuning knobs (emb_set_tuning); 0 = default
+};
+
+/* Process-wide knobs (emb_set_tuning, emb_set_host_path); 0 = default.  They survive emb_shutdown(). */
+struct Tuning {
     int unroll = 0;     // rows in flight per sub-warp: 4 or 8
     int variant = 0;    // 1 = bag-per-sub-warp kernel, 4 = TMA gather4, 6 = stretch kernel
     int bags_mult = 0;  // stretch kernel: bags per CTA = mult * sub-warps per CTA (1, 2, 4, 8)
     int host_path = EMB_HOST_AUTO;  // emb_set_host_path
 };
+Tuning g_tune;
 
-Ctx g;
+/* One context per GPU of the device group (emb_configure_devices / $EMB_NGPUS; a group of one by default).  Every
+ * function below works on "the current context" `g`; entry points that name a table switch to the context of the GPU
+ * that holds it (UseCtx), the host-pointer lookups cut a call by GPU and run the parts concurrently.  Everything is
+ * serialised by g_mu, so the current context is a plain global. */
+constexpr int kMaxDevices = EMB_MAX_PEERS;
+Ctx g_ctxs[kMaxDevices];
+Ctx *g_cur = &g_ctxs[0];
+#define g (*g_cur)
+struct Group {
+    int n = 1;                      // contexts in use: g_ctxs[0 .. n)
+    std::vector<int> table_device;  // explicit placement (index into the group), empty = table_id % n
+};
+Group g_grp;
+uint64_t g_next_ticket = 1;  // tickets of emb_lookup_ex_async: slot = ticket % kHostSlots, on every GPU of the group
+emb_timings g_group_last = {0, 0, 0, 0, 0, 0, 0, 0};  // emb_last_timings() of a call that ran on several GPUs
+bool g_group_last_valid = false;
 std::mutex g_mu;
 std::atomic<uint64_t> g_launches{0};
 thread_local char g_err[512] = "";
@@ -169,6 +187,35 @@ double now_s()
     struct timespec t;
     clock_gettime(CLOCK_MONOTONIC, &t);
     return t.tv_sec + t.tv_nsec * 1e-9;
+}
+
+/* Make context k (and its GPU) the current one for the lifetime of the object. */
+struct UseCtx {
+    Ctx *prev;
+    explicit UseCtx(int k) : prev(g_cur)
+    {
+        g_cur = &g_ctxs[k];
+        if (g_cur != prev && g_cur->device_ready)
+            cudaSetDevice(g_cur->device);
+    }
+    ~UseCtx()
+    {
+        if (g_cur != prev && prev->device_ready)
+            cudaSetDevice(prev->device);
+        g_cur = prev;
+    }
+    UseCtx(const UseCtx &) = delete;
+    UseCtx &operator=(const UseCtx &) = delete;
+};
+
+/* Which GPU of the group holds a table: whole tables, dealt round-robin unless the caller gave a map. */
+int owner_of(uint32_t table_id)
+{
+    if (g_grp.n <= 1)
+        return 0;
+    if (table_id < g_grp.table_device.size())
+        return g_grp.table_device[table_id];
+    return (int)(table_id % (uint32_t)g_grp.n);
 }
 
 int ensure_device()
@@ -236,6 +283,66 @@ int configure_locked(uint32_t T, uint32_t D, uint32_t B, uint32_t P, int device)
     return ensure_device();
 }
 
+/* Configure a device group: context k on devices[k], all with the same shape.  A group can only change while no
+ * context holds a device (emb_shutdown() first). */
+int configure_group(uint32_t T, uint32_t D, uint32_t B, uint32_t P, const int *devices, int n, const uint32_t *table_device)
+{
+    if (!devices || n < 1 || n > kMaxDevices)
+        return fail(EMB_EINVAL, "a device group has 1..%d GPUs", kMaxDevices);
+    bool live = false;
+    for (const Ctx &c : g_ctxs)
+        live |= c.device_ready;
+    if (live) {
+        bool same = n == g_grp.n;
+        for (int k = 0; k < n && same; k++)
+            same = g_ctxs[k].device_ready && g_ctxs[k].device == devices[k];
+        if (!same)
+            return fail(EMB_ESTATE, "the device group cannot change while the library holds devices: emb_shutdown() first");
+    }
+    if (table_device)
+        for (uint32_t t = 0; t < T; t++)
+            if (table_device[t] >= (uint32_t)n)
+                return fail(EMB_EINVAL, "table %u placed on GPU %u of a group of %d", t, table_device[t], n);
+    for (int k = 0; k < n; k++) {
+        if (devices[k] < 0)
+            return fail(EMB_EINVAL, "device group member %d: device %d", k, devices[k]);
+        UseCtx u(k);
+        int rc = configure_locked(T, D, B, P, devices[k]);
+        if (rc)
+            return rc;
+    }
+    g_grp.n = n;
+    g_grp.table_device.clear();
+    if (table_device)
+        g_grp.table_device.assign(table_device, table_device + T);
+    if (g_cur->device_ready)
+        cudaSetDevice(g_cur->device);
+    return EMB_OK;
+}
+
+/* $EMB_DEVICES ("0,1,2,3") or $EMB_NGPUS (devices 0..n-1): the device group of a caller that knows nothing about
+ * this library beyond populate_mram() / lookup().  Returns the number of devices (0: no group asked for). */
+int group_from_env(int *devices)
+{
+    const char *v = getenv("EMB_DEVICES");
+    int n = 0;
+    if (v && *v) {
+        while (*v && n < kMaxDevices) {
+            char *end = nullptr;
+            long d = strtol(v, &end, 10);
+            if (end == v)
+                break;
+            devices[n++] = (int)d;
+            v = (*end == ',') ? end + 1 : end;
+        }
+        return n;
+    }
+    n = (int)std::min<uint32_t>(env_u32("EMB_NGPUS", 0), kMaxDevices);
+    for (int k = 0; k < n; k++)
+        devices[k] = k;
+    return n;
+}
+
 /* The reference bakes these four in with -D at build time (upmem/Makefile:69-81) and its
  * Python reads NR_TABLES from the environment (dlrm_dpu_pytorch.py:128); the run scripts
  * export all of them (upmem/run.sh:40-45,93-101).  Same names, read at first use. */
@@ -243,12 +350,18 @@ int ensure_configured()
 {
     if (g.configured)
         return ensure_device();
+    if (g_cur != &g_ctxs[0])
+        return fail(EMB_ESTATE, "GPU %d of the device group is not configured", (int)(g_cur - g_ctxs));
     uint32_t T = env_u32("NR_TABLES", 0), D = env_u32("NR_COLS", 0);
     uint32_t B = env_u32("MAX_NR_BATCHES", 0), P = env_u32("MAX_INDICES_PER_BATCH", 0);
     if (!T || !D)
         return fail(EMB_ESTATE, "shape unknown: set NR_TABLES, NR_COLS, MAX_NR_BATCHES, "
                                 "MAX_INDICES_PER_BATCH in the environment or call emb_configure()");
-    return configure_locked(T, D, B, P, -1);
+    int devices[kMaxDevices];
+    const int n = group_from_env(devices);
+    if (n > 1)
+        return configure_group(T, D, B, P, devices, n, nullptr);
+    return configure_locked(T, D, B, P, n == 1 ? devices[0] : -1);
 }
 
 int table_slot(uint32_t table_id, Table **out)
@@ -439,14 +552,14 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = fal
         return v;
     }
     static const int dflt_kind = (int)env_u32("EMB_DEFAULT_VARIANT", 6);  // measurement knob
-    v.kind = g.variant ? g.variant : (dflt_kind == 1 || dflt_kind == 4 ? dflt_kind : 6);
+    v.kind = g_tune.variant ? g_tune.variant : (dflt_kind == 1 || dflt_kind == 4 ? dflt_kind : 6);
     if (v.kind == 4 && lanes < 4)
         v.kind = 6;  // the TMA kernel is for rows of 64 bytes and more
     if (any_float && v.kind != 4 && !(v.kind == 6 && all_float))
         v.kind = 1;  // fp32 sums in strict index order (embedding_lookup_idx.cc:33-77): kinds 1 and 4; the stretch
                      // kernel pools fp32 tables too (deterministic, reassociated at its cut points), but a launch
                      // is compiled for one element kind
-    v.unroll = g.unroll ? g.unroll : (lanes >= 16 ? 8 : 4);
+    v.unroll = g_tune.unroll ? g_tune.unroll : (lanes >= 16 ? 8 : 4);
     v.mult = 1;
     v.bags = emb::kThreads / lanes;  // kind 1: one bag per sub-warp of a 256-thread CTA
     if (v.kind == 6) {
@@ -457,8 +570,8 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = fal
         //   256-byte rows (C4):  K8 m4 0.5761 | K8 m2 0.5924 | K4 m4 0.6148 | K8 m8 0.6206
         //   512-byte rows (C5):  K8 m1 0.4222 | K8 m2 0.4469 | K8 m4 0.4828
         const bool short_bags = avg_pool > 0.0 && avg_pool <= 4.0;
-        v.unroll = g.unroll ? g.unroll : (short_bags && lanes <= 8 ? 4 : 8);
-        v.mult = g.bags_mult ? g.bags_mult : (lanes >= 32 ? 1 : lanes >= 16 ? 4 : short_bags ? 4 : 2);
+        v.unroll = g_tune.unroll ? g_tune.unroll : (short_bags && lanes <= 8 ? 4 : 8);
+        v.mult = g_tune.bags_mult ? g_tune.bags_mult : (lanes >= 32 ? 1 : lanes >= 16 ? 4 : short_bags ? 4 : 2);
         static const int big_stage = (int)env_u32("EMB_STRETCH_STAGE", 0);  // measurement knob: 1 = the larger pass
         v.stage = big_stage;
         v.bags = std::min<uint32_t>(32 / lanes * v.mult, 64);  // one marker byte per lookup names the bag
@@ -576,10 +689,11 @@ void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uin
         constexpr int WARPS = emb::kThreads / 32;
         constexpr size_t smem = (size_t)WARPS * emb::kTmaStages * emb::kTmaStageBytes + WARPS * emb::kTmaStages * 8 +
                                 WARPS * (4 * (32 / LANES) + 1) * 4;
-        static bool once = false;
-        if (!once) {
+        static bool once[64] = {};  // a function attribute is per device
+        if (g.device < 0 || g.device >= 64 || !once[g.device]) {
             cudaFuncSetAttribute(emb::bag_sum_tma_kernel<LANES, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            once = true;
+            if (g.device >= 0 && g.device < 64)
+                once[g.device] = true;
         }
         emb::bag_sum_tma_kernel<LANES, 3><<<grid, emb::kThreads, smem, s>>>(d, n, uni, g.d_err);
     } else {
@@ -746,7 +860,41 @@ int emb_configure(uint32_t nr_tables, uint32_t nr_cols, uint32_t max_nr_batches,
                   uint32_t max_indices_per_batch, int device)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    if (g_grp.n > 1) {  // a group exists: the shape changes on every GPU of it
+        if (device >= 0 && device != g_ctxs[0].device)
+            return fail(EMB_ESTATE, "a device group is configured: emb_shutdown() before binding to device %d", device);
+        for (int k = 0; k < g_grp.n; k++) {
+            UseCtx u(k);
+            int rc = configure_locked(nr_tables, nr_cols, max_nr_batches, max_indices_per_batch, g.device);
+            if (rc)
+                return rc;
+        }
+        return EMB_OK;
+    }
+    if (!g.configured && device < 0) {
+        int devices[kMaxDevices];
+        const int n = group_from_env(devices);
+        if (n > 1)
+            return configure_group(nr_tables, nr_cols, max_nr_batches, max_indices_per_batch, devices, n, nullptr);
+        if (n == 1)
+            device = devices[0];
+    }
     return configure_locked(nr_tables, nr_cols, max_nr_batches, max_indices_per_batch, device);
+}
+
+int emb_configure_devices(uint32_t nr_tables, uint32_t nr_cols, uint32_t max_nr_batches, uint32_t max_indices_per_batch,
+                          const int *devices, uint32_t n_devices, const uint32_t *table_device)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    return configure_group(nr_tables, nr_cols, max_nr_batches, max_indices_per_batch, devices, (int)n_devices, table_device);
+}
+
+int emb_group_size(void) { return g_grp.n; }
+
+int emb_table_device(uint32_t table_id)
+{
+    const int k = owner_of(table_id);
+    return g_ctxs[k].device_ready ? g_ctxs[k].device : -1;
 }
 
 int emb_get_shape(emb_shape *out)
@@ -770,7 +918,7 @@ int emb_set_unroll(int unroll)
 {
     if (unroll != 0 && unroll != 4 && unroll != 8)
         return fail(EMB_EINVAL, "unroll must be 0, 4 or 8");
-    g.unroll = unroll;
+    g_tune.unroll = unroll;
     return EMB_OK;
 }
 
@@ -784,8 +932,8 @@ int emb_set_tuning(int variant, int unroll, int bags_mult)
     int rc = emb_set_unroll(unroll);
     if (rc)
         return rc;
-    g.variant = variant;
-    g.bags_mult = bags_mult;
+    g_tune.variant = variant;
+    g_tune.bags_mult = bags_mult;
     return EMB_OK;
 }
 
@@ -794,13 +942,12 @@ int emb_set_host_path(int path)
     if (path < EMB_HOST_AUTO || path > EMB_HOST_BOUNCE)
         return fail(EMB_EINVAL, "host path must be EMB_HOST_AUTO, _COPY, _MAPPED, _MAPPED_OUT or _BOUNCE");
     std::lock_guard<std::mutex> lk(g_mu);
-    g.host_path = path;
+    g_tune.host_path = path;
     return EMB_OK;
 }
 
-void emb_shutdown(void)
+static void shutdown_current()
 {
-    std::lock_guard<std::mutex> lk(g_mu);
     if (g.device_ready) {
         cudaSetDevice(g.device);
         host_drain();
@@ -847,12 +994,19 @@ void emb_shutdown(void)
         if (g.stream_in)
             cudaStreamDestroy(g.stream_in);
     }
-    int unroll = g.unroll, variant = g.variant, bags_mult = g.bags_mult, host_path = g.host_path;
     g = Ctx();
-    g.unroll = unroll;
-    g.variant = variant;
-    g.bags_mult = bags_mult;
-    g.host_path = host_path;
+}
+
+void emb_shutdown(void)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (int k = kMaxDevices - 1; k >= 0; k--) {  // every GPU of the group; the tuning knobs survive
+        g_cur = &g_ctxs[k];
+        shutdown_current();
+    }
+    g_cur = &g_ctxs[0];
+    g_grp = Group();
+    g_group_last_valid = false;
 }
 
 /* ---------------------------------------------------------------- tables -------------- */
@@ -865,6 +1019,7 @@ struct dpu_set_t *populate_mram(uint32_t table_id, uint64_t nr_rows, uint32_t co
     int rc = ensure_configured();
     if (rc)
         die("populate_mram", rc);
+    UseCtx on_owner(owner_of(table_id));  // the GPU of the device group that holds this table
     const uint32_t D = g.shape.nr_cols;
     if (col >= D || !table_data) {
         fail(EMB_EINVAL, "col %u >= NR_COLS %u or NULL data", col, D);
@@ -894,7 +1049,7 @@ struct dpu_set_t *populate_mram(uint32_t table_id, uint64_t nr_rows, uint32_t co
     }
     if (runtime)
         runtime->execution_time_populate_copy_in += now_s() - t0;
-    return reinterpret_cast<struct dpu_set_t *>(&g);
+    return reinterpret_cast<struct dpu_set_t *>(&g_ctxs[0]);
 }
 
 static int populate_whole(uint32_t table_id, uint64_t nr_rows, const void *src, bool src_device,
@@ -927,12 +1082,20 @@ static int populate_whole(uint32_t table_id, uint64_t nr_rows, const void *src, 
 int emb_populate_table_i32(uint32_t table_id, uint64_t nr_rows, const int32_t *row_major)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    UseCtx on_owner(owner_of(table_id));
     return populate_whole(table_id, nr_rows, row_major, false, false, EMB_TABLE_FIXED, g.stream);
 }
 
 int emb_populate_table_f32(uint32_t table_id, uint64_t nr_rows, const float *row_major, int kind)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ensure_configured();
+    if (rc)
+        return rc;
+    UseCtx on_owner(owner_of(table_id));
     return populate_whole(table_id, nr_rows, row_major, false, true, kind, g.stream);
 }
 
@@ -943,13 +1106,17 @@ int emb_populate_table_device(uint32_t table_id, uint64_t nr_rows, const void *d
     int rc = ensure_configured();
     if (rc)
         return rc;
+    UseCtx on_owner(owner_of(table_id));
+    // in a device group the caller's stream belongs to another GPU than the table's for most tables: the copy then
+    // runs on the owner's own stream and the source must be complete when the call is made
     return populate_whole(table_id, nr_rows, dev_row_major, true, src_is_f32 != 0, kind,
-                          stream ? (cudaStream_t)stream : g.stream);
+                          (stream && g_grp.n <= 1) ? (cudaStream_t)stream : g.stream);
 }
 
 int emb_table_set_row_base(uint32_t table_id, uint64_t row_base)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
     if (row_base > 0xffffffffull)
@@ -964,6 +1131,7 @@ int emb_table_set_row_base(uint32_t table_id, uint64_t row_base)
 int emb_table_read(uint32_t table_id, uint64_t row0, uint64_t n, void *dst_host)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
     const Table &t = g.tables[table_id];
@@ -978,6 +1146,7 @@ int emb_table_read(uint32_t table_id, uint64_t row0, uint64_t n, void *dst_host)
 int emb_table_info(uint32_t table_id, uint64_t *nr_rows, int *kind, const void **dev_ptr)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
     const Table &t = g.tables[table_id];
@@ -993,6 +1162,7 @@ int emb_table_info(uint32_t table_id, uint64_t *nr_rows, int *kind, const void *
 int emb_free_table(uint32_t table_id)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
     host_drain();
@@ -1046,6 +1216,7 @@ int emb_l2_persist(uint32_t table_id, uint64_t first_row, uint64_t nr_rows, floa
 int emb_table_set_hot_rows(uint32_t table_id, uint64_t hot_rows, int mode)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
     if (mode < 0 || mode > (EMB_HOT_KEEP | EMB_HOT_STREAM_COLD))
@@ -1073,6 +1244,7 @@ int emb_hot_order(const uint64_t *counts, uint64_t nr_rows, uint32_t *new_of_old
 int emb_table_remap(uint32_t table_id, const uint32_t *new_of_old)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    UseCtx on_owner(owner_of(table_id));
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -1141,6 +1313,7 @@ int emb_table_remap(uint32_t table_id, const uint32_t *new_of_old)
 int emb_remap_indices(uint32_t table_id, uint32_t *indices_dev, uint64_t n, void *stream)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
     const Table &t = g.tables[table_id];
@@ -1349,14 +1522,19 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
 int emb_check_indices(void)
 {
     std::lock_guard<std::mutex> lk(g_mu);
-    if (!g.device_ready)
-        return 0;
-    uint32_t v = 0;
-    CU(cudaDeviceSynchronize());
-    CU(cudaMemcpy(&v, g.d_err, 4, cudaMemcpyDeviceToHost));
-    if (v)
-        CU(cudaMemset(g.d_err, 0, 4));
-    return v ? 1 : 0;
+    int any = 0;
+    for (int k = 0; k < g_grp.n; k++) {  // every GPU of the device group
+        UseCtx u(k);
+        if (!g.device_ready)
+            continue;
+        uint32_t v = 0;
+        CU(cudaDeviceSynchronize());
+        CU(cudaMemcpy(&v, g.d_err, 4, cudaMemcpyDeviceToHost));
+        if (v)
+            CU(cudaMemset(g.d_err, 0, 4));
+        any |= v ? 1 : 0;
+    }
+    return any;
 }
 
 int emb_reduce_partials(const void *const *parts_dev, uint32_t n_parts, uint32_t part_stride, void *out_dev,
@@ -1562,24 +1740,25 @@ static uintptr_t alloc_base(const void *p)
  * is marked with hs.ev_done, because by the time it is waited for the streams may hold the next call's work too. */
 static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t T, const uint32_t *const *indices,
                         const uint32_t *const *offsets, const uint32_t *indices_len, const uint32_t *nr_batches,
-                        float *const *final_results)
+                        float *const *final_results, const uint32_t *tids = nullptr)
 {
+    // the T arrays describe tables tids[0..T) of the current context (a device group hands every GPU its own
+    // tables); NULL: tables 0..T-1
     double t_begin = now_s();
     hs.p.active = false;
     const uint32_t D = g.shape.nr_cols;
-    if (T > g.tables.size())
-        return fail(EMB_ESTATE, "lookup over %u tables but only %zu slots exist", T, g.tables.size());
+    auto tid = [tids](uint32_t t) { return tids ? tids[t] : t; };
     uint64_t tot_idx = 0, tot_bags = 0;
     bool any_float = false, all_float = true;
     for (uint32_t t = 0; t < T; t++) {
-        if (!g.tables[t].kind)
-            return fail(EMB_ESTATE, "table %u is not populated", t);
+        if (tid(t) >= g.tables.size() || !g.tables[tid(t)].kind)
+            return fail(EMB_ESTATE, "table %u is not populated", tid(t));
         if ((indices_len[t] && !indices[t]) || (nr_batches[t] && (!offsets[t] || !final_results[t])))
-            return fail(EMB_EINVAL, "NULL array for table %u", t);
+            return fail(EMB_EINVAL, "NULL array for table %u", tid(t));
         tot_idx += indices_len[t];
         tot_bags += nr_batches[t];
-        any_float |= g.tables[t].kind == EMB_TABLE_FLOAT;
-        all_float &= g.tables[t].kind == EMB_TABLE_FLOAT;
+        any_float |= g.tables[tid(t)].kind == EMB_TABLE_FLOAT;
+        all_float &= g.tables[tid(t)].kind == EMB_TABLE_FLOAT;
     }
     int rc;
     if (hs.desc_cap < T) {
@@ -1602,12 +1781,12 @@ static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t
     std::vector<float *> a_out(T, nullptr);
     // A tiny call (the reference's mini-batch-1 inference) is bounced whatever the arrays
     // are: copying a few KB costs less host time than asking the driver about 3 T pointers.
-    const bool tiny = g.host_path == EMB_HOST_AUTO && h2d_payload + d2h_payload <= kTinyBytes;
-    bool out_mapped = g.host_path != EMB_HOST_COPY && !tiny, in_mapped = out_mapped;
+    const bool tiny = g_tune.host_path == EMB_HOST_AUTO && h2d_payload + d2h_payload <= kTinyBytes;
+    bool out_mapped = g_tune.host_path != EMB_HOST_COPY && !tiny, in_mapped = out_mapped;
     for (uint32_t t = 0; t < T && out_mapped; t++)
         if (nr_batches[t] && !(a_out[t] = (float *)mapped_alias(final_results[t])))
             out_mapped = false;
-    in_mapped = out_mapped && (g.host_path == EMB_HOST_MAPPED || h2d_payload <= kMapInputsMaxBytes);
+    in_mapped = out_mapped && (g_tune.host_path == EMB_HOST_MAPPED || h2d_payload <= kMapInputsMaxBytes);
     for (uint32_t t = 0; t < T && in_mapped; t++) {
         if (indices_len[t] && !(a_idx[t] = (const uint32_t *)mapped_alias(indices[t])))
             in_mapped = false;
@@ -1619,8 +1798,8 @@ static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t
     // hundred KB faster than the 3 T cudaMemcpyAsync calls of the staged path cost to enqueue
     // (each CUDA call is several microseconds of host time), and the launch is the mapped one.
     bool bounce = false;
-    if ((g.host_path == EMB_HOST_AUTO && !(in_mapped && out_mapped) && h2d_payload + d2h_payload <= bounce_limit(T)) ||
-        g.host_path == EMB_HOST_BOUNCE) {
+    if ((g_tune.host_path == EMB_HOST_AUTO && !(in_mapped && out_mapped) && h2d_payload + d2h_payload <= bounce_limit(T)) ||
+        g_tune.host_path == EMB_HOST_BOUNCE) {
         const size_t need = (size_t)(h2d_payload + d2h_payload) + 64;
         if (hs.bounce_cap < need) {
             if (hs.h_bounce)
@@ -1651,12 +1830,12 @@ static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t
         }
         bounce = in_mapped = out_mapped = true;
     }
-    if (g.host_path == EMB_HOST_MAPPED && !(in_mapped && out_mapped))
+    if (g_tune.host_path == EMB_HOST_MAPPED && !(in_mapped && out_mapped))
         return fail(EMB_EINVAL, "EMB_HOST_MAPPED: a host array is not page-locked (cudaHostAlloc / "
                                 "cudaHostRegister / emb_host_alloc / emb_host_register)");
-    if (g.host_path == EMB_HOST_MAPPED_OUT && !out_mapped)
+    if (g_tune.host_path == EMB_HOST_MAPPED_OUT && !out_mapped)
         return fail(EMB_EINVAL, "EMB_HOST_MAPPED_OUT: a final_results array is not page-locked");
-    if (g.host_path == EMB_HOST_MAPPED_OUT)
+    if (g_tune.host_path == EMB_HOST_MAPPED_OUT)
         in_mapped = false;
     // AUTO on a large call: both directions go through the copy engines, also when the result arrays are
     // page-locked.  Measured on C2 (tools/e2e_sweep.py, profiles/r2_host_path.md): 2.75 ms per call with copies
@@ -1665,7 +1844,7 @@ static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t
     // write rate and holds the SMs the next group's kernel wants.  EMB_AUTO_LARGE=0 (measurement knob) restores
     // the mapped results.
     static const bool auto_copy = env_u32("EMB_AUTO_LARGE", 1) != 0;
-    if (g.host_path == EMB_HOST_AUTO && auto_copy && out_mapped && !in_mapped && !bounce &&
+    if (g_tune.host_path == EMB_HOST_AUTO && auto_copy && out_mapped && !in_mapped && !bounce &&
         h2d_payload + d2h_payload >= kPipelineMinBytes)
         out_mapped = false;
     // MAPPED_OUT: the offsets (4 bytes per bag) are still read in place when they are page-locked:
@@ -1714,8 +1893,8 @@ static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t
     {  // the caller's indices are in the caller's row order: reordered tables are translated by the kernel
         bool any_hot = false, any_remap = false;
         for (uint32_t t = 0; t < T; t++) {
-            any_hot |= g.tables[t].hot_mode != 0 && g.tables[t].hot_rows != 0;
-            any_remap |= g.tables[t].d_remap != nullptr;
+            any_hot |= g.tables[tid(t)].hot_mode != 0 && g.tables[tid(t)].hot_rows != 0;
+            any_remap |= g.tables[tid(t)].d_remap != nullptr;
         }
         if ((rc = apply_hot(variant, any_hot, any_remap, false)))
             return rc;
@@ -1760,7 +1939,7 @@ static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t
         for (uint32_t t = g_first[gi]; t < g_first[gi + 1]; t++) {
             emb_dev_query q;
             memset(&q, 0, sizeof q);
-            q.table_id = t;
+            q.table_id = tid(t);
             q.nr_batches = nr_batches[t];
             q.indices_len = indices_len[t];
             q.indices = in_mapped ? a_idx[t] : hs.d_idx + io;
@@ -1946,16 +2125,103 @@ static int host_drain()
     return rc;
 }
 
-/* The synchronous call: slot 0, enqueue + wait. */
+/* ... on every GPU of the device group. */
+static int host_drain_group()
+{
+    int rc = EMB_OK;
+    for (int k = 0; k < g_grp.n; k++) {
+        UseCtx u(k);
+        const int r = host_drain();
+        if (r && !rc)
+            rc = r;
+    }
+    return rc;
+}
+
+/* A call's tables cut by the GPU of the device group that holds them: whole tables, so the parts share nothing and
+ * the reference's per-table result arrays need no exchange -- every GPU moves its tables' indices in and its tables'
+ * pooled rows out over its own PCIe link, concurrently with the others. */
+struct GroupParts {
+    std::vector<const uint32_t *> idx[kMaxDevices], off[kMaxDevices];
+    std::vector<float *> res[kMaxDevices];
+    std::vector<uint32_t> ilen[kMaxDevices], nb[kMaxDevices], tids[kMaxDevices];
+
+    GroupParts(uint32_t T, const uint32_t *const *indices, const uint32_t *const *offsets, const uint32_t *indices_len,
+               const uint32_t *nr_batches, float *const *final_results)
+    {
+        for (uint32_t t = 0; t < T; t++) {
+            const int k = owner_of(t);
+            idx[k].push_back(indices[t]);
+            off[k].push_back(offsets[t]);
+            res[k].push_back(final_results[t]);
+            ilen[k].push_back(indices_len[t]);
+            nb[k].push_back(nr_batches[t]);
+            tids[k].push_back(t);
+        }
+    }
+    /* enqueue GPU k's part on its slot `slot` (the current context must be k) */
+    int enqueue(int k, int slot, uint64_t ticket, bool overlapped)
+    {
+        return host_enqueue(g.hslot[slot], ticket, overlapped, (uint32_t)tids[k].size(), idx[k].data(), off[k].data(),
+                            ilen[k].data(), nb[k].data(), res[k].data(), tids[k].data());
+    }
+};
+
+/* emb_last_timings() of a call that ran on several GPUs: the stages overlap across GPUs, so times are the slowest
+ * GPU's and bytes / launches are sums. */
+static void merge_timings(emb_timings &a, const emb_timings &l)
+{
+    a.h2d_ms = std::max(a.h2d_ms, l.h2d_ms);
+    a.kernel_ms = std::max(a.kernel_ms, l.kernel_ms);
+    a.d2h_ms = std::max(a.d2h_ms, l.d2h_ms);
+    a.total_ms = std::max(a.total_ms, l.total_ms);
+    a.h2d_bytes += l.h2d_bytes;
+    a.d2h_bytes += l.d2h_bytes;
+    a.launches += l.launches;
+    a.path = l.path;
+}
+
+static const emb_timings &last_call()
+{
+    return (g_grp.n > 1 && g_group_last_valid) ? g_group_last : g_ctxs[0].last;
+}
+
+/* The synchronous call: slot 0 (of every GPU of the group that holds one of the tables), enqueue + wait. */
 static int lookup_host(uint32_t T, const uint32_t *const *indices, const uint32_t *const *offsets,
                        const uint32_t *indices_len, const uint32_t *nr_batches, float *const *final_results)
 {
-    int rc = host_drain();
+    int rc = host_drain_group();
     if (rc)
         return rc;
-    if ((rc = host_enqueue(g.hslot[0], 0, false, T, indices, offsets, indices_len, nr_batches, final_results)))
-        return rc;
-    return host_complete(g.hslot[0]);
+    if (g_grp.n <= 1) {
+        if ((rc = host_enqueue(g.hslot[0], 0, false, T, indices, offsets, indices_len, nr_batches, final_results)))
+            return rc;
+        return host_complete(g.hslot[0]);
+    }
+    const double t0 = now_s();
+    GroupParts gp(T, indices, offsets, indices_len, nr_batches, final_results);
+    bool queued[kMaxDevices] = {};
+    for (int k = 0; k < g_grp.n && !rc; k++) {  // everything is enqueued on every GPU before anything is waited for
+        if (gp.tids[k].empty())
+            continue;
+        UseCtx u(k);
+        if (!(rc = gp.enqueue(k, 0, 0, false)))
+            queued[k] = true;
+    }
+    emb_timings agg = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < g_grp.n; k++) {
+        if (!queued[k])
+            continue;
+        UseCtx u(k);
+        const int r = host_complete(g.hslot[0]);
+        if (r && !rc)
+            rc = r;
+        merge_timings(agg, g.last);
+    }
+    agg.total_ms = (now_s() - t0) * 1e3;
+    g_group_last = agg;
+    g_group_last_valid = true;
+    return rc;
 }
 
 int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results, void *dpu_set_ptr,
@@ -1965,9 +2231,9 @@ int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results, v
     int rc = ensure_configured();
     if (rc)
         die("lookup", rc);
-    if (dpu_set_ptr && dpu_set_ptr != (void *)&g)
+    if (dpu_set_ptr && dpu_set_ptr != (void *)&g_ctxs[0])
         fprintf(stderr, "emblib(B200): lookup: dpu_set_ptr %p is not the handle populate_mram returned (%p); ignored\n",
-                dpu_set_ptr, (void *)&g);
+                dpu_set_ptr, (void *)&g_ctxs[0]);
     const uint32_t T = g.shape.nr_tables, B = g.shape.max_nr_batches;
     const uint32_t ilen = B * g.shape.max_indices_per_batch;  // INDICES_LEN, emb_host.h:30
     if (!B || !indices || !offsets || !final_results) {
@@ -1979,13 +2245,14 @@ int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results, v
     if (rc)
         die("lookup", rc);
     if (latency_print == 1) {  // the reference's six lines, emb_host.h:395-402
-        printf("C: Indices and offsets copying latency: %ldμs\n", (long)(g.last.h2d_ms * 1e3));
+        const emb_timings &l = last_call();
+        printf("C: Indices and offsets copying latency: %ldμs\n", (long)(l.h2d_ms * 1e3));
         printf("C: Query copying latency: %ldμs\n", 0L);
-        printf("C: Dpu launch latency: %ldμs\n", (long)(g.last.kernel_ms * 1e3));
-        printf("C: Results copy latency: %ldμs\n", (long)(g.last.d2h_ms * 1e3));
+        printf("C: Dpu launch latency: %ldμs\n", (long)(l.kernel_ms * 1e3));
+        printf("C: Results copy latency: %ldμs\n", (long)(l.d2h_ms * 1e3));
         printf("C: Callback prep latency: %ldμs\n", 0L);
         printf("C: DPU sync latency: %ldμs\n",
-               (long)(std::max(0.0, g.last.total_ms - g.last.h2d_ms - g.last.kernel_ms - g.last.d2h_ms) * 1e3));
+               (long)(std::max(0.0, l.total_ms - l.h2d_ms - l.kernel_ms - l.d2h_ms) * 1e3));
     }
     return nullptr;
 }
@@ -2012,16 +2279,32 @@ int emb_lookup_ex_async(uint32_t nr_tables, const uint32_t *const *indices, cons
         return rc;
     if (!nr_tables || !indices || !offsets || !indices_len || !nr_batches || !final_results || !ticket)
         return fail(EMB_EINVAL, "emb_lookup_ex_async: NULL/empty arguments");
-    const uint64_t tk = g.next_ticket;
-    HostSlot &hs = g.hslot[tk % kHostSlots];
+    const uint64_t tk = g_next_ticket;
+    const int slot = (int)(tk % kHostSlots), other = (int)((tk + 1) % kHostSlots);
     // the slot's previous call (ticket tk - 2) completes first if nobody has waited for it yet: its results are in
     // host memory from here on, and emb_lookup_wait on it returns at once
-    if ((rc = host_complete(hs)))
-        return rc;
-    const bool overlapped = g.hslot[(tk + 1) % kHostSlots].p.active;  // the previous call has not been waited for
-    if ((rc = host_enqueue(hs, tk, overlapped, nr_tables, indices, offsets, indices_len, nr_batches, final_results)))
-        return rc;
-    g.next_ticket = tk + 1;
+    bool overlapped = false;  // the previous call (ticket tk - 1) has not been waited for
+    for (int k = 0; k < g_grp.n; k++) {
+        UseCtx u(k);
+        if ((rc = host_complete(g.hslot[slot])))
+            return rc;
+        overlapped |= g.hslot[other].p.active;
+    }
+    if (g_grp.n <= 1) {
+        if ((rc = host_enqueue(g.hslot[slot], tk, overlapped, nr_tables, indices, offsets, indices_len, nr_batches,
+                               final_results)))
+            return rc;
+    } else {
+        GroupParts gp(nr_tables, indices, offsets, indices_len, nr_batches, final_results);
+        for (int k = 0; k < g_grp.n; k++) {
+            if (gp.tids[k].empty())
+                continue;
+            UseCtx u(k);
+            if ((rc = gp.enqueue(k, slot, tk, overlapped)))
+                return rc;  // parts already enqueued keep this ticket: the next call on the slot completes them
+        }
+    }
+    g_next_ticket = tk + 1;
     *ticket = tk;
     return EMB_OK;
 }
@@ -2029,28 +2312,44 @@ int emb_lookup_ex_async(uint32_t nr_tables, const uint32_t *const *indices, cons
 int emb_lookup_wait(emb_ticket ticket)
 {
     std::unique_lock<std::mutex> lk(g_mu);
-    if (!ticket || ticket >= g.next_ticket)
+    if (!ticket || ticket >= g_next_ticket)
         return fail(EMB_EINVAL, "emb_lookup_wait: ticket %llu was never issued", (unsigned long long)ticket);
-    HostSlot &hs = g.hslot[ticket % kHostSlots];
-    if (!hs.p.active || hs.p.ticket != ticket)
-        return EMB_OK;  // completed earlier (waited for already, or displaced by a later call on its slot)
-    // Block outside the lock, so that another thread can enqueue the next call meanwhile.
-    cudaEvent_t done = hs.ev_done;
-    lk.unlock();
-    cudaError_t e = cudaEventSynchronize(done);
-    lk.lock();
-    if (e != cudaSuccess)
-        return fail(EMB_ECUDA, "emb_lookup_wait: %s", cudaGetErrorString(e));
-    if (hs.p.active && hs.p.ticket == ticket)
-        return host_complete(hs);
-    return EMB_OK;
+    const int slot = (int)(ticket % kHostSlots);
+    emb_timings agg = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool any = false;
+    int rc = EMB_OK;
+    for (int k = 0; k < g_grp.n; k++) {  // the call's part on every GPU of the group
+        HostSlot &hs = g_ctxs[k].hslot[slot];
+        if (!hs.p.active || hs.p.ticket != ticket)
+            continue;  // completed earlier (waited for already, or displaced by a later call on its slot)
+        // Block outside the lock, so that another thread can enqueue the next call meanwhile.
+        cudaEvent_t done = hs.ev_done;
+        lk.unlock();
+        cudaError_t e = cudaEventSynchronize(done);
+        lk.lock();
+        if (e != cudaSuccess)
+            return fail(EMB_ECUDA, "emb_lookup_wait: %s", cudaGetErrorString(e));
+        if (hs.p.active && hs.p.ticket == ticket) {
+            UseCtx u(k);
+            const int r = host_complete(hs);
+            if (r && !rc)
+                rc = r;
+            merge_timings(agg, g.last);
+            any = true;
+        }
+    }
+    if (g_grp.n > 1 && any) {
+        g_group_last = agg;
+        g_group_last_valid = true;
+    }
+    return rc;
 }
 
 int emb_last_timings(emb_timings *out)
 {
     if (!out)
         return fail(EMB_EINVAL, "NULL out");
-    *out = g.last;
+    *out = last_call();
     return EMB_OK;
 }
 

@@ -51,6 +51,9 @@ def _declare(lib):
     # --- extensions ---
     sig = {
         "emb_configure": ([C.c_uint32] * 4 + [C.c_int], C.c_int),
+        "emb_configure_devices": ([C.c_uint32] * 4 + [C.POINTER(C.c_int), C.c_uint32, u32p], C.c_int),
+        "emb_group_size": ([], C.c_int),
+        "emb_table_device": ([C.c_uint32], C.c_int),
         "emb_get_shape": ([C.POINTER(EmbShape)], C.c_int),
         "emb_device": ([], C.c_int),
         "emb_shutdown": ([], None),
@@ -147,6 +150,18 @@ def _ptr_array(arrs, ty):
 
 def configure(nr_tables, nr_cols, max_nr_batches=0, max_indices_per_batch=0, device=-1):
     check(load().emb_configure(nr_tables, nr_cols, max_nr_batches, max_indices_per_batch, device), "emb_configure")
+
+
+def configure_devices(nr_tables, nr_cols, devices, max_nr_batches=0, max_indices_per_batch=0, table_device=None):
+    """Device group (emb_configure_devices): whole tables over several GPUs of the box behind lookup()."""
+    devs = (C.c_int * len(devices))(*devices)
+    td = None
+    if table_device is not None:
+        keep = np.ascontiguousarray(table_device, dtype=np.uint32)
+        assert keep.size == nr_tables
+        td = _p(keep, u32p)
+    check(load().emb_configure_devices(nr_tables, nr_cols, max_nr_batches, max_indices_per_batch, devs, len(devices), td),
+          "emb_configure_devices")
 
 
 def shutdown():
