@@ -264,9 +264,12 @@ int emb_lookup_wait(emb_ticket ticket);
  *                      MAPPED launch runs on the arena, the CPU copies the results out.  For
  *                      small calls (the reference's own shapes) this is one CUDA launch instead
  *                      of three copies per table.
- * EMB_HOST_AUTO        (default) MAPPED when every array is page-locked and the inputs are
- *                      small (<= 1 MiB); else BOUNCE when the whole call is <= 1 MiB; else
- *                      MAPPED_OUT when every final_results array is page-locked; else COPY.
+ * EMB_HOST_AUTO        (default) BOUNCE for tiny calls (<= 64 KiB) whatever the arrays are; MAPPED when
+ *                      every array is page-locked and the inputs are small (<= 1 MiB); else BOUNCE when
+ *                      the whole call is <= max(1 MiB, 128 KiB x tables); else COPY, cut into ~32 MB groups
+ *                      of tables (one group for an asynchronous call issued under a call in flight).
+ *                      Large calls are copied both ways also when the result arrays are page-locked:
+ *                      measured faster than MAPPED_OUT (profiles/r2_host_path.md).
  * "Page-locked" = cudaHostAlloc, cudaHostRegister, emb_host_alloc or emb_host_register memory.
  * A forced path whose requirement is not met returns EMB_EINVAL. */
 #define EMB_HOST_AUTO 0
