@@ -537,7 +537,7 @@ int apply_hot(Variant &v, bool any_hot, bool any_remap, bool compact)
  * round-1 load-balanced kernels (per CTA with atomics, per warp) on every workload (profiles/r2_stretch_ab_rotated.txt).
  * Variant 1 stays for strictly index-ordered fp32 sums and for launches that mix fp32 and int32 tables, variant 4
  * (TMA gather4) as the measured alternative north_star asks for. */
-Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = false)
+Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = false, uint64_t total_bags = 0)
 {
     Variant v;
     uint32_t D = g.shape.nr_cols;
@@ -572,6 +572,13 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = fal
         const bool short_bags = avg_pool > 0.0 && avg_pool <= 4.0;
         v.unroll = g_tune.unroll ? g_tune.unroll : (short_bags && lanes <= 8 ? 4 : 8);
         v.mult = g_tune.bags_mult ? g_tune.bags_mult : (lanes >= 32 ? 1 : lanes >= 16 ? 4 : short_bags ? 4 : 2);
+        // Few bags (the reference's own shapes: RM2 as shipped is 32 tables x 64 bags x 120 lookups, upmem/r.sh:6-10):
+        // the defaults above were swept at 65536 bags per table and would leave most SMs without a CTA -- 256 one-warp
+        // CTAs walking 960 lookups each.  Fewer bags per CTA until the launch has a few CTAs per SM: a bag's lookups are
+        // still spread over the sub-warps of its CTA, so long bags cost nothing extra.
+        if (!g_tune.bags_mult && total_bags)
+            while (v.mult > 1 && total_bags / (32 / lanes * (uint64_t)v.mult) < 8ull * (uint64_t)g.sm_count)
+                v.mult /= 2;
         static const int big_stage = (int)env_u32("EMB_STRETCH_STAGE", 0);  // measurement knob: 1 = the larger pass
         v.stage = big_stage;
         v.bags = std::min<uint32_t>(32 / lanes * v.mult, 64);  // one marker byte per lookup names the bag
@@ -1359,7 +1366,7 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
             li += queries[i].indices_len;
             nb += queries[i].nr_batches;
         }
-        p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0, all_float);
+        p->variant = pick_variant(any_float, nb ? (double)li / (double)nb : 0.0, all_float, nb);
     }
     // Row shards of fixed-point tables: the compacting instantiation (K = 8).  EMB_SHARD_COMPACT=0 (measurement
     // knob) pools them with the plain kernel, where a foreign index gathers the all-zero row.
@@ -1490,7 +1497,7 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
         tot_li += queries[i].indices_len;
         tot_nb += queries[i].nr_batches;
     }
-    Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0, all_float);
+    Variant variant = pick_variant(any_float, tot_nb ? (double)tot_li / (double)tot_nb : 0.0, all_float, tot_nb);
     {
         bool any_hot = false, any_remap = false;
         for (uint32_t i = 0; i < n; i++)
@@ -1889,7 +1896,7 @@ static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t
         n_groups = std::min(std::min(T, kMaxGroups), forced_groups);
     if ((rc = ensure_events(hs, 3 * n_groups + 2)))
         return rc;
-    Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, all_float);
+    Variant variant = pick_variant(any_float, tot_bags ? (double)tot_idx / (double)tot_bags : 0.0, all_float, tot_bags);
     {  // the caller's indices are in the caller's row order: reordered tables are translated by the kernel
         bool any_hot = false, any_remap = false;
         for (uint32_t t = 0; t < T; t++) {
