@@ -156,6 +156,8 @@ int emb_device(void);
  *     the summed bytes and launches.
  * Device-resident entry points (plans, emb_lookup_device, the exchange, emb_device_alloc ...) act on the group's FIRST
  * GPU only; several GPUs with device-resident data are one process per GPU (ShardedTables).
+ * emb_plan_launch and the other entry points that take no lock must not run in one thread while another thread is
+ * inside a group's host-pointer call (which switches the library's current GPU); with one GPU there is no such rule.
  * An unmodified caller gets a group from the environment: EMB_DEVICES="0,1,2,3" or EMB_NGPUS=4, read where the shape
  * variables are read.  The group can change only after emb_shutdown().  devices[] may name a GPU more than once (two
  * contexts on one GPU: of use for tests only). */
