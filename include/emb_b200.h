@@ -330,6 +330,61 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream);
 /* Non-zero once any launch has seen an out-of-range index (cleared by the call; syncs). */
 int emb_check_indices(void);
 
+/* ---- a lookup that allocates nothing --------------------------------------------------------- */
+
+/* No counterpart in the reference (its host library allocates DPUs and transfer buffers as it pleases).
+ *
+ * Who this is for.  Every other lookup here leans on memory the library got from cudaMalloc: the table slabs, the
+ * descriptor buffers the pooling kernel reads its work list from, the word an out-of-range index sets.  Some callers
+ * cannot afford that:
+ *   - a plugin in a process whose own allocator owns the GPU (a serving engine or a framework caching allocator that
+ *     reserves almost all of HBM at start-up): a cudaMalloc from a library then fails, or takes memory the host
+ *     application had counted on;
+ *   - a latency-bound serving loop: cudaMalloc / cudaFree stall the whole device, and the other entry points
+ *     re-allocate whenever a call outgrows the previous one.
+ * emb_lookup_static() never calls cudaMalloc, cudaFree, cudaHostAlloc, nor creates streams or events.  EVERYTHING it
+ * touches is the caller's -- tables included, so populate_mram() / emb_configure() are not needed (and not used) --
+ * except the kernel's work list and error word, which sit in a fixed array compiled into emblib.so (static
+ * __device__, 11.5 KB).  Every GPU the library is loaded on carries that array until the process exits.
+ *
+ * The price of a fixed array:
+ *   - at most EMB_STATIC_MAX_QUERIES queries (tables) per call; more is refused with EMB_EINVAL and a message that
+ *     says so -- cut the call in two;
+ *   - all calls on a GPU share the one array, and it keeps what the previous call left in it.  A call rewrites the
+ *     descriptors it uses and clears the error word itself, on `stream`, before its pooling launch, so calls issued
+ *     one after the other on ONE stream (or otherwise ordered on the GPU) are fine.  Two calls that may execute at
+ *     the same time -- different streams without an event between them, or two threads -- overwrite each other's
+ *     descriptors: wrong results or wild reads.  The library orders the enqueues of concurrent threads but cannot
+ *     order the GPU; that is the caller's job;
+ *   - the first call on each GPU looks up the array's device address (cudaGetSymbolAddress; the call works on the
+ *     calling thread's CURRENT device, and the arrays and `stream` must belong to it).  Make that first call during
+ *     start-up, outside any stream capture; later calls on that GPU only launch kernels.
+ *
+ * Arithmetic and bag bounds are those of lookup() / emb_lookup_ex(); the kernel is the index-ordered one (tuning
+ * variant 1), so fp32 tables are summed strictly in index order.  An index outside [0, nr_rows) adds nothing. */
+#define EMB_STATIC_MAX_QUERIES 64
+
+typedef struct emb_static_query {
+    const void *table;       /* DEVICE, row-major [nr_rows][nr_cols], 4-byte elements; 16-byte aligned when nr_cols
+                                is 4, 8, 16, 32, 64 or 128                                              */
+    uint64_t nr_rows;        /* 1 .. 2^32-2                                                             */
+    uint32_t kind;           /* EMB_TABLE_FIXED or EMB_TABLE_FLOAT                                      */
+    uint32_t flags;          /* 0 or EMB_Q_RAW_SUMS                                                     */
+    uint32_t nr_batches;     /* bags                                                                    */
+    uint32_t indices_len;    /* end of the last bag                                                     */
+    const uint32_t *indices; /* DEVICE, uint32 [indices_len]                                            */
+    const uint32_t *offsets; /* DEVICE, uint32 [nr_batches]                                             */
+    void *out;               /* DEVICE, bag b -> out + b*out_stride elements (4 B each)                 */
+    uint32_t out_stride;     /* elements between bags; 0 means nr_cols                                  */
+    uint32_t reserved_;
+} emb_static_query;
+
+/* Enqueue on `stream` (a cudaStream_t; NULL = the legacy default stream -- this entry point owns no stream).
+ * out_of_range == NULL: returns as soon as the kernels are enqueued.  Otherwise the call waits for `stream` and stores
+ * 1 there if an index of THIS call fell outside its table, else 0. */
+int emb_lookup_static(const emb_static_query *queries, uint32_t n, uint32_t nr_cols, void *stream,
+                      int *out_of_range);
+
 /* out[b*out_stride + j] = combine over s < n_parts of parts[s][b*part_stride + j]:
  * raw int32 partials are wrap-added then divided by 1e9 (is_raw_i32 = 1); fp32 partials are
  * added in order s = 0,1,...  Used at the receiving rank for row-split tables. */

@@ -2475,3 +2475,194 @@ int emb_ipc_close(void *peer_dev_ptr)
 }
 
 }  // extern "C"
+
+/* ---------------------------------------------------------------- pooling without any allocation --- */
+
+/* emb_lookup_static (include/emb_b200.h): a lookup for callers that cannot let this library allocate.  Two kinds of
+ * caller are meant.  One is a plugin inside a process whose own allocator has already taken (nearly) all of the GPU's
+ * memory -- a serving engine or a framework's caching allocator that reserves HBM up front: every cudaMalloc of
+ * ours (tables, the descriptor ring of emb_lookup_device, the error word) may fail there, or carve memory out from
+ * under that allocator.  The other is a latency-bound loop: cudaMalloc and cudaFree synchronise the whole device, and
+ * the other entry points may (re)allocate whenever a call is larger than the last one.
+ *
+ * The pooling kernels need two things beyond the caller's arrays: the list of per-table descriptors they read, and
+ * the word an out-of-range index sets.  Everywhere else both live in cudaMalloc memory.  Here they live in this
+ * file-scope array, which is part of the loaded module: every GPU that loads emblib.so holds these 11.5 KB from
+ * the moment the module is loaded on it until the process exits, whether or not emb_lookup_static is ever called. */
+namespace {
+
+constexpr uint32_t kStaticMaxQueries = EMB_STATIC_MAX_QUERIES;
+constexpr uint32_t kStaticPack = 16;  // descriptors per set-up launch: 16 * 176 B + 16 B of kernel parameters (< 4 KB)
+
+struct StaticScratch {
+    uint32_t err;  // bit 0: an index fell outside its table (cleared by every call before its pooling launch)
+    uint32_t pad_[63];
+    BagDesc descs[kStaticMaxQueries];
+};
+static_assert(sizeof(StaticScratch) == 256 + kStaticMaxQueries * sizeof(BagDesc), "static scratch layout");
+
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+struct StaticPack {
+    BagDesc d[kStaticPack];
+};
+
+/* Device code may name the array; host code may not (there the name is only a handle for cudaGetSymbolAddress).
+ * Writes descriptors [first, first + count) from the kernel's own parameters -- no host buffer has to outlive the
+ * call, no copy is staged -- and, in the first launch of a call, clears the error word. */
+__global__ void static_setup_kernel(StaticPack pack, uint32_t first, uint32_t count, uint32_t clear_err)
+{
+    StaticScratch *sc = reinterpret_cast<StaticScratch *>(g_static_scratch);
+    const uint4 *src = reinterpret_cast<const uint4 *>(pack.d);
+    uint4 *dst = reinterpret_cast<uint4 *>(sc->descs + first);
+    const uint32_t n16 = count * (uint32_t)(sizeof(BagDesc) / 16);
+    for (uint32_t i = threadIdx.x; i < n16; i += blockDim.x)
+        dst[i] = src[i];
+    if (clear_err && threadIdx.x == 0)
+        sc->err = 0;
+}
+
+struct StaticDevice {
+    bool ready = false;
+    StaticScratch *scratch = nullptr;  // DEVICE address of g_static_scratch on this GPU
+};
+constexpr int kStaticMaxDevices = 64;
+StaticDevice g_static_dev[kStaticMaxDevices];
+std::mutex g_static_mu;
+
+template <int LANES>
+void launch_static(int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni, uint32_t *err)
+{
+    if (unroll == 8)
+        emb::bag_sum_kernel<LANES, 8><<<grid, emb::kThreads, 0, s>>>(d, n, uni, err);
+    else
+        emb::bag_sum_kernel<LANES, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, err);
+}
+
+}  // namespace
+
+extern "C" {
+
+int emb_lookup_static(const emb_static_query *queries, uint32_t n, uint32_t nr_cols, void *stream, int *out_of_range)
+{
+    if (out_of_range)
+        *out_of_range = 0;
+    if (!queries || !n)
+        return fail(EMB_EINVAL, "emb_lookup_static: NULL/empty arguments");
+    if (n > kStaticMaxQueries)
+        return fail(EMB_EINVAL, "emb_lookup_static: %u queries in one call, the static descriptor array holds at most %u "
+                                "(EMB_STATIC_MAX_QUERIES): split the call", n, kStaticMaxQueries);
+    if (nr_cols == 0 || nr_cols > 4096)
+        return fail(EMB_EINVAL, "emb_lookup_static: nr_cols %u unsupported (1 .. 4096)", nr_cols);
+    const uint32_t D = nr_cols;
+    const uint32_t lanes = lanes_for_dim(D);           // 0: the any-dimension kernel, one warp per bag
+    const uint32_t per = emb::kThreads / (lanes ? lanes : 32);  // bags per CTA
+    const int unroll = lanes >= 16 ? 8 : 4;
+
+    // descriptors, built in ordinary host memory (they travel as kernel parameters below)
+    BagDesc h[kStaticMaxQueries];
+    uint64_t chunk = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        const emb_static_query &q = queries[i];
+        BagDesc *d = &h[i];
+        memset(d, 0, sizeof *d);
+        if (q.kind != EMB_TABLE_FIXED && q.kind != EMB_TABLE_FLOAT)
+            return fail(EMB_EINVAL, "emb_lookup_static: query %u: kind %u is neither EMB_TABLE_FIXED nor EMB_TABLE_FLOAT", i, q.kind);
+        if (!q.table || q.nr_rows == 0 || q.nr_rows > 0xfffffffeull)
+            return fail(EMB_EINVAL, "emb_lookup_static: query %u: NULL table or nr_rows %llu outside 1 .. 2^32-2", i,
+                        (unsigned long long)q.nr_rows);
+        if (lanes && (uintptr_t)q.table % 16 != 0)
+            return fail(EMB_EINVAL, "emb_lookup_static: query %u: table is not 16-byte aligned", i);
+        if (q.flags & ~EMB_Q_RAW_SUMS)
+            return fail(EMB_EINVAL, "emb_lookup_static: query %u: only EMB_Q_RAW_SUMS is understood here", i);
+        const uint32_t stride = q.out_stride ? q.out_stride : D;
+        if (stride < D)
+            return fail(EMB_EINVAL, "emb_lookup_static: query %u: out_stride %u < nr_cols %u", i, stride, D);
+        if (q.nr_batches && (!q.offsets || !q.out || (q.indices_len && !q.indices)))
+            return fail(EMB_EINVAL, "emb_lookup_static: query %u has NULL indices/offsets/out", i);
+        d->table = q.table;
+        d->indices = q.indices;
+        d->offsets = q.offsets;
+        d->out = q.out;
+        d->rows = (uint32_t)q.nr_rows;
+        d->nr_batches = q.nr_batches;
+        d->indices_len = q.indices_len;
+        d->out_stride = stride;
+        d->bag_first = 0;
+        d->bag_end = q.nr_batches;
+        uint32_t flags = 0;
+        if (q.kind == EMB_TABLE_FLOAT)
+            flags |= emb::kDescFloat;
+        else if (q.flags & EMB_Q_RAW_SUMS)
+            flags |= emb::kDescRaw;
+        if (stride % 4 == 0 && (uintptr_t)q.out % 16 == 0)
+            flags |= emb::kDescVecStore;
+        d->flags = flags;
+        d->chunk_begin = (uint32_t)chunk;
+        d->n_chunks = (q.nr_batches + per - 1) / per;
+        chunk += d->n_chunks;
+        if (chunk > 0x7fffffffull)
+            return fail(EMB_EINVAL, "emb_lookup_static: too many bags for one launch");
+    }
+    if (chunk == 0)
+        return EMB_OK;  // no bags anywhere: nothing to pool, nothing to flag
+
+    // One call at a time builds its descriptors in the shared array.  The lock orders the ENQUEUES of two threads; it
+    // does not stop two calls on different streams from running on the GPU at the same time (see the header).
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kStaticMaxDevices)
+        return fail(EMB_EINVAL, "emb_lookup_static: current device %d outside 0 .. %d", dev, kStaticMaxDevices - 1);
+    StaticDevice &sd = g_static_dev[dev];
+    if (!sd.ready) {
+        // Set-up, once per GPU, with that GPU current: ask the runtime where THIS GPU keeps its copy of the array.
+        // `g_static_scratch` itself is not that address in host code -- handing it to a kernel would make the kernel
+        // fault or, where the GPU can reach host memory, quietly use the wrong bytes.
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(EMB_ECUDA, "emb_lookup_static: cudaGetSymbolAddress(static scratch) on device %d -> %s", dev,
+                        cudaGetErrorString(e));
+        sd.scratch = static_cast<StaticScratch *>(p);
+        sd.ready = true;
+    }
+    // NULL = the legacy default stream here: this entry point creates nothing, so it has no stream of its own
+    cudaStream_t s = (cudaStream_t)stream;
+
+    for (uint32_t first = 0; first < n; first += kStaticPack) {
+        StaticPack pack;
+        const uint32_t count = std::min(kStaticPack, n - first);
+        memset(&pack, 0, sizeof pack);
+        memcpy(pack.d, h + first, count * sizeof(BagDesc));
+        static_setup_kernel<<<1, 128, 0, s>>>(pack, first, count, first == 0 ? 1u : 0u);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+    }
+    CU(cudaGetLastError());
+
+    const BagDesc *d_descs = sd.scratch->descs;  // address arithmetic only: nothing is dereferenced on the host
+    uint32_t *d_err = &sd.scratch->err;
+    const uint32_t uni = uniform_chunks(h, n);
+    const uint32_t grid = (uint32_t)chunk;
+    switch (lanes) {
+    case 0: emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, uni, D, d_err); break;
+    case 1: launch_static<1>(unroll, grid, s, d_descs, n, uni, d_err); break;
+    case 2: launch_static<2>(unroll, grid, s, d_descs, n, uni, d_err); break;
+    case 4: launch_static<4>(unroll, grid, s, d_descs, n, uni, d_err); break;
+    case 8: launch_static<8>(unroll, grid, s, d_descs, n, uni, d_err); break;
+    case 16: launch_static<16>(unroll, grid, s, d_descs, n, uni, d_err); break;
+    default: launch_static<32>(unroll, grid, s, d_descs, n, uni, d_err); break;
+    }
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+
+    if (out_of_range) {
+        uint32_t v = 0;
+        CU(cudaMemcpyAsync(&v, d_err, sizeof v, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        *out_of_range = (v & 1u) ? 1 : 0;
+    }
+    return EMB_OK;
+}
+
+}  // extern "C"

@@ -117,6 +117,15 @@ class EmbDevQuery(Structure):
                 ("bag_first", c_uint32), ("bag_count", c_uint32), ("bag_rotate", c_uint32), ("reserved_", c_uint32)]
 
 
+EMB_STATIC_MAX_QUERIES = 64  # emb_lookup_static: queries per call its fixed descriptor array holds
+
+
+class EmbStaticQuery(Structure):  # include/emb_b200.h emb_static_query
+    _fields_ = [("table", c_void_p), ("nr_rows", c_uint64), ("kind", c_uint32), ("flags", c_uint32),
+                ("nr_batches", c_uint32), ("indices_len", c_uint32), ("indices", c_void_p), ("offsets", c_void_p),
+                ("out", c_void_p), ("out_stride", c_uint32), ("reserved_", c_uint32)]
+
+
 class EmbReduceJob(Structure):  # include/emb_b200.h emb_reduce_job
     _fields_ = [("parts", c_void_p * EMB_MAX_PEERS), ("out", c_void_p), ("n_parts", c_uint32),
                 ("part_stride", c_uint32), ("out_stride", c_uint32), ("is_raw_i32", c_uint32), ("nr_bags", c_uint64)]

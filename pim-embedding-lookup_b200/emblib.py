@@ -17,7 +17,7 @@ import subprocess
 import numpy as np
 
 from .dputypes import (EMB_MAX_PEERS, EMB_Q_RAW_SUMS, EMB_TABLE_FIXED, EMB_TABLE_FLOAT, DpuRuntimeTotals,
-                       EmbDevQuery, EmbIpcHandle, EmbReduceJob, EmbShape, EmbTimings)
+                       EmbDevQuery, EmbIpcHandle, EmbReduceJob, EmbShape, EmbStaticQuery, EmbTimings)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "lib", "emblib.so")
@@ -81,6 +81,8 @@ def _declare(lib):
         "emb_plan_grid": ([C.c_void_p], C.c_uint32),
         "emb_lookup_device": ([C.POINTER(EmbDevQuery), C.c_uint32, C.c_void_p], C.c_int),
         "emb_check_indices": ([], C.c_int),
+        "emb_lookup_static": ([C.POINTER(EmbStaticQuery), C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_int)],
+                              C.c_int),
         "emb_reduce_partials": ([C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
                                  C.c_uint64, C.c_int, C.c_void_p], C.c_int),
         "emb_finish_create": ([C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32, C.POINTER(EmbReduceJob), C.c_uint32,
@@ -391,6 +393,33 @@ def lookup_device(queries, stream=None) -> None:
     `stream` (a torch.cuda.Stream, a raw handle, or None for the library's stream)."""
     arr, n = _query_array(queries)
     check(load().emb_lookup_device(arr, n, _stream(stream)), "emb_lookup_device")
+
+
+def lookup_static(queries, nr_cols: int, stream=None, check_range: bool = False):
+    """emb_lookup_static: pool caller-owned device arrays without the library allocating anything (for hosts whose
+    own allocator owns the GPU, and for loops that cannot take cudaMalloc's device-wide stall).  `queries` is a list of
+    dicts with keys table (device array [nr_rows][nr_cols]), nr_rows, indices, offsets, out and optional kind
+    (EMB_TABLE_FIXED), flags, nr_batches, indices_len, out_stride; at most EMB_STATIC_MAX_QUERIES of them.
+    Asynchronous on `stream` (None = the legacy default stream) unless check_range, which waits and returns whether
+    an index fell outside its table.  Calls share one fixed scratch array per GPU: keep them ordered on the GPU."""
+    n = len(queries)
+    arr = (EmbStaticQuery * max(n, 1))()
+    for i, q in enumerate(queries):
+        e = arr[i]
+        e.table = _addr(q["table"])
+        e.nr_rows = q["nr_rows"]
+        e.kind = q.get("kind", EMB_TABLE_FIXED)
+        e.flags = q.get("flags", 0)
+        e.indices = _addr(q["indices"])
+        e.offsets = _addr(q["offsets"])
+        e.out = _addr(q.get("out"))
+        e.nr_batches = q["nr_batches"] if "nr_batches" in q else _numel(q["offsets"])
+        e.indices_len = q["indices_len"] if "indices_len" in q else _numel(q["indices"])
+        e.out_stride = q.get("out_stride", 0)
+    s = None if stream is None else (stream if isinstance(stream, int) else int(stream.cuda_stream))
+    oor = C.c_int(0)
+    check(load().emb_lookup_static(arr, n, nr_cols, s, C.byref(oor) if check_range else None), "emb_lookup_static")
+    return bool(oor.value) if check_range else None
 
 
 def _addr(x):
