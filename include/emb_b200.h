@@ -155,9 +155,11 @@ int emb_device(void);
  *   - emb_check_indices / emb_shutdown cover every GPU; emb_last_timings reports the slowest GPU's stage times and
  *     the summed bytes and launches.
  * Device-resident entry points (plans, emb_lookup_device, the exchange, emb_device_alloc ...) act on the group's FIRST
- * GPU only; several GPUs with device-resident data are one process per GPU (ShardedTables).
- * emb_plan_launch and the other entry points that take no lock must not run in one thread while another thread is
- * inside a group's host-pointer call (which switches the library's current GPU); with one GPU there is no such rule.
+ * GPU only (a call that takes a device pointer or a caller's stream for a table on another GPU of the group returns
+ * EMB_EINVAL and says so); several GPUs with device-resident data are one process per GPU (ShardedTables,
+ * INTEGRATION.md section 6).  emb_plan_launch / emb_finish_launch take no lock and use the GPU the plan / finish object
+ * was made on, so they may run in one thread while another thread is inside a group's host-pointer call.
+ * Every entry point leaves the calling thread's current CUDA device as it found it, whatever GPU it worked on.
  * An unmodified caller gets a group from the environment: EMB_DEVICES="0,1,2,3" or EMB_NGPUS=4, read where the shape
  * variables are read.  The group can change only after emb_shutdown().  devices[] may name a GPU more than once (two
  * contexts on one GPU: of use for tests only). */

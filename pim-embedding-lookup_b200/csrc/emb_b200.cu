@@ -189,7 +189,55 @@ double now_s()
     return t.tv_sec + t.tv_nsec * 1e-9;
 }
 
-/* Make context k (and its GPU) the current one for the lifetime of the object. */
+/* The calling thread's CUDA device, saved at the top of every entry point that takes the lock and put back when it
+ * returns.  In between the thread works on the current context's GPU: a caller whose own current device is another
+ * one (torch.cuda.set_device(1) beside EMB_DEVICE=0, a second thread at its default device 0 beside a library bound
+ * to GPU 2, any thread beside a device group) would otherwise have the library's allocations, events and copies land
+ * on the caller's device -- and would get its device switched behind its back by a group call.  Declared after the
+ * lock_guard, so it is destroyed (device restored) before the lock is released. */
+struct DeviceScope {
+    int saved = -1;
+    DeviceScope()
+    {
+        if (cudaGetDevice(&saved) != cudaSuccess) {
+            saved = -1;
+            cudaGetLastError();  // no device visible: the entry point reports that itself
+        } else if (g_cur->device_ready && saved != g_cur->device) {
+            cudaSetDevice(g_cur->device);
+        }
+    }
+    ~DeviceScope()
+    {
+        int now = -1;
+        if (saved >= 0 && cudaGetDevice(&now) == cudaSuccess && now != saved)
+            cudaSetDevice(saved);
+    }
+    DeviceScope(const DeviceScope &) = delete;
+    DeviceScope &operator=(const DeviceScope &) = delete;
+};
+
+/* For the entry points that take no lock (emb_plan_launch, emb_finish_launch): launch on the GPU the object was made
+ * on even when the calling thread's current device is another one, and leave that device as it was. */
+struct OnDevice {
+    int saved = -1;
+    explicit OnDevice(int device)
+    {
+        if (cudaGetDevice(&saved) != cudaSuccess || saved == device)
+            saved = -1;
+        else
+            cudaSetDevice(device);
+    }
+    ~OnDevice()
+    {
+        if (saved >= 0)
+            cudaSetDevice(saved);
+    }
+    OnDevice(const OnDevice &) = delete;
+    OnDevice &operator=(const OnDevice &) = delete;
+};
+
+/* Make context k (and its GPU) the current one for the lifetime of the object.  Used inside a DeviceScope only, which
+ * has put the thread on the previous context's GPU (and restores the caller's own device at the very end). */
 struct UseCtx {
     Ctx *prev;
     explicit UseCtx(int k) : prev(g_cur)
@@ -589,12 +637,12 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = fal
 }
 
 template <int LANES>
-void launch_ordered(int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+void launch_ordered(const Ctx &c, int unroll, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     if (unroll == 8)
-        emb::bag_sum_kernel<LANES, 8><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
+        emb::bag_sum_kernel<LANES, 8><<<grid, emb::kThreads, 0, s>>>(d, n, uni, c.d_err);
     else
-        emb::bag_sum_kernel<LANES, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, g.d_err);
+        emb::bag_sum_kernel<LANES, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, c.d_err);
 }
 
 /* Stretch kernel: K rows in flight per lane, BAGS = sub-warps x mult bags per one-warp CTA, STAGE lookups per
@@ -622,7 +670,7 @@ void launch_dependent(void (*kern)(KArgs...), dim3 grid, uint32_t block, cudaStr
 constexpr int kHotMinBlocks = 32;  // resident one-warp CTAs per SM the HOT instantiation is compiled for
 
 template <int LANES, int K, int MULT, bool IS_FLOAT>
-void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni, uint32_t overlap)
+void launch_stretch_m(const Ctx &c, int big_stage, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni, uint32_t overlap)
 {
     constexpr int SUB = 32 / LANES;
     constexpr int BAGS = SUB * MULT < 64 ? SUB * MULT : 64;  // stretch_bags() below
@@ -640,10 +688,10 @@ void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDes
         if (overlap & 2u) {
             if (big_stage)
                 launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, LARGE, IS_FLOAT, MINB, true>, g2, 32, s, d, n, uni,
-                                 g.d_err, overlap & 1u);
+                                 c.d_err, overlap & 1u);
             else
                 launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, MINB, true>, g2, 32, s, d, n, uni,
-                                 g.d_err, overlap & 1u);
+                                 c.d_err, overlap & 1u);
             return;
         }
     }
@@ -651,73 +699,73 @@ void launch_stretch_m(int big_stage, uint32_t grid, cudaStream_t s, const BagDes
     if constexpr (K == 8) {
         if (overlap & 4u) {
             launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, kHotMinBlocks, false, true>, g2, 32, s, d,
-                             n, uni, g.d_err, overlap & 1u);
+                             n, uni, c.d_err, overlap & 1u);
             return;
         }
     }
     overlap &= 1u;
     if (big_stage)
-        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, LARGE, IS_FLOAT, MINB>, g2, 32, s, d, n, uni, g.d_err,
+        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, LARGE, IS_FLOAT, MINB>, g2, 32, s, d, n, uni, c.d_err,
                          overlap);
     else
-        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, MINB>, g2, 32, s, d, n, uni, g.d_err,
+        launch_dependent(emb::bag_sum_stretch_kernel<LANES, K, BAGS, SMALL, IS_FLOAT, MINB>, g2, 32, s, d, n, uni, c.d_err,
                          overlap);
 }
 
 template <int LANES, int K, bool IS_FLOAT>
-void launch_stretch_k(const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni, uint32_t overlap)
+void launch_stretch_k(const Ctx &c, const Variant &v, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni, uint32_t overlap)
 {
     switch (v.mult) {
-    case 1: return launch_stretch_m<LANES, K, 1, IS_FLOAT>(v.stage, grid, s, d, n, uni, overlap);
-    case 4: return launch_stretch_m<LANES, K, 4, IS_FLOAT>(v.stage, grid, s, d, n, uni, overlap);
-    case 8: return launch_stretch_m<LANES, K, 8, IS_FLOAT>(v.stage, grid, s, d, n, uni, overlap);
-    default: return launch_stretch_m<LANES, K, 2, IS_FLOAT>(v.stage, grid, s, d, n, uni, overlap);
+    case 1: return launch_stretch_m<LANES, K, 1, IS_FLOAT>(c, v.stage, grid, s, d, n, uni, overlap);
+    case 4: return launch_stretch_m<LANES, K, 4, IS_FLOAT>(c, v.stage, grid, s, d, n, uni, overlap);
+    case 8: return launch_stretch_m<LANES, K, 8, IS_FLOAT>(c, v.stage, grid, s, d, n, uni, overlap);
+    default: return launch_stretch_m<LANES, K, 2, IS_FLOAT>(c, v.stage, grid, s, d, n, uni, overlap);
     }
 }
 
 template <int LANES>
-void launch_stretch(const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni,
+void launch_stretch(const Ctx &c, const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni,
                     uint32_t overlap)
 {
     if (is_float) {
         if (v.unroll == 4)
-            return launch_stretch_k<LANES, 4, true>(v, grid, s, d, n, uni, overlap);
-        return launch_stretch_k<LANES, 8, true>(v, grid, s, d, n, uni, overlap);
+            return launch_stretch_k<LANES, 4, true>(c, v, grid, s, d, n, uni, overlap);
+        return launch_stretch_k<LANES, 8, true>(c, v, grid, s, d, n, uni, overlap);
     }
     if (v.unroll == 4)
-        return launch_stretch_k<LANES, 4, false>(v, grid, s, d, n, uni, overlap);
-    launch_stretch_k<LANES, 8, false>(v, grid, s, d, n, uni, overlap);
+        return launch_stretch_k<LANES, 4, false>(c, v, grid, s, d, n, uni, overlap);
+    launch_stretch_k<LANES, 8, false>(c, v, grid, s, d, n, uni, overlap);
 }
 
 template <int LANES>
-void launch_tma(uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+void launch_tma(const Ctx &c, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
 {
     if constexpr (LANES >= 4) {
         constexpr int WARPS = emb::kThreads / 32;
         constexpr size_t smem = (size_t)WARPS * emb::kTmaStages * emb::kTmaStageBytes + WARPS * emb::kTmaStages * 8 +
                                 WARPS * (4 * (32 / LANES) + 1) * 4;
         static bool once[64] = {};  // a function attribute is per device
-        if (g.device < 0 || g.device >= 64 || !once[g.device]) {
+        if (c.device < 0 || c.device >= 64 || !once[c.device]) {
             cudaFuncSetAttribute(emb::bag_sum_tma_kernel<LANES, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (g.device >= 0 && g.device < 64)
-                once[g.device] = true;
+            if (c.device >= 0 && c.device < 64)
+                once[c.device] = true;
         }
-        emb::bag_sum_tma_kernel<LANES, 3><<<grid, emb::kThreads, smem, s>>>(d, n, uni, g.d_err);
+        emb::bag_sum_tma_kernel<LANES, 3><<<grid, emb::kThreads, smem, s>>>(d, n, uni, c.d_err);
     } else {
         (void)grid; (void)s; (void)d; (void)n; (void)uni;
     }
 }
 
 template <int LANES>
-void launch_for_lanes(const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni,
+void launch_for_lanes(const Ctx &c, const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni,
                       uint32_t overlap)
 {
     if (v.kind == 6)  // the one kernel that orders its result stores itself (EMB_Q_OVERLAP)
-        launch_stretch<LANES>(v, is_float, grid, s, d, n, uni, overlap);
+        launch_stretch<LANES>(c, v, is_float, grid, s, d, n, uni, overlap);
     else if (v.kind == 4)
-        launch_tma<LANES>(grid, s, d, n, uni);
+        launch_tma<LANES>(c, grid, s, d, n, uni);
     else
-        launch_ordered<LANES>(v.unroll, grid, s, d, n, uni);
+        launch_ordered<LANES>(c, v.unroll, grid, s, d, n, uni);
 }
 
 /* Every query of the launch owns the same number of CTAs (the usual case: all tables pool the same
@@ -735,21 +783,21 @@ uint32_t uniform_chunks(const BagDesc *h, uint32_t n)
 }
 
 /* `uni` = uniform_chunks() of the n descriptors (0 = search). */
-int launch_bag_sum(const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_t uni, uint32_t grid, cudaStream_t s,
+int launch_bag_sum(const Ctx &c, const Variant &v, const BagDesc *d_descs, uint32_t n, uint32_t uni, uint32_t grid, cudaStream_t s,
                    bool is_float = false, bool overlap = false, bool compact = false)
 {
     if (grid == 0)
         return EMB_OK;
-    uint32_t D = g.shape.nr_cols;
+    uint32_t D = c.shape.nr_cols;
     const uint32_t obits = (overlap ? 1u : 0u) | (compact ? 2u : 0u) | (v.hot ? 4u : 0u);
     switch (v.kind ? lanes_for_dim(D) : 0) {
-    case 0: emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, uni, D, g.d_err); break;
-    case 1: launch_for_lanes<1>(v, is_float, grid, s, d_descs, n, uni, obits); break;
-    case 2: launch_for_lanes<2>(v, is_float, grid, s, d_descs, n, uni, obits); break;
-    case 4: launch_for_lanes<4>(v, is_float, grid, s, d_descs, n, uni, obits); break;
-    case 8: launch_for_lanes<8>(v, is_float, grid, s, d_descs, n, uni, obits); break;
-    case 16: launch_for_lanes<16>(v, is_float, grid, s, d_descs, n, uni, obits); break;
-    default: launch_for_lanes<32>(v, is_float, grid, s, d_descs, n, uni, obits); break;
+    case 0: emb::bag_sum_generic_kernel<<<grid, emb::kThreads, 0, s>>>(d_descs, n, uni, D, c.d_err); break;
+    case 1: launch_for_lanes<1>(c, v, is_float, grid, s, d_descs, n, uni, obits); break;
+    case 2: launch_for_lanes<2>(c, v, is_float, grid, s, d_descs, n, uni, obits); break;
+    case 4: launch_for_lanes<4>(c, v, is_float, grid, s, d_descs, n, uni, obits); break;
+    case 8: launch_for_lanes<8>(c, v, is_float, grid, s, d_descs, n, uni, obits); break;
+    case 16: launch_for_lanes<16>(c, v, is_float, grid, s, d_descs, n, uni, obits); break;
+    default: launch_for_lanes<32>(c, v, is_float, grid, s, d_descs, n, uni, obits); break;
     }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
@@ -846,6 +894,9 @@ struct emb_plan {
     std::vector<BagDesc> h;
     std::vector<std::pair<uint32_t, uint32_t>> gen;  // (table slot, Table::generation) of every query
     BagDesc *d = nullptr;
+    // The context (GPU) the plan was made on -- the group's first GPU.  emb_plan_launch takes no lock and must not look at
+    // the library's current context, which another thread's device-group call switches while it runs.
+    Ctx *ctx = nullptr;
     uint32_t grid = 0;
     uint32_t uni = 0;  // uniform_chunks() of the descriptors
     uint64_t bytes = 0;
@@ -867,6 +918,7 @@ int emb_configure(uint32_t nr_tables, uint32_t nr_cols, uint32_t max_nr_batches,
                   uint32_t max_indices_per_batch, int device)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     if (g_grp.n > 1) {  // a group exists: the shape changes on every GPU of it
         if (device >= 0 && device != g_ctxs[0].device)
             return fail(EMB_ESTATE, "a device group is configured: emb_shutdown() before binding to device %d", device);
@@ -893,6 +945,7 @@ int emb_configure_devices(uint32_t nr_tables, uint32_t nr_cols, uint32_t max_nr_
                           const int *devices, uint32_t n_devices, const uint32_t *table_device)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     return configure_group(nr_tables, nr_cols, max_nr_batches, max_indices_per_batch, devices, (int)n_devices, table_device);
 }
 
@@ -907,6 +960,7 @@ int emb_table_device(uint32_t table_id)
 int emb_get_shape(emb_shape *out)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     if (!out)
         return fail(EMB_EINVAL, "NULL out");
     if (!g.configured)
@@ -949,6 +1003,7 @@ int emb_set_host_path(int path)
     if (path < EMB_HOST_AUTO || path > EMB_HOST_BOUNCE)
         return fail(EMB_EINVAL, "host path must be EMB_HOST_AUTO, _COPY, _MAPPED, _MAPPED_OUT or _BOUNCE");
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     g_tune.host_path = path;
     return EMB_OK;
 }
@@ -1007,6 +1062,7 @@ static void shutdown_current()
 void emb_shutdown(void)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     for (int k = kMaxDevices - 1; k >= 0; k--) {  // every GPU of the group; the tuning knobs survive
         g_cur = &g_ctxs[k];
         shutdown_current();
@@ -1022,6 +1078,7 @@ struct dpu_set_t *populate_mram(uint32_t table_id, uint64_t nr_rows, uint32_t co
                                 dpu_runtime_totals *runtime)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     double t0 = now_s();
     int rc = ensure_configured();
     if (rc)
@@ -1089,6 +1146,7 @@ static int populate_whole(uint32_t table_id, uint64_t nr_rows, const void *src, 
 int emb_populate_table_i32(uint32_t table_id, uint64_t nr_rows, const int32_t *row_major)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -1099,6 +1157,7 @@ int emb_populate_table_i32(uint32_t table_id, uint64_t nr_rows, const int32_t *r
 int emb_populate_table_f32(uint32_t table_id, uint64_t nr_rows, const float *row_major, int kind)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -1110,6 +1169,7 @@ int emb_populate_table_device(uint32_t table_id, uint64_t nr_rows, const void *d
                               int src_is_f32, int kind, void *stream)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -1123,6 +1183,7 @@ int emb_populate_table_device(uint32_t table_id, uint64_t nr_rows, const void *d
 int emb_table_set_row_base(uint32_t table_id, uint64_t row_base)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
@@ -1138,6 +1199,7 @@ int emb_table_set_row_base(uint32_t table_id, uint64_t row_base)
 int emb_table_read(uint32_t table_id, uint64_t row0, uint64_t n, void *dst_host)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
@@ -1153,6 +1215,7 @@ int emb_table_read(uint32_t table_id, uint64_t row0, uint64_t n, void *dst_host)
 int emb_table_info(uint32_t table_id, uint64_t *nr_rows, int *kind, const void **dev_ptr)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
@@ -1169,6 +1232,7 @@ int emb_table_info(uint32_t table_id, uint64_t *nr_rows, int *kind, const void *
 int emb_free_table(uint32_t table_id)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
@@ -1186,9 +1250,16 @@ int emb_free_table(uint32_t table_id)
 int emb_l2_persist(uint32_t table_id, uint64_t first_row, uint64_t nr_rows, float hit_ratio, void *stream)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
+    const int owner = nr_rows ? owner_of(table_id) : 0;
+    if (owner != 0 && stream)
+        return fail(EMB_EINVAL, "emb_l2_persist: table %u lives on GPU %d of the device group; a caller's stream can only "
+                                "belong to the group's first GPU (pass NULL for the library's stream on the owner)",
+                    table_id, owner);
+    UseCtx on_owner(owner);
     cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
     cudaStreamAttrValue attr;
     memset(&attr, 0, sizeof attr);
@@ -1223,6 +1294,7 @@ int emb_l2_persist(uint32_t table_id, uint64_t first_row, uint64_t nr_rows, floa
 int emb_table_set_hot_rows(uint32_t table_id, uint64_t hot_rows, int mode)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     UseCtx on_owner(owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
@@ -1251,6 +1323,7 @@ int emb_hot_order(const uint64_t *counts, uint64_t nr_rows, uint32_t *new_of_old
 int emb_table_remap(uint32_t table_id, const uint32_t *new_of_old)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     UseCtx on_owner(owner_of(table_id));
     int rc = ensure_configured();
     if (rc)
@@ -1264,6 +1337,14 @@ int emb_table_remap(uint32_t table_id, const uint32_t *new_of_old)
         return fail(EMB_EINVAL, "table %u is a row shard: reorder whole tables only", table_id);
     if (t.d_remap)
         return fail(EMB_ESTATE, "table %u is already reordered: populate it again first", table_id);
+    // Only the stretch kernel translates indices (apply_hot): refuse now what every later lookup would refuse -- and
+    // lookup() has no error return, it would end the process.
+    if (!lanes_for_dim(g.shape.nr_cols))
+        return fail(EMB_EINVAL, "emb_table_remap: NR_COLS %u is pooled by the any-dimension kernel, which cannot translate "
+                                "indices (needs 4, 8, 16, 32, 64 or 128 columns)", g.shape.nr_cols);
+    if (g_tune.variant == 1 || g_tune.variant == 4)
+        return fail(EMB_EINVAL, "emb_table_remap: emb_set_tuning selected kernel variant %d, which cannot translate indices "
+                                "(variant 6 or the default)", g_tune.variant);
     const uint64_t rows = t.rows;
     {  // a permutation of 0 .. rows-1?
         std::vector<bool> seen((size_t)rows, false);
@@ -1320,7 +1401,10 @@ int emb_table_remap(uint32_t table_id, const uint32_t *new_of_old)
 int emb_remap_indices(uint32_t table_id, uint32_t *indices_dev, uint64_t n, void *stream)
 {
     std::lock_guard<std::mutex> lk(g_mu);
-    UseCtx on_owner(owner_of(table_id));
+    DeviceScope caller_device;
+    if (owner_of(table_id) != 0)
+        return fail(EMB_EINVAL, "emb_remap_indices: table %u lives on GPU %d of the device group; calls that take device "
+                                "pointers act on the group's first GPU only", table_id, owner_of(table_id));
     if (table_id >= g.tables.size() || !g.tables[table_id].kind)
         return fail(EMB_ESTATE, "table %u is not populated", table_id);
     const Table &t = g.tables[table_id];
@@ -1341,6 +1425,7 @@ int emb_remap_indices(uint32_t table_id, uint32_t *indices_dev, uint64_t n, void
 int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -1350,6 +1435,7 @@ int emb_plan_create(const emb_dev_query *queries, uint32_t n, emb_plan **out)
     if (!p)
         return fail(EMB_ENOMEM, "out of host memory");
     p->h.resize(n);
+    p->ctx = g_cur;
     const uint64_t D = g.shape.nr_cols;
     bool any_float = false, all_float = true, overlap = true;
     for (uint32_t i = 0; i < n; i++) {
@@ -1432,11 +1518,13 @@ int emb_plan_launch(emb_plan *plan, void *stream)
         return fail(EMB_EINVAL, "NULL plan");
     // the descriptors hold raw slab pointers: a table freed or re-allocated since the plan was made would be
     // read after free
+    const Ctx &c = *plan->ctx;
+    OnDevice on(c.device);
     for (const auto &tg : plan->gen)
-        if (tg.first >= g.tables.size() || g.tables[tg.first].generation != tg.second || !g.tables[tg.first].kind)
+        if (tg.first >= c.tables.size() || c.tables[tg.first].generation != tg.second || !c.tables[tg.first].kind)
             return fail(EMB_ESTATE, "plan is stale: table %u was freed or re-allocated after emb_plan_create", tg.first);
-    return launch_bag_sum(plan->variant, plan->d, (uint32_t)plan->h.size(), plan->uni, plan->grid,
-                          stream ? (cudaStream_t)stream : g.stream, plan->all_float, plan->overlap, plan->compact);
+    return launch_bag_sum(c, plan->variant, plan->d, (uint32_t)plan->h.size(), plan->uni, plan->grid,
+                          stream ? (cudaStream_t)stream : c.stream, plan->all_float, plan->overlap, plan->compact);
 }
 
 void emb_plan_destroy(emb_plan *plan)
@@ -1456,6 +1544,7 @@ uint32_t emb_plan_grid(const emb_plan *plan) { return plan ? plan->grid : 0; }
 int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -1519,7 +1608,7 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
     if (chunk > 0x7fffffffull)
         return fail(EMB_EINVAL, "too many bags for one launch");
     CU(cudaMemcpyAsync(g.ring_d[slot], h, n * sizeof(BagDesc), cudaMemcpyHostToDevice, s));
-    rc = launch_bag_sum(variant, g.ring_d[slot], n, uniform_chunks(h, n), (uint32_t)chunk, s, all_float);
+    rc = launch_bag_sum(g, variant, g.ring_d[slot], n, uniform_chunks(h, n), (uint32_t)chunk, s, all_float);
     // recorded AFTER the launch: the slot (pinned copy and device copy) is recycled only once the kernel that
     // reads its descriptors has run, whatever stream the next user of the slot launches on
     CU(cudaEventRecord(g.ring_ev[slot], s));
@@ -1529,6 +1618,7 @@ int emb_lookup_device(const emb_dev_query *queries, uint32_t n, void *stream)
 int emb_check_indices(void)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int any = 0;
     for (int k = 0; k < g_grp.n; k++) {  // every GPU of the device group
         UseCtx u(k);
@@ -1548,6 +1638,7 @@ int emb_reduce_partials(const void *const *parts_dev, uint32_t n_parts, uint32_t
                         uint32_t out_stride, uint64_t nr_bags, int is_raw_i32, void *stream)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -1579,6 +1670,7 @@ struct emb_finish {
     emb::FlagList flags;
     uint32_t n_ranks = 0, my_rank = 0, n_jobs = 0, grid = 1;
     emb::ReduceJob *d_jobs = nullptr;
+    Ctx *ctx = nullptr;  // where it was made (the group's first GPU); emb_finish_launch takes no lock, see emb_plan
 };
 
 extern "C" {
@@ -1587,6 +1679,7 @@ int emb_finish_create(void *const *flag_blocks, uint32_t n_ranks, uint32_t my_ra
                       uint32_t n_jobs, emb_finish **out)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -1595,6 +1688,7 @@ int emb_finish_create(void *const *flag_blocks, uint32_t n_ranks, uint32_t my_ra
     emb_finish *f = new (std::nothrow) emb_finish();
     if (!f)
         return fail(EMB_ENOMEM, "out of host memory");
+    f->ctx = g_cur;
     memset(&f->flags, 0, sizeof f->flags);
     for (uint32_t r = 0; r < n_ranks; r++) {
         if (!flag_blocks[r]) {
@@ -1651,9 +1745,13 @@ int emb_finish_launch(emb_finish *f, uint32_t epoch, void *stream)
 {
     if (!f)
         return fail(EMB_EINVAL, "NULL finish object");
-    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    const Ctx &c = *f->ctx;
+    if (!c.device_ready)
+        return fail(EMB_ESTATE, "emb_finish_launch after emb_shutdown()");
+    OnDevice on(c.device);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c.stream;
     launch_dependent(emb::exchange_finish_kernel, dim3(f->grid, 1, 1), 256, s, f->flags, f->n_ranks, f->my_rank, epoch, f->d_jobs, f->n_jobs,
-                     g.shape.nr_cols, g.d_err);
+                     c.shape.nr_cols, c.d_err);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
     return EMB_OK;
@@ -2019,7 +2117,7 @@ static int host_enqueue(HostSlot &hs, uint64_t ticket, bool overlapped, uint32_t
             CU(cudaStreamWaitEvent(s_k, ev[3 * gi], 0));
         }
         CU(cudaEventRecord(ev[3 * gi + 1], s_k));
-        if ((rc = launch_bag_sum(variant, hs.d_descs + t0, t1 - t0, uniform_chunks(hs.h_descs + t0, t1 - t0), g_grid[gi], s_k,
+        if ((rc = launch_bag_sum(g, variant, hs.d_descs + t0, t1 - t0, uniform_chunks(hs.h_descs + t0, t1 - t0), g_grid[gi], s_k,
                                  all_float)))
             return rc;
         launches += g_grid[gi] ? 1 : 0;
@@ -2235,6 +2333,7 @@ int32_t *lookup(uint32_t **indices, uint32_t **offsets, float **final_results, v
                 int64_t latency_print)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         die("lookup", rc);
@@ -2268,6 +2367,7 @@ int emb_lookup_ex(uint32_t nr_tables, const uint32_t *const *indices, const uint
                   const uint32_t *indices_len, const uint32_t *nr_batches, float *const *final_results)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -2281,6 +2381,7 @@ int emb_lookup_ex_async(uint32_t nr_tables, const uint32_t *const *indices, cons
                         emb_ticket *ticket)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -2319,6 +2420,7 @@ int emb_lookup_ex_async(uint32_t nr_tables, const uint32_t *const *indices, cons
 int emb_lookup_wait(emb_ticket ticket)
 {
     std::unique_lock<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     if (!ticket || ticket >= g_next_ticket)
         return fail(EMB_EINVAL, "emb_lookup_wait: ticket %llu was never issued", (unsigned long long)ticket);
     const int slot = (int)(ticket % kHostSlots);
@@ -2365,6 +2467,7 @@ int emb_last_timings(emb_timings *out)
 int emb_device_alloc(void **dev_ptr, size_t nbytes)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -2385,6 +2488,7 @@ int emb_device_free(void *dev_ptr)
 int emb_host_alloc(void **host_ptr, size_t nbytes)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -2405,6 +2509,7 @@ int emb_host_free(void *host_ptr)
 int emb_host_register(void *host_ptr, size_t nbytes)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    DeviceScope caller_device;
     int rc = ensure_configured();
     if (rc)
         return rc;
@@ -2420,9 +2525,11 @@ int emb_host_unregister(void *host_ptr)
     return EMB_OK;
 }
 
+/* These three take no lock: like every device-resident entry point they act on the group's first GPU, named
+ * explicitly (the library's current context may be switched by a group call in another thread). */
 int emb_memcpy_h2d(void *dst_dev, const void *src_host, size_t nbytes, void *stream)
 {
-    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    cudaStream_t s = stream ? (cudaStream_t)stream : g_ctxs[0].stream;
     CU(cudaMemcpyAsync(dst_dev, src_host, nbytes, cudaMemcpyHostToDevice, s));
     if (!stream)
         CU(cudaStreamSynchronize(s));
@@ -2431,7 +2538,7 @@ int emb_memcpy_h2d(void *dst_dev, const void *src_host, size_t nbytes, void *str
 
 int emb_memcpy_d2h(void *dst_host, const void *src_dev, size_t nbytes, void *stream)
 {
-    cudaStream_t s = stream ? (cudaStream_t)stream : g.stream;
+    cudaStream_t s = stream ? (cudaStream_t)stream : g_ctxs[0].stream;
     CU(cudaMemcpyAsync(dst_host, src_dev, nbytes, cudaMemcpyDeviceToHost, s));
     if (!stream)
         CU(cudaStreamSynchronize(s));
@@ -2442,8 +2549,10 @@ int emb_stream_sync(void *stream)
 {
     if (stream)
         CU(cudaStreamSynchronize((cudaStream_t)stream));
-    else if (g.device_ready)
+    else if (g_ctxs[0].device_ready) {
+        OnDevice on(g_ctxs[0].device);  // the library's GPU, whatever the caller's current device is
         CU(cudaDeviceSynchronize());
+    }
     return EMB_OK;
 }
 

@@ -141,6 +141,101 @@ def test_device_resident_entry_points_stay_on_the_first_gpu(emblib):
         emblib.Plan([dict(table_id=1, indices=di, offsets=do, out=out)])
 
 
+def test_plan_launches_in_one_thread_beside_group_host_calls_in_another(emblib):
+    """A plan carries the context it was made on: emb_plan_launch (which takes no lock) no longer looks at the library's
+    current context, which a device-group host call in another thread switches from GPU to GPU while it runs."""
+    import threading
+    rng = np.random.default_rng(11)
+    T, D, R, B = 4, 16, 3000, 2000
+    emblib.configure_devices(T, D, [0, 0], table_device=[0, 1, 0, 1])
+    tabs = make_tables(rng, T, R, D)
+    for t in range(T):
+        emblib.populate_table_i32(t, tabs[t])
+    idx, off = zip(*[ragged(rng, tabs[t].shape[0], B, 10) for t in range(T)])
+    want_host = eo.lookup_rows(tabs, idx, off)
+    i, o = ragged(rng, R, 700, 9)
+    di = torch.from_numpy(i.view(np.int32)).cuda()
+    do = torch.from_numpy(o.view(np.int32)).cuda()
+    want_plan = eo.lookup_rows([tabs[0]], [i], [o])[0]
+    out = torch.empty((700, D), dtype=torch.float32, device="cuda")
+    plan = emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=out)])
+    stream = torch.cuda.Stream()
+    errors = []
+
+    def host_calls():
+        try:
+            for _ in range(30):
+                got = emblib.lookup_ex(idx, off)
+                for t in range(T):
+                    if not np.array_equal(bits(got[t]), bits(want_host[t])):
+                        errors.append(f"host call, table {t}")
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    def plan_launches():
+        try:
+            for _ in range(300):
+                out.zero_()
+                stream.wait_stream(torch.cuda.current_stream())
+                plan.launch(stream)
+                stream.synchronize()
+                if not np.array_equal(bits(out.cpu().numpy()), bits(want_plan)):
+                    errors.append("plan launch")
+                    break
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    a, b = threading.Thread(target=host_calls), threading.Thread(target=plan_launches)
+    a.start(); b.start(); a.join(); b.join()
+    plan.close()
+    assert not errors, errors[:3]
+    assert emblib.load().emb_check_indices() == 0
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_the_callers_current_device_is_left_alone(emblib):
+    """A caller whose own current device is not the library's: allocations, copies and launches still land on the
+    library's GPU, and the caller finds its device unchanged after every call (single GPU and device group)."""
+    rng = np.random.default_rng(12)
+    T, D, R, B = 3, 16, 2000, 900
+    tabs = make_tables(rng, T, R, D)
+    idx, off = zip(*[ragged(rng, tabs[t].shape[0], B, 10) for t in range(T)])
+    want = eo.lookup_rows(tabs, idx, off)
+    torch.cuda.set_device(1)
+    try:
+        torch.zeros(1, device="cuda")  # the caller's context on GPU 1 exists
+        for devices in (None, [0, 1]):
+            emblib.shutdown()
+            if devices is None:
+                emblib.configure(T, D, device=0)
+            else:
+                emblib.configure_devices(T, D, devices)
+            assert torch.cuda.current_device() == 1
+            for t in range(T):
+                emblib.populate_table_i32(t, tabs[t])
+                assert torch.cuda.current_device() == 1
+            for _ in range(2):  # the second call re-uses, the first one allocates
+                got = emblib.lookup_ex(idx, off)
+                assert torch.cuda.current_device() == 1
+                for t in range(T):
+                    assert np.array_equal(bits(got[t]), bits(want[t])), (devices, t)
+            assert emblib.load().emb_check_indices() == 0
+            assert torch.cuda.current_device() == 1
+            if devices is None:  # a plan made on GPU 0 launches there although the thread sits on GPU 1
+                di = torch.from_numpy(idx[0].view(np.int32)).to("cuda:0")
+                do = torch.from_numpy(off[0].view(np.int32)).to("cuda:0")
+                out = torch.empty((B, D), dtype=torch.float32, device="cuda:0")
+                plan = emblib.Plan([dict(table_id=0, indices=di, offsets=do, out=out)])
+                torch.cuda.synchronize(0)
+                plan.launch(None)  # the library's own stream on GPU 0
+                emblib.load().emb_stream_sync(None)
+                assert torch.cuda.current_device() == 1
+                assert np.array_equal(bits(out.cpu().numpy()), bits(want[0]))
+                plan.close()
+    finally:
+        torch.cuda.set_device(0)
+
+
 def test_an_unmodified_caller_gets_the_group_from_the_environment():
     """populate_mram() / lookup() only, shapes AND the group from the environment (EMB_DEVICES beside the reference's
     NR_TABLES ...): what dlrm_dpu_pytorch.py would see on a box with several GPUs."""

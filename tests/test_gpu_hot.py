@@ -200,3 +200,13 @@ def test_rules_around_reordered_tables(emblib):
     assert np.array_equal(emblib.table_read(0, 0, R), q)
     got = emblib.lookup_ex([i, i], [o, o])
     assert np.array_equal(bits(got[0]), bits(want)) and np.array_equal(bits(got[1]), bits(want))
+    # a reordering asked for while a kernel that cannot translate is selected is refused up front (not at the first
+    # lookup() afterwards, which has no error return)
+    emblib.check(lib.emb_set_tuning(1, 0, 0))
+    try:
+        with pytest.raises(emblib.EmbError, match="cannot translate"):
+            emblib.remap_table(0, m)
+    finally:
+        emblib.check(lib.emb_set_tuning(0, 0, 0))
+    got = emblib.lookup_ex([i, i], [o, o])
+    assert np.array_equal(bits(got[0]), bits(want))
