@@ -64,6 +64,10 @@ WORKLOADS = {
                        11938, 155, 4, 976, 14, 39979771, 25641295, 39664984, 585935, 12972, 108, 36],
                  D=64, B=65536, pool=(10, 10), dist="uniform", sharded=True),
 }
+# The same tables with every table above 3 GB CUT BY ROWS over the ranks (the only layout for a table that exceeds one
+# GPU's HBM; north_star): raw int32 partial sums cross NVLink and the completion kernel reduces them at the receiver.
+WORKLOADS["c4rc"] = dict(WORKLOADS["c4tb"], max_table_bytes=3e9,
+                         name=WORKLOADS["c4tb"]["name"] + "; tables above 3 GB cut by rows (partial sums reduced at the receiver)")
 N_BATCHES = 4  # distinct index batches rotated through the timed steps
 
 
@@ -84,6 +88,8 @@ def parse_args(argv=None):
                     help="plans without EMB_Q_OVERLAP: a pooling launch reads nothing before the kernel in front of it "
                          "has completed (comparator for the programmatic-dependent-launch overlap)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-unmodified-caller", action="store_true",
+                    help="skip e2e.unmodified_caller (lookup() on pageable arrays)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the bit-exact check of one batch on every rank")
     ap.add_argument("--extras", default="auto",
@@ -354,7 +360,7 @@ def run_reference(args, w):
         "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": dt / steps * 1e3,
         "higher_is_better": True, "scaling": scaling,
         "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
-        "cpu_baseline": {"value": val, "unit": "lookups/s", "cores": cores, "kind": "reference", "sample": sample,
+        "cpu_baseline": {"value": val, "unit": "lookups/s", "cores": cores, "kind": "port", "sample": sample,
                          "what": "the reference's CPU lookup path restated call for call: nn.EmbeddingBag(mode=sum, "
                                  "sparse=True) per table on stock torch, fp32 tables, int64 indices "
                                  "(dlrm_s_pytorch.py:295,483-488); its DPU path (oracle/_ref) is undefined at this shape "
@@ -434,6 +440,18 @@ def compare_rows(got, want, mag=None):
     if mag is None:
         return int((got.contiguous().view(torch.int32) != want.contiguous().view(torch.int32)).sum().item())
     return int(((got - want).abs() > 1e-5 * mag + 1e-30).sum().item())
+
+
+def gather_over_ranks(vals, world):
+    """[v0, v1, ...] of this rank -> one list per value holding every rank's figure (rank order)."""
+    if world == 1:
+        return [[float(v)] for v in vals]
+    import torch
+    import torch.distributed as dist
+    mine = torch.tensor([float(v) for v in vals], dtype=torch.float64, device="cuda")
+    every = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine)
+    return [[round(float(e[i]), 6) for e in every] for i in range(len(vals))]
 
 
 def reduce_over_ranks(vals, world, ops):
@@ -659,8 +677,10 @@ def bench_tablewise(args, w, steps, warmup):
     kdist = dist_summary([a.elapsed_time(b) for a, b in ev])
     kernel_ms = kdist["mean"]
     n_lookups = sum(lookups[k % N_BATCHES] for k in range(K))
+    lookups_rank = float(n_lookups) / K
     total_ms, n_lookups, kernel_ms_max = reduce_over_ranks([total_ms, float(n_lookups), kernel_ms], world,
                                                            ["max", "sum", "max"])
+    kernel_ms_per_rank, lookups_per_rank = gather_over_ranks([kernel_ms, lookups_rank], world)
     value = n_lookups / (total_ms * 1e-3)
 
     # roofline of the pooling kernel on this rank (algorithmic bytes / mean launch duration)
@@ -683,7 +703,7 @@ def bench_tablewise(args, w, steps, warmup):
         Ke = max(3, min(K, 50))
         if world == 1:
             e2e = e2e_host_call(args, lib, emblib, batches, lookups, T, B, D, Ke,
-                                (EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED))
+                                (EMB_HOST_AUTO, EMB_HOST_COPY, EMB_HOST_MAPPED), rows_t=rows_t)
         else:
             e2e = e2e_sharded_path(args, lib, emblib, exchange, slabs, batches, lookups, T, B, D, per, rank, world,
                                    Ke, stream, sync_all)
@@ -695,7 +715,7 @@ def bench_tablewise(args, w, steps, warmup):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         import torch as _t
-        T_s = min(T, 8)
+        T_s = T  # every table of the batch, like the --impl reference arm
         tabs = [emblib.table_read(t, 0, rows_t[t], dtype=np.float32 if is_float else np.int32) for t in range(T_s)]
         sidx, soff = batches[0][0][:T_s], batches[0][1][:T_s]
         ftabs = tabs if is_float else [x.astype(np.float32) * np.float32(1e-9) for x in tabs]
@@ -704,7 +724,7 @@ def bench_tablewise(args, w, steps, warmup):
         tv, treps = time_passes(torch_bags(ftabs, sidx, soff), ns, budget_s=8.0)
         cores = _t.get_num_threads()
         sample = f"{T_s} of {T} tables x {B} bags ({ns} lookups) x {treps} passes"
-        cpu = {"value": tv, "unit": "lookups/s", "cores": cores, "kind": "reference", "sample": sample,
+        cpu = {"value": tv, "unit": "lookups/s", "cores": cores, "kind": "port", "sample": sample,
                "what": "nn.EmbeddingBag(mode=sum, sparse=True) per table, fp32, stock torch (dlrm_s_pytorch.py:295,483-488)"}
         _t.set_num_threads(1)
         n1 = sum(len(i) for i in sidx[:2])
@@ -712,7 +732,7 @@ def bench_tablewise(args, w, steps, warmup):
         _t.set_num_threads(cores)
         cpu["single_thread"] = {"value": v1, "unit": "lookups/s", "cores": 1, "sample": f"2 tables x {r1} passes"}
         if not is_float:
-            v, pc, reps = time_oracle_port(tabs, sidx, soff, budget_s=5.0)
+            v, pc, reps = time_oracle_port(tabs[:8], sidx[:8], soff[:8], budget_s=5.0)
             cpu["oracle_port"] = {"value": v, "unit": "lookups/s", "cores": pc, "passes": reps, "kind": "port"}
 
     out = None
@@ -729,6 +749,7 @@ def bench_tablewise(args, w, steps, warmup):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel_ms": kernel_ms,
                          "kernel_ms_dist": kdist, "kernel_ms_max_over_ranks": kernel_ms_max,
+                         "kernel_ms_per_rank": kernel_ms_per_rank, "lookups_per_launch_per_rank": lookups_per_rank,
                          "kernel_ms_what": "mean duration of one ISOLATED pooling launch: the K steps repeated right "
                                            "after the timed region with an event on either side of every pooling "
                                            "launch; in the timed region itself nothing separates the launches and "
@@ -753,7 +774,7 @@ def bench_tablewise(args, w, steps, warmup):
     return out
 
 
-def e2e_host_call(args, lib, emblib, batches, lookups, T, B, D, Ke, paths):
+def e2e_host_call(args, lib, emblib, batches, lookups, T, B, D, Ke, paths, rows_t=None):
     """N = 1: the reference-facing call, emb_lookup_ex on HOST arrays.  The arrays are page-locked and carved out of
     one arena per kind, the way a caller that owns its buffers would allocate them (the reference allocates its
     index / offset / result arrays once, dlrm_dpu_pytorch.py:484-498,1028-1051)."""
@@ -817,34 +838,96 @@ def e2e_host_call(args, lib, emblib, batches, lookups, T, B, D, Ke, paths):
              3: "inputs staged by the copy engine, pooled rows written to the host arrays by the kernel's "
                 "store epilogue over PCIe, pipelined over table groups"}
     v, ms, tm = time_e2e(Ke)  # default path (EMB_HOST_AUTO) on page-locked arrays
-    # the synchronous result of the last call is the check for the calls in flight: same batch, same bits
-    want_bits = [r.view(np.uint32).copy() for r in calls[(Ke - 1) % 2].results[:2]]
-    for r in calls[(Ke - 1) % 2].results[:2]:
-        r[:] = 0
-    va, msa = time_e2e_in_flight(Ke)
-    for r, wb in zip(calls[(Ke - 1) % 2].results[:2], want_bits):
-        if not np.array_equal(r.view(np.uint32), wb):
-            raise SystemExit("PARITY FAILURE: emb_lookup_ex_async rows differ from emb_lookup_ex rows")
+    # the synchronous results are the check for the calls in flight: same batches, same bits -- every table of BOTH
+    # calls (each call object has run synchronously by now; its result arrays are zeroed in between)
+    want_bits = [[r.view(np.uint32).copy() for r in c.results] for c in calls]
+    for c in calls:
+        for r in c.results:
+            r[:] = 0
+    va, msa = time_e2e_in_flight(max(Ke, 2))
+    tma = emblib.last_timings()  # of the call completed last in the in-flight run
+    for c, wbs in zip(calls, want_bits):
+        for t, (r, wb) in enumerate(zip(c.results, wbs)):
+            if not np.array_equal(r.view(np.uint32), wb):
+                raise SystemExit(f"PARITY FAILURE: emb_lookup_ex_async rows differ from emb_lookup_ex rows (table {t})")
+
+    def stage_times(x):
+        return {"path": PATHS[int(x.path)], "h2d": x.h2d_ms, "kernel": x.kernel_ms, "d2h": x.d2h_ms, "total": x.total_ms,
+                "launches": int(x.launches)}
     in_flight = va >= v  # the headline is the better of the two ways to call; both are in the line
-    e2e = {"value": va if in_flight else v, "unit": "lookups/s", "h2d_bytes_per_step": int(tm.h2d_bytes),
-           "d2h_bytes_per_step": int(tm.d2h_bytes), "ms_per_step": msa if in_flight else ms, "steps": Ke,
+    tm_head = tma if in_flight else tm
+    e2e = {"value": va if in_flight else v, "unit": "lookups/s", "h2d_bytes_per_step": int(tm_head.h2d_bytes),
+           "d2h_bytes_per_step": int(tm_head.d2h_bytes), "ms_per_step": msa if in_flight else ms, "steps": Ke,
            "calls_in_flight": 2 if in_flight else 1,
            "call": ("emb_lookup_ex_async + emb_lookup_wait (host pointers, page-locked arrays carved from one arena per "
                     "kind), two calls in flight: call k+1 is issued before call k is waited for; wall clock from the "
                     "first issue to the last call's rows in host memory") if in_flight else
                    "emb_lookup_ex (host pointers, page-locked arrays carved from one arena per kind)",
-           "two_calls_in_flight": {"value": va, "ms_per_step": msa, "call": "emb_lookup_ex_async + emb_lookup_wait"},
-           "synchronous_call": {"value": v, "ms_per_step": ms, "call": "emb_lookup_ex, one call at a time (what an "
-                                "unmodified caller of lookup() gets)"},
-           "path": PATHS[int(tm.path)],
-           "last_call_ms": {"h2d": tm.h2d_ms, "kernel": tm.kernel_ms, "d2h": tm.d2h_ms, "total": tm.total_ms},
+           "two_calls_in_flight": {"value": va, "ms_per_step": msa, "call": "emb_lookup_ex_async + emb_lookup_wait",
+                                   "last_call_ms": stage_times(tma),
+                                   "parity": f"all {T} result arrays of both calls in flight equal the synchronous rows"},
+           "synchronous_call": {"value": v, "ms_per_step": ms, "call": "emb_lookup_ex, one call at a time on page-locked "
+                                "arrays", "last_call_ms": stage_times(tm)},
+           "path": PATHS[int(tm_head.path)],
+           "last_call_ms": stage_times(tm_head),
            "other_paths": {}}
     for forced in (EMB_HOST_COPY, EMB_HOST_MAPPED):
         emblib.set_host_path(forced)
         v2, ms2, _ = time_e2e(max(3, Ke // 5))
         e2e["other_paths"][PATHS[forced].split(":")[0]] = {"value": v2, "ms_per_step": ms2}
     emblib.set_host_path(EMB_HOST_AUTO)
+    if rows_t is not None and not args.no_unmodified_caller:
+        e2e["unmodified_caller"] = e2e_unmodified_caller(lib, emblib, rows_t, T, B, D, max(3, Ke // 2))
     return e2e
+
+
+def e2e_unmodified_caller(lib, emblib, rows_t, T, B, D, n_steps, P=10):
+    """What a caller that changes NOTHING gets: the reference-signature lookup() with the fixed shape of a reference
+    build (MAX_NR_BATCHES = B, MAX_INDICES_PER_BATCH = P = 10), on plain pageable NumPy arrays, one
+    allocation per table and kind, pointer arrays built once (dlrm_dpu_pytorch.py:484-498,1028-1051).  Then the same
+    call after the one-line change INTEGRATION.md section 3 recommends: emb_host_register() of the result arrays."""
+    import ctypes as C
+    emblib.configure(T, D, B, P)  # the -D shape macros of the reference build (upmem/Makefile:69-81)
+    rng = np.random.default_rng(77)
+    idx = [rng.integers(0, rows_t[t], size=B * P, dtype=np.int64).astype(np.uint32) for t in range(T)]
+    off = [(np.arange(B, dtype=np.uint32) * np.uint32(P)) for _ in range(T)]
+    res = [np.empty((B, D), dtype=np.float32) for _ in range(T)]
+    ip = (emblib.u32p * T)(*[a.ctypes.data_as(emblib.u32p) for a in idx])
+    op = (emblib.u32p * T)(*[a.ctypes.data_as(emblib.u32p) for a in off])
+    rp = (emblib.f32p * T)(*[a.ctypes.data_as(emblib.f32p) for a in res])
+    n_lookups = T * B * P
+
+    def timed():
+        for _ in range(3):
+            lib.lookup(ip, op, rp, None, 0)
+        t0 = time.perf_counter()
+        for _ in range(n_steps):
+            lib.lookup(ip, op, rp, None, 0)
+        dt = (time.perf_counter() - t0) / n_steps
+        tm = emblib.last_timings()
+        return {"value": n_lookups / dt, "unit": "lookups/s", "ms_per_step": dt * 1e3,
+                "last_call_ms": {"path": int(tm.path), "h2d": tm.h2d_ms, "kernel": tm.kernel_ms, "d2h": tm.d2h_ms,
+                                 "total": tm.total_ms},
+                "h2d_bytes_per_step": int(tm.h2d_bytes), "d2h_bytes_per_step": int(tm.d2h_bytes)}
+
+    out = {"shape": f"lookup(): {T} tables x {B} bags x fixed pooling {P}, pageable NumPy arrays, one per table",
+           "lookup_pageable": timed()}
+    # parity of the fixed-shape entry point against emb_lookup_ex on the same arrays (page-locked copies)
+    want = emblib.lookup_ex(idx, off)
+    for t in range(T):
+        if not np.array_equal(res[t].view(np.uint32), want[t].view(np.uint32)):
+            raise SystemExit(f"PARITY FAILURE: lookup() rows differ from emb_lookup_ex rows (table {t})")
+    out["parity"] = f"all {T} result arrays equal emb_lookup_ex on the same arrays"
+    for a in res:
+        emblib.check(lib.emb_host_register(C.c_void_p(a.ctypes.data), a.nbytes), "emb_host_register")
+    try:
+        out["lookup_registered"] = timed()
+        out["lookup_registered"]["what"] = "the same call after emb_host_register() of the result arrays only"
+    finally:
+        for a in res:
+            lib.emb_host_unregister(C.c_void_p(a.ctypes.data))
+    emblib.configure(T, D, 0, 0)
+    return out
 
 
 def run_host_pipeline(torch, stream, n_steps, copy_in, launch, finish, copy_out):
@@ -968,8 +1051,8 @@ def bench_sharded(args, w, steps, warmup):
     P = (w["pool"][0] + w["pool"][1]) / 2.0
     emblib.check(lib.emb_set_tuning(args.variant, args.unroll, args.mult))
     kw = {}
-    if args.max_table_bytes:
-        kw["max_table_bytes"] = args.max_table_bytes
+    if args.max_table_bytes or w.get("max_table_bytes"):
+        kw["max_table_bytes"] = args.max_table_bytes or w["max_table_bytes"]
     st = ShardedTables(rows, D, B, lookups=[B * P] * T, hbm_budget=150e9, layout=args.layout,
                        rotate=not args.no_rotate, **kw)
     stream = torch.cuda.Stream()
@@ -1075,6 +1158,9 @@ def bench_sharded(args, w, steps, warmup):
     kernel_ms = kdist["mean"]
     total_ms_max, kernel_ms_max, agg_gbps = reduce_over_ranks(
         [total_ms, kernel_ms, my_bytes / (kernel_ms * 1e-3) / 1e9], world, ["max", "max", "sum"])
+    # every rank's isolated pooling launch and the work the planner gave it: what the cost model is judged by
+    my_lookups = sum(B * P * ((sh.bag_hi - sh.bag_lo) / B if sh.sliced else 1.0) for sh in st.local)
+    kernel_ms_per_rank, bytes_per_rank, lookups_per_rank = gather_over_ranks([kernel_ms, my_bytes, my_lookups], world)
     value = lookups_global * K / (total_ms_max * 1e-3)
     peak, peak_src = load_peaks()
     achieved = my_bytes / (kernel_ms * 1e-3) / 1e9  # rank 0's pooling launch
@@ -1140,7 +1226,10 @@ def bench_sharded(args, w, steps, warmup):
                     "tuning": {"variant": args.variant, "unroll": args.unroll, "mult": args.mult}},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms, "kernel_ms_dist": kdist,
-                         "kernel_ms_max_over_ranks": kernel_ms_max, "algorithmic_bytes_per_launch": my_bytes,
+                         "kernel_ms_max_over_ranks": kernel_ms_max, "kernel_ms_per_rank": kernel_ms_per_rank,
+                         "kernel_ms_max_over_mean": round(max(kernel_ms_per_rank) / (sum(kernel_ms_per_rank) / world), 4),
+                         "algorithmic_bytes_per_rank": bytes_per_rank, "index_positions_read_per_rank": lookups_per_rank,
+                         "algorithmic_bytes_per_launch": my_bytes,
                          "aggregate_GBps_all_ranks": agg_gbps, "note": "rank 0's pooling launch; bytes = indices + "
                          "in-range rows + outputs + offsets of its shards (sharding.shard_cost)"},
             "parity": parity, "gpu_launches": int(gpu_launches),
@@ -1158,9 +1247,12 @@ def bench_sharded(args, w, steps, warmup):
 
 def condensed(r):
     """What an `extra` workload contributes to the main JSON line."""
-    keep = {k: r[k] for k in ("value", "unit", "ms_per_step", "steps", "scaling", "gpu_launches", "parity")}
+    keep = {k: r[k] for k in ("value", "unit", "ms_per_step", "steps", "scaling", "gpu_launches")}
+    # compact: the driver keeps only the tail of the line, and every extra must fit in it
+    keep["parity"] = {k: v for k, v in r["parity"].items() if k != "against" and v is not None}
     keep["workload"] = r["config"]["workload"]
     keep["roofline"] = {k: r["roofline"].get(k) for k in ("achieved", "frac", "kernel_ms", "kernel_ms_max_over_ranks",
+                                                           "kernel_ms_per_rank", "kernel_ms_max_over_mean",
                                                            "algorithmic_bytes_per_launch", "aggregate_GBps_all_ranks")}
     if "placement" in r.get("run", {}):
         keep["placement"] = r["run"]["placement"]
@@ -1184,7 +1276,8 @@ def run_b200(args, w):
     torch.cuda.set_device(local)
     extras = args.extras
     if extras == "auto":
-        extras = "c4tb,c5" if (args.workload == "c2" and args.dtype == "int32") else "none"
+        # c4rc (tables cut by rows) needs ranks to cut over
+        extras = ("c4tb,c5" if world == 1 else "c4tb,c4rc,c5") if (args.workload == "c2" and args.dtype == "int32") else "none"
     extras = [e for e in extras.split(",") if e and e != "none"]
     need_group = world > 1 or bool(w.get("sharded")) or any(WORKLOADS[e].get("sharded") for e in extras)
     if need_group:
@@ -1200,18 +1293,22 @@ def run_b200(args, w):
         out = one(w, args.steps, args.warmup)
         extra = {}
         for name in extras:
-            saved = args.no_cpu_baseline
-            args.no_cpu_baseline = True
+            saved = args.no_cpu_baseline, args.no_unmodified_caller
+            args.no_cpu_baseline = args.no_unmodified_caller = True
             try:
                 r = one(WORKLOADS[name], max(3, min(args.steps, 50)), min(args.warmup, 5))
             finally:
-                args.no_cpu_baseline = saved
+                args.no_cpu_baseline, args.no_unmodified_caller = saved
             if rank == 0:
                 extra[name] = condensed(r)
     if rank == 0:
         out["clocks"] = clk.summary()
         if extra:
             out["extra"] = extra
+        # the headline, its parity block and the launch count first; the extras last (the driver keeps head and tail)
+        front = ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                 "vs_baseline", "dtype", "data", "parity", "gpu_launches")
+        out = {**{k: out[k] for k in front if k in out}, **{k: v for k, v in out.items() if k not in front}}
         print(json.dumps(out))
     if need_group:
         dist.destroy_process_group()
