@@ -16,7 +16,24 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _worker(rank, world, port, tmp):
+def _init(rank, world, port, one_gpu):
+    """One process per rank.  one_gpu: every rank uses GPU 0 (two processes time-slice it; CUDA IPC, the peer-slab
+    stores, the flag barrier of the completion kernel and its reduce jobs work the same between two processes on one
+    device as between two devices), and the process group is gloo, because NCCL refuses two ranks on one GPU -- the
+    product path needs the group only to hand the IPC handles around."""
+    import torch
+    import torch.distributed as dist
+    dev = 0 if one_gpu else rank
+    torch.cuda.set_device(dev)
+    if one_gpu:
+        dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    else:
+        dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                                device_id=torch.device("cuda", rank))
+    return dev
+
+
+def _worker(rank, world, port, tmp, one_gpu=False):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import ctypes as C
@@ -27,9 +44,7 @@ def _worker(rank, world, port, tmp):
     import emb_oracle as eo
     from pim_embedding_lookup_b200 import emblib, exchange
     from pim_embedding_lookup_b200.dputypes import EMB_Q_RAW_SUMS
-    torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
-                            device_id=torch.device("cuda", rank))
+    dev_id = _init(rank, world, port, one_gpu)
     ok = {}
     try:
         D, B, R = 16, 4096, 20000
@@ -47,7 +62,7 @@ def _worker(rank, world, port, tmp):
         want = want_all[rank * per:(rank + 1) * per]
 
         T_local = tables_per_rank[rank]
-        emblib.configure(T_local + 1, D, device=rank)
+        emblib.configure(T_local + 1, D, device=dev_id)
         mine = list(range(first[rank], first[rank] + T_local))
         dev = []
         for lt, t in enumerate(mine):
@@ -80,8 +95,12 @@ def _worker(rank, world, port, tmp):
         plan = emblib.Plan([dict(table_id=lt, indices=dev[lt][0], offsets=dev[lt][1], out=send[:, lt, :],
                                  out_stride=T_local * D) for lt in range(T_local)])
         plan.launch(stream)
-        got = exchange.nccl_all_to_all(send, B, tables_per_rank, D).cpu().numpy()
-        ok["nccl"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
+        if one_gpu:  # no NCCL between two ranks on one GPU: the comparator transport is left to the real-GPU case
+            ok["nccl"] = True
+            torch.cuda.synchronize()
+        else:
+            got = exchange.nccl_all_to_all(send, B, tables_per_rank, D).cpu().numpy()
+            ok["nccl"] = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
         plan.close()
 
         # (3) table 0 split row-wise over the two ranks: raw int32 partials into the OWNER
@@ -113,16 +132,17 @@ def _worker(rank, world, port, tmp):
         dist.destroy_process_group()
 
 
-def test_exchange_two_gpus(tmp_path):
+@pytest.mark.parametrize("one_gpu", [True, False], ids=["two_ranks_on_one_gpu", "two_gpus"])
+def test_exchange_two_gpus(tmp_path, one_gpu):
     torch = pytest.importorskip("torch")
-    if torch.cuda.device_count() < 2:
+    if not one_gpu and torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
     port = s.getsockname()[1]
     s.close()
-    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, port, str(tmp_path), one_gpu), nprocs=2, join=True)
     for r in range(2):
         got = eval(open(tmp_path / f"ok{r}").read())
         assert got == {"fused": True, "nccl": True, "rowsplit": True, "no_oob": True}, (r, got)
@@ -130,7 +150,7 @@ def test_exchange_two_gpus(tmp_path):
 
 # ---- ShardedTables: planner placement + row-range shards + fused exchange + partial reduction ----
 
-def _sharded_worker(rank, world, port, tmp):
+def _sharded_worker(rank, world, port, tmp, one_gpu=False):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import torch
@@ -139,9 +159,7 @@ def _sharded_worker(rank, world, port, tmp):
     import emb_oracle as eo
     from pim_embedding_lookup_b200 import emblib
     from pim_embedding_lookup_b200.sharded import ShardedTables
-    torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
-                            device_id=torch.device("cuda", rank))
+    _init(rank, world, port, one_gpu)
     ok = {}
     try:
         D, B = 16, 2048
@@ -230,6 +248,22 @@ def test_sharded_tables(tmp_path, world):
     port = s.getsockname()[1]
     s.close()
     mp.spawn(_sharded_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        got = eval(open(tmp_path / f"ok{r}").read())
+        assert got == {"split": True, "sliced": True, "bits": True, "inflight": True, "no_oob": True}, (r, got)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_tables_ranks_on_one_gpu(tmp_path, world):
+    """The same worker with every rank on GPU 0 (one process per rank): the row-cut tables' partial sums, the peer-slab
+    stores, the flag barrier and the reduce jobs of the completion kernel run on a one-GPU box too."""
+    pytest.importorskip("torch")
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_sharded_worker, args=(world, port, str(tmp_path), True), nprocs=world, join=True)
     for r in range(world):
         got = eval(open(tmp_path / f"ok{r}").read())
         assert got == {"split": True, "sliced": True, "bits": True, "inflight": True, "no_oob": True}, (r, got)
