@@ -1262,6 +1262,23 @@ def condensed(r):
     return keep
 
 
+def small_call_c1(calls=200, max_rows=2_000_000):
+    """BASELINE.json configs[0] (C1): the reference's --mini-batch-size=1 inference shape -- ONE lookup() call over the
+    26 Kaggle tables, one bag of one index each (dlrm_s_pytorch.py:444,492-494) -- as host wall time per synchronous
+    call, beside nn.EmbeddingBag per table on the host cores (tools/small_call_latency.py).  Launch-bound, so the
+    figure is microseconds per call, not lookups/s."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import small_call_latency as scl
+    r = scl.run("c1", scl.PRESETS["c1"], calls, max_rows)
+    return {"workload": r["what"], "unit": "us per lookup() call (median of %d)" % calls, "higher_is_better": False,
+            "lookup_on_numpy_arrays": r["lookup_pageable"], "lookup_on_page_locked_arrays": r["lookup_pinned"],
+            "plan_launch_kernel": r["plan_launch_kernel"], "cpu_embedding_bag_all_cores": r["cpu_all_cores"],
+            "cpu_embedding_bag_one_core": r["cpu_one_core"], "rows_capped_at": r.get("rows_capped_at"),
+            "parity": {"host_and_device_flows_bit_equal": r["pageable_pinned_device_bits_equal"],
+                       "max_abs_diff_vs_cpu_float": r["max_abs_diff_vs_cpu_float"]},
+            "speedup_vs_cpu_all_cores": r["speedup_vs_cpu_all_cores"]}
+
+
 def run_b200(args, w):
     import torch
     import torch.distributed as dist
@@ -1276,10 +1293,13 @@ def run_b200(args, w):
     torch.cuda.set_device(local)
     extras = args.extras
     if extras == "auto":
-        # c4rc (tables cut by rows) needs ranks to cut over
-        extras = ("c4tb,c5" if world == 1 else "c4tb,c4rc,c5") if (args.workload == "c2" and args.dtype == "int32") else "none"
+        # Every BASELINE.json config and both element kinds in the one line: c3 = configs[2]'s lookup shape, c1 =
+        # configs[0] (one lookup() call at mini-batch 1, N = 1 only), f32 = the default workload on fp32 tables;
+        # c4rc (tables cut by rows) needs ranks to cut over.
+        extras = (("c4tb,c5,c3,f32,c1" if world == 1 else "c4tb,c4rc,c5,c3")
+                  if (args.workload == "c2" and args.dtype == "int32") else "none")
     extras = [e for e in extras.split(",") if e and e != "none"]
-    need_group = world > 1 or bool(w.get("sharded")) or any(WORKLOADS[e].get("sharded") for e in extras)
+    need_group = world > 1 or bool(w.get("sharded")) or any(WORKLOADS.get(e, {}).get("sharded") for e in extras)
     if need_group:
         if world == 1:  # ShardedTables wants a process group even for one rank
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -1293,14 +1313,22 @@ def run_b200(args, w):
         out = one(w, args.steps, args.warmup)
         extra = {}
         for name in extras:
-            saved = args.no_cpu_baseline, args.no_unmodified_caller
+            if name == "c1":
+                if world == 1:
+                    extra[name] = small_call_c1()
+                continue
+            saved = args.no_cpu_baseline, args.no_unmodified_caller, args.dtype
             args.no_cpu_baseline = args.no_unmodified_caller = True
+            if name == "f32":
+                args.dtype = "f32"
             try:
-                r = one(WORKLOADS[name], max(3, min(args.steps, 50)), min(args.warmup, 5))
+                r = one(w if name == "f32" else WORKLOADS[name], max(3, min(args.steps, 50)), min(args.warmup, 5))
             finally:
-                args.no_cpu_baseline, args.no_unmodified_caller = saved
+                args.no_cpu_baseline, args.no_unmodified_caller, args.dtype = saved
             if rank == 0:
                 extra[name] = condensed(r)
+                if name == "f32":
+                    extra[name]["dtype"] = "f32"
     if rank == 0:
         out["clocks"] = clk.summary()
         if extra:

@@ -467,6 +467,8 @@ uint64_t emb_launch_count(void);
 int emb_set_unroll(int unroll);
 /* All tuning knobs at once (0 = default): variant 1 = one bag per sub-warp (fp32 sums strictly in index
  * order; also used when a launch mixes fp32 and int32 tables), 4 = TMA gather4 (rows of 64..512 bytes),
+ * 7 = the short-bag kernel (a warp per 32 bags, no shared memory; what the default picks by itself for launches that
+ * average at most 1.25 indices per bag -- the reference's Kaggle shape, one index per bag; fp32 in index order),
  * 6 = the stretch kernel (default: load-balanced, no atomics; int32 bit-exact, fp32 deterministic and within
  * 1e-5 relative of the sequential sum); unroll = rows in flight per lane (4 or 8); bags_mult = bags per CTA
  * in units of sub-warps per CTA (1, 2, 4 or 8; variant 6).  Variants 2, 3 and 5 were round-1 kernels and no

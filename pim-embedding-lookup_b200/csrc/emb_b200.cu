@@ -552,7 +552,8 @@ uint32_t lanes_for_dim(uint32_t D)
 /* Which kernel pools a launch, decided when the descriptors are built (the CTA -> bag mapping depends on it). */
 struct Variant {
     int kind;      // 0 generic (any D), 1 bag-per-sub-warp (index-ordered adds, any table kind), 4 TMA gather4 (rows of
-                   // 64..512 bytes, any table kind), 6 stretch kernel (load-balanced, no atomics; int32 or fp32 launches)
+                   // 64..512 bytes, any table kind), 6 stretch kernel (load-balanced, no atomics; int32 or fp32 launches),
+                   // 7 short-bag kernel (launches of about one index per bag; index-ordered adds, any table kind)
     int unroll;    // K: rows in flight per lane
     int mult;      // stretch kernel: bags per CTA / sub-warps per CTA
     uint32_t bags; // bags per CTA
@@ -585,6 +586,17 @@ int apply_hot(Variant &v, bool any_hot, bool any_remap, bool compact)
  * round-1 load-balanced kernels (per CTA with atomics, per warp) on every workload (profiles/r2_stretch_ab_rotated.txt).
  * Variant 1 stays for strictly index-ordered fp32 sums and for launches that mix fp32 and int32 tables, variant 4
  * (TMA gather4) as the measured alternative north_star asks for. */
+int short_tpw()
+{
+    static const int tpw = [] {
+        const uint32_t v = env_u32("EMB_SHORT_TPW", 2);  // measurement knob
+        return v == 1 || v == 4 ? (int)v : 2;
+    }();
+    return tpw;
+}
+
+constexpr double kShortBagPool = 1.25;  // average indices per bag up to which a launch takes the short-bag kernel
+
 Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = false, uint64_t total_bags = 0)
 {
     Variant v;
@@ -601,6 +613,22 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = fal
     }
     static const int dflt_kind = (int)env_u32("EMB_DEFAULT_VARIANT", 6);  // measurement knob
     v.kind = g_tune.variant ? g_tune.variant : (dflt_kind == 1 || dflt_kind == 4 ? dflt_kind : 6);
+    // About one index per bag (the reference's Kaggle shape, README.md:14): the short-bag kernel, unless a table of this
+    // GPU is reordered or carries an L2 policy (only the stretch kernel knows those).  EMB_SHORT_BAGS=0: measurement knob.
+    static const bool short_on = env_u32("EMB_SHORT_BAGS", 1) != 0;
+    if ((v.kind == 6 && !g_tune.variant && short_on && avg_pool > 0.0 && avg_pool <= kShortBagPool) || v.kind == 7) {
+        bool special = false;
+        for (const Table &t : g.tables)
+            special |= t.d_remap != nullptr || (t.hot_mode != 0 && t.hot_rows != 0);
+        if (!special) {
+            v.kind = 7;
+            v.unroll = (int)std::min<uint32_t>(lanes, 4);
+            v.mult = 1;
+            v.bags = emb::kThreads * (uint32_t)short_tpw();  // a warp owns 32 bags per tile whatever the dimension
+            return v;
+        }
+        v.kind = 6;
+    }
     if (v.kind == 4 && lanes < 4)
         v.kind = 6;  // the TMA kernel is for rows of 64 bytes and more
     if (any_float && v.kind != 4 && !(v.kind == 6 && all_float))
@@ -611,7 +639,7 @@ Variant pick_variant(bool any_float, double avg_pool = 0.0, bool all_float = fal
     v.mult = 1;
     v.bags = emb::kThreads / lanes;  // kind 1: one bag per sub-warp of a 256-thread CTA
     if (v.kind == 6) {
-        // One warp per CTA.  Defaults from the round-2 sweeps on the B200 (tools/r2_quick_ab.sh,
+        // One warp per CTA.  Defaults from the round-2 sweeps on the B200 (tools/sweep.py,
         // profiles/r2_stretch_ab_rotated.txt; K = rows in flight per lane, mult = bags per CTA / sub-warps):
         //   64-byte rows (C2):   K8 m2 0.2257 ms | K4 m2 0.2360 | K8 m4 0.2545 (two passes) | K8 m1 0.2503
         //   ... one index per bag (C3): K4 m4 0.0353 | K8 m4 0.0373 | K8 m8 0.0414
@@ -757,10 +785,27 @@ void launch_tma(const Ctx &c, uint32_t grid, cudaStream_t s, const BagDesc *d, u
 }
 
 template <int LANES>
+void launch_short(const Ctx &c, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni)
+{
+    constexpr int UN = LANES < 4 ? LANES : 4;  // steps whose row loads are in flight together
+    // Tiles of 32 bags per warp (short_tpw(), also the descriptors' bags per CTA), compiled for 4 resident CTAs per SM
+    // (54-63 registers).  C3 on one box, isolated launch (profiles/r3_c3_short_bags.md): 1 tile 0.0366 ms, 2 tiles
+    // 0.0314, 4 tiles 0.0325; compiled for 8 CTAs per SM (32 registers, spills) 0.0321 / 0.0321 / 0.0343; the stretch
+    // kernel 0.0411.
+    switch (short_tpw()) {
+    case 1: emb::bag_sum_short_kernel<LANES, UN, 1, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, c.d_err); break;
+    case 4: emb::bag_sum_short_kernel<LANES, UN, 4, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, c.d_err); break;
+    default: emb::bag_sum_short_kernel<LANES, UN, 2, 4><<<grid, emb::kThreads, 0, s>>>(d, n, uni, c.d_err); break;
+    }
+}
+
+template <int LANES>
 void launch_for_lanes(const Ctx &c, const Variant &v, bool is_float, uint32_t grid, cudaStream_t s, const BagDesc *d, uint32_t n, uint32_t uni,
                       uint32_t overlap)
 {
-    if (v.kind == 6)  // the one kernel that orders its result stores itself (EMB_Q_OVERLAP)
+    if (v.kind == 7)
+        launch_short<LANES>(c, grid, s, d, n, uni);
+    else if (v.kind == 6)  // the one kernel that orders its result stores itself (EMB_Q_OVERLAP)
         launch_stretch<LANES>(c, v, is_float, grid, s, d, n, uni, overlap);
     else if (v.kind == 4)
         launch_tma<LANES>(c, grid, s, d, n, uni);
@@ -985,9 +1030,9 @@ int emb_set_unroll(int unroll)
 
 int emb_set_tuning(int variant, int unroll, int bags_mult)
 {
-    if (variant != 0 && variant != 1 && variant != 4 && variant != 6)
-        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp, index-ordered), 4 (TMA gather4) or "
-                                "6 (stretch kernel); 2, 3 and 5 were round-1 kernels, removed");
+    if (variant != 0 && variant != 1 && variant != 4 && variant != 6 && variant != 7)
+        return fail(EMB_EINVAL, "variant must be 0 (auto), 1 (bag per sub-warp, index-ordered), 4 (TMA gather4), "
+                                "6 (stretch kernel) or 7 (short-bag kernel); 2, 3 and 5 were round-1 kernels, removed");
     if (bags_mult != 0 && bags_mult != 1 && bags_mult != 2 && bags_mult != 4 && bags_mult != 8)
         return fail(EMB_EINVAL, "bags_mult must be 0, 1, 2, 4 or 8");
     int rc = emb_set_unroll(unroll);

@@ -348,6 +348,168 @@ bag_sum_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni,
     }
 }
 
+/* ---- short-bag kernel -----------------------------------------------------------------------------
+ *
+ * bag_sum_short_kernel: launches whose bags hold about ONE index each -- the reference's Kaggle shape (README.md:14,
+ * dlrm_s_pytorch.py:444: one categorical value per feature and sample), where pooling degenerates to "fetch row
+ * indices[b], convert, store".  The stretch kernel's machinery (start markers, heads, the merge of sub-warp partials,
+ * shared-memory staging, a barrier per pass) is pure overhead there, and its one-warp CTAs make such a launch ~32 000
+ * CTAs of almost no work each (C3: 0.0353 ms, 0.60 of the copy peak; profiles/r3_c3_short_bags.md).
+ *
+ * Here a warp owns 32 consecutive bags.  Lane l reads the bounds of bag l (one coalesced load of the offsets; the end
+ * of a bag is the neighbour's start, taken with a shuffle) and the FIRST index of its bag (coalesced again when every
+ * bag holds one index).  The warp then walks its 32 bags in steps of 32/LANES bags -- a sub-warp of LANES lanes per
+ * bag, 16 bytes of the row per lane -- with UN steps' row loads issued before any is consumed.  Nothing goes through
+ * shared memory and no barrier is needed.  A bag with more than one index is finished by its sub-warp in a plain loop
+ * (index order, so fp32 sums are the sequential ones); an empty bag stores zeros.  Arithmetic: emb_dpu_lookup.c:106-116,
+ * emb_host.h:207-212, as in every other kernel of this file.  Correct for any bag lengths; chosen by the host only when
+ * the launch averages at most kShortBagPool indices per bag.
+ */
+template <int LANES, int UN, int TPW, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
+bag_sum_short_kernel(const BagDesc *__restrict__ descs, uint32_t n_desc, uint32_t uni, uint32_t *__restrict__ err_flag)
+{
+    constexpr int GROUPS = 32 / LANES;  // bags a warp handles per step
+    constexpr uint32_t FULL = 0xffffffffu;
+    const uint32_t q = find_desc(descs, n_desc, uni, blockIdx.x);
+    const BagDesc *__restrict__ d = descs + q;
+    const uint32_t lane = threadIdx.x & 31u;
+    // a warp owns TPW tiles of 32 consecutive bags; the bounds and first indices of ALL its tiles are loaded before
+    // any row, so the offsets -> index -> row chain of dependent loads is paid once per warp, not once per tile
+    const uint32_t b0 = chunk_first_bag(d, blockIdx.x - d->chunk_begin, kThreads * TPW) + (threadIdx.x >> 5) * (32u * TPW);
+    const uint32_t bag_end = d->bag_end;
+    if (b0 >= bag_end)
+        return;  // whole warp
+    const uint32_t B = d->nr_batches;
+    const uint32_t ilen = d->indices_len;
+    const uint32_t *__restrict__ g_idx = d->indices;
+    const uint32_t *__restrict__ g_off = d->offsets;
+    const uint32_t row_base = d->row_base;
+
+    // bag bounds, emb_dpu_lookup.c:60-63,109-110: bag 0 starts at 0 whatever offsets[0] is, bag i ends where bag
+    // i+1 starts, the last bag ends at indices_len
+    uint32_t start[TPW], end[TPW], first[TPW];
+#pragma unroll
+    for (int t = 0; t < TPW; t++) {
+        const uint32_t b = b0 + t * 32u + lane;
+        start[t] = 0;
+        if (b < bag_end && b != 0)
+            start[t] = min(ldg_stream_u32(g_off + b), ilen);
+    }
+#pragma unroll
+    for (int t = 0; t < TPW; t++) {
+        const uint32_t b = b0 + t * 32u + lane;
+        // the end of a bag is its neighbour's start: lane + 1 of this tile, lane 0 of the next tile, else a load
+        uint32_t nxt = __shfl_down_sync(FULL, start[t], 1);
+        if (t + 1 < TPW) {
+            const uint32_t nt = __shfl_sync(FULL, start[t + 1 < TPW ? t + 1 : t], 0);
+            if (lane == 31)
+                nxt = nt;
+        }
+        end[t] = 0;
+        if (b < bag_end) {
+            const bool have = (lane < 31 || t + 1 < TPW) && b + 1 < bag_end;
+            end[t] = (b + 1 >= B) ? ilen : have ? nxt : min(ldg_stream_u32(g_off + b + 1), ilen);
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < TPW; t++) {
+        first[t] = 0xffffffffu;
+        if (end[t] > start[t])
+            first[t] = ldg_stream_u32(g_idx + start[t]) - row_base;  // unsigned: rows below a shard wrap to huge values
+    }
+
+    const uint32_t flags = d->flags;
+    const uint32_t rows = d->rows;
+    const bool is_float = flags & kDescFloat;
+    const uint32_t grp = lane / LANES, sub = lane % LANES;
+    const uint4 *__restrict__ table = reinterpret_cast<const uint4 *>(d->table) + sub;
+    const uint32_t bpr = d->bags_per_rank;
+    const uint32_t out_stride = d->out_stride;
+    bool bad = false;
+
+#pragma unroll
+    for (int t = 0; t < TPW; t++) {
+        const uint32_t bt = b0 + t * 32u;
+        if (bt >= bag_end)
+            break;  // whole warp
+#pragma unroll 1
+        for (int u0 = 0; u0 < LANES; u0 += UN) {
+            uint32_t s_[UN], e_[UN];
+            uint4 v[UN];
+#pragma unroll
+            for (int u = 0; u < UN; u++) {
+                const int j = (u0 + u) * GROUPS + (int)grp;
+                s_[u] = __shfl_sync(FULL, start[t], j);
+                e_[u] = __shfl_sync(FULL, end[t], j);
+                const uint32_t r = __shfl_sync(FULL, first[t], j);
+                v[u] = make_uint4(0u, 0u, 0u, 0u);
+                if (e_[u] > s_[u]) {
+                    if (r < rows)
+                        v[u] = ldg_row16<(LANES <= 4)>(table + (size_t)r * LANES);
+                    else
+                        bad = true;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UN; u++) {
+                const uint32_t bj = bt + (uint32_t)((u0 + u) * GROUPS) + grp;
+                if (bj >= bag_end)
+                    continue;
+                uint4 acc = v[u];
+                float4 facc = make_float4(__fadd_rn(0.f, __uint_as_float(v[u].x)), __fadd_rn(0.f, __uint_as_float(v[u].y)),
+                                          __fadd_rn(0.f, __uint_as_float(v[u].z)), __fadd_rn(0.f, __uint_as_float(v[u].w)));
+                for (uint32_t p = s_[u] + 1; p < e_[u]; p++) {  // the rare longer bag: index order
+                    const uint32_t r = __ldg(g_idx + p) - row_base;
+                    if (r < rows) {
+                        const uint4 x = ldg_row16<(LANES <= 4)>(table + (size_t)r * LANES);
+                        acc.x += x.x;  // int32 wrap-around adds (emb_dpu_lookup.c:114)
+                        acc.y += x.y;
+                        acc.z += x.z;
+                        acc.w += x.w;
+                        facc.x = __fadd_rn(facc.x, __uint_as_float(x.x));
+                        facc.y = __fadd_rn(facc.y, __uint_as_float(x.y));
+                        facc.z = __fadd_rn(facc.z, __uint_as_float(x.z));
+                        facc.w = __fadd_rn(facc.w, __uint_as_float(x.w));
+                    } else {
+                        bad = true;
+                    }
+                }
+                uint4 o;
+                if (is_float)
+                    o = make_uint4(__float_as_uint(facc.x), __float_as_uint(facc.y), __float_as_uint(facc.z),
+                                   __float_as_uint(facc.w));
+                else if (flags & kDescRaw)
+                    o = acc;
+                else  // post_process, emb_host.h:210
+                    o = make_uint4(__float_as_uint(dequant(acc.x)), __float_as_uint(dequant(acc.y)),
+                                   __float_as_uint(dequant(acc.z)), __float_as_uint(dequant(acc.w)));
+                uint32_t *base;
+                uint32_t row;
+                if (bpr) {  // pooled row goes straight to the slab of the rank that owns sample bj
+                    const uint32_t rk = bj / bpr;
+                    base = reinterpret_cast<uint32_t *>(d->out_peer[rk]);
+                    row = bj - rk * bpr;
+                } else {
+                    base = reinterpret_cast<uint32_t *>(d->out);
+                    row = bj;
+                }
+                uint32_t *dst = base + (size_t)row * out_stride + sub * 4;
+                if (flags & kDescVecStore) {
+                    stg_stream16(dst, o);
+                } else {
+                    dst[0] = o.x;
+                    dst[1] = o.y;
+                    dst[2] = o.z;
+                    dst[3] = o.w;
+                }
+            }
+        }
+    }
+    if (bad && !(flags & kDescSharded))
+        atomicOr(err_flag, 1u);
+}
+
 /* ---- stretch kernel -----------------------------------------------------------------------------
  *
  * bag_sum_stretch_kernel: load-balanced sum pooling with NO atomics and a branch-free inner loop.

@@ -339,7 +339,7 @@ def test_large_call_pipelines_groups(emblib):
         emblib.set_host_path(EMB_HOST_AUTO)
 
 
-TUNINGS = [(1, 4, 0), (1, 8, 0), (4, 0, 0), (6, 8, 1), (6, 8, 2), (6, 4, 4), (6, 8, 8), (6, 4, 1), (6, 4, 2), (6, 8, 4)]
+TUNINGS = [(7, 0, 0), (1, 4, 0), (1, 8, 0), (4, 0, 0), (6, 8, 1), (6, 8, 2), (6, 4, 4), (6, 8, 8), (6, 4, 1), (6, 4, 2), (6, 8, 4)]
 
 
 @pytest.mark.parametrize("tuning", TUNINGS, ids=[f"v{v}k{k}m{m}" for v, k, m in TUNINGS])
@@ -364,7 +364,7 @@ def test_kernel_variants_agree(emblib, tuning, D):
         emblib.load().emb_set_tuning(0, 0, 0)
 
 
-@pytest.mark.parametrize("variant", [1, 4, 6])
+@pytest.mark.parametrize("variant", [1, 4, 6, 7])
 def test_overlapping_and_backward_bags(emblib, variant):
     """lookup() accepts any offsets: bag i covers [offsets[i], offsets[i+1]) on its own
     (emb_dpu_lookup.c:109-116), so bags may overlap or be empty because they run backwards."""

@@ -309,3 +309,86 @@ def test_row_shards_pool_only_their_own_lookups(emblib, D, parts):
             assert np.array_equal(outs[0].cpu().numpy(), sums[0]), (D, parts, pi, "whole")
             plan.close()
     assert lib.emb_check_indices() == 0
+
+
+@pytest.mark.parametrize("D", [4, 16, 64, 128])
+@pytest.mark.parametrize("kind", ["fixed", "float"])
+def test_about_one_index_per_bag_takes_the_short_bag_kernel(emblib, D, kind):
+    """The reference's Kaggle shape (README.md:14; dlrm_s_pytorch.py:444): one categorical value per feature and sample.
+    Launches that average at most 1.25 indices per bag are pooled by bag_sum_short_kernel -- a warp per 32 bags, no
+    shared memory -- chosen by the host on its own.  Bit-exact for fixed-point tables; fp32 sums are the sequential ones
+    (bit-equal to the oracle's).  Mixed in: empty bags, a few bags of two and three indices, a partial last warp, a bag
+    slice with a strided output, and an out-of-range index."""
+    import torch
+    from pim_embedding_lookup_b200.dputypes import EMB_TABLE_FLOAT
+    rng = np.random.default_rng(100 + D)
+    T = 3
+    emblib.configure(T, D)
+    lib = emblib.load()
+    tabs, idxs, offs = [], [], []
+    for t in range(T):
+        R, B = 5000 + 37 * t, 4001 + 300 * t  # not a multiple of 32: partial last warp
+        if kind == "float":
+            w = rng.uniform(-1, 1, size=(R, D)).astype(np.float32)
+            emblib.populate_table_f32(t, w, EMB_TABLE_FLOAT)
+        else:
+            w = table(rng, R, D)
+            emblib.populate_table_i32(t, w)
+        lens = np.ones(B, dtype=np.int64)
+        lens[rng.integers(0, B, size=B // 20)] = 0
+        lens[rng.integers(0, B, size=B // 20)] = 2
+        lens[rng.integers(0, B, size=B // 50)] = 3
+        tabs.append(w)
+        offs.append(offsets_of(lens))
+        idxs.append(rng.integers(0, R, size=int(lens.sum())).astype(np.uint32))
+        assert len(idxs[t]) <= 1.25 * B
+
+    def want_rows(ix, of):
+        if kind == "float":
+            return [eo.bag_sum_f32(tabs[t], ix[t], of[t]) for t in range(T)]
+        return eo.lookup_rows(tabs, ix, of)
+
+    want = want_rows(idxs, offs)
+    got = emblib.lookup_ex(idxs, offs)  # host-pointer path
+    for t in range(T):
+        assert np.array_equal(bits(got[t]), bits(want[t])), t
+    assert lib.emb_check_indices() == 0
+    # device-resident plan: the grid says which kernel it is (512 bags per CTA), strided output, a bag slice
+    di = [torch.from_numpy(i.view(np.int32)).cuda() for i in idxs]
+    do = [torch.from_numpy(o.view(np.int32)).cuda() for o in offs]
+    Bs = [len(o) for o in offs]
+    out = [torch.full((Bs[t], 2 * D), -1.0, dtype=torch.float32, device="cuda") for t in range(T)]
+    qs = [dict(table_id=t, indices=di[t], offsets=do[t], out=out[t][:, D:], out_stride=2 * D) for t in range(T)]
+    qs[1].update(bag_first=1000, bag_count=1500)
+    plan = emblib.Plan(qs)
+    per = 512  # 8 warps x 2 tiles of 32 bags
+    assert plan.grid == (Bs[0] + per - 1) // per + (1500 + per - 1) // per + (Bs[2] + per - 1) // per
+    plan.launch(torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    for t in range(T):
+        o = out[t].cpu().numpy()
+        lo, hi = (1000, 2500) if t == 1 else (0, Bs[t])
+        assert np.array_equal(bits(o[lo:hi, D:]), bits(want[t][lo:hi])), t
+        assert (o[:, :D] == -1.0).all() and (o[:lo, D:] == -1.0).all() and (o[hi:, D:] == -1.0).all()
+    plan.close()
+    # the stretch kernel on the same launch agrees (fixed point: bit for bit)
+    if kind == "fixed":
+        emblib.check(lib.emb_set_tuning(6, 0, 0))
+        try:
+            again = emblib.lookup_ex(idxs, offs)
+        finally:
+            emblib.check(lib.emb_set_tuning(0, 0, 0))
+        for t in range(T):
+            assert np.array_equal(bits(again[t]), bits(want[t])), t
+    # an index outside its table adds nothing and is reported
+    bad = [i.copy() for i in idxs]
+    bad[2][::9] = tabs[2].shape[0] + 11
+    got = emblib.lookup_ex(bad, offs)
+    assert lib.emb_check_indices() == 1
+    keep = np.ones(len(bad[2]), dtype=bool)
+    keep[::9] = False
+    csum = np.concatenate([[0], np.cumsum(keep)])
+    ends = np.concatenate([offs[2][1:], [len(bad[2])]]).astype(np.int64)
+    keep_lens = csum[ends] - csum[offs[2].astype(np.int64)]
+    w2 = want_rows([idxs[0], idxs[1], idxs[2][keep]], [offs[0], offs[1], offsets_of(keep_lens)])
+    assert np.array_equal(bits(got[2]), bits(w2[2]))
