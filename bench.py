@@ -1295,8 +1295,9 @@ def run_b200(args, w):
     if extras == "auto":
         # Every BASELINE.json config and both element kinds in the one line: c3 = configs[2]'s lookup shape, c1 =
         # configs[0] (one lookup() call at mini-batch 1, N = 1 only), f32 = the default workload on fp32 tables;
-        # c4rc (tables cut by rows) needs ranks to cut over.
-        extras = (("c4tb,c5,c3,f32,c1" if world == 1 else "c4tb,c4rc,c5,c3")
+        # c4rc (tables cut by rows) needs ranks to cut over.  c3 / f32 / c1 are one-GPU figures (c3's batch of 39292 does
+        # not divide over 8 ranks).
+        extras = (("c4tb,c5,c3,f32,c1" if world == 1 else "c4tb,c4rc,c5")
                   if (args.workload == "c2" and args.dtype == "int32") else "none")
     extras = [e for e in extras.split(",") if e and e != "none"]
     need_group = world > 1 or bool(w.get("sharded")) or any(WORKLOADS.get(e, {}).get("sharded") for e in extras)
@@ -1313,6 +1314,10 @@ def run_b200(args, w):
         out = one(w, args.steps, args.warmup)
         extra = {}
         for name in extras:
+            if name in WORKLOADS and WORKLOADS[name]["B"] % world:
+                if rank == 0:
+                    extra[name] = {"skipped": f"batch {WORKLOADS[name]['B']} does not divide over {world} ranks"}
+                continue
             if name == "c1":
                 if world == 1:
                     extra[name] = small_call_c1()
